@@ -1,0 +1,176 @@
+/* b200svs - C ABI of the B200-native VISinger synthesis forward (sm_100a only).
+ *
+ * The reference (GuluOfficial/music_generation) has no FFI/plugin registry: its boundary for this
+ * path is the Python method SynthesizerTrn.infer (VISinger/models_ae.py:608, VISinger/models.py:622).
+ * music_generation_b200.SynthesizerTrn mirrors that method and drives the entry points below through
+ * ctypes.  Each entry point replaces the PyTorch/cuDNN/cuBLAS call sequence cited beside it.
+ *
+ * Conventions
+ *  - Every pointer is a DEVICE pointer owned by the caller; nothing here allocates or frees.
+ *  - Activations are channels-last: x[b][t][c] at  x + (b*T + t)*ld + c   ("[B,T,C] with row stride ld").
+ *    The reference's [B,C,T] tensors are the transposes of these.
+ *  - All work is enqueued on `stream` (a cudaStream_t passed as void*); calls are re-entrant and
+ *    keep no state between calls apart from a per-thread last-error string.
+ *  - Return value: 0 on success, a negative B200SVS_E* code otherwise (see b200svs_last_error()).
+ *  - There is no CPU fallback: on a machine without an sm_100 device every compute call returns
+ *    B200SVS_ENODEV / a CUDA error.
+ */
+#ifndef B200SVS_H_
+#define B200SVS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200SVS_ABI_VERSION 1
+
+enum {
+  B200SVS_OK = 0,
+  B200SVS_EINVAL = -1,  /* bad shape / alignment / argument */
+  B200SVS_ECUDA = -2,   /* CUDA runtime or driver error (text in b200svs_last_error) */
+  B200SVS_ENODEV = -3,  /* no sm_100 device / driver entry point missing */
+  B200SVS_EUNSUPPORTED = -4
+};
+
+/* pre-activation applied to (acc + bias) */
+enum {
+  B200SVS_ACT_NONE = 0,
+  B200SVS_ACT_RELU = 1,
+  B200SVS_ACT_GELU = 2,    /* exact erf GELU  (ext_modules/frame_prior_network.py:38) */
+  B200SVS_ACT_SIGMOID = 3, /* DurationPredictor (models_ae.py:147) */
+  B200SVS_ACT_TANH = 4,
+  B200SVS_ACT_GATE = 5     /* tanh(a)*sigmoid(b): commons.fused_add_tanh_sigmoid_multiply (commons.py:100-107);
+                              packed weight tile columns [0,N/2) = tanh half, [N/2,N) = sigmoid half */
+};
+enum { B200SVS_DT_F16 = 0, B200SVS_DT_BF16 = 1 };
+
+/* Fused epilogue shared by the conv1d kernels.  For output row (b,t) and packed column c:
+ *   v = acc + bias[c] + gbias[b*gbias_ld + c]
+ *   v = act(v)                                   (GATE halves the column count)
+ *   v = alpha*v + res1[b,t,c'] + res2[b,t,c']    (c' = output column)
+ *   v = v*scale;  v *= (t < lens[b])             (lens == NULL: no mask)
+ *   out32[b,t,c'] = v;  out16[b,t,c'] = cvt16(post_lrelu ? lrelu(v, post_slope) : v)
+ * Columns c' >= n_valid are not stored.  out32 may alias res1 or res2 (same element, same thread). */
+typedef struct b200svs_epilogue {
+  const float* bias;
+  const float* gbias;
+  int32_t gbias_ld;
+  int32_t act;
+  float alpha;
+  float scale;
+  const float* res1;
+  int32_t res1_ld;
+  const float* res2;
+  int32_t res2_ld;
+  const int32_t* lens;
+  int32_t lens_div;   /* row t is valid iff t / lens_div < lens[b]  (1 normally) */
+  float* out32;
+  int32_t out32_ld;
+  void* out16;
+  int32_t out16_ld;
+  int32_t out16_dtype; /* B200SVS_DT_* */
+  int32_t post_lrelu;
+  float post_slope;
+  int32_t n_valid;
+} b200svs_epilogue;
+
+/* 1-D convolution over time as an implicit GEMM (replaces nn.Conv1d / ConvTranspose1d + the pointwise
+ * ops around it: models_ae.py:327-346, modules.py:148-176,210-223,329-349, attentions.py:138-146,277-285).
+ *   out[b,t,:] = sum_{tap<ntaps} W[tap] . x[b, t + tap*dil - pad_left, 0:Cin]      (zero outside [0,T))
+ * w is packed [ntaps][Cout_pad][Cin_pad] (Cin contiguous), Cin_pad % 64 == 0, Cout_pad % block_n == 0.
+ * A ConvTranspose1d of stride s is issued as a 3-tap conv over input time with Cout = s*Cout'
+ * (polyphase) writing a [B,T,s*Cout'] view of the [B,s*T,Cout'] output. */
+typedef struct b200svs_conv_args {
+  const void* x; /* tc: 16-bit (x_dtype); f32 variant: float */
+  int32_t x_dtype;
+  int32_t B, T, Cin, x_ld;
+  const void* w;
+  int32_t ntaps, Cout_pad, Cin_pad, dil, pad_left;
+  int32_t block_n; /* tc only: N tile (16..256, multiple of 16; GATE needs multiple of 32) */
+  b200svs_epilogue ep;
+} b200svs_conv_args;
+
+const char* b200svs_last_error(void);
+int b200svs_abi_version(void);
+/* 0 if an sm_100 device is current and the driver exports cuTensorMapEncodeTiled */
+int b200svs_check_device(void);
+
+/* tcgen05/TMEM/TMA implicit-GEMM conv, fp16|bf16 operands, fp32 accumulate */
+int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream);
+/* fp32 SIMT conv (phoneme-level + F0 path where the float->int boundaries need fp32);
+ * w packed [ntaps][Cin][Cout_pad] fp32 (Cout contiguous) */
+int b200svs_conv1d_f32(const b200svs_conv_args* a, void* stream);
+
+/* Windowed relative-position multi-head self-attention (attentions.py:148-179,199-243), fp32, flash style
+ * (never materialises [B,H,T,T]).  qkv: [B,T,3*C] fp32 (q|k|v), out: [B,T,C]; rel_k/rel_v: [2*window+1, C/H];
+ * keys >= lens[b] are masked with -1e4 exactly like masked_fill; rows >= lens[b] are written as 0. */
+int b200svs_attention_f32(const float* qkv, int32_t qkv_ld, float* out, int32_t out_ld, void* out16,
+                          int32_t out16_ld, int32_t out16_dtype, const float* rel_k, const float* rel_v,
+                          const int32_t* lens, int32_t B, int32_t T, int32_t C, int32_t H, int32_t window,
+                          void* stream);
+
+/* y = LayerNorm_C(x (+ res)) * mask  (modules.py:29-32 + the residual adds of attentions.py:42,46) */
+int b200svs_layernorm(const float* x, int32_t x_ld, const float* res, int32_t res_ld, const float* gamma,
+                      const float* beta, float eps, const int32_t* lens, float* out32, int32_t out32_ld,
+                      void* out16, int32_t out16_ld, int32_t out16_dtype, int32_t B, int32_t T, int32_t C,
+                      void* stream);
+
+/* TextEncoder input (models_ae.py:204-215): (E_ph[x] + W_dur*dur + b_dur + E_pitch[p] + E_tone[s])*sqrt(C)*mask */
+int b200svs_text_embed(const int64_t* phon, const int64_t* pitch, const int64_t* tone, const float* dur,
+                       const float* e_ph, const float* e_pitch, const float* e_tone, const float* w_dur,
+                       const float* b_dur, const int64_t* x_lengths, int32_t* lens32_out, float* out,
+                       int32_t B, int32_t P, int32_t C, void* stream);
+
+/* floor(pred * note_dur / 0.0116) -> int64 (models_ae.py:624-625), bit-exact fp32 op order */
+int b200svs_duration_quantize(const float* pred, const float* note_dur, int64_t* dur_out, int32_t n,
+                              void* stream);
+
+/* Length regulator (models_ae.py:689-721 + utils/utils.py:344-361) as a gather.
+ * pass 1: mel_len[b] = sum_i max(dur[b,i],0), ends = inclusive cumsum (int32 workspace [B,P]).
+ * pass 2: out[b,t,:] = h[b, idx(b,t), :] for t < mel_len[b] else 0; index[b,t] = idx or -1. */
+int b200svs_lr_scan(const int64_t* dur, int32_t B, int32_t P, int32_t* ends, int64_t* mel_len64,
+                    int32_t* mel_len32, void* stream);
+int b200svs_lr_gather(const float* h, int32_t h_ld, const int32_t* ends, const int32_t* mel_len32,
+                      int32_t B, int32_t P, int32_t T, int32_t C, float* out, int32_t out_ld,
+                      int32_t* index_out, void* stream);
+
+/* (x + pos[t]) * mask  (ext_modules/text_post_net.py:67-75) -> fp32 + optional 16-bit copy */
+int b200svs_add_pos_mask(const float* x, int32_t x_ld, const float* pos, const int32_t* lens, float* out32,
+                         int32_t out32_ld, void* out16, int32_t out16_ld, int32_t out16_dtype, int32_t B,
+                         int32_t T, int32_t C, void* stream);
+
+/* f0_to_coarse(exp(log_f0)-1) (utils/pitch_utils.py:22-31) + f0_emb gather * mask
+ * (text_post_net.py:80-85).  coarse_in != NULL overrides the prediction (f0_score argument). */
+int b200svs_f0_embed(const float* log_f0, const int64_t* coarse_in, const float* f0_emb,
+                     const int32_t* lens, int64_t* coarse_out, float* out32, int32_t out32_ld, void* out16,
+                     int32_t out16_ld, int32_t out16_dtype, int32_t B, int32_t T, int32_t C, void* stream);
+
+/* z_p = m_p + noise * exp(logs_p) * noise_scale (models_ae.py:643); stats: [B,T,2C] (m|logs);
+ * noise is the reference layout [B,C,T]; writes z_p fp32 [B,T,C] (+16-bit copy) */
+int b200svs_sample_prior(const float* stats, int32_t stats_ld, const float* noise_bct, float noise_scale,
+                         float* zp32, int32_t zp_ld, void* zp16, int32_t zp16_ld, int32_t out16_dtype,
+                         int32_t B, int32_t T, int32_t C, void* stream);
+
+/* Generator tail (models_ae.py:342-344): tanh(conv_post_k7(x)) with x = leaky_relu(.,0.01) already
+ * applied by the producer; x: 16-bit [B,L,C], w: fp32 [7][C]; out: fp32 [B,L] */
+int b200svs_conv_post_tanh(const void* x, int32_t x_dtype, int32_t x_ld, const float* w, int32_t B,
+                           int32_t L, int32_t C, int32_t ktaps, float* out, void* stream);
+
+/* layout helpers: [B,C,T] fp32 <-> channels-last fp32/16-bit */
+int b200svs_bct_to_btc(const float* in_bct, int32_t B, int32_t C, int32_t T, float* out32, int32_t out32_ld,
+                       void* out16, int32_t out16_ld, int32_t out16_dtype, const int32_t* lens, void* stream);
+int b200svs_btc_to_bct(const float* in_btc, int32_t in_ld, int32_t B, int32_t C, int32_t T, float* out_bct,
+                       void* stream);
+
+/* Debug probe: GEMM of a row-shifted smem operand view, used once to pin the UMMA descriptor
+ * base-offset semantics on hardware (DESIGN.md "A-tile reuse"). */
+int b200svs_probe_rowshift(const void* a_f16, const void* b_f16, float* out, int32_t rows_a, int32_t shift,
+                           int32_t base_offset_mode, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SVS_H_ */

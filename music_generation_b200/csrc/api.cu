@@ -1,0 +1,100 @@
+// C-ABI plumbing: error strings, device checks, tensor-map encoding through the driver entry point
+// (resolved at run time so the library loads - and exports every symbol - on a machine without a GPU).
+#include "api_internal.h"
+#include <string.h>
+
+namespace b200svs {
+
+static thread_local char g_err[512] = "";
+
+int set_error(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+int check_cuda(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return B200SVS_OK;
+  return set_error(B200SVS_ECUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+
+int check_launch(const char* what) { return check_cuda(cudaGetLastError(), what); }
+
+EncodeTiledFn get_encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres);
+    if (e == cudaSuccess && qres == cudaDriverEntryPointSuccess) fn = reinterpret_cast<EncodeTiledFn>(p);
+    (void)cudaGetLastError();
+  }
+  return fn;
+}
+
+int make_tmap_16bit(CUtensorMap* out, int dtype, const void* base, int rank, const uint64_t* dims,
+                    const uint64_t* strides_bytes, const uint32_t* box) {
+  EncodeTiledFn enc = get_encode_tiled();
+  if (!enc) return set_error(B200SVS_ENODEV, "cuTensorMapEncodeTiled driver entry point not available");
+  cuuint64_t gdim[5];
+  cuuint64_t gstr[5];
+  cuuint32_t bx[5];
+  cuuint32_t es[5];
+  for (int i = 0; i < rank; ++i) {
+    gdim[i] = dims[i];
+    bx[i] = box[i];
+    es[i] = 1;
+    if (i > 0) gstr[i - 1] = strides_bytes[i - 1];
+  }
+  CUtensorMapDataType dt = dtype == B200SVS_DT_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  CUresult r = enc(out, dt, rank, const_cast<void*>(base), gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return set_error(B200SVS_ECUDA, "cuTensorMapEncodeTiled failed (CUresult %d) rank %d dims %llu,%llu,%llu", (int)r, rank,
+                     (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 0),
+                     (unsigned long long)(rank > 2 ? dims[2] : 0));
+  return B200SVS_OK;
+}
+
+static int g_sms = 0, g_smem = 0, g_cc = 0;
+static void query_device() {
+  if (g_sms) return;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) { (void)cudaGetLastError(); return; }
+  cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaDeviceGetAttribute(&g_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  int major = 0, minor = 0;
+  cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+  cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev);
+  g_cc = major * 10 + minor;
+}
+int num_sms() { query_device(); return g_sms > 0 ? g_sms : 148; }
+int max_smem_optin() { query_device(); return g_smem > 0 ? g_smem : 227 * 1024; }
+
+}  // namespace b200svs
+
+extern "C" {
+
+const char* b200svs_last_error(void) { return b200svs::g_err; }
+int b200svs_abi_version(void) { return B200SVS_ABI_VERSION; }
+
+int b200svs_check_device(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+    (void)cudaGetLastError();
+    return b200svs::set_error(B200SVS_ENODEV, "no CUDA device visible");
+  }
+  b200svs::query_device();
+  if (b200svs::g_cc / 10 != 10)
+    return b200svs::set_error(B200SVS_ENODEV, "device is sm_%d, this library is sm_100a only", b200svs::g_cc);
+  if (!b200svs::get_encode_tiled())
+    return b200svs::set_error(B200SVS_ENODEV, "driver lacks cuTensorMapEncodeTiled");
+  return B200SVS_OK;
+}
+
+}  // extern "C"

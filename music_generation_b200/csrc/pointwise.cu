@@ -1,0 +1,420 @@
+// Bandwidth-bound and integer kernels of the VISinger forward: LayerNorm, embeddings, duration
+// quantisation, the length regulator (bit-exact gather), f0 quantisation, prior sampling, conv_post.
+// All are coalesced / 128-bit vectorised where the layout allows; none reshapes work into a GEMM.
+#include "common.cuh"
+#include "api_internal.h"
+
+namespace b200svs {
+
+__device__ __forceinline__ void store16(void* base, size_t idx, float v, int dtype) {
+  if (dtype == B200SVS_DT_BF16) reinterpret_cast<__nv_bfloat16*>(base)[idx] = __float2bfloat16_rn(v);
+  else reinterpret_cast<__half*>(base)[idx] = __float2half_rn(v);
+}
+__device__ __forceinline__ float load16(const void* base, size_t idx, int dtype) {
+  if (dtype == B200SVS_DT_BF16) return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(base)[idx]);
+  return __half2float(reinterpret_cast<const __half*>(base)[idx]);
+}
+
+// ------------------------------------------------------------------ LayerNorm over channels
+// One warp per (b,t) row; C <= 32*8.  Two-pass (mean, then centred variance) like ATen's CPU kernel.
+struct LnParams {
+  const float* x; int x_ld; const float* res; int res_ld; const float* gamma; const float* beta; float eps;
+  const int32_t* lens; float* out32; int out32_ld; void* out16; int out16_ld; int out16_dtype; int B, T, C;
+};
+__global__ void __launch_bounds__(256) layernorm_kernel(const LnParams p) {
+  const int warps_per_block = blockDim.x >> 5;
+  const long long row = static_cast<long long>(blockIdx.x) * warps_per_block + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= static_cast<long long>(p.B) * p.T) return;
+  const int b = static_cast<int>(row / p.T), t = static_cast<int>(row - static_cast<long long>(b) * p.T);
+  const bool live = p.lens ? (t < p.lens[b]) : true;
+  float v[8];
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = lane + i * 32;
+    float a = 0.f;
+    if (c < p.C) {
+      a = p.x[row * p.x_ld + c];
+      if (p.res) a += p.res[row * p.res_ld + c];
+    }
+    v[i] = a;
+    sum += a;
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
+  const float mean = sum / p.C;
+  float var = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = lane + i * 32;
+    if (c < p.C) { const float d = v[i] - mean; var += d * d; }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) var += __shfl_xor_sync(0xffffffffu, var, off);
+  const float rstd = rsqrtf(var / p.C + p.eps);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = lane + i * 32;
+    if (c < p.C) {
+      float y = (v[i] - mean) * rstd * p.gamma[c] + p.beta[c];
+      if (!live) y = 0.f;
+      if (p.out32) p.out32[row * p.out32_ld + c] = y;
+      if (p.out16) store16(p.out16, row * p.out16_ld + c, y, p.out16_dtype);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ TextEncoder input embedding
+__global__ void text_embed_kernel(const int64_t* phon, const int64_t* pitch, const int64_t* tone, const float* dur,
+                                  const float* e_ph, const float* e_pitch, const float* e_tone, const float* w_dur,
+                                  const float* b_dur, const int64_t* x_lengths, int32_t* lens32, float* out, int B,
+                                  int P, int C, float scale) {
+  const int bp = blockIdx.x;
+  const int b = bp / P, i = bp - b * P;
+  const int len = static_cast<int>(x_lengths[b]);
+  if (i == 0 && threadIdx.x == 0 && lens32) lens32[b] = len;
+  const bool live = i < len;
+  const long long ip = phon[bp], it = pitch[bp], is = tone[bp];
+  const float d = dur[bp];
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    // (emb_phoneme + emb_note_duration + emb_note_pitch + emb_phone_shengdiao) * sqrt(C), same add order
+    // as models_ae.py:213;  Linear(1->C): d * w[c] + b[c]
+    float v = e_ph[ip * C + c] + (d * w_dur[c] + b_dur[c]);
+    v = v + e_pitch[it * C + c];
+    v = v + e_tone[is * C + c];
+    v = v * scale;
+    out[static_cast<size_t>(bp) * C + c] = live ? v : 0.f;
+  }
+}
+
+// ------------------------------------------------------------------ duration quantisation
+__global__ void duration_quantize_kernel(const float* pred, const float* note_dur, int64_t* out, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  // torch: floor((pred * note_dur) / 0.0116) in fp32 (0.0116 rounded to fp32), no FMA contraction
+  const float prod = __fmul_rn(pred[i], note_dur[i]);
+  const float q = __fdiv_rn(prod, 0.0116f);
+  out[i] = static_cast<int64_t>(floorf(q));
+}
+
+// ------------------------------------------------------------------ length regulator
+// scan: one warp per utterance, inclusive prefix sum of clamped durations.
+__global__ void lr_scan_kernel(const int64_t* dur, int B, int P, int32_t* ends, int64_t* mel64, int32_t* mel32) {
+  const int b = blockIdx.x;
+  const int lane = threadIdx.x;
+  int carry = 0;
+  for (int base = 0; base < P; base += 32) {
+    const int i = base + lane;
+    long long dl = (i < P) ? dur[static_cast<size_t>(b) * P + i] : 0;
+    int d = dl > 0 ? static_cast<int>(dl) : 0;
+    int x = d;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, x, off);
+      if (lane >= off) x += y;
+    }
+    if (i < P) ends[static_cast<size_t>(b) * P + i] = carry + x;
+    carry += __shfl_sync(0xffffffffu, x, 31);
+  }
+  if (lane == 0) {
+    if (mel64) mel64[b] = carry;
+    if (mel32) mel32[b] = carry;
+  }
+}
+// gather: one warp per output frame; binary search of t in ends[b,:], then a 128-bit row copy.
+__global__ void __launch_bounds__(256) lr_gather_kernel(const float* h, int h_ld, const int32_t* ends,
+                                                        const int32_t* mel32, int B, int P, int T, int C, float* out,
+                                                        int out_ld, int32_t* index_out) {
+  const long long row = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= static_cast<long long>(B) * T) return;
+  const int b = static_cast<int>(row / T), t = static_cast<int>(row - static_cast<long long>(b) * T);
+  const int32_t* e = ends + static_cast<size_t>(b) * P;
+  int idx = -1;
+  if (t < mel32[b]) {
+    int lo = 0, hi = P - 1;   // first i with ends[i] > t
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (e[mid] > t) hi = mid; else lo = mid + 1;
+    }
+    idx = lo;
+  }
+  if (lane == 0 && index_out) index_out[row] = idx;
+  float* o = out + row * out_ld;
+  if (idx < 0) {
+    for (int c = lane; c < C; c += 32) o[c] = 0.f;
+  } else {
+    const float* src = h + (static_cast<size_t>(b) * P + idx) * h_ld;
+    for (int c = lane; c < C; c += 32) o[c] = src[c];
+  }
+}
+
+// ------------------------------------------------------------------ (x + pos[t]) * mask
+__global__ void add_pos_mask_kernel(const float* x, int x_ld, const float* pos, const int32_t* lens, float* out32,
+                                    int out32_ld, void* out16, int out16_ld, int dt, int B, int T, int C) {
+  const long long n = static_cast<long long>(B) * T * C;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long row = i / C;
+    const int c = static_cast<int>(i - row * C);
+    const int b = static_cast<int>(row / T), t = static_cast<int>(row - static_cast<long long>(b) * T);
+    float v = x[row * x_ld + c] + pos[static_cast<size_t>(t) * C + c];
+    if (lens && t >= lens[b]) v = 0.f;
+    if (out32) out32[row * out32_ld + c] = v;
+    if (out16) store16(out16, row * out16_ld + c, v, dt);
+  }
+}
+
+// ------------------------------------------------------------------ f0_to_coarse + embedding gather
+__device__ __forceinline__ long long f0_coarse_of(float lf0) {
+  // utils/pitch_utils.py:22-31 on f0 = exp(log_f0) - 1, fp32 op for op
+  const float f0 = expf(lf0) - 1.0f;
+  float mel = 1127.0f * logf(1.0f + f0 / 700.0f);
+  const float mel_min = 1127.0 * 0.06899287148695143;   // ln(1 + 50/700)
+  const float denom = static_cast<float>(1127.0 * 0.9444616088408514 - 1127.0 * 0.06899287148695143);
+  if (mel > 0.f) mel = (mel - mel_min) * 254.0f / denom + 1.0f;
+  if (mel <= 1.f) mel = 1.f;
+  if (mel > 255.f) mel = 255.f;
+  return static_cast<long long>(mel + 0.5f);
+}
+__global__ void __launch_bounds__(256) f0_embed_kernel(const float* log_f0, const int64_t* coarse_in, const float* f0_emb,
+                                                       const int32_t* lens, int64_t* coarse_out, float* out32,
+                                                       int out32_ld, void* out16, int out16_ld, int dt, int B, int T,
+                                                       int C) {
+  const long long row = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= static_cast<long long>(B) * T) return;
+  const int b = static_cast<int>(row / T), t = static_cast<int>(row - static_cast<long long>(b) * T);
+  const bool live = lens ? t < lens[b] : true;
+  long long k = coarse_in ? coarse_in[row] : f0_coarse_of(log_f0[row]);
+  if (lane == 0 && coarse_out) coarse_out[row] = k;
+  const float* src = f0_emb + static_cast<size_t>(k) * C;
+  for (int c = lane; c < C; c += 32) {
+    const float v = live ? src[c] : 0.f;
+    if (out32) out32[row * out32_ld + c] = v;
+    if (out16) store16(out16, row * out16_ld + c, v, dt);
+  }
+}
+
+// ------------------------------------------------------------------ z_p = m + noise*exp(logs)*scale
+// stats is channels-last [B,T,2C]; noise is the reference layout [B,C,T] (tile transpose via smem).
+__global__ void __launch_bounds__(256) sample_prior_kernel(const float* stats, int stats_ld, const float* noise,
+                                                           float noise_scale, float* zp32, int zp_ld, void* zp16,
+                                                           int zp16_ld, int dt, int B, int T, int C) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
+  for (int j = ty; j < 32; j += 8) {
+    const int c = c0 + j, t = t0 + tx;
+    tile[j][tx] = (c < C && t < T) ? noise[(static_cast<size_t>(b) * C + c) * T + t] : 0.f;
+  }
+  __syncthreads();
+  for (int j = ty; j < 32; j += 8) {
+    const int t = t0 + j, c = c0 + tx;
+    if (t < T && c < C) {
+      const size_t row = static_cast<size_t>(b) * T + t;
+      const float m = stats[row * stats_ld + c], logs = stats[row * stats_ld + C + c];
+      // torch: m_p + randn * exp(logs_p) * noise_scale  (left to right)
+      const float v = m + (tile[tx][j] * expf(logs)) * noise_scale;
+      if (zp32) zp32[row * zp_ld + c] = v;
+      if (zp16) store16(zp16, row * zp16_ld + c, v, dt);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ conv_post (C -> 1, k taps) + tanh
+// One thread per output sample; each tap is a dot product over C contiguous 16-bit channels
+// (128-bit loads); weights live in shared memory.  Memory-bound: reads k*C*2 B per sample through L1.
+__global__ void __launch_bounds__(256) conv_post_tanh_kernel(const void* x, int dt, int x_ld, const float* w, int B,
+                                                             int L, int C, int ktaps, float* out) {
+  extern __shared__ float ws[];   // [ktaps][C]
+  for (int i = threadIdx.x; i < ktaps * C; i += blockDim.x) ws[i] = w[i];
+  __syncthreads();
+  const long long n = static_cast<long long>(B) * L;
+  const int pad = ktaps / 2;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int b = static_cast<int>(i / L), t = static_cast<int>(i - static_cast<long long>(b) * L);
+    float acc = 0.f;
+    for (int k = 0; k < ktaps; ++k) {
+      const int tt = t + k - pad;
+      if (tt < 0 || tt >= L) continue;
+      const size_t base = (static_cast<size_t>(b) * L + tt) * x_ld;
+      const float* wk = ws + k * C;
+      for (int c = 0; c < C; c += 8) {
+        const uint4 q = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(x) + base + c);
+        const uint32_t u[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float lo, hi;
+          if (dt == B200SVS_DT_BF16) {
+            lo = __uint_as_float(u[j] << 16); hi = __uint_as_float(u[j] & 0xFFFF0000u);
+          } else {
+            const __half2 h2 = *reinterpret_cast<const __half2*>(&u[j]);
+            lo = __low2float(h2); hi = __high2float(h2);
+          }
+          acc = fmaf(lo, wk[c + 2 * j], acc);
+          acc = fmaf(hi, wk[c + 2 * j + 1], acc);
+        }
+      }
+    }
+    out[i] = tanhf(acc);
+  }
+}
+
+// ------------------------------------------------------------------ layout helpers (32x32 smem transpose)
+__global__ void __launch_bounds__(256) bct_to_btc_kernel(const float* in, int B, int C, int T, float* out32, int out32_ld,
+                                                         void* out16, int out16_ld, int dt, const int32_t* lens) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int j = ty; j < 32; j += 8) {
+    const int c = c0 + j, t = t0 + tx;
+    tile[j][tx] = (c < C && t < T) ? in[(static_cast<size_t>(b) * C + c) * T + t] : 0.f;
+  }
+  __syncthreads();
+  for (int j = ty; j < 32; j += 8) {
+    const int t = t0 + j, c = c0 + tx;
+    if (t < T && c < C) {
+      float v = tile[tx][j];
+      if (lens && t >= lens[b]) v = 0.f;
+      const size_t row = static_cast<size_t>(b) * T + t;
+      if (out32) out32[row * out32_ld + c] = v;
+      if (out16) store16(out16, row * out16_ld + c, v, dt);
+    }
+  }
+}
+__global__ void __launch_bounds__(256) btc_to_bct_kernel(const float* in, int in_ld, int B, int C, int T, float* out) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int j = ty; j < 32; j += 8) {
+    const int t = t0 + j, c = c0 + tx;
+    tile[j][tx] = (c < C && t < T) ? in[(static_cast<size_t>(b) * T + t) * in_ld + c] : 0.f;
+  }
+  __syncthreads();
+  for (int j = ty; j < 32; j += 8) {
+    const int c = c0 + j, t = t0 + tx;
+    if (t < T && c < C) out[(static_cast<size_t>(b) * C + c) * T + t] = tile[tx][j];
+  }
+}
+
+static inline int grid_1d(long long n, int block, int cap) {
+  long long g = (n + block - 1) / block;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return static_cast<int>(g);
+}
+
+}  // namespace b200svs
+
+using namespace b200svs;
+
+extern "C" {
+
+int b200svs_layernorm(const float* x, int32_t x_ld, const float* res, int32_t res_ld, const float* gamma,
+                      const float* beta, float eps, const int32_t* lens, float* out32, int32_t out32_ld, void* out16,
+                      int32_t out16_ld, int32_t out16_dtype, int32_t B, int32_t T, int32_t C, void* stream) {
+  B200SVS_REQUIRE(x && gamma && beta && (out32 || out16), "layernorm: null argument");
+  B200SVS_REQUIRE(B > 0 && T > 0 && C > 0 && C <= 256, "layernorm: B=%d T=%d C=%d (C <= 256)", B, T, C);
+  LnParams p{x, x_ld, res, res_ld, gamma, beta, eps, lens, out32, out32_ld, out16, out16_ld, out16_dtype, B, T, C};
+  const long long rows = static_cast<long long>(B) * T;
+  layernorm_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, as_stream(stream)>>>(p);
+  return check_launch("layernorm_kernel");
+}
+
+int b200svs_text_embed(const int64_t* phon, const int64_t* pitch, const int64_t* tone, const float* dur,
+                       const float* e_ph, const float* e_pitch, const float* e_tone, const float* w_dur,
+                       const float* b_dur, const int64_t* x_lengths, int32_t* lens32_out, float* out, int32_t B,
+                       int32_t P, int32_t C, void* stream) {
+  B200SVS_REQUIRE(phon && pitch && tone && dur && e_ph && e_pitch && e_tone && w_dur && b_dur && x_lengths && out,
+                  "text_embed: null argument");
+  B200SVS_REQUIRE(B > 0 && P > 0 && C > 0, "text_embed: B=%d P=%d C=%d", B, P, C);
+  text_embed_kernel<<<B * P, 64, 0, as_stream(stream)>>>(phon, pitch, tone, dur, e_ph, e_pitch, e_tone, w_dur, b_dur,
+                                                        x_lengths, lens32_out, out, B, P, C, sqrtf((float)C));
+  return check_launch("text_embed_kernel");
+}
+
+int b200svs_duration_quantize(const float* pred, const float* note_dur, int64_t* dur_out, int32_t n, void* stream) {
+  B200SVS_REQUIRE(pred && note_dur && dur_out && n > 0, "duration_quantize: bad argument");
+  duration_quantize_kernel<<<(n + 255) / 256, 256, 0, as_stream(stream)>>>(pred, note_dur, dur_out, n);
+  return check_launch("duration_quantize_kernel");
+}
+
+int b200svs_lr_scan(const int64_t* dur, int32_t B, int32_t P, int32_t* ends, int64_t* mel_len64, int32_t* mel_len32,
+                    void* stream) {
+  B200SVS_REQUIRE(dur && ends && B > 0 && P > 0, "lr_scan: bad argument");
+  lr_scan_kernel<<<B, 32, 0, as_stream(stream)>>>(dur, B, P, ends, mel_len64, mel_len32);
+  return check_launch("lr_scan_kernel");
+}
+
+int b200svs_lr_gather(const float* h, int32_t h_ld, const int32_t* ends, const int32_t* mel_len32, int32_t B,
+                      int32_t P, int32_t T, int32_t C, float* out, int32_t out_ld, int32_t* index_out, void* stream) {
+  B200SVS_REQUIRE(h && ends && mel_len32 && out, "lr_gather: null argument");
+  B200SVS_REQUIRE(B > 0 && P > 0 && C > 0, "lr_gather: B=%d P=%d C=%d", B, P, C);
+  if (T <= 0) return B200SVS_OK;   // every utterance has zero frames
+  const long long rows = static_cast<long long>(B) * T;
+  lr_gather_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, as_stream(stream)>>>(h, h_ld, ends, mel_len32, B, P,
+                                                                                       T, C, out, out_ld, index_out);
+  return check_launch("lr_gather_kernel");
+}
+
+int b200svs_add_pos_mask(const float* x, int32_t x_ld, const float* pos, const int32_t* lens, float* out32,
+                         int32_t out32_ld, void* out16, int32_t out16_ld, int32_t out16_dtype, int32_t B, int32_t T,
+                         int32_t C, void* stream) {
+  B200SVS_REQUIRE(x && pos && (out32 || out16) && B > 0 && T > 0 && C > 0, "add_pos_mask: bad argument");
+  const long long n = static_cast<long long>(B) * T * C;
+  add_pos_mask_kernel<<<grid_1d(n, 256, num_sms() * 16), 256, 0, as_stream(stream)>>>(x, x_ld, pos, lens, out32, out32_ld,
+                                                                                     out16, out16_ld, out16_dtype, B, T, C);
+  return check_launch("add_pos_mask_kernel");
+}
+
+int b200svs_f0_embed(const float* log_f0, const int64_t* coarse_in, const float* f0_emb, const int32_t* lens,
+                     int64_t* coarse_out, float* out32, int32_t out32_ld, void* out16, int32_t out16_ld,
+                     int32_t out16_dtype, int32_t B, int32_t T, int32_t C, void* stream) {
+  B200SVS_REQUIRE((log_f0 || coarse_in) && f0_emb && (out32 || out16) && B > 0 && T > 0, "f0_embed: bad argument");
+  const long long rows = static_cast<long long>(B) * T;
+  f0_embed_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, as_stream(stream)>>>(
+      log_f0, coarse_in, f0_emb, lens, coarse_out, out32, out32_ld, out16, out16_ld, out16_dtype, B, T, C);
+  return check_launch("f0_embed_kernel");
+}
+
+int b200svs_sample_prior(const float* stats, int32_t stats_ld, const float* noise_bct, float noise_scale, float* zp32,
+                         int32_t zp_ld, void* zp16, int32_t zp16_ld, int32_t out16_dtype, int32_t B, int32_t T,
+                         int32_t C, void* stream) {
+  B200SVS_REQUIRE(stats && noise_bct && (zp32 || zp16) && B > 0 && T > 0 && C > 0, "sample_prior: bad argument");
+  dim3 grid((T + 31) / 32, (C + 31) / 32, B);
+  sample_prior_kernel<<<grid, 256, 0, as_stream(stream)>>>(stats, stats_ld, noise_bct, noise_scale, zp32, zp_ld, zp16,
+                                                          zp16_ld, out16_dtype, B, T, C);
+  return check_launch("sample_prior_kernel");
+}
+
+int b200svs_conv_post_tanh(const void* x, int32_t x_dtype, int32_t x_ld, const float* w, int32_t B, int32_t L,
+                           int32_t C, int32_t ktaps, float* out, void* stream) {
+  B200SVS_REQUIRE(x && w && out && B > 0 && L > 0, "conv_post_tanh: bad argument");
+  B200SVS_REQUIRE(C % 8 == 0 && x_ld % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0,
+                  "conv_post_tanh: C=%d ld=%d must be multiples of 8, x 16-B aligned", C, x_ld);
+  const long long n = static_cast<long long>(B) * L;
+  conv_post_tanh_kernel<<<grid_1d(n, 256, num_sms() * 32), 256, ktaps * C * sizeof(float), as_stream(stream)>>>(
+      x, x_dtype, x_ld, w, B, L, C, ktaps, out);
+  return check_launch("conv_post_tanh_kernel");
+}
+
+int b200svs_bct_to_btc(const float* in_bct, int32_t B, int32_t C, int32_t T, float* out32, int32_t out32_ld,
+                       void* out16, int32_t out16_ld, int32_t out16_dtype, const int32_t* lens, void* stream) {
+  B200SVS_REQUIRE(in_bct && (out32 || out16) && B > 0 && C > 0 && T > 0, "bct_to_btc: bad argument");
+  dim3 grid((T + 31) / 32, (C + 31) / 32, B);
+  bct_to_btc_kernel<<<grid, 256, 0, as_stream(stream)>>>(in_bct, B, C, T, out32, out32_ld, out16, out16_ld, out16_dtype, lens);
+  return check_launch("bct_to_btc_kernel");
+}
+
+int b200svs_btc_to_bct(const float* in_btc, int32_t in_ld, int32_t B, int32_t C, int32_t T, float* out_bct,
+                       void* stream) {
+  B200SVS_REQUIRE(in_btc && out_bct && B > 0 && C > 0 && T > 0, "btc_to_bct: bad argument");
+  dim3 grid((T + 31) / 32, (C + 31) / 32, B);
+  btc_to_bct_kernel<<<grid, 256, 0, as_stream(stream)>>>(in_btc, in_ld, B, C, T, out_bct);
+  return check_launch("btc_to_bct_kernel");
+}
+
+}  // extern "C"

@@ -1,0 +1,196 @@
+"""Thin torch-tensor wrappers over the C ABI (include/b200svs.h).
+
+Tensors are channels-last [B, T, C] views (last dim contiguous, rows `ld` elements apart, batch
+stride = T*ld).  PyTorch is used for device memory and streams only; every numeric op below is a
+hand-written sm_100a kernel in libb200svs.so.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import (ACT_GATE, ACT_GELU, ACT_NONE, ACT_RELU, ACT_SIGMOID, ACT_TANH, DT_BF16, DT_F16,
+                   ConvArgs, Epilogue)
+
+__all__ = ["conv1d", "attention", "layernorm", "ACT_NONE", "ACT_RELU", "ACT_GELU", "ACT_SIGMOID",
+           "ACT_TANH", "ACT_GATE"]
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def dt_code(dtype):
+    if dtype == torch.float16:
+        return DT_F16
+    if dtype == torch.bfloat16:
+        return DT_BF16
+    raise TypeError(f"16-bit operand dtype expected, got {dtype}")
+
+
+def _btc(t, name):
+    """Checks a [B,T,C] channels-last view and returns its row stride."""
+    if t is None:
+        return 0
+    if t.dim() != 3 or t.stride(2) != 1 or (t.shape[0] > 1 and t.stride(0) != t.shape[1] * t.stride(1)):
+        raise ValueError(f"{name}: expected a [B,T,C] view with unit channel stride and dense batch stride, "
+                         f"got shape {tuple(t.shape)} strides {t.stride()}")
+    if not t.is_cuda:
+        raise ValueError(f"{name}: CUDA tensor required (there is no CPU path)")
+    return t.stride(1)
+
+
+class PackedConv:
+    """Device-resident packed weights of one convolution (see packer.py)."""
+    __slots__ = ("w", "bias", "ntaps", "dil", "pad_left", "cin", "cin_pad", "cout", "cout_pad", "block_n",
+                 "gate", "f32", "n_out")
+
+    def __init__(self, w, bias, ntaps, dil, pad_left, cin, cin_pad, cout, cout_pad, block_n, gate, f32):
+        self.w, self.bias, self.ntaps, self.dil, self.pad_left = w, bias, ntaps, dil, pad_left
+        self.cin, self.cin_pad, self.cout, self.cout_pad = cin, cin_pad, cout, cout_pad
+        self.block_n, self.gate, self.f32 = block_n, gate, f32
+        self.n_out = cout // 2 if gate else cout      # columns the epilogue stores
+
+    def to(self, device):
+        self.w = self.w.to(device)
+        self.bias = None if self.bias is None else self.bias.to(device)
+        return self
+
+
+def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, res2=None, lens=None,
+           out32=None, out16=None, post_lrelu=None, w_rows=None, n_valid=None):
+    """out = epilogue(conv(x, pc)).  See b200svs_epilogue in include/b200svs.h for the formula.
+    `w_rows=(row0, nrows)` restricts the conv to a block of packed output channels (WN res/skip split)."""
+    B, T, cin = x.shape
+    x_ld = _btc(x, "x")
+    if cin != pc.cin:
+        raise ValueError(f"conv1d: input has {cin} channels, weights expect {pc.cin}")
+    a = ConvArgs()
+    a.x = x.data_ptr()
+    a.B, a.T, a.Cin, a.x_ld = B, T, cin, x_ld
+    a.ntaps, a.Cin_pad, a.dil, a.pad_left = pc.ntaps, pc.cin_pad, pc.dil, pc.pad_left
+    bias = pc.bias
+    cout_pad, n_out, w = pc.cout_pad, pc.n_out, pc.w
+    if w_rows is not None:
+        if pc.f32 or pc.gate:
+            raise ValueError("w_rows is only supported for plain tensor-core convs")
+        r0, nr = w_rows
+        # packed [ntaps, Cout_pad, Cin_pad]: a row block is a strided view -> only valid for 1 tap
+        if pc.ntaps != 1:
+            raise ValueError("w_rows needs a 1-tap conv")
+        w = pc.w[0, r0:r0 + nr]
+        bias = None if bias is None else bias[r0:r0 + nr]
+        cout_pad, n_out = nr, nr
+    a.w = w.data_ptr()
+    a.Cout_pad = cout_pad
+    a.block_n = pc.block_n if w_rows is None else min(pc.block_n, cout_pad)
+    e = a.ep
+    e.bias = None if bias is None else bias.data_ptr()
+    if gbias is not None:
+        e.gbias, e.gbias_ld = gbias.data_ptr(), gbias.stride(0)
+    e.act = ACT_GATE if pc.gate else act
+    e.alpha, e.scale = alpha, scale
+    if res1 is not None:
+        e.res1, e.res1_ld = res1.data_ptr(), _btc(res1, "res1")
+    if res2 is not None:
+        e.res2, e.res2_ld = res2.data_ptr(), _btc(res2, "res2")
+    if lens is not None:
+        e.lens = lens.data_ptr()
+    e.lens_div = 1
+    if out32 is not None:
+        e.out32, e.out32_ld = out32.data_ptr(), _btc(out32, "out32")
+    if out16 is not None:
+        e.out16, e.out16_ld, e.out16_dtype = out16.data_ptr(), _btc(out16, "out16"), dt_code(out16.dtype)
+    if post_lrelu is not None:
+        e.post_lrelu, e.post_slope = 1, float(post_lrelu)
+    e.n_valid = n_out if n_valid is None else n_valid
+    if pc.f32:
+        if x.dtype != torch.float32:
+            raise TypeError("fp32 conv needs fp32 activations")
+        _lib.call("b200svs_conv1d_f32", C.byref(a), _stream())
+    else:
+        a.x_dtype = dt_code(x.dtype)
+        if pc.w.dtype != x.dtype:
+            raise TypeError(f"operand dtype mismatch: x {x.dtype}, w {pc.w.dtype}")
+        _lib.call("b200svs_conv1d_tc", C.byref(a), _stream())
+
+
+def attention(qkv, out32, out16, rel_k, rel_v, lens, heads=2, window=4):
+    B, T, c3 = qkv.shape
+    c = c3 // 3
+    _lib.call("b200svs_attention_f32", _ptr(qkv), _btc(qkv, "qkv"), _ptr(out32), _btc(out32, "out32"),
+              _ptr(out16), _btc(out16, "out16"), 0 if out16 is None else dt_code(out16.dtype),
+              _ptr(rel_k), _ptr(rel_v), _ptr(lens), B, T, c, heads, window, _stream())
+
+
+def layernorm(x, gamma, beta, lens, out32=None, out16=None, res=None, eps=1e-5):
+    B, T, c = x.shape
+    _lib.call("b200svs_layernorm", _ptr(x), _btc(x, "x"), _ptr(res), _btc(res, "res"), _ptr(gamma), _ptr(beta),
+              eps, _ptr(lens), _ptr(out32), _btc(out32, "out32"), _ptr(out16), _btc(out16, "out16"),
+              0 if out16 is None else dt_code(out16.dtype), B, T, c, _stream())
+
+
+def text_embed(phon, pitch, tone, dur, e_ph, e_pitch, e_tone, w_dur, b_dur, x_lengths, lens32, out):
+    B, P = phon.shape
+    _lib.call("b200svs_text_embed", _ptr(phon), _ptr(pitch), _ptr(tone), _ptr(dur), _ptr(e_ph), _ptr(e_pitch),
+              _ptr(e_tone), _ptr(w_dur), _ptr(b_dur), _ptr(x_lengths), _ptr(lens32), _ptr(out), B, P,
+              out.shape[-1], _stream())
+
+
+def duration_quantize(pred, note_dur, out):
+    _lib.call("b200svs_duration_quantize", _ptr(pred), _ptr(note_dur), _ptr(out), pred.numel(), _stream())
+
+
+def lr_scan(dur, ends, mel64, mel32):
+    B, P = dur.shape
+    _lib.call("b200svs_lr_scan", _ptr(dur), B, P, _ptr(ends), _ptr(mel64), _ptr(mel32), _stream())
+
+
+def lr_gather(h, ends, mel32, out, index_out=None):
+    B, P, c = h.shape
+    T = out.shape[1]
+    _lib.call("b200svs_lr_gather", _ptr(h), _btc(h, "h"), _ptr(ends), _ptr(mel32), B, P, T, c, _ptr(out),
+              _btc(out, "out"), _ptr(index_out), _stream())
+
+
+def add_pos_mask(x, pos, lens, out32=None, out16=None):
+    B, T, c = x.shape
+    _lib.call("b200svs_add_pos_mask", _ptr(x), _btc(x, "x"), _ptr(pos), _ptr(lens), _ptr(out32),
+              _btc(out32, "out32"), _ptr(out16), _btc(out16, "out16"),
+              0 if out16 is None else dt_code(out16.dtype), B, T, c, _stream())
+
+
+def f0_embed(log_f0, coarse_in, table, lens, coarse_out, out32=None, out16=None):
+    o = out32 if out32 is not None else out16
+    B, T, c = o.shape
+    _lib.call("b200svs_f0_embed", _ptr(log_f0), _ptr(coarse_in), _ptr(table), _ptr(lens), _ptr(coarse_out),
+              _ptr(out32), _btc(out32, "out32"), _ptr(out16), _btc(out16, "out16"),
+              0 if out16 is None else dt_code(out16.dtype), B, T, c, _stream())
+
+
+def sample_prior(stats, noise_bct, noise_scale, zp32=None, zp16=None):
+    B, T, c2 = stats.shape
+    _lib.call("b200svs_sample_prior", _ptr(stats), _btc(stats, "stats"), _ptr(noise_bct), float(noise_scale),
+              _ptr(zp32), _btc(zp32, "zp32"), _ptr(zp16), _btc(zp16, "zp16"),
+              0 if zp16 is None else dt_code(zp16.dtype), B, T, c2 // 2, _stream())
+
+
+def conv_post_tanh(x16, w, out):
+    B, L, c = x16.shape
+    _lib.call("b200svs_conv_post_tanh", _ptr(x16), dt_code(x16.dtype), _btc(x16, "x"), _ptr(w), B, L, c,
+              w.shape[0], _ptr(out), _stream())
+
+
+def bct_to_btc(x_bct, out32=None, out16=None, lens=None):
+    B, c, T = x_bct.shape
+    _lib.call("b200svs_bct_to_btc", _ptr(x_bct), B, c, T, _ptr(out32), _btc(out32, "out32"), _ptr(out16),
+              _btc(out16, "out16"), 0 if out16 is None else dt_code(out16.dtype), _ptr(lens), _stream())
+
+
+def btc_to_bct(x_btc, out_bct):
+    B, T, c = x_btc.shape
+    _lib.call("b200svs_btc_to_bct", _ptr(x_btc), _btc(x_btc, "x"), B, c, T, _ptr(out_bct), _stream())

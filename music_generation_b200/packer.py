@@ -1,0 +1,120 @@
+"""Load-time weight packing: fold weight-norm once, lay weights out for the kernels.
+
+The reference never calls remove_weight_norm at inference, so every forward recomputes
+w = g * v / ||v|| for ~100 convs (VISinger/models_ae.py:311, modules.py:135,145,
+191-206).  Here that happens once per load_state_dict.
+
+Layouts (see include/b200svs.h):
+  tensor-core convs : [ntaps][Cout_pad][Cin_pad] 16-bit, Cin contiguous (K-major B operand for TMA)
+  fp32 SIMT convs   : [ntaps][Cin][Cout_pad] fp32, Cout contiguous
+ConvTranspose1d(stride s, kernel 2s, padding s/2) becomes a 3-tap conv over input time with s*Cout
+output columns (polyphase).  WN in_layers are packed so each N tile holds a tanh
+half and the matching sigmoid half (GATE epilogue).  The flow's channel Flips are folded into the
+pre/post 1x1 weights.
+"""
+import torch
+
+from .ops import PackedConv
+
+
+def fold_weight_norm(sd, prefix):
+    """Old-style torch.nn.utils.weight_norm, dim=0: w = g * v / ||v||_2 over all dims but 0."""
+    if prefix + ".weight" in sd:
+        return sd[prefix + ".weight"].detach().float()
+    v = sd[prefix + ".weight_v"].detach().float()
+    g = sd[prefix + ".weight_g"].detach().float()
+    norm = v.reshape(v.shape[0], -1).norm(dim=1).reshape(-1, *([1] * (v.dim() - 1)))
+    return v * (g / norm)
+
+
+def _round_up(x, m):
+    return (x + m - 1) // m * m
+
+
+def choose_block_n(cout):
+    """N tile of the tensor-core conv: a multiple of 16, <= 256, minimising padded columns."""
+    if cout <= 256:
+        return _round_up(cout, 16)
+    best = None
+    for bn in (256, 192, 128):
+        pad = _round_up(cout, bn)
+        if best is None or pad < best[0]:
+            best = (pad, bn)
+    return best[1]
+
+
+def pack_conv(weight, bias, *, dil=1, pad_left=None, dtype=torch.float16, f32=False, gate=False,
+              block_n=None):
+    """weight: [Cout, Cin, k] effective (weight-norm folded) Conv1d weight."""
+    weight = weight.detach().float()
+    cout, cin, k = weight.shape
+    if pad_left is None:
+        pad_left = (k * dil - dil) // 2          # commons.get_padding (VISinger/commons.py:14-15)
+    b = None if bias is None else bias.detach().float()
+    if f32:
+        cout_pad = _round_up(cout, 64)
+        w = torch.zeros(k, cin, cout_pad)
+        w[:, :, :cout] = weight.permute(2, 1, 0)
+        bp = None
+        if b is not None:
+            bp = torch.zeros(cout_pad)
+            bp[:cout] = b
+        return PackedConv(w.contiguous(), bp, k, dil, pad_left, cin, cin, cout, cout_pad, 64, False, True)
+    cin_pad = _round_up(cin, 64)
+    if gate:
+        half = cout // 2
+        bn = block_n or 128
+        hb = bn // 2
+        if half % hb:
+            raise ValueError(f"gate packing needs hidden {half} divisible by {hb}")
+        order = []
+        for n in range(half // hb):
+            order += list(range(n * hb, (n + 1) * hb)) + list(range(half + n * hb, half + (n + 1) * hb))
+        idx = torch.tensor(order)
+        weight = weight[idx]
+        if b is not None:
+            b = b[idx]
+        cout_pad = cout
+    else:
+        bn = block_n or choose_block_n(cout)
+        cout_pad = _round_up(cout, bn)
+    w = torch.zeros(k, cout_pad, cin_pad)
+    w[:, :cout, :cin] = weight.permute(2, 0, 1)
+    bp = None
+    if b is not None:
+        bp = torch.zeros(cout_pad)
+        bp[:cout] = b
+    return PackedConv(w.to(dtype).contiguous(), bp, k, dil, pad_left, cin, cin_pad, cout, cout_pad, bn, gate, False)
+
+
+def gate_order(hidden, block_n=128):
+    """Packed column order of a gated [tanh | sigmoid] 2*hidden conv (also used for cond biases)."""
+    hb = block_n // 2
+    order = []
+    for n in range(hidden // hb):
+        order += list(range(n * hb, (n + 1) * hb)) + list(range(hidden + n * hb, hidden + (n + 1) * hb))
+    return torch.tensor(order)
+
+
+def pack_conv_transpose(weight, bias, stride, padding, *, dtype=torch.float16, block_n=None):
+    """weight: [Cin, Cout, K] ConvTranspose1d weight with K == 2*stride, padding == stride//2... any
+    K <= 2*stride + padding works as long as every output phase needs only input offsets -1, 0, +1.
+
+    y[q*s + r, co] = sum_{j in 0..2} sum_ci x[q + j - 1, ci] * w[ci, co, (1 - j)*s + r + p]
+    -> a 3-tap conv (pad_left 1) with output column r*Cout + co; the [B, Tin, s*Cout] result is the
+    [B, s*Tin, Cout] tensor."""
+    weight = weight.detach().float()
+    cin, cout, K = weight.shape
+    s, p = stride, padding
+    w3 = torch.zeros(s * cout, cin, 3)
+    for r in range(s):
+        for j in range(3):
+            k = (1 - j) * s + r + p
+            if 0 <= k < K:
+                w3[r * cout:(r + 1) * cout, :, j] = weight[:, :, k].t()
+    # every kernel tap must be reachable with offsets -1..+1
+    reach = {(1 - j) * s + r + p for r in range(s) for j in range(3)}
+    if not set(range(K)) <= reach:
+        raise ValueError(f"ConvTranspose1d(k={K}, s={s}, p={p}) does not fit the 3-tap polyphase form")
+    b3 = None if bias is None else bias.detach().float().repeat(s)
+    return pack_conv(w3, b3, dil=1, pad_left=1, dtype=dtype, block_n=block_n)
