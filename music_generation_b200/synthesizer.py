@@ -1,0 +1,479 @@
+"""SynthesizerTrn - drop-in for the reference's VISinger synthesis model on B200.
+
+Mirrors the constructor and `infer(...)` of VISinger/models_ae.py:446-651 (variant "ae", SVS v5/v6,
+6-tuple result) and VISinger/models.py:622-673 (variant "v4", 5-tuple result).  Same state-dict keys,
+same `.cuda()/.eval()/.load_state_dict()` behaviour, so pipline_inference_svs_*.Synthesiser works
+unchanged.  Everything numeric runs in the hand-written sm_100a kernels of
+libb200svs.so; there is no PyTorch/CPU fallback - without the library or a B200 `infer` raises.
+
+Precision plan (DESIGN.md "Numerics"): phoneme-level path and F0 predictor in fp32 (their outputs
+cross float->int boundaries), every other conv on the tcgen05 tensor cores with 16-bit operands and
+fp32 accumulation, residual streams kept in fp32.
+"""
+import math
+
+import torch
+from torch import nn
+
+from . import ops, packer, params
+from .ops import ACT_GELU, ACT_NONE, ACT_RELU, ACT_SIGMOID
+
+LRELU_SLOPE = 0.1   # VISinger/modules.py:17
+
+
+def _require_cuda(t):
+    if not t.is_cuda:
+        raise RuntimeError("SynthesizerTrn.infer: inputs must be CUDA tensors - this build has no CPU path")
+
+
+class _Enc:
+    """Packed weights of one attentions.Encoder layer."""
+    __slots__ = ("qkv", "o", "ffn1", "ffn2", "rel_k", "rel_v", "ln1", "ln2")
+
+
+class SynthesizerTrn(nn.Module):
+    variant = "ae"
+
+    def __init__(self, n_vocab, spec_channels, segment_size, inter_channels, hidden_channels, filter_channels,
+                 n_heads, n_layers, kernel_size, p_dropout, resblock, resblock_kernel_sizes,
+                 resblock_dilation_sizes, upsample_rates, upsample_initial_channel, upsample_kernel_sizes,
+                 n_speakers=0, gin_channels=0, use_sdp=True, n_vocab_note=100, *, operand_dtype="fp16",
+                 max_position_embeddings=2000, generator_chunk_frames=32768, seed=1234, **kwargs):
+        super().__init__()
+        if hidden_channels != 192 or n_heads != 2:
+            raise ValueError("kernels are specialised for hidden_channels=192, n_heads=2 (ours_ae.json)")
+        self.n_vocab, self.spec_channels, self.segment_size = n_vocab, spec_channels, segment_size
+        self.inter_channels, self.hidden_channels, self.filter_channels = inter_channels, hidden_channels, filter_channels
+        self.n_heads, self.n_layers, self.kernel_size, self.p_dropout = n_heads, n_layers, kernel_size, p_dropout
+        self.resblock = str(resblock)
+        self.resblock_kernel_sizes = list(resblock_kernel_sizes)
+        self.resblock_dilation_sizes = [list(d) for d in resblock_dilation_sizes]
+        self.upsample_rates, self.upsample_kernel_sizes = list(upsample_rates), list(upsample_kernel_sizes)
+        self.upsample_initial_channel = upsample_initial_channel
+        self.n_speakers, self.gin_channels, self.use_sdp = n_speakers, gin_channels, use_sdp
+        self.operand_dtype = {"fp16": torch.float16, "bf16": torch.bfloat16}[operand_dtype]
+        self.generator_chunk_frames = generator_chunk_frames
+        self.hop = 1
+        for u in self.upsample_rates:
+            self.hop *= u
+        spec = params.build_spec(
+            variant=self.variant, n_vocab=n_vocab, spec_channels=spec_channels, inter=inter_channels,
+            hidden=hidden_channels, filt=filter_channels, heads=n_heads, n_layers=n_layers, ksize=kernel_size,
+            resblock=self.resblock, rb_kernels=self.resblock_kernel_sizes, rb_dils=self.resblock_dilation_sizes,
+            up_rates=self.upsample_rates, up_init=upsample_initial_channel, up_kernels=self.upsample_kernel_sizes,
+            gin=gin_channels, n_vocab_note=n_vocab_note, max_pos=max_position_embeddings)
+        params.materialise(self, spec, seed=seed)
+        self._packed = None
+        self.last_aux = {}
+
+    # ------------------------------------------------------------------ nn.Module plumbing
+    def _apply(self, fn, *a, **k):
+        self._packed = None
+        return super()._apply(fn, *a, **k)
+
+    def load_state_dict(self, state_dict, strict=True, **k):
+        self._packed = None
+        # tolerate a position table enlarged for T > 2000
+        kp = "text_post_net.position_embeddings.weight"
+        if kp in state_dict and state_dict[kp].shape != self.text_post_net.position_embeddings.weight.shape:
+            n = state_dict[kp].shape[0]
+            dev = self.text_post_net.position_embeddings.weight.device
+            self.text_post_net.position_embeddings.weight = nn.Parameter(
+                torch.empty(n, self.hidden_channels, device=dev), requires_grad=False)
+            self.text_post_net.position_ids = torch.arange(n, device=dev).unsqueeze(0)
+        return super().load_state_dict(state_dict, strict=strict, **k)
+
+    @property
+    def device(self):
+        return self.text_post_net.f0_emb.weight.device
+
+    # ------------------------------------------------------------------ weight packing (once per load)
+    def _pack(self):
+        sd = {k: v.detach().float().cpu() for k, v in self.state_dict().items()}
+        dev, dt = self.device, self.operand_dtype
+        W = lambda p: packer.fold_weight_norm(sd, p)
+        Bv = lambda p: sd.get(p + ".bias")
+        P = {}
+
+        def enc(prefix, n_layers, f32):
+            layers = []
+            for i in range(n_layers):
+                a, e = f"{prefix}.attn_layers.{i}", _Enc()
+                wqkv = torch.cat([W(f"{a}.conv_{n}") for n in "qkv"], 0)
+                bqkv = torch.cat([Bv(f"{a}.conv_{n}") for n in "qkv"], 0)
+                e.qkv = packer.pack_conv(wqkv, bqkv, dtype=dt, f32=f32).to(dev)
+                e.o = packer.pack_conv(W(a + ".conv_o"), Bv(a + ".conv_o"), dtype=dt, f32=f32).to(dev)
+                f = f"{prefix}.ffn_layers.{i}"
+                e.ffn1 = packer.pack_conv(W(f + ".conv_1"), Bv(f + ".conv_1"), dtype=dt, f32=f32).to(dev)
+                e.ffn2 = packer.pack_conv(W(f + ".conv_2"), Bv(f + ".conv_2"), dtype=dt, f32=f32).to(dev)
+                e.rel_k = sd[a + ".emb_rel_k"][0].contiguous().to(dev)
+                e.rel_v = sd[a + ".emb_rel_v"][0].contiguous().to(dev)
+                e.ln1 = (sd[f"{prefix}.norm_layers_1.{i}.gamma"].to(dev), sd[f"{prefix}.norm_layers_1.{i}.beta"].to(dev))
+                e.ln2 = (sd[f"{prefix}.norm_layers_2.{i}.gamma"].to(dev), sd[f"{prefix}.norm_layers_2.{i}.beta"].to(dev))
+                layers.append(e)
+            return layers
+
+        def conv(p, f32=False, **kw):
+            return packer.pack_conv(W(p), Bv(p), dtype=dt, f32=f32, **kw).to(dev)
+
+        def wn_stack(prefix):
+            n = 0
+            while f"{prefix}.in_layers.{n}.bias" in sd:
+                n += 1
+            st = {"in": [], "rs": [], "n": n, "cond": None}
+            for i in range(n):
+                st["in"].append(packer.pack_conv(W(f"{prefix}.in_layers.{i}"), Bv(f"{prefix}.in_layers.{i}"),
+                                                 dtype=dt, gate=True).to(dev))
+                st["rs"].append(packer.pack_conv(W(f"{prefix}.res_skip_layers.{i}"), Bv(f"{prefix}.res_skip_layers.{i}"),
+                                                 dtype=dt, block_n=192).to(dev))
+            if self.gin_channels:
+                wc, bc = W(prefix + ".cond_layer"), Bv(prefix + ".cond_layer")
+                h2 = 2 * self.hidden_channels
+                order = packer.gate_order(self.hidden_channels)
+                idx = torch.cat([order + i * h2 for i in range(n)])
+                st["cond"] = packer.pack_conv(wc[idx], bc[idx], f32=True).to(dev)
+            return st
+
+        te = "text_encoder"
+        P["emb"] = tuple(sd[f"{te}.{n}"].contiguous().to(dev) for n in
+                         ("emb_phoneme.weight", "emb_note_pitch.weight", "emb_phone_shengdiao.weight"))
+        P["emb_dur"] = (sd[te + ".emb_note_duration.weight"].reshape(-1).contiguous().to(dev),
+                        sd[te + ".emb_note_duration.bias"].contiguous().to(dev))
+        P["text_enc"] = enc(te + ".encoder", self.n_layers, True)
+        dp = "duration_predictor"
+        P["dp"] = [(conv(f"{dp}.conv_{i}", f32=True), sd[f"{dp}.norm_{i}.gamma"].to(dev), sd[f"{dp}.norm_{i}.beta"].to(dev))
+                   for i in (1, 2, 3)]
+        P["dp_proj"] = conv(dp + ".proj", f32=True)
+        tp = "text_post_net"
+        P["pos"] = sd[tp + ".position_embeddings.weight"].contiguous().to(dev)
+        P["f0_enc"] = enc(tp + ".f0_predictor.encoder", 6, True)
+        P["f0_out"] = conv(tp + ".f0_predictor.output_layer", f32=True)
+        P["f0_emb"] = sd[tp + ".f0_emb.weight"].contiguous().to(dev)
+        P["mel_cond"] = conv(tp + ".mel_predict_net.condition_proj")
+        P["mel_enc"] = enc(tp + ".mel_predict_net.encoder", 4, False)
+        P["mel_out"] = conv(tp + ".mel_predict_net.output_layer")
+        P["fp_cond"] = conv(tp + ".frame_prior_net.condition_proj")
+        P["fp"] = []
+        i = 0
+        while f"{tp}.frame_prior_net.conv_layers.{i}.weight" in sd:
+            P["fp"].append(conv(f"{tp}.frame_prior_net.conv_layers.{i}"))
+            i += 1
+        P["proj"] = conv(tp + ".proj")
+        # flow: Flip folded into pre (input order) / post (output order); reverse order of application
+        half = self.inter_channels // 2
+        n_flows = 0
+        while f"spec_flow.spec_flows.{2 * n_flows}.pre.weight" in sd:
+            n_flows += 1
+        P["flow"] = []
+        for i in reversed(range(n_flows)):
+            p = f"spec_flow.spec_flows.{2 * i}"
+            flipped = (n_flows - 1 - i) % 2 == 0
+            wpre, wpost, bpost = W(p + ".pre"), W(p + ".post"), Bv(p + ".post")
+            if flipped:
+                wpre, wpost, bpost = wpre.flip(1), wpost.flip(0), bpost.flip(0)
+            P["flow"].append(dict(
+                pre=packer.pack_conv(wpre, Bv(p + ".pre"), dtype=dt).to(dev),
+                post=packer.pack_conv(wpost, bpost, dtype=dt).to(dev),
+                wn=wn_stack(p + ".enc"),
+                in_off=half if flipped else 0, out_off=0 if flipped else half))
+        if self.variant == "ae":
+            P["sd_pre"] = conv("spec_decoder.pre")
+            P["sd_wn"] = wn_stack("spec_decoder.enc")
+            P["sd_proj"] = conv("spec_decoder.proj")
+            P["spec_proj"] = conv("spec_proj")
+        # generator
+        d = "decoder"
+        P["g_pre"] = conv(d + ".conv_pre")
+        P["g_cond"] = conv(d + ".cond", f32=True) if self.gin_channels else None
+        P["g_ups"] = []
+        for i, (u, k) in enumerate(zip(self.upsample_rates, self.upsample_kernel_sizes)):
+            P["g_ups"].append(packer.pack_conv_transpose(W(f"{d}.ups.{i}"), Bv(f"{d}.ups.{i}"), u, (k - u) // 2,
+                                                         dtype=dt).to(dev))
+        P["g_rb"] = []
+        nk = len(self.resblock_kernel_sizes)
+        for i in range(len(self.upsample_rates)):
+            stage = []
+            for j, (k, dils) in enumerate(zip(self.resblock_kernel_sizes, self.resblock_dilation_sizes)):
+                p = f"{d}.resblocks.{i * nk + j}"
+                if self.resblock == "1":
+                    pairs = [(conv(f"{p}.convs1.{m}", dil=dl), conv(f"{p}.convs2.{m}", dil=1)) for m, dl in enumerate(dils)]
+                else:
+                    pairs = [(conv(f"{p}.convs.{m}", dil=dl), None) for m, dl in enumerate(dils)]
+                stage.append(pairs)
+            P["g_rb"].append(stage)
+        wpost = W(d + ".conv_post")                     # [1, C, 7] -> [7][C] fp32
+        P["g_post"] = wpost[0].t().contiguous().to(dev)
+        self._packed = P
+        return P
+
+    # ------------------------------------------------------------------ building blocks
+    def _encoder(self, layers, x32, x16, lens, f32):
+        """attentions.Encoder (VISinger/attentions.py:35-47), channels-last, in place on x32 (/x16).
+        x is masked on entry and after every LayerNorm; valid rows equal the reference's."""
+        B, T, Cc = x32.shape
+        dev = x32.device
+        dt = self.operand_dtype
+        qkv = torch.empty(B, T, 3 * Cc, device=dev, dtype=torch.float32)
+        att32 = torch.empty(B, T, Cc, device=dev, dtype=torch.float32)
+        att16 = None if f32 else torch.empty(B, T, Cc, device=dev, dtype=dt)
+        tmp = torch.empty(B, T, Cc, device=dev, dtype=torch.float32)
+        hdt = torch.float32 if f32 else dt
+        hid = torch.empty(B, T, self.filter_channels, device=dev, dtype=hdt)
+        for e in layers:
+            xin = x32 if f32 else x16
+            ops.conv1d(e.qkv, xin, out32=qkv)
+            ops.attention(qkv, att32, att16, e.rel_k, e.rel_v, lens)
+            ops.conv1d(e.o, att32 if f32 else att16, res1=x32, out32=tmp)
+            ops.layernorm(tmp, e.ln1[0], e.ln1[1], lens, out32=x32, out16=x16)
+            xin = x32 if f32 else x16
+            if f32:
+                ops.conv1d(e.ffn1, xin, act=ACT_RELU, lens=lens, out32=hid)
+            else:
+                ops.conv1d(e.ffn1, xin, act=ACT_RELU, lens=lens, out16=hid)
+            ops.conv1d(e.ffn2, hid, res1=x32, lens=lens, out32=tmp)
+            ops.layernorm(tmp, e.ln2[0], e.ln2[1], lens, out32=x32, out16=x16)
+
+    def _wn(self, st, x32, x16, lens, out16, gcond=None):
+        """modules.WN (VISinger/modules.py:148-176): x32/x16 hold the masked input and are updated in
+        place; the masked skip sum is written to out16 (16-bit, consumer is always a 1x1 conv)."""
+        B, T, H = x32.shape
+        dev = x32.device
+        acts = torch.empty(B, T, H, device=dev, dtype=self.operand_dtype)
+        skip = torch.empty(B, T, H, device=dev, dtype=torch.float32)
+        n = st["n"]
+        for i in range(n):
+            gb = None if gcond is None else gcond[:, i * 2 * H:(i + 1) * 2 * H]
+            ops.conv1d(st["in"][i], x16, gbias=gb, out16=acts)
+            rs = st["rs"][i]
+            if i < n - 1:
+                ops.conv1d(rs, acts, w_rows=(0, H), res1=x32, lens=lens, out32=x32, out16=x16)
+                ops.conv1d(rs, acts, w_rows=(H, H), res1=skip if i > 0 else None, out32=skip)
+            else:
+                ops.conv1d(rs, acts, res1=skip if i > 0 else None, lens=lens, out16=out16)
+
+    def _generator(self, x16, gbias=None):
+        """Generator.forward (VISinger/models_ae.py:327-346).  x16: [B,T,C] masked input; returns [B,1,T*hop]."""
+        P = self._packed
+        B, T, _ = x16.shape
+        dev, dt = x16.device, self.operand_dtype
+        out = torch.empty(B, 1, T * self.hop, device=dev, dtype=torch.float32)
+        # utterance chunks bound the activation working set (stage tensors are hop*C*T elements)
+        per = max(1, self.generator_chunk_frames // max(T, 1))
+        for b0 in range(0, B, per):
+            b1 = min(B, b0 + per)
+            self._generator_chunk(P, x16[b0:b1], None if gbias is None else gbias[b0:b1], out[b0:b1])
+        return out
+
+    def _generator_chunk(self, P, x16, gbias, out):
+        B, T, _ = x16.shape
+        dev, dt = x16.device, self.operand_dtype
+        up0 = self.upsample_initial_channel
+        cur16 = torch.empty(B, T, up0, device=dev, dtype=dt)
+        ops.conv1d(P["g_pre"], x16, gbias=gbias, out16=cur16, post_lrelu=LRELU_SLOPE)
+        L = T
+        n_st = len(self.upsample_rates)
+        for i, u in enumerate(self.upsample_rates):
+            ch = up0 // (2 ** (i + 1))
+            Lo = L * u
+            x32 = torch.empty(B, Lo, ch, device=dev, dtype=torch.float32)
+            xl16 = torch.empty(B, Lo, ch, device=dev, dtype=dt)
+            # ConvTranspose1d as a 3-tap conv writing the [B, L, u*ch] view of [B, L*u, ch]
+            ops.conv1d(P["g_ups"][i], cur16, out32=x32.view(B, L, u * ch), out16=xl16.view(B, L, u * ch),
+                       post_lrelu=LRELU_SLOPE)
+            c32 = torch.empty_like(x32)
+            cl16 = torch.empty_like(xl16)
+            t16 = torch.empty_like(xl16)
+            mrf = torch.empty_like(x32)
+            nxt16 = torch.empty_like(xl16)
+            nk = len(P["g_rb"][i])
+            next_slope = LRELU_SLOPE if i < n_st - 1 else 0.01      # F.leaky_relu default (models_ae.py:342)
+            for j, pairs in enumerate(P["g_rb"][i]):
+                src32, src16 = x32, xl16
+                for m, (c1, c2) in enumerate(pairs):
+                    last = m == len(pairs) - 1
+                    kw = {}
+                    if last:
+                        # MRF: xs = sum_j resblock_j(x); x = xs / num_kernels (models_ae.py:335-341)
+                        if j > 0:
+                            kw["res2"] = mrf
+                        if j < nk - 1:
+                            kw.update(out32=mrf)
+                        else:
+                            kw.update(scale=1.0 / nk, out16=nxt16, post_lrelu=next_slope)
+                    else:
+                        kw.update(out32=c32, out16=cl16, post_lrelu=LRELU_SLOPE)
+                    if c2 is not None:      # ResBlock1 (modules.py:210-223)
+                        ops.conv1d(c1, src16, out16=t16, post_lrelu=LRELU_SLOPE)
+                        ops.conv1d(c2, t16, res1=src32, **kw)
+                        src32, src16 = c32, cl16
+                    else:                   # ResBlock2 (modules.py:243-252): ping-pong the 16-bit stream,
+                        dst16 = t16 if src16 is cl16 else cl16      # the conv reads halo rows of its input
+                        if "out16" in kw and not last:
+                            kw["out16"] = dst16
+                        ops.conv1d(c1, src16, res1=src32, **kw)
+                        src32, src16 = c32, dst16
+            cur16, L = nxt16, Lo
+        ops.conv_post_tanh(cur16, P["g_post"], out.view(B, L))
+
+    # ------------------------------------------------------------------ the public entry point
+    @torch.no_grad()
+    def infer(self, x, x_lengths, note_pitch_id, note_duration, phone_shengdiao, ph_dur=None, lf0=None, sid=None,
+              noise_scale=1, length_scale=1, noise_scale_w=1., max_len=None, *, noise=None, g=None, f0_score=None):
+        """Same signature and result tuple as the reference (models_ae.py:608-651 / models.py:622-673).
+        Extensions (keyword-only, not in the reference): `noise` [B,C,T] replaces torch.randn_like for
+        parity runs; `g` [B,gin,1] speaker conditioning (the reference hard-codes g=None, :634);
+        `f0_score` [B,T] int64 overrides the predicted coarse f0 (TextPostNet.forward's own argument)."""
+        _require_cuda(x)
+        P = self._packed or self._pack()
+        dev, dt = x.device, self.operand_dtype
+        f32 = torch.float32
+        B, Pn = x.shape
+        H = self.hidden_channels
+        x = x.contiguous(); note_pitch_id = note_pitch_id.contiguous(); phone_shengdiao = phone_shengdiao.contiguous()
+        note_duration = note_duration.contiguous().float(); x_lengths = x_lengths.contiguous()
+        aux = self.last_aux = {}
+
+        # 1. TextEncoder (models_ae.py:203-220), fp32
+        plen = torch.empty(B, device=dev, dtype=torch.int32)
+        h = torch.empty(B, Pn, H, device=dev, dtype=f32)
+        ops.text_embed(x, note_pitch_id, phone_shengdiao, note_duration, *P["emb"], *P["emb_dur"], x_lengths, plen, h)
+        self._encoder(P["text_enc"], h, None, plen, True)
+
+        # 2. durations (models_ae.py:622-627)
+        if ph_dur is None:
+            d32 = torch.empty(B, Pn, 256, device=dev, dtype=f32)
+            dn = torch.empty(B, Pn, 256, device=dev, dtype=f32)
+            src = h
+            for pc, gamma, beta in P["dp"]:
+                ops.conv1d(pc, src, act=ACT_RELU, out32=d32)
+                ops.layernorm(d32, gamma, beta, plen, out32=dn)
+                src = dn
+            pred = torch.empty(B, Pn, 1, device=dev, dtype=f32)
+            ops.conv1d(P["dp_proj"], dn, act=ACT_SIGMOID, lens=plen, out32=pred)
+            durations = torch.empty(B, Pn, device=dev, dtype=torch.int64)
+            ops.duration_quantize(pred, note_duration, durations)
+            aux["dur_pred"] = pred.view(B, Pn)
+        else:
+            durations = ph_dur.to(device=dev, dtype=torch.int64).contiguous()
+        aux["durations"] = durations
+
+        # 3. LengthRegulator (models_ae.py:689-721) - one host sync for T instead of B*P .item() calls
+        ends = torch.empty(B, Pn, device=dev, dtype=torch.int32)
+        mel_len = torch.empty(B, device=dev, dtype=torch.int64)
+        mlen = torch.empty(B, device=dev, dtype=torch.int32)
+        ops.lr_scan(durations, ends, mel_len, mlen)
+        T = int(mel_len.max().item())
+        if T <= 0:
+            raise RuntimeError("SynthesizerTrn.infer: every utterance has zero frames")
+        n_pos = P["pos"].shape[0]
+        if T > n_pos:
+            # the reference fails here too: position table has 2000 rows (text_post_net.py:26,69-72)
+            raise RuntimeError(f"The size of tensor a ({T}) must match the size of tensor b ({n_pos}) at "
+                               f"non-singleton dimension 1 (frames exceed the position table)")
+        h_lr = torch.empty(B, T, H, device=dev, dtype=f32)
+        lr_index = torch.empty(B, T, device=dev, dtype=torch.int32)
+        ops.lr_gather(h, ends, mlen, h_lr, lr_index)
+        aux["lr_index"] = lr_index
+        y_mask = (torch.arange(T, device=dev).unsqueeze(0) < mel_len.unsqueeze(1)).unsqueeze(1).to(x.dtype)
+
+        # 4. TextPostNet (ext_modules/text_post_net.py:64-94)
+        xe32 = torch.empty(B, T, H, device=dev, dtype=f32)
+        xe16 = torch.empty(B, T, H, device=dev, dtype=dt)
+        ops.add_pos_mask(h_lr, P["pos"], mlen, out32=xe32, out16=xe16)
+        f0h = xe32.clone()
+        self._encoder(P["f0_enc"], f0h, None, mlen, True)
+        log_f0 = torch.empty(B, T, 1, device=dev, dtype=f32)
+        ops.conv1d(P["f0_out"], f0h, lens=mlen, out32=log_f0)
+        log_f0 = log_f0.view(B, T)
+        coarse = torch.empty(B, T, device=dev, dtype=torch.int64)
+        f0e16 = torch.empty(B, T, H, device=dev, dtype=dt)
+        cin = None if f0_score is None else f0_score.to(device=dev, dtype=torch.int64).contiguous()
+        ops.f0_embed(log_f0, cin, P["f0_emb"], mlen, coarse, out16=f0e16)
+        aux["f0_coarse"] = coarse
+        # MelPredictNetwork (mel_predict_network.py:37-45)
+        m32 = torch.empty(B, T, H, device=dev, dtype=f32)
+        m16 = torch.empty(B, T, H, device=dev, dtype=dt)
+        ops.conv1d(P["mel_cond"], f0e16, res1=xe32, lens=mlen, out32=m32, out16=m16)
+        self._encoder(P["mel_enc"], m32, m16, mlen, False)
+        mel32 = torch.empty(B, T, 80, device=dev, dtype=f32)
+        ops.conv1d(P["mel_out"], m16, lens=mlen, out32=mel32)
+        # FramePriorNetwork (frame_prior_network.py:31-41)
+        fp_a = torch.empty(B, T, 80, device=dev, dtype=dt)
+        ops.conv1d(P["fp_cond"], f0e16, res1=mel32, lens=mlen, out16=fp_a)
+        src = fp_a
+        for pc in P["fp"]:
+            dst = torch.empty(B, T, H, device=dev, dtype=dt)
+            ops.conv1d(pc, src, act=ACT_GELU, lens=mlen, out16=dst)
+            src = dst
+        stats = torch.empty(B, T, 2 * self.inter_channels, device=dev, dtype=f32)
+        ops.conv1d(P["proj"], src, lens=mlen, out32=stats)
+        Ci = self.inter_channels
+
+        # 5. z_p = m_p + noise * exp(logs_p) * noise_scale (models_ae.py:643)
+        if noise is None:
+            noise = torch.randn(B, Ci, T, device=dev, dtype=f32)
+        noise = noise.to(device=dev, dtype=f32).contiguous()
+        zp32 = torch.empty(B, T, Ci, device=dev, dtype=f32)
+        z16 = torch.empty(B, T, Ci, device=dev, dtype=dt)
+        ops.sample_prior(stats, noise, float(noise_scale), zp32=zp32, zp16=z16)
+        z32 = zp32.clone()
+
+        # speaker conditioning (optional; WN.cond_layer modules.py:152-159, Generator.cond models_ae.py:329-330)
+        g_btc = None
+        if g is not None:
+            if not self.gin_channels:
+                raise ValueError("model was built with gin_channels=0")
+            g_btc = g.to(device=dev, dtype=f32).reshape(B, 1, self.gin_channels).contiguous()
+
+        def cond_of(st):
+            if g_btc is None:
+                return None
+            out = torch.empty(B, 1, st["cond"].cout, device=dev, dtype=f32)
+            ops.conv1d(st["cond"], g_btc, out32=out)
+            return out.view(B, -1)
+
+        # 6. reverse flow (models_ae.py:246-253; modules.py:329-349), Flips folded into the weights
+        half = Ci // 2
+        hx32 = torch.empty(B, T, H, device=dev, dtype=f32)
+        hx16 = torch.empty(B, T, H, device=dev, dtype=dt)
+        wo16 = torch.empty(B, T, H, device=dev, dtype=dt)
+        for fl in P["flow"]:
+            io, oo = fl["in_off"], fl["out_off"]
+            ops.conv1d(fl["pre"], z16[:, :, io:io + half], lens=mlen, out32=hx32, out16=hx16)
+            self._wn(fl["wn"], hx32, hx16, mlen, wo16, cond_of(fl["wn"]))
+            ops.conv1d(fl["post"], wo16, alpha=-1.0, res1=z32[:, :, oo:oo + half], lens=mlen,
+                       out32=z32[:, :, oo:oo + half], out16=z16[:, :, oo:oo + half])
+
+        # 7. SpecDecoder + spec_proj (ae only; spec_decoder.py:41-46, models_ae.py:647-648)
+        gen_g = None
+        if g_btc is not None:
+            gg = torch.empty(B, 1, self.upsample_initial_channel, device=dev, dtype=f32)
+            ops.conv1d(P["g_cond"], g_btc, out32=gg)
+            gen_g = gg.view(B, -1)
+        Tg = T if max_len is None else min(T, int(max_len))
+        if self.variant == "ae":
+            ops.conv1d(P["sd_pre"], z16, lens=mlen, out32=hx32, out16=hx16)
+            self._wn(P["sd_wn"], hx32, hx16, mlen, wo16, cond_of(P["sd_wn"]))
+            sc_ld = 576
+            spec32 = torch.empty(B, T, sc_ld, device=dev, dtype=f32)
+            spec16 = torch.empty(B, T, sc_ld, device=dev, dtype=dt)
+            sc = self.spec_channels
+            ops.conv1d(P["sd_proj"], wo16, lens=mlen, out32=spec32[:, :, :sc], out16=spec16[:, :, :sc])
+            gin16 = torch.empty(B, T, Ci, device=dev, dtype=dt)
+            ops.conv1d(P["spec_proj"], spec16[:, :, :sc], lens=mlen, out16=gin16)
+            gen_in = gin16
+        else:
+            gen_in = z16          # z is already masked ((x1 - m) * mask; x0 masked upstream)
+        if Tg != T:
+            gen_in = gen_in[:, :Tg].contiguous()
+
+        # 8. Generator
+        o = self._generator(gen_in, gen_g)
+
+        bct = lambda t: t.transpose(1, 2)
+        m_p, logs_p = bct(stats[:, :, :Ci]), bct(stats[:, :, Ci:])
+        if lf0 is not None:
+            log_f0 = lf0
+        if self.variant == "ae":
+            return o, y_mask, (bct(z32), bct(zp32), m_p, logs_p), log_f0, bct(spec32[:, :, :sc]), bct(mel32)
+        return o, y_mask, (bct(z32), bct(zp32), m_p, logs_p), log_f0, bct(mel32)

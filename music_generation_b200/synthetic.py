@@ -58,7 +58,7 @@ def make_noise(batch, channels, frames, seed=1234, device="cpu"):
     return torch.randn(batch, channels, frames, generator=g).to(device)
 
 
-def apply_recipe(sd, seed=1234, generator_gain=0.7, f0_bias=math.log(250.0), positions=None):
+def apply_recipe(sd, seed=1234, generator_gain=0.7, f0_bias=math.log(250.0), positions=None, pre_gain=None):
     """Seeded, in-place edit of a state-dict (SURVEY.md 7.3-A / 8c "weight recipe").
 
     * spec_flow.*.post.{weight,bias} ~ N(0, 0.05)   (zero-init in the reference => flow vacuous)
@@ -83,7 +83,9 @@ def apply_recipe(sd, seed=1234, generator_gain=0.7, f0_bias=math.log(250.0), pos
             elif k in ("decoder.conv_pre.weight", "decoder.conv_post.weight"):
                 w = sd[k]
                 fan = w[0].numel()
-                gain = 4.0 if "pre" in k else 1.0       # spec_hidden has std ~0.14 at random init
+                # generator input std at random init: spec_hidden ~0.14 (ae), z ~1.0 (v4, no spec_proj)
+                default_pre = 4.0 if "spec_proj.weight" in sd else 0.6
+                gain = (pre_gain or default_pre) if "pre" in k else 1.0
                 sd[k] = torch.randn(w.shape, generator=g) * gain * math.sqrt(1.0 / fan)
             elif k.endswith(".bias"):
                 sd[k] = torch.randn(sd[k].shape, generator=g) * 0.05

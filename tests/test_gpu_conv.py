@@ -1,0 +1,185 @@
+"""-m gpu: the conv kernels through the C ABI vs the documented semantics (tests/emu_ops.py, plain torch
+fp32 on CPU) on identical seeded inputs.  Tolerances: operands are rounded to fp16 on both sides, so the
+only difference is fp32 accumulation order -> 2e-3 relative to the output scale."""
+import pytest
+import torch
+
+import emu_ops
+from common import max_abs
+from music_generation_b200 import ops, packer
+from music_generation_b200._lib import ACT_GELU, ACT_NONE, ACT_RELU, ACT_SIGMOID
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _rand(*shape, seed=0, scale=1.0):
+    return torch.randn(*shape, generator=torch.Generator().manual_seed(seed)) * scale
+
+
+def _run_both(pc_cpu, x_cpu, *, out_cols, want32=True, want16=False, res1=None, res2=None, lens=None, gbias=None,
+              out_ld=None, **kw):
+    """Runs the real kernel on the GPU and the emulation on the CPU; returns (real32, emu32, real16, emu16)."""
+    import copy
+    B, T, _ = x_cpu.shape
+    ld = out_ld or out_cols
+    pc_gpu = copy.copy(pc_cpu)
+    pc_gpu = pc_gpu.to(DEV)
+    outs = {}
+    for side, dev, fn, pc in (("emu", "cpu", emu_ops.conv1d, pc_cpu), ("real", DEV, ops.conv1d, pc_gpu)):
+        o32 = torch.full((B, T, ld), 7.0, device=dev) if want32 else None
+        o16 = torch.full((B, T, ld), 7.0, device=dev, dtype=x_cpu.dtype if x_cpu.dtype != torch.float32 else torch.float16) if want16 else None
+        args = dict(kw)
+        if res1 is not None:
+            args["res1"] = res1.to(dev)
+        if res2 is not None:
+            args["res2"] = res2.to(dev)
+        if lens is not None:
+            args["lens"] = lens.to(dev)
+        if gbias is not None:
+            args["gbias"] = gbias.to(dev)
+        fn(pc, x_cpu.to(dev), out32=None if o32 is None else o32[:, :, :out_cols],
+           out16=None if o16 is None else o16[:, :, :out_cols], **args)
+        if dev != "cpu":
+            torch.cuda.synchronize()
+        outs[side] = (None if o32 is None else o32.cpu(), None if o16 is None else o16.float().cpu())
+    return outs["real"][0], outs["emu"][0], outs["real"][1], outs["emu"][1]
+
+
+TC_CASES = [
+    # name, B, T, Cin, Cout, k, dil
+    ("1x1_192", 2, 300, 192, 192, 1, 1),
+    ("k3_ffn1", 1, 257, 192, 768, 3, 1),
+    ("k3_ffn2", 1, 130, 768, 192, 3, 1),
+    ("k7_pre", 2, 200, 192, 512, 7, 1),
+    ("k11_d5_256", 1, 700, 256, 256, 11, 5),
+    ("k7_d3_128", 2, 513, 128, 128, 7, 3),
+    ("k3_d1_64", 1, 1000, 64, 64, 3, 1),
+    ("k11_d1_32", 1, 900, 32, 32, 11, 1),
+    ("cin80", 1, 140, 80, 192, 1, 1),
+    ("cin513", 1, 140, 513, 192, 1, 1),
+    ("cout513", 1, 140, 192, 513, 1, 1),
+    ("cout96", 2, 140, 192, 96, 1, 1),
+    ("tiny_T", 3, 5, 192, 192, 5, 1),
+]
+
+
+@pytest.mark.parametrize("name,B,T,cin,cout,k,dil", TC_CASES, ids=[c[0] for c in TC_CASES])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16], ids=["fp16", "bf16"])
+def test_conv1d_tc_plain(name, B, T, cin, cout, k, dil, dtype):
+    w = _rand(cout, cin, k, seed=1, scale=(cin * k) ** -0.5)
+    b = _rand(cout, seed=2, scale=0.1)
+    x = _rand(B, T, cin, seed=3).to(dtype)
+    pc = packer.pack_conv(w, b, dil=dil, dtype=dtype)
+    ld = (cout + 7) // 8 * 8
+    real, emu, _, _ = _run_both(pc, x, out_cols=cout, out_ld=ld)
+    assert max_abs(emu[:, :, :cout], real[:, :, :cout]) < 3e-3
+    if ld != cout:   # columns >= n_valid untouched
+        assert float((real[:, :, cout:] - 7.0).abs().max()) == 0.0
+
+
+def test_conv1d_tc_full_epilogue():
+    """bias + residuals + alpha/scale + mask + both outputs + post leaky-relu on the 16-bit copy."""
+    B, T, c = 3, 400, 128
+    w, b = _rand(c, c, 7, seed=4, scale=(7 * c) ** -0.5), _rand(c, seed=5, scale=0.1)
+    x = _rand(B, T, c, seed=6).half()
+    pc = packer.pack_conv(w, b, dil=3)
+    res1, res2 = _rand(B, T, c, seed=7), _rand(B, T, c, seed=8)
+    lens = torch.tensor([400, 133, 0], dtype=torch.int32)
+    r32, e32, r16, e16 = _run_both(pc, x, out_cols=c, want16=True, res1=res1, res2=res2, lens=lens, alpha=-1.0,
+                                   scale=1.0 / 3, post_lrelu=0.1)
+    assert max_abs(e32, r32) < 3e-3 and max_abs(e16, r16) < 6e-3
+    assert float(r32[1, 133:].abs().max()) == 0.0 and float(r32[2].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("act", [ACT_RELU, ACT_GELU, ACT_SIGMOID])
+def test_conv1d_tc_activations(act):
+    w, b = _rand(192, 192, 1, seed=9, scale=192 ** -0.5), _rand(192, seed=10, scale=0.1)
+    x = _rand(2, 150, 192, seed=11).half()
+    pc = packer.pack_conv(w, b)
+    real, emu, _, _ = _run_both(pc, x, out_cols=192, act=act)
+    assert max_abs(emu, real) < 3e-3
+
+
+def test_conv1d_tc_gate_with_speaker_bias():
+    H = 192
+    w, b = _rand(2 * H, H, 5, seed=12, scale=(5 * H) ** -0.5), _rand(2 * H, seed=13, scale=0.1)
+    x = _rand(2, 300, H, seed=14).half()
+    pc = packer.pack_conv(w, b, gate=True)
+    gb = _rand(2, 2 * H, seed=15, scale=0.3)[:, packer.gate_order(H)].contiguous()
+    _, _, r16, e16 = _run_both(pc, x, out_cols=H, want32=False, want16=True, gbias=gb)
+    assert max_abs(e16, r16) < 3e-3
+
+
+def test_conv1d_tc_channel_views_and_in_place():
+    """Flow coupling pattern: read a 96-channel view of a 192-wide tensor, write the other half in place."""
+    B, T = 2, 260
+    z32 = _rand(B, T, 192, seed=16)
+    z16 = z32.half()
+    wpre = _rand(192, 96, 1, seed=17, scale=96 ** -0.5)
+    pc = packer.pack_conv(wpre, _rand(192, seed=18, scale=0.1))
+    real, emu, _, _ = _run_both(pc, z16[:, :, 96:], out_cols=192)
+    assert max_abs(emu, real) < 3e-3
+    wpost = _rand(96, 192, 1, seed=19, scale=192 ** -0.5)
+    pcp = packer.pack_conv(wpost, _rand(96, seed=20, scale=0.1)).to(DEV)
+    h16 = _rand(B, T, 192, seed=21).half()
+    zg32, zg16 = z32.to(DEV), z16.to(DEV)
+    lens = torch.tensor([260, 100], dtype=torch.int32)
+    ops.conv1d(pcp, h16.to(DEV), alpha=-1.0, res1=zg32[:, :, :96], lens=lens.to(DEV), out32=zg32[:, :, :96],
+               out16=zg16[:, :, :96])
+    torch.cuda.synchronize()
+    zc32, zc16 = z32.clone(), z16.clone()
+    pcc = packer.pack_conv(wpost, _rand(96, seed=20, scale=0.1))
+    emu_ops.conv1d(pcc, h16, alpha=-1.0, res1=zc32[:, :, :96], lens=lens, out32=zc32[:, :, :96], out16=zc16[:, :, :96])
+    assert max_abs(zc32, zg32.cpu()) < 3e-3 and max_abs(zc16.float(), zg16.float().cpu()) < 6e-3
+    assert torch.equal(zg32[:, :, 96:].cpu(), z32[:, :, 96:])          # untouched half
+
+
+@pytest.mark.parametrize("k,s,cin,cout", [(16, 8, 512, 256), (16, 8, 256, 128), (4, 2, 128, 64), (4, 2, 64, 32)])
+def test_conv_transpose_polyphase_on_gpu(k, s, cin, cout):
+    import torch.nn.functional as F
+    w, b = _rand(cin, cout, k, seed=22, scale=(cin * k / s) ** -0.5), _rand(cout, seed=23, scale=0.1)
+    B, T = 2, 150
+    x = _rand(B, T, cin, seed=24).half()
+    ref = F.conv_transpose1d(x.float().transpose(1, 2), w.half().float(), b, stride=s, padding=(k - s) // 2).transpose(1, 2)
+    pc = packer.pack_conv_transpose(w, b, s, (k - s) // 2).to(DEV)
+    out = torch.empty(B, T * s, cout, device=DEV)
+    ops.conv1d(pc, x.to(DEV), out32=out.view(B, T, s * cout))
+    torch.cuda.synchronize()
+    assert max_abs(ref, out.cpu()) < 3e-3
+
+
+def test_conv1d_tc_w_rows_split():
+    H = 192
+    w, b = _rand(2 * H, H, 1, seed=25, scale=H ** -0.5), _rand(2 * H, seed=26, scale=0.1)
+    x = _rand(2, 200, H, seed=27).half()
+    pc = packer.pack_conv(w, b, block_n=192)
+    for r0 in (0, H):
+        real, emu, _, _ = _run_both(pc, x, out_cols=H, w_rows=(r0, H))
+        assert max_abs(emu, real) < 3e-3
+
+
+F32_CASES = [("k3_192_256", 2, 70, 192, 256, 3), ("qkv", 1, 130, 192, 576, 1), ("k3_768_192", 2, 33, 768, 192, 3),
+             ("to1", 3, 50, 256, 1, 1), ("gin", 4, 1, 256, 1536, 1)]
+
+
+@pytest.mark.parametrize("name,B,T,cin,cout,k", F32_CASES, ids=[c[0] for c in F32_CASES])
+def test_conv1d_f32(name, B, T, cin, cout, k):
+    w, b = _rand(cout, cin, k, seed=28, scale=(cin * k) ** -0.5), _rand(cout, seed=29, scale=0.1)
+    x = _rand(B, T, cin, seed=30)
+    pc = packer.pack_conv(w, b, f32=True)
+    res1 = _rand(B, T, cout, seed=31)
+    lens = torch.tensor([T] + [max(T // 2, 0)] * (B - 1), dtype=torch.int32)
+    real, emu, _, _ = _run_both(pc, x, out_cols=cout, res1=res1, lens=lens, act=ACT_RELU)
+    assert max_abs(emu, real) < 2e-5
+
+
+def test_bad_arguments_raise():
+    pc = packer.pack_conv(_rand(192, 192, 1), None).to(DEV)
+    x = torch.zeros(1, 10, 192, device=DEV, dtype=torch.float16)
+    with pytest.raises(RuntimeError, match="no output"):
+        ops.conv1d(pc, x)
+    with pytest.raises(ValueError, match="channels"):
+        ops.conv1d(pc, x[:, :, :96], out32=torch.zeros(1, 10, 192, device=DEV))
+    with pytest.raises(TypeError):
+        ops.conv1d(pc, x.bfloat16(), out32=torch.zeros(1, 10, 192, device=DEV))

@@ -1,0 +1,11 @@
+#!/bin/bash
+# GPU bring-up: every test file in its own process so one faulting kernel cannot hide the others.
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > gpurun_out/gpu.txt 2>&1
+for f in test_gpu_misc test_gpu_conv test_gpu_infer; do
+  timeout 900 python -m pytest tests/$f.py -q -m gpu --timeout 300 -p no:cacheprovider > gpurun_out/$f.log 2>&1
+  echo "$f exit $?" >> gpurun_out/summary.txt
+  tail -5 gpurun_out/$f.log
+done
+timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit $?" >> gpurun_out/summary.txt
+cat gpurun_out/summary.txt
