@@ -100,5 +100,11 @@ def check(rc, what=""):
         raise RuntimeError(f"b200svs {what} failed (code {rc}): {msg}")
 
 
+# number of C-ABI compute calls issued by this process; each one launches exactly one kernel
+LAUNCHES = 0
+
+
 def call(name, *args):
+    global LAUNCHES
+    LAUNCHES += 1
     check(getattr(lib(), name)(*args), name)

@@ -47,18 +47,26 @@ def _btc(t, name):
 class PackedConv:
     """Device-resident packed weights of one convolution (see packer.py)."""
     __slots__ = ("w", "bias", "ntaps", "dil", "pad_left", "cin", "cin_pad", "cout", "cout_pad", "block_n",
-                 "gate", "f32", "n_out")
+                 "gate", "f32", "n_out", "alg_macs_per_row", "tag")
 
     def __init__(self, w, bias, ntaps, dil, pad_left, cin, cin_pad, cout, cout_pad, block_n, gate, f32):
         self.w, self.bias, self.ntaps, self.dil, self.pad_left = w, bias, ntaps, dil, pad_left
         self.cin, self.cin_pad, self.cout, self.cout_pad = cin, cin_pad, cout, cout_pad
         self.block_n, self.gate, self.f32 = block_n, gate, f32
         self.n_out = cout // 2 if gate else cout      # columns the epilogue stores
+        # algorithmic MACs per input row (the reference conv's own count; the polyphase ConvTranspose
+        # form executes 1.5x of that, packer.pack_conv_transpose overrides it) - used by bench.py only
+        self.alg_macs_per_row = cin * cout * ntaps
+        self.tag = ""
 
     def to(self, device):
         self.w = self.w.to(device)
         self.bias = None if self.bias is None else self.bias.to(device)
         return self
+
+
+# bench.py's instrumented pass: when a list, every conv1d appends (tag, kind, alg_flops, ev0, ev1)
+PROFILE = None
 
 
 def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, res2=None, lens=None,
@@ -108,6 +116,10 @@ def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, 
     if post_lrelu is not None:
         e.post_lrelu, e.post_slope = 1, float(post_lrelu)
     e.n_valid = n_out if n_valid is None else n_valid
+    prof = PROFILE
+    if prof is not None:
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
     if pc.f32:
         if x.dtype != torch.float32:
             raise TypeError("fp32 conv needs fp32 activations")
@@ -117,6 +129,10 @@ def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, 
         if pc.w.dtype != x.dtype:
             raise TypeError(f"operand dtype mismatch: x {x.dtype}, w {pc.w.dtype}")
         _lib.call("b200svs_conv1d_tc", C.byref(a), _stream())
+    if prof is not None:
+        ev1.record()
+        frac = 1.0 if w_rows is None else w_rows[1] / pc.cout_pad
+        prof.append((pc.tag, "f32" if pc.f32 else "tc", 2.0 * B * T * pc.alg_macs_per_row * frac, ev0, ev1))
 
 
 def attention(qkv, out32, out16, rel_k, rel_v, lens, heads=2, window=4):

@@ -117,4 +117,6 @@ def pack_conv_transpose(weight, bias, stride, padding, *, dtype=torch.float16, b
     if not set(range(K)) <= reach:
         raise ValueError(f"ConvTranspose1d(k={K}, s={s}, p={p}) does not fit the 3-tap polyphase form")
     b3 = None if bias is None else bias.detach().float().repeat(s)
-    return pack_conv(w3, b3, dil=1, pad_left=1, dtype=dtype, block_n=block_n)
+    pc = pack_conv(w3, b3, dil=1, pad_left=1, dtype=dtype, block_n=block_n)
+    pc.alg_macs_per_row = cin * cout * K      # the ConvTranspose1d's own MAC count per input frame
+    return pc

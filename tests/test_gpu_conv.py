@@ -17,6 +17,16 @@ def _rand(*shape, seed=0, scale=1.0):
     return torch.randn(*shape, generator=torch.Generator().manual_seed(seed)) * scale
 
 
+def _to_dev(x, dev):
+    """.to() makes non-dense views contiguous; keep the padded row stride instead."""
+    if x.is_contiguous() or dev == "cpu":
+        return x.to(dev)
+    ld = x.stride(1)
+    base = torch.zeros(x.shape[0], x.shape[1], ld, dtype=x.dtype, device=dev)
+    base[:, :, :x.shape[2]] = x.to(dev)
+    return base[:, :, :x.shape[2]]
+
+
 def _run_both(pc_cpu, x_cpu, *, out_cols, want32=True, want16=False, res1=None, res2=None, lens=None, gbias=None,
               out_ld=None, **kw):
     """Runs the real kernel on the GPU and the emulation on the CPU; returns (real32, emu32, real16, emu16)."""
@@ -38,7 +48,7 @@ def _run_both(pc_cpu, x_cpu, *, out_cols, want32=True, want16=False, res1=None, 
             args["lens"] = lens.to(dev)
         if gbias is not None:
             args["gbias"] = gbias.to(dev)
-        fn(pc, x_cpu.to(dev), out32=None if o32 is None else o32[:, :, :out_cols],
+        fn(pc, _to_dev(x_cpu, dev), out32=None if o32 is None else o32[:, :, :out_cols],
            out16=None if o16 is None else o16[:, :, :out_cols], **args)
         if dev != "cpu":
             torch.cuda.synchronize()
@@ -70,6 +80,10 @@ def test_conv1d_tc_plain(name, B, T, cin, cout, k, dil, dtype):
     w = _rand(cout, cin, k, seed=1, scale=(cin * k) ** -0.5)
     b = _rand(cout, seed=2, scale=0.1)
     x = _rand(B, T, cin, seed=3).to(dtype)
+    if cin % 8:     # TMA needs 16-B aligned rows: odd channel counts live in a padded buffer (spec16, ld 576)
+        xp = torch.zeros(B, T, (cin + 7) // 8 * 8, dtype=dtype)
+        xp[:, :, :cin] = x
+        x = xp[:, :, :cin]
     pc = packer.pack_conv(w, b, dil=dil, dtype=dtype)
     ld = (cout + 7) // 8 * 8
     real, emu, _, _ = _run_both(pc, x, out_cols=cout, out_ld=ld)
