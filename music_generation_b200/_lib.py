@@ -104,7 +104,23 @@ def check(rc, what=""):
 LAUNCHES = 0
 
 
+# bench.py's instrumented pass: when PROFILE is a list every call appends
+# (entry point, tag, algorithmic flops, start event, end event); NEXT_META is set by ops.conv1d
+PROFILE = None
+NEXT_META = None
+
+
 def call(name, *args):
-    global LAUNCHES
+    global LAUNCHES, NEXT_META
     LAUNCHES += 1
+    if PROFILE is None:
+        check(getattr(lib(), name)(*args), name)
+        return
+    import torch
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
     check(getattr(lib(), name)(*args), name)
+    ev1.record()
+    tag, flops = NEXT_META or ("", 0.0)
+    NEXT_META = None
+    PROFILE.append((name.replace("b200svs_", ""), tag, flops, ev0, ev1))

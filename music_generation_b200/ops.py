@@ -65,10 +65,6 @@ class PackedConv:
         return self
 
 
-# bench.py's instrumented pass: when a list, every conv1d appends (tag, kind, alg_flops, ev0, ev1)
-PROFILE = None
-
-
 def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, res2=None, lens=None,
            out32=None, out16=None, post_lrelu=None, w_rows=None, n_valid=None):
     """out = epilogue(conv(x, pc)).  See b200svs_epilogue in include/b200svs.h for the formula.
@@ -116,10 +112,9 @@ def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, 
     if post_lrelu is not None:
         e.post_lrelu, e.post_slope = 1, float(post_lrelu)
     e.n_valid = n_out if n_valid is None else n_valid
-    prof = PROFILE
-    if prof is not None:
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record()
+    if _lib.PROFILE is not None:
+        frac = 1.0 if w_rows is None else w_rows[1] / pc.cout_pad
+        _lib.NEXT_META = (pc.tag, 2.0 * B * T * pc.alg_macs_per_row * frac)
     if pc.f32:
         if x.dtype != torch.float32:
             raise TypeError("fp32 conv needs fp32 activations")
@@ -129,10 +124,6 @@ def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, 
         if pc.w.dtype != x.dtype:
             raise TypeError(f"operand dtype mismatch: x {x.dtype}, w {pc.w.dtype}")
         _lib.call("b200svs_conv1d_tc", C.byref(a), _stream())
-    if prof is not None:
-        ev1.record()
-        frac = 1.0 if w_rows is None else w_rows[1] / pc.cout_pad
-        prof.append((pc.tag, "f32" if pc.f32 else "tc", 2.0 * B * T * pc.alg_macs_per_row * frac, ev0, ev1))
 
 
 def attention(qkv, out32, out16, rel_k, rel_v, lens, heads=2, window=4):

@@ -203,6 +203,30 @@ class SynthesizerTrn(nn.Module):
             P["g_rb"].append(stage)
         wpost = W(d + ".conv_post")                     # [1, C, 7] -> [7][C] fp32
         P["g_post"] = wpost[0].t().contiguous().to(dev)
+        # stage tags for bench.py's per-stage breakdown
+        def tag(obj, name):
+            if isinstance(obj, ops.PackedConv):
+                obj.tag = name
+            elif isinstance(obj, _Enc):
+                for a in ("qkv", "o", "ffn1", "ffn2"):
+                    getattr(obj, a).tag = name
+            elif isinstance(obj, dict):
+                for v in obj.values():
+                    tag(v, name)
+            elif isinstance(obj, (list, tuple)):
+                for v in obj:
+                    tag(v, name)
+        for key, name in (("text_enc", "text"), ("dp", "text"), ("dp_proj", "text"), ("f0_enc", "f0"), ("f0_out", "f0"),
+                          ("mel_cond", "mel"), ("mel_enc", "mel"), ("mel_out", "mel"), ("fp_cond", "prior"),
+                          ("fp", "prior"), ("proj", "prior"), ("flow", "flow"), ("sd_pre", "specdec"),
+                          ("sd_wn", "specdec"), ("sd_proj", "specdec"), ("spec_proj", "specdec"), ("g_pre", "gen_pre"),
+                          ("g_cond", "gen_pre")):
+            if key in P and P[key] is not None:
+                tag(P[key], name)
+        for i, pc in enumerate(P["g_ups"]):
+            tag(pc, f"gen_up{i}")
+        for i, st in enumerate(P["g_rb"]):
+            tag(st, f"gen_rb{i}")
         self._packed = P
         return P
 
