@@ -53,7 +53,10 @@ enum { B200SVS_DT_F16 = 0, B200SVS_DT_BF16 = 1 };
  *   v = alpha*v + res1[b,t,c'] + res2[b,t,c']    (c' = output column)
  *   v = v*scale;  v *= (t < lens[b])             (lens == NULL: no mask)
  *   out32[b,t,c'] = v;  out16[b,t,c'] = cvt16(post_lrelu ? lrelu(v, post_slope) : v)
- * Columns c' >= n_valid are not stored.  out32 may alias res1 or res2 (same element, same thread). */
+ * Columns c' >= n_valid are not stored by conv1d_f32; conv1d_tc stores through TMA, which clips at
+ * 16-byte granularity: columns up to the next multiple of 4 (fp32) / 8 (16-bit) may be written with the
+ * zero-padded channels' values, so out32_ld / out16_ld must cover that rounding.  out32 may alias res1
+ * (in-place update of the same tile). */
 typedef struct b200svs_epilogue {
   const float* bias;
   const float* gbias;

@@ -38,6 +38,11 @@ EncodeTiledFn get_encode_tiled() {
 
 int make_tmap_16bit(CUtensorMap* out, int dtype, const void* base, int rank, const uint64_t* dims,
                     const uint64_t* strides_bytes, const uint32_t* box) {
+  return make_tmap(out, dtype == B200SVS_DT_BF16 ? 1 : 0, base, rank, dims, strides_bytes, box, 128);
+}
+
+int make_tmap(CUtensorMap* out, int elem, const void* base, int rank, const uint64_t* dims,
+              const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes) {
   EncodeTiledFn enc = get_encode_tiled();
   if (!enc) return set_error(B200SVS_ENODEV, "cuTensorMapEncodeTiled driver entry point not available");
   cuuint64_t gdim[5];
@@ -50,10 +55,13 @@ int make_tmap_16bit(CUtensorMap* out, int dtype, const void* base, int rank, con
     es[i] = 1;
     if (i > 0) gstr[i - 1] = strides_bytes[i - 1];
   }
-  CUtensorMapDataType dt = dtype == B200SVS_DT_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  CUtensorMapDataType dt = elem == 2 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                           : elem == 1 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                          : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                          : swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
   CUresult r = enc(out, dt, rank, const_cast<void*>(base), gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
     return set_error(B200SVS_ECUDA, "cuTensorMapEncodeTiled failed (CUresult %d) rank %d dims %llu,%llu,%llu", (int)r, rank,
                      (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 0),

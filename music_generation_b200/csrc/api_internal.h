@@ -22,6 +22,10 @@ EncodeTiledFn get_encode_tiled();
 int make_tmap_16bit(CUtensorMap* out, int dtype, const void* base, int rank, const uint64_t* dims,
                     const uint64_t* strides_bytes, const uint32_t* box);
 
+// General tiled tensor map: elem 0 = fp16, 1 = bf16, 2 = fp32; swizzle_bytes in {0, 32, 64, 128}.
+int make_tmap(CUtensorMap* out, int elem, const void* base, int rank, const uint64_t* dims,
+              const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes);
+
 int num_sms();
 int max_smem_optin();
 

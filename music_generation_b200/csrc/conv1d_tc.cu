@@ -1,19 +1,26 @@
-// conv1d_tc: implicit-GEMM 1-D convolution on the 5th-gen tensor cores (tcgen05 + TMEM), operands
-// staged by TMA (SWIZZLE_128B, K-major), fp16/bf16 in, fp32 accumulate, fused epilogue.
+// conv1d_tc (v2): implicit-GEMM 1-D convolution on the 5th-gen tensor cores (tcgen05 + TMEM), every
+// global<->shared transfer done by TMA, fp16/bf16 operands, fp32 accumulate, fused epilogue.
 //
 //   D[t, co] = sum_tap sum_ci  X[b, t + tap*dil - pad, ci] * W[tap][co][ci]
 //
-//   GEMM view per CTA tile:  M = 128 time rows (TMEM lanes), N = block_n output channels (TMEM
-//   columns), K = 64 input channels per pipeline step, ntaps * ceil(Cin/64) steps.  The zero padding
-//   of the convolution and the batch boundaries come for free from TMA out-of-bounds zero fill on a
-//   rank-3 tensor map {C, T, B}.
+// Tile: msub*128 time rows (msub in {1,2}; one 128-lane TMEM accumulator per sub-tile) x block_n
+// output channels.  Per 64-channel K chunk the activation rows [t0-pad, t0+msub*128+(ntaps-1)*dil-pad)
+// are loaded ONCE (rank-3 map {C,T,B}: conv zero padding and batch edges are TMA out-of-bounds fill)
+// and every tap reads them through a UMMA descriptor whose start address is shifted by tap*dil rows
+// (SWIZZLE_128B is a function of the absolute smem address, so a row shift keeps the pattern; checked
+// on hardware by b200svs_probe_rowshift).  Each weight tile [block_n x 64] feeds msub MMAs.
 //
-//   Warp roles (256 threads, 1 CTA/SM, persistent over tiles):
-//     warp 0 lane 0 : TMA producer           (smem ring: full/empty mbarriers)
-//     warp 1 lane 0 : tcgen05.mma issuer     (accumulator ring in TMEM: 2 x block_n columns)
-//     warp 2        : TMEM alloc / dealloc
-//     warps 4..7    : epilogue, one TMEM lane (= one time row) per thread: tcgen05.ld -> fused
-//                     bias/act/residual/mask -> vectorised global stores (fp32 and/or 16-bit)
+// Epilogue I/O goes through shared memory: the residual tile is TMA-loaded into a staging slot ahead
+// of time, the epilogue warps (one TMEM lane = one time row per thread) combine it with the
+// accumulator in place, and TMA stores write the fp32 and the 16-bit result (the latter with the next
+// layer's leaky-ReLU applied) fully coalesced; the tensor maps clip rows >= T and columns >= n_valid.
+//
+// Warp roles (256 threads, 1 CTA/SM, persistent over tiles):
+//   warp 0 lane 0 : TMA producer of the mainloop (activation ring, weight ring)
+//   warp 1 lane 0 : tcgen05.mma issuer (accumulators double-buffered in TMEM)
+//   warp 2        : TMEM alloc / dealloc
+//   warp 3 lane 0 : TMA producer of the epilogue staging slots (residual tiles)
+//   warps 4..7    : epilogue
 //
 // Replaces: nn.Conv1d/ConvTranspose1d + surrounding pointwise ops of the reference
 // (VISinger/models_ae.py:327-346, modules.py:148-176,210-223,329-349, attentions.py:138-146,277-285).
@@ -22,36 +29,44 @@
 
 namespace b200svs {
 
-constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;
-constexpr int kATileBytes = kBlockM * kBlockK * 2;  // 16 KB
-constexpr int kMaxStages = 8;
+constexpr int kRowBytes = kBlockK * 2;     // one K-chunk row of a 16-bit operand tile: 128 B
+constexpr int kAStages = 2;
+constexpr int kMaxWStages = 8;
+constexpr int kMaxSlots = 4;
+constexpr int kEpiCols = 32;               // output columns per epilogue chunk
+constexpr int kSlot32Bytes = 128 * kEpiCols * 4;   // 16 KB: [128 rows][32 fp32], SWIZZLE_128B
+constexpr int kSlot16Bytes = 128 * kEpiCols * 2;   //  8 KB: [128 rows][32 x 16-bit], SWIZZLE_64B
 constexpr int kTcThreads = 256;
+constexpr int kEpiThreads = 128;
 
 struct ConvTcParams {
-  int B, T, tiles_t, m_tiles, n_tiles, total_tiles;
-  int ntaps, nchunks, dil, pad_left, cout_pad, block_n;
-  int num_stages, stage_bytes, tmem_cols;
+  int T, tiles_t, m_tiles, n_tiles, total_tiles;
+  int ntaps, nchunks, dil, pad_left, cout_pad, block_n, msub;
+  int a_boxes, a_box_rows, a_stage_bytes;  // activation tile = a_boxes TMA boxes of a_box_rows rows
+  int w_stages, w_stage_bytes;
+  int n_slots, slot_bytes, slot16_off;     // epilogue staging slot: [fp32 area][16-bit area]
+  int chunks_per_sub, n_out_tile;          // output chunks per 128-row sub-tile; output columns per N tile
+  int tmem_cols;
   uint32_t idesc;
   b200svs_epilogue ep;
 };
 
 struct __align__(8) TcBarriers {
-  uint64_t full[kMaxStages];
-  uint64_t empty[kMaxStages];
-  uint64_t tmem_full[2];
-  uint64_t tmem_empty[2];
+  uint64_t a_full[kAStages], a_empty[kAStages];
+  uint64_t w_full[kMaxWStages], w_empty[kMaxWStages];
+  uint64_t tmem_full[2], tmem_empty[2];
+  uint64_t e_full[kMaxSlots], e_empty[kMaxSlots];
   uint32_t tmem_base;
 };
 
-__device__ __forceinline__ float apply_act(float v, int act) {
-  switch (act) {
-    case B200SVS_ACT_RELU: return fmaxf(v, 0.f);
-    case B200SVS_ACT_GELU: return gelu_erf(v);
-    case B200SVS_ACT_SIGMOID: return 1.0f / (1.0f + expf(-v));
-    case B200SVS_ACT_TANH: return tanhf(v);
-    default: return v;
-  }
+template <int ACT>
+__device__ __forceinline__ float act_fn(float v) {
+  if (ACT == B200SVS_ACT_RELU) return fmaxf(v, 0.f);
+  if (ACT == B200SVS_ACT_GELU) return gelu_erf(v);
+  if (ACT == B200SVS_ACT_SIGMOID) return 1.0f / (1.0f + expf(-v));
+  if (ACT == B200SVS_ACT_TANH) return tanhf(v);
+  return v;
 }
 
 __device__ __forceinline__ uint32_t pack16(float a, float b, int dtype) {
@@ -63,101 +78,128 @@ __device__ __forceinline__ uint32_t pack16(float a, float b, int dtype) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
-// Finishes 16 consecutive output columns [col0, col0+16) of row (b,t): v[] already holds
-// act(acc + bias).  Residual add, scale, mask and the (vectorised) stores.
-__device__ __forceinline__ void finish_store16(float* v, const b200svs_epilogue& ep, int b, int T, int t,
-                                               int col0, bool row_ok, bool row_live) {
-  if (!row_ok) return;
-  const size_t row = static_cast<size_t>(b) * T + t;
-  const int nv = ep.n_valid - col0;  // valid columns in this chunk
-  if (nv <= 0) return;
-  const bool full = nv >= 16;
-  if (ep.res1) {
-    const float* r = ep.res1 + row * ep.res1_ld + col0;
-    if (full) {
+struct EpiCtx {
+  const b200svs_epilogue* ep;
+  uint8_t* slot;          // staging slot base (fp32 area); 16-bit area at slot + slot16_off
+  int slot16_off;
+  int row;                // row inside the 128-row sub-tile (= TMEM lane)
+  int b, t, T;            // batch index, global time row, rows per batch element
+  int pcol;               // first packed accumulator column of this chunk (bias / gbias index)
+  int ocol;               // first output column of this chunk
+  int gate_off;           // GATE: packed-column distance between the tanh and the sigmoid half
+  bool row_ok, row_live;
+  bool need32;            // fp32 area is stored (out32 != NULL)
+};
+
+// One chunk of 32 output columns for one row.  acc[] holds the raw accumulator bits (for GATE: acc =
+// tanh half, acc2 = sigmoid half).  Static indexing only: everything stays in registers.
+template <int ACT>
+__device__ __forceinline__ void epi_chunk(const EpiCtx& c, const uint32_t* acc, const uint32_t* acc2) {
+  const b200svs_epilogue& ep = *c.ep;
+  const float* gb = ep.gbias ? ep.gbias + static_cast<size_t>(c.b) * ep.gbias_ld : nullptr;
+  const float s = c.row_live ? ep.scale : 0.0f;
+  const bool has_res1 = ep.res1 != nullptr;
+  const bool has_res2 = ep.res2 != nullptr && c.row_ok;
+  const float* r2 = has_res2 ? ep.res2 + (static_cast<size_t>(c.b) * c.T + c.t) * ep.res2_ld + c.ocol : nullptr;
+  const int nv = ep.n_valid - c.ocol;      // valid output columns from ocol on
+  uint8_t* row32 = c.slot + c.row * 128;
+  uint32_t p16[16];
 #pragma unroll
-      for (int i = 0; i < 16; i += 4) {
-        float4 q = *reinterpret_cast<const float4*>(r + i);
-        v[i] = ep.alpha * v[i] + q.x; v[i + 1] = ep.alpha * v[i + 1] + q.y;
-        v[i + 2] = ep.alpha * v[i + 2] + q.z; v[i + 3] = ep.alpha * v[i + 3] + q.w;
+  for (int j = 0; j < 8; ++j) {
+    float v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int k = 4 * j + i;
+      float x = __uint_as_float(acc[k]);
+      if (ACT == B200SVS_ACT_GATE) {
+        float y = __uint_as_float(acc2[k]);
+        if (ep.bias) { x += __ldg(ep.bias + c.pcol + k); y += __ldg(ep.bias + c.pcol + c.gate_off + k); }
+        if (gb) { x += __ldg(gb + c.pcol + k); y += __ldg(gb + c.pcol + c.gate_off + k); }
+        x = tanhf(x) * (1.0f / (1.0f + expf(-y)));
+      } else {
+        if (ep.bias) x += __ldg(ep.bias + c.pcol + k);
+        if (gb) x += __ldg(gb + c.pcol + k);
+        x = act_fn<ACT>(x);
       }
-    } else {
-      for (int i = 0; i < nv; ++i) v[i] = ep.alpha * v[i] + r[i];
+      v[i] = x * ep.alpha;
     }
-  } else if (ep.alpha != 1.0f) {
+    const int phys = (j ^ (c.row & 7)) << 4;
+    if (has_res1) {
+      const float4 q = *reinterpret_cast<const float4*>(row32 + phys);
+      v[0] += q.x; v[1] += q.y; v[2] += q.z; v[3] += q.w;
+    }
+    if (has_res2) {
+      if (4 * j + 3 < nv) {
+        const float4 q = *reinterpret_cast<const float4*>(r2 + 4 * j);
+        v[0] += q.x; v[1] += q.y; v[2] += q.z; v[3] += q.w;
+      } else {
 #pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] *= ep.alpha;
-  }
-  if (ep.res2) {
-    const float* r = ep.res2 + row * ep.res2_ld + col0;
-    if (full) {
-#pragma unroll
-      for (int i = 0; i < 16; i += 4) {
-        float4 q = *reinterpret_cast<const float4*>(r + i);
-        v[i] += q.x; v[i + 1] += q.y; v[i + 2] += q.z; v[i + 3] += q.w;
+        for (int i = 0; i < 4; ++i)
+          if (4 * j + i < nv) v[i] += r2[4 * j + i];
       }
-    } else {
-      for (int i = 0; i < nv; ++i) v[i] += r[i];
     }
-  }
-  const float s = row_live ? ep.scale : 0.0f;
 #pragma unroll
-  for (int i = 0; i < 16; ++i) v[i] *= s;
-  if (ep.out32) {
-    float* o = ep.out32 + row * ep.out32_ld + col0;
-    if (full) {
+    for (int i = 0; i < 4; ++i) v[i] *= s;
+    if (c.need32) *reinterpret_cast<float4*>(row32 + phys) = make_float4(v[0], v[1], v[2], v[3]);
+    if (ep.out16) {
+      if (ep.post_lrelu) {
 #pragma unroll
-      for (int i = 0; i < 16; i += 4) *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
-    } else {
-      for (int i = 0; i < nv; ++i) o[i] = v[i];
+        for (int i = 0; i < 4; ++i) v[i] = lrelu(v[i], ep.post_slope);
+      }
+      p16[2 * j] = pack16(v[0], v[1], ep.out16_dtype);
+      p16[2 * j + 1] = pack16(v[2], v[3], ep.out16_dtype);
     }
   }
   if (ep.out16) {
-    if (ep.post_lrelu) {
+    uint8_t* row16 = c.slot + c.slot16_off + c.row * 64;
+    const int sw = (c.row >> 1) & 3;     // SWIZZLE_64B: 16-B chunk index ^= address bits [7:8]
 #pragma unroll
-      for (int i = 0; i < 16; ++i) v[i] = lrelu(v[i], ep.post_slope);
-    }
-    uint16_t* o = reinterpret_cast<uint16_t*>(ep.out16) + row * ep.out16_ld + col0;
-    if (full) {
-      uint4 q0, q1;
-      q0.x = pack16(v[0], v[1], ep.out16_dtype); q0.y = pack16(v[2], v[3], ep.out16_dtype);
-      q0.z = pack16(v[4], v[5], ep.out16_dtype); q0.w = pack16(v[6], v[7], ep.out16_dtype);
-      q1.x = pack16(v[8], v[9], ep.out16_dtype); q1.y = pack16(v[10], v[11], ep.out16_dtype);
-      q1.z = pack16(v[12], v[13], ep.out16_dtype); q1.w = pack16(v[14], v[15], ep.out16_dtype);
-      *reinterpret_cast<uint4*>(o) = q0;
-      *reinterpret_cast<uint4*>(o + 8) = q1;
-    } else {
-      for (int i = 0; i < nv; ++i) {
-        uint32_t pk = pack16(v[i], 0.f, ep.out16_dtype);
-        o[i] = static_cast<uint16_t>(pk & 0xFFFF);
-      }
-    }
+    for (int j = 0; j < 4; ++j)
+      *reinterpret_cast<uint4*>(row16 + ((j ^ sw) << 4)) =
+          make_uint4(p16[4 * j], p16[4 * j + 1], p16[4 * j + 2], p16[4 * j + 3]);
   }
+}
+
+struct TileCoord {
+  int n_idx, b, t0;
+};
+__device__ __forceinline__ TileCoord tile_coord(const ConvTcParams& p, int tile) {
+  TileCoord c;
+  c.n_idx = tile / p.m_tiles;
+  const int m = tile - c.n_idx * p.m_tiles;
+  c.b = m / p.tiles_t;
+  c.t0 = (m - c.b * p.tiles_t) * (128 * p.msub);
+  return c;
 }
 
 __global__ void __launch_bounds__(kTcThreads, 1)
 conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
-                 const ConvTcParams p) {
+                 const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmO32,
+                 const __grid_constant__ CUtensorMap tmO16, const ConvTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  TcBarriers* bars = reinterpret_cast<TcBarriers*>(smem + static_cast<size_t>(p.num_stages) * p.stage_bytes);
+  uint8_t* smA = smem;
+  uint8_t* smW = smA + kAStages * p.a_stage_bytes;
+  uint8_t* smE = smW + p.w_stages * p.w_stage_bytes;
+  TcBarriers* bars = reinterpret_cast<TcBarriers*>(smE + p.n_slots * p.slot_bytes);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const b200svs_epilogue& ep = p.ep;
+  const bool has_res1 = ep.res1 != nullptr;
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmW);
+    if (has_res1) prefetch_tmap(&tmR);
+    if (ep.out32) prefetch_tmap(&tmO32);
+    if (ep.out16) prefetch_tmap(&tmO16);
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < p.num_stages; ++s) {
-      mbar_init(&bars->full[s], 1);
-      mbar_init(&bars->empty[s], 1);
-    }
-    for (int s = 0; s < 2; ++s) {
-      mbar_init(&bars->tmem_full[s], 1);
-      mbar_init(&bars->tmem_empty[s], 4);
-    }
+    for (int s = 0; s < kAStages; ++s) { mbar_init(&bars->a_full[s], 1); mbar_init(&bars->a_empty[s], 1); }
+    for (int s = 0; s < p.w_stages; ++s) { mbar_init(&bars->w_full[s], 1); mbar_init(&bars->w_empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], 4); }
+    for (int s = 0; s < p.n_slots; ++s) { mbar_init(&bars->e_full[s], 1); mbar_init(&bars->e_empty[s], 1); }
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -168,28 +210,30 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
-  const int ksteps = p.ntaps * p.nchunks;
+  const int acc_cols = p.msub * p.block_n;
 
   if (warp == 0) {
     if (lane == 0) {
-      // ------------------------------------------------------------ TMA producer
-      int stage = 0;
-      uint32_t phase = 0;
+      // ------------------------------------------------------------ mainloop TMA producer
+      int as = 0, ws = 0;
+      uint32_t aph = 0, wph = 0;
+      const uint32_t a_tx = static_cast<uint32_t>(p.a_boxes) * p.a_box_rows * kRowBytes;
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-        const int n_idx = tile / p.m_tiles;
-        const int m = tile - n_idx * p.m_tiles;
-        const int b = m / p.tiles_t;
-        const int t0 = (m - b * p.tiles_t) * kBlockM;
-        for (int tap = 0; tap < p.ntaps; ++tap) {
-          const int trow = t0 + tap * p.dil - p.pad_left;
-          const int wrow = tap * p.cout_pad + n_idx * p.block_n;
-          for (int ch = 0; ch < p.nchunks; ++ch) {
-            mbar_wait(&bars->empty[stage], phase ^ 1);
-            uint8_t* sa = smem + static_cast<size_t>(stage) * p.stage_bytes;
-            mbar_arrive_expect_tx(&bars->full[stage], p.stage_bytes);
-            tma_load_3d(sa, &tmA, &bars->full[stage], ch * kBlockK, trow, b);
-            tma_load_2d(sa + kATileBytes, &tmW, &bars->full[stage], ch * kBlockK, wrow);
-            if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
+        const TileCoord tc = tile_coord(p, tile);
+        for (int ch = 0; ch < p.nchunks; ++ch) {
+          mbar_wait(&bars->a_empty[as], aph ^ 1);
+          uint8_t* sa = smA + as * p.a_stage_bytes;
+          mbar_arrive_expect_tx(&bars->a_full[as], a_tx);
+          for (int bx = 0; bx < p.a_boxes; ++bx)
+            tma_load_3d(sa + bx * p.a_box_rows * kRowBytes, &tmA, &bars->a_full[as], ch * kBlockK,
+                        tc.t0 - p.pad_left + bx * p.a_box_rows, tc.b);
+          if (++as == kAStages) { as = 0; aph ^= 1; }
+          for (int tap = 0; tap < p.ntaps; ++tap) {
+            mbar_wait(&bars->w_empty[ws], wph ^ 1);
+            mbar_arrive_expect_tx(&bars->w_full[ws], p.w_stage_bytes);
+            tma_load_2d(smW + ws * p.w_stage_bytes, &tmW, &bars->w_full[ws], ch * kBlockK,
+                        tap * p.cout_pad + tc.n_idx * p.block_n);
+            if (++ws == p.w_stages) { ws = 0; wph ^= 1; }
           }
         }
       }
@@ -197,89 +241,123 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp == 1) {
     if (lane == 0) {
       // ------------------------------------------------------------ MMA issuer
-      int stage = 0;
-      uint32_t phase = 0;
-      int it = 0;
+      int as = 0, ws = 0, it = 0;
+      uint32_t aph = 0, wph = 0;
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
         const int acc = it & 1;
-        const uint32_t acc_phase = (it >> 1) & 1;
-        mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
+        mbar_wait(&bars->tmem_empty[acc], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * p.block_n;
-        for (int ks = 0; ks < ksteps; ++ks) {
-          mbar_wait(&bars->full[stage], phase);
-          tc_fence_after();
-          const uint32_t sa = smem_u32(smem + static_cast<size_t>(stage) * p.stage_bytes);
-          const uint64_t da = make_desc_k128(sa);
-          const uint64_t db = make_desc_k128(sa + kATileBytes);
+        const uint32_t d_tmem = tmem_base + acc * acc_cols;
+        for (int ch = 0; ch < p.nchunks; ++ch) {
+          mbar_wait(&bars->a_full[as], aph);
+          const uint32_t sa = smem_u32(smA + as * p.a_stage_bytes);
+          for (int tap = 0; tap < p.ntaps; ++tap) {
+            mbar_wait(&bars->w_full[ws], wph);
+            tc_fence_after();
+            const uint64_t db = make_desc_k128(smem_u32(smW + ws * p.w_stage_bytes));
+            for (int ms = 0; ms < p.msub; ++ms) {
+              const uint64_t da = make_desc_k128(sa + (ms * 128 + tap * p.dil) * kRowBytes);
 #pragma unroll
-          for (int k = 0; k < kBlockK / 16; ++k) {
-            // advance 16 elements (32 B) along K inside the 128-B swizzle row: +2 in 16-B units
-            umma_f16(d_tmem, da + 2 * k, db + 2 * k, p.idesc, (ks | k) != 0);
+              for (int k = 0; k < kBlockK / 16; ++k)
+                umma_f16(d_tmem + ms * p.block_n, da + 2 * k, db + 2 * k, p.idesc, (ch | tap | k) != 0);
+            }
+            umma_commit(&bars->w_empty[ws]);
+            if (++ws == p.w_stages) { ws = 0; wph ^= 1; }
           }
-          umma_commit(&bars->empty[stage]);
-          if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
+          umma_commit(&bars->a_empty[as]);
+          if (++as == kAStages) { as = 0; aph ^= 1; }
         }
         umma_commit(&bars->tmem_full[acc]);
       }
     }
+  } else if (warp == 3) {
+    if (lane == 0) {
+      // ------------------------------------------------------------ epilogue staging producer
+      int sl = 0;
+      uint32_t eph = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        const TileCoord tc = tile_coord(p, tile);
+        for (int ms = 0; ms < p.msub; ++ms) {
+          const int t = tc.t0 + ms * 128;
+          for (int c = 0; c < p.chunks_per_sub; ++c) {
+            mbar_wait(&bars->e_empty[sl], eph ^ 1);
+            if (has_res1 && t < p.T) {
+              mbar_arrive_expect_tx(&bars->e_full[sl], kSlot32Bytes);
+              tma_load_3d(smE + sl * p.slot_bytes, &tmR, &bars->e_full[sl], tc.n_idx * p.n_out_tile + c * kEpiCols, t,
+                          tc.b);
+            } else {
+              mbar_arrive(&bars->e_full[sl]);
+            }
+            if (++sl == p.n_slots) { sl = 0; eph ^= 1; }
+          }
+        }
+      }
+    }
   } else if (warp >= 4) {
     // -------------------------------------------------------------- epilogue
-    const int q = warp & 3;  // TMEM lane quarter this warp may access
-    const int row_in_tile = q * 32 + lane;
-    const b200svs_epilogue& ep = p.ep;
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
     const bool gate = ep.act == B200SVS_ACT_GATE;
     const int half_n = p.block_n >> 1;
-    int it = 0;
+    const bool leader = threadIdx.x == 4 * 32;
+    int it = 0, sl = 0, prev_sl = -1;
+    uint32_t eph = 0;
+    EpiCtx c;
+    c.ep = &ep; c.slot16_off = p.slot16_off; c.row = row; c.T = p.T; c.need32 = ep.out32 != nullptr;
+    c.gate_off = half_n;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
       const int acc = it & 1;
-      const uint32_t acc_phase = (it >> 1) & 1;
-      const int n_idx = tile / p.m_tiles;
-      const int m = tile - n_idx * p.m_tiles;
-      const int b = m / p.tiles_t;
-      const int t = (m - b * p.tiles_t) * kBlockM + row_in_tile;
-      const bool row_ok = t < p.T;
-      bool row_live = true;
-      if (ep.lens) row_live = t < ep.lens[b];
-      mbar_wait(&bars->tmem_full[acc], acc_phase);
+      const TileCoord tc = tile_coord(p, tile);
+      c.b = tc.b;
+      const int len_b = ep.lens ? __ldg(ep.lens + tc.b) : p.T;
+      mbar_wait(&bars->tmem_full[acc], (it >> 1) & 1);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * p.block_n;
-      const float* gb = ep.gbias ? ep.gbias + static_cast<size_t>(b) * ep.gbias_ld : nullptr;
-      if (!gate) {
-        for (int c0 = 0; c0 < p.block_n; c0 += 16) {
-          float v[16];
-          tmem_ld16(taddr + c0, v);
-          const int col0 = n_idx * p.block_n + c0;
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            float x = v[i];
-            if (ep.bias) x += __ldg(ep.bias + col0 + i);
-            if (gb) x += __ldg(gb + col0 + i);
-            v[i] = apply_act(x, ep.act);
+      for (int ms = 0; ms < p.msub; ++ms) {
+        const int tsub = tc.t0 + ms * 128;
+        c.t = tsub + row;
+        c.row_ok = c.t < p.T;
+        c.row_live = c.t < len_b;
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * acc_cols + ms * p.block_n;
+        for (int ch = 0; ch < p.chunks_per_sub; ++ch) {
+          uint32_t r0[32], r1[32];
+          const int pc = gate ? ch * kEpiCols : ch * kEpiCols;
+          tmem_ld32_nowait(taddr + pc, r0);
+          if (gate) tmem_ld32_nowait(taddr + half_n + pc, r1);
+          c.pcol = tc.n_idx * p.block_n + pc;
+          c.ocol = tc.n_idx * p.n_out_tile + ch * kEpiCols;
+          c.slot = smE + sl * p.slot_bytes;
+          mbar_wait(&bars->e_full[sl], eph);
+          tmem_ld_wait();
+          if (tsub < p.T) {
+            switch (ep.act) {
+              case B200SVS_ACT_GATE: epi_chunk<B200SVS_ACT_GATE>(c, r0, r1); break;
+              case B200SVS_ACT_RELU: epi_chunk<B200SVS_ACT_RELU>(c, r0, r0); break;
+              case B200SVS_ACT_GELU: epi_chunk<B200SVS_ACT_GELU>(c, r0, r0); break;
+              case B200SVS_ACT_SIGMOID: epi_chunk<B200SVS_ACT_SIGMOID>(c, r0, r0); break;
+              case B200SVS_ACT_TANH: epi_chunk<B200SVS_ACT_TANH>(c, r0, r0); break;
+              default: epi_chunk<B200SVS_ACT_NONE>(c, r0, r0); break;
+            }
           }
-          finish_store16(v, ep, b, p.T, t, col0, row_ok, row_live);
-        }
-      } else {
-        for (int c0 = 0; c0 < half_n; c0 += 16) {
-          float va[16], vb[16];
-          tmem_ld16(taddr + c0, va);
-          tmem_ld16(taddr + half_n + c0, vb);
-          const int pa = n_idx * p.block_n + c0;  // packed column of the tanh half
-          const int pb = pa + half_n;
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            float xa = va[i], xb = vb[i];
-            if (ep.bias) { xa += __ldg(ep.bias + pa + i); xb += __ldg(ep.bias + pb + i); }
-            if (gb) { xa += __ldg(gb + pa + i); xb += __ldg(gb + pb + i); }
-            va[i] = tanhf(xa) * (1.0f / (1.0f + expf(-xb)));
+          fence_proxy_async();
+          named_bar_sync(1, kEpiThreads);
+          if (leader) {
+            if (tsub < p.T) {
+              if (ep.out32) tma_store_3d(&tmO32, c.slot, c.ocol, tsub, tc.b);
+              if (ep.out16) tma_store_3d(&tmO16, c.slot + p.slot16_off, c.ocol, tsub, tc.b);
+            }
+            tma_store_commit();
+            tma_store_wait_read<1>();              // every group but the newest has finished reading smem
+            if (prev_sl >= 0) mbar_arrive(&bars->e_empty[prev_sl]);
           }
-          finish_store16(va, ep, b, p.T, t, n_idx * half_n + c0, row_ok, row_live);
+          prev_sl = sl;
+          if (++sl == p.n_slots) { sl = 0; eph ^= 1; }
         }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
     }
+    if (leader) tma_store_wait_all<0>();
   }
 
   tc_fence_before();
@@ -295,6 +373,7 @@ static int next_pow2_cols(int c) {
   while (v < c) v <<= 1;
   return v;
 }
+static int round_up_i(int x, int m) { return (x + m - 1) / m * m; }
 
 }  // namespace b200svs
 
@@ -304,58 +383,100 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   B200SVS_REQUIRE(a && a->x && a->w, "conv1d_tc: null argument");
   B200SVS_REQUIRE(a->B > 0 && a->T > 0 && a->Cin > 0, "conv1d_tc: empty shape B=%d T=%d Cin=%d", a->B, a->T, a->Cin);
   B200SVS_REQUIRE(a->Cin_pad % kBlockK == 0 && a->Cin_pad >= a->Cin, "conv1d_tc: Cin_pad=%d must be a multiple of 64 >= Cin=%d", a->Cin_pad, a->Cin);
-  B200SVS_REQUIRE(a->block_n >= 16 && a->block_n <= 256 && a->block_n % 16 == 0, "conv1d_tc: block_n=%d", a->block_n);
+  B200SVS_REQUIRE(a->block_n >= 32 && a->block_n <= 256 && a->block_n % 32 == 0, "conv1d_tc: block_n=%d must be a multiple of 32 in [32,256]", a->block_n);
   B200SVS_REQUIRE(a->Cout_pad % a->block_n == 0, "conv1d_tc: Cout_pad=%d not a multiple of block_n=%d", a->Cout_pad, a->block_n);
   B200SVS_REQUIRE(a->x_ld % 8 == 0 && (reinterpret_cast<uintptr_t>(a->x) & 15) == 0, "conv1d_tc: x must be 16-B aligned with ld %% 8 == 0 (ld=%d)", a->x_ld);
   B200SVS_REQUIRE((reinterpret_cast<uintptr_t>(a->w) & 15) == 0, "conv1d_tc: w must be 16-B aligned");
   B200SVS_REQUIRE(a->ntaps >= 1 && a->dil >= 1, "conv1d_tc: ntaps=%d dil=%d", a->ntaps, a->dil);
+  B200SVS_REQUIRE((a->ntaps - 1) * a->dil <= 120, "conv1d_tc: receptive field (ntaps-1)*dil=%d exceeds 120 rows", (a->ntaps - 1) * a->dil);
   const b200svs_epilogue& ep = a->ep;
   const bool gate = ep.act == B200SVS_ACT_GATE;
-  B200SVS_REQUIRE(!gate || a->block_n % 32 == 0, "conv1d_tc: GATE needs block_n %% 32 == 0");
+  B200SVS_REQUIRE(!gate || a->block_n % 64 == 0, "conv1d_tc: GATE needs block_n %% 64 == 0");
   B200SVS_REQUIRE(ep.out32 || ep.out16, "conv1d_tc: no output");
   B200SVS_REQUIRE(!ep.out32 || (ep.out32_ld % 4 == 0 && (reinterpret_cast<uintptr_t>(ep.out32) & 15) == 0), "conv1d_tc: out32 alignment");
   B200SVS_REQUIRE(!ep.out16 || (ep.out16_ld % 8 == 0 && (reinterpret_cast<uintptr_t>(ep.out16) & 15) == 0), "conv1d_tc: out16 alignment");
   B200SVS_REQUIRE(!ep.res1 || (ep.res1_ld % 4 == 0 && (reinterpret_cast<uintptr_t>(ep.res1) & 15) == 0), "conv1d_tc: res1 alignment");
   B200SVS_REQUIRE(!ep.res2 || (ep.res2_ld % 4 == 0 && (reinterpret_cast<uintptr_t>(ep.res2) & 15) == 0), "conv1d_tc: res2 alignment");
-  B200SVS_REQUIRE(ep.n_valid > 0, "conv1d_tc: n_valid=%d", ep.n_valid);
+  const int n_tiles = a->Cout_pad / a->block_n;
+  const int n_out_tile = gate ? a->block_n / 2 : a->block_n;
+  B200SVS_REQUIRE(ep.n_valid > 0 && ep.n_valid <= n_tiles * n_out_tile, "conv1d_tc: n_valid=%d", ep.n_valid);
 
-  CUtensorMap tmA, tmW;
+  ConvTcParams p;
+  p.T = a->T;
+  p.ntaps = a->ntaps; p.nchunks = (a->Cin + kBlockK - 1) / kBlockK;
+  p.dil = a->dil; p.pad_left = a->pad_left; p.cout_pad = a->Cout_pad; p.block_n = a->block_n;
+  p.n_tiles = n_tiles; p.n_out_tile = n_out_tile;
+  p.chunks_per_sub = n_out_tile / kEpiCols;
+  // 256-row tiles (each weight tile feeds two MMAs) when TMEM holds 2 x 2 accumulators and the grid stays full
+  p.msub = 1;
+  if (4 * a->block_n <= 512) {
+    const long long tiles2 = static_cast<long long>((a->T + 255) / 256) * a->B * n_tiles;
+    if (tiles2 >= 2LL * num_sms()) p.msub = 2;
+  }
+  p.tiles_t = (a->T + 128 * p.msub - 1) / (128 * p.msub);
+  p.m_tiles = p.tiles_t * a->B;
+  p.total_tiles = p.m_tiles * n_tiles;
+  const int ra = 128 * p.msub + (a->ntaps - 1) * a->dil;
+  p.a_boxes = ra > 256 ? 2 : 1;
+  p.a_box_rows = round_up_i((ra + p.a_boxes - 1) / p.a_boxes, 8);
+  p.a_stage_bytes = p.a_boxes * p.a_box_rows * kRowBytes;
+  p.w_stage_bytes = a->block_n * kRowBytes;
+  const bool area32 = ep.res1 || ep.out32;
+  p.slot16_off = area32 ? kSlot32Bytes : 0;
+  p.slot_bytes = p.slot16_off + (ep.out16 ? kSlot16Bytes : 0);
+  p.n_slots = ep.res1 ? kMaxSlots : 2;
+  const int budget = max_smem_optin() - 1024 - 1024;   // alignment slack + barriers
+  int fixed = kAStages * p.a_stage_bytes + p.n_slots * p.slot_bytes;
+  int w_stages = (budget - fixed) / p.w_stage_bytes;
+  while (w_stages < 3 && p.n_slots > 2) {   // trade residual prefetch depth for weight stages
+    --p.n_slots;
+    fixed = kAStages * p.a_stage_bytes + p.n_slots * p.slot_bytes;
+    w_stages = (budget - fixed) / p.w_stage_bytes;
+  }
+  if (w_stages > kMaxWStages) w_stages = kMaxWStages;
+  B200SVS_REQUIRE(w_stages >= 2, "conv1d_tc: not enough shared memory (block_n=%d)", a->block_n);
+  p.w_stages = w_stages;
+  p.tmem_cols = next_pow2_cols(2 * p.msub * a->block_n);
+  p.idesc = make_idesc_f16(128, a->block_n, a->x_dtype == B200SVS_DT_BF16);
+  p.ep = ep;
+
+  const int el16 = a->x_dtype == B200SVS_DT_BF16 ? 1 : 0;
+  CUtensorMap tmA, tmW, tmR, tmO32, tmO16;
   {
     uint64_t dims[3] = {(uint64_t)a->Cin, (uint64_t)a->T, (uint64_t)a->B};
     uint64_t strides[2] = {(uint64_t)a->x_ld * 2, (uint64_t)a->T * a->x_ld * 2};
-    uint32_t box[3] = {(uint32_t)kBlockK, (uint32_t)kBlockM, 1};
-    int r = make_tmap_16bit(&tmA, a->x_dtype, a->x, 3, dims, strides, box);
+    uint32_t box[3] = {(uint32_t)kBlockK, (uint32_t)p.a_box_rows, 1};
+    int r = make_tmap(&tmA, el16, a->x, 3, dims, strides, box, 128);
     if (r) return r;
   }
   {
     uint64_t dims[2] = {(uint64_t)a->Cin_pad, (uint64_t)a->ntaps * a->Cout_pad};
     uint64_t strides[1] = {(uint64_t)a->Cin_pad * 2};
     uint32_t box[2] = {(uint32_t)kBlockK, (uint32_t)a->block_n};
-    int r = make_tmap_16bit(&tmW, a->x_dtype, a->w, 2, dims, strides, box);
+    int r = make_tmap(&tmW, el16, a->w, 2, dims, strides, box, 128);
+    if (r) return r;
+  }
+  tmR = tmA; tmO32 = tmA; tmO16 = tmA;
+  const uint32_t ebox[3] = {(uint32_t)kEpiCols, 128, 1};
+  const uint64_t edims[3] = {(uint64_t)ep.n_valid, (uint64_t)a->T, (uint64_t)a->B};
+  if (ep.res1) {
+    uint64_t strides[2] = {(uint64_t)ep.res1_ld * 4, (uint64_t)a->T * ep.res1_ld * 4};
+    int r = make_tmap(&tmR, 2, ep.res1, 3, edims, strides, ebox, 128);
+    if (r) return r;
+  }
+  if (ep.out32) {
+    uint64_t strides[2] = {(uint64_t)ep.out32_ld * 4, (uint64_t)a->T * ep.out32_ld * 4};
+    int r = make_tmap(&tmO32, 2, ep.out32, 3, edims, strides, ebox, 128);
+    if (r) return r;
+  }
+  if (ep.out16) {
+    uint64_t strides[2] = {(uint64_t)ep.out16_ld * 2, (uint64_t)a->T * ep.out16_ld * 2};
+    int r = make_tmap(&tmO16, ep.out16_dtype == B200SVS_DT_BF16 ? 1 : 0, ep.out16, 3, edims, strides, ebox, 64);
     if (r) return r;
   }
 
-  ConvTcParams p;
-  p.B = a->B; p.T = a->T;
-  p.tiles_t = (a->T + kBlockM - 1) / kBlockM;
-  p.m_tiles = p.tiles_t * a->B;
-  p.n_tiles = a->Cout_pad / a->block_n;
-  p.total_tiles = p.m_tiles * p.n_tiles;
-  p.ntaps = a->ntaps;
-  p.nchunks = (a->Cin + kBlockK - 1) / kBlockK;
-  p.dil = a->dil; p.pad_left = a->pad_left; p.cout_pad = a->Cout_pad; p.block_n = a->block_n;
-  p.stage_bytes = kATileBytes + a->block_n * kBlockK * 2;
-  const int budget = max_smem_optin() - 2048;   // 1 KB alignment slack + barriers
-  int stages = budget / p.stage_bytes;
-  if (stages > kMaxStages) stages = kMaxStages;
-  B200SVS_REQUIRE(stages >= 2, "conv1d_tc: not enough shared memory for 2 stages");
-  p.num_stages = stages;
-  p.tmem_cols = next_pow2_cols(2 * a->block_n);
-  p.idesc = make_idesc_f16(kBlockM, a->block_n, a->x_dtype == B200SVS_DT_BF16);
-  p.ep = ep;
-  if (p.ep.lens_div <= 0) p.ep.lens_div = 1;
-
-  const size_t smem = (size_t)stages * p.stage_bytes + sizeof(TcBarriers) + 1024;
+  const size_t smem = (size_t)kAStages * p.a_stage_bytes + (size_t)p.w_stages * p.w_stage_bytes +
+                      (size_t)p.n_slots * p.slot_bytes + sizeof(TcBarriers) + 1024;
   static size_t configured = 0;
   if (smem > configured) {
     int r = check_cuda(cudaFuncSetAttribute(conv1d_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
@@ -364,6 +485,6 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     configured = smem;
   }
   int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
-  conv1d_tc_kernel<<<grid, kTcThreads, smem, as_stream(stream)>>>(tmA, tmW, p);
+  conv1d_tc_kernel<<<grid, kTcThreads, smem, as_stream(stream)>>>(tmA, tmW, tmR, tmO32, tmO16, p);
   return check_launch("conv1d_tc_kernel");
 }

@@ -32,11 +32,13 @@ def _round_up(x, m):
 
 
 def choose_block_n(cout):
-    """N tile of the tensor-core conv: a multiple of 16, <= 256, minimising padded columns."""
-    if cout <= 256:
-        return _round_up(cout, 16)
+    """N tile of the tensor-core conv: a multiple of 32 (epilogue chunk), <= 256.  128 is preferred
+    for wide layers: TMEM then holds 2 x 2 accumulators and the kernel runs 256-row tiles in which
+    every weight tile feeds two MMAs (conv1d_tc.cu)."""
+    if cout <= 128:
+        return _round_up(cout, 32)
     best = None
-    for bn in (256, 192, 128):
+    for bn in (128, 192, 160, 224, 256):
         pad = _round_up(cout, bn)
         if best is None or pad < best[0]:
             best = (pad, bn)

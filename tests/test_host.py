@@ -59,7 +59,7 @@ def test_gate_packing_equals_fused_add_tanh_sigmoid_multiply():
 def test_choose_block_n():
     for cout in (1, 32, 80, 96, 192, 256, 384, 512, 513, 576, 768, 1024, 2048):
         bn = packer.choose_block_n(cout)
-        assert bn % 16 == 0 and 16 <= bn <= 256
+        assert bn % 32 == 0 and 32 <= bn <= 256
         assert packer._round_up(cout, bn) - cout < bn
 
 
