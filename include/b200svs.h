@@ -115,6 +115,20 @@ int b200svs_attention_f32(const float* qkv, int32_t qkv_ld, float* out, int32_t 
                           const int32_t* lens, int32_t B, int32_t T, int32_t C, int32_t H, int32_t window,
                           void* stream);
 
+/* Tensor-core version of the same attention (tcgen05 QK^T and PV, softmax in registers).
+ * b200svs_attn_prep splits the fp32 qkv [B,T,3C] into (q|k) 16-bit [B,T,2C] and V^T 16-bit [B,C,Tp]
+ * (Tp >= T, multiple of 8).  With qk_lo / vt_lo != NULL every operand is an fp16 (hi, lo) pair and every
+ * product three MMAs (hi.hi + hi.lo + lo.hi): fp32-class accuracy for the F0 predictor, whose output is
+ * quantised by f0_to_coarse (utils/pitch_utils.py:22-31).  out16_split: out16 is [B,T,3C] = hi | lo | hi
+ * (fp16), the K-concatenated operand of a split-precision conv. */
+int b200svs_attn_prep(const float* qkv, int32_t qkv_ld, void* qk_hi, void* qk_lo, void* vt_hi, void* vt_lo,
+                      int32_t dtype, int32_t B, int32_t T, int32_t Tp, int32_t C, void* stream);
+int b200svs_attention_tc(const void* qk_hi, const void* qk_lo, const void* vt_hi, const void* vt_lo,
+                         int32_t dtype, int32_t Tp, float* out32, int32_t out32_ld, void* out16, int32_t out16_ld,
+                         int32_t out16_dtype, int32_t out16_split, const float* rel_k, const float* rel_v,
+                         const int32_t* lens, int32_t B, int32_t T, int32_t C, int32_t H, int32_t window,
+                         void* stream);
+
 /* y = LayerNorm_C(x (+ res)) * mask  (modules.py:29-32 + the residual adds of attentions.py:42,46) */
 int b200svs_layernorm(const float* x, int32_t x_ld, const float* res, int32_t res_ld, const float* gamma,
                       const float* beta, float eps, const int32_t* lens, float* out32, int32_t out32_ld,

@@ -48,6 +48,9 @@ PROTOTYPES = {
     "b200svs_conv1d_tc": [C.POINTER(ConvArgs), _vp],
     "b200svs_conv1d_f32": [C.POINTER(ConvArgs), _vp],
     "b200svs_attention_f32": [_vp, _i32, _vp, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
+    "b200svs_attn_prep": [_vp, _i32, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
+    "b200svs_attention_tc": [_vp, _vp, _vp, _vp, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _i32, _i32,
+                             _i32, _i32, _i32, _vp],
     "b200svs_layernorm": [_vp, _i32, _vp, _i32, _vp, _vp, _f32, _vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
     "b200svs_text_embed": [_vp] * 12 + [_i32, _i32, _i32, _vp],
     "b200svs_duration_quantize": [_vp, _vp, _vp, _i32, _vp],

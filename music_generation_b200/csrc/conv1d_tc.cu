@@ -33,7 +33,7 @@ constexpr int kBlockK = 64;
 constexpr int kRowBytes = kBlockK * 2;     // one K-chunk row of a 16-bit operand tile: 128 B
 constexpr int kAStages = 2;
 constexpr int kMaxWStages = 8;
-constexpr int kMaxSlots = 4;
+constexpr int kMaxSlots = 8;
 constexpr int kEpiCols = 32;               // output columns per epilogue chunk
 constexpr int kSlot32Bytes = 128 * kEpiCols * 4;   // 16 KB: [128 rows][32 fp32], SWIZZLE_128B
 constexpr int kSlot16Bytes = 128 * kEpiCols * 2;   //  8 KB: [128 rows][32 x 16-bit], SWIZZLE_64B
@@ -45,7 +45,9 @@ struct ConvTcParams {
   int ntaps, nchunks, dil, pad_left, cout_pad, block_n, msub;
   int a_boxes, a_box_rows, a_stage_bytes;  // activation tile = a_boxes TMA boxes of a_box_rows rows
   int w_stages, w_stage_bytes;
-  int n_slots, slot_bytes, slot16_off;     // epilogue staging slot: [fp32 area][16-bit area]
+  int n_slots, slot_bytes, slot16_off;     // epilogue staging slot: [fp32 area][res2 fp32 area][16-bit area]
+  int slot_r2_off;                         // offset of the res2 area inside a slot (0 = none)
+  int stores_in_flight;                    // TMA store groups left pending before a slot is recycled
   int chunks_per_sub, n_out_tile;          // output chunks per 128-row sub-tile; output columns per N tile
   int tmem_cols;
   uint32_t idesc;
@@ -81,7 +83,7 @@ __device__ __forceinline__ uint32_t pack16(float a, float b, int dtype) {
 struct EpiCtx {
   const b200svs_epilogue* ep;
   uint8_t* slot;          // staging slot base (fp32 area); 16-bit area at slot + slot16_off
-  int slot16_off;
+  int slot16_off, slot_r2_off;
   int row;                // row inside the 128-row sub-tile (= TMEM lane)
   int b, t, T;            // batch index, global time row, rows per batch element
   int pcol;               // first packed accumulator column of this chunk (bias / gbias index)
@@ -99,9 +101,7 @@ __device__ __forceinline__ void epi_chunk(const EpiCtx& c, const uint32_t* acc, 
   const float* gb = ep.gbias ? ep.gbias + static_cast<size_t>(c.b) * ep.gbias_ld : nullptr;
   const float s = c.row_live ? ep.scale : 0.0f;
   const bool has_res1 = ep.res1 != nullptr;
-  const bool has_res2 = ep.res2 != nullptr && c.row_ok;
-  const float* r2 = has_res2 ? ep.res2 + (static_cast<size_t>(c.b) * c.T + c.t) * ep.res2_ld + c.ocol : nullptr;
-  const int nv = ep.n_valid - c.ocol;      // valid output columns from ocol on
+  const bool has_res2 = ep.res2 != nullptr;
   uint8_t* row32 = c.slot + c.row * 128;
   uint32_t p16[16];
 #pragma unroll
@@ -129,14 +129,8 @@ __device__ __forceinline__ void epi_chunk(const EpiCtx& c, const uint32_t* acc, 
       v[0] += q.x; v[1] += q.y; v[2] += q.z; v[3] += q.w;
     }
     if (has_res2) {
-      if (4 * j + 3 < nv) {
-        const float4 q = *reinterpret_cast<const float4*>(r2 + 4 * j);
-        v[0] += q.x; v[1] += q.y; v[2] += q.z; v[3] += q.w;
-      } else {
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-          if (4 * j + i < nv) v[i] += r2[4 * j + i];
-      }
+      const float4 q = *reinterpret_cast<const float4*>(row32 + c.slot_r2_off + phys);
+      v[0] += q.x; v[1] += q.y; v[2] += q.z; v[3] += q.w;
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i) v[i] *= s;
@@ -174,7 +168,8 @@ __device__ __forceinline__ TileCoord tile_coord(const ConvTcParams& p, int tile)
 
 __global__ void __launch_bounds__(kTcThreads, 1)
 conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
-                 const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmO32,
+                 const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmR2,
+                 const __grid_constant__ CUtensorMap tmO32,
                  const __grid_constant__ CUtensorMap tmO16, const ConvTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -187,11 +182,13 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int lane = threadIdx.x & 31;
   const b200svs_epilogue& ep = p.ep;
   const bool has_res1 = ep.res1 != nullptr;
+  const bool has_res2 = ep.res2 != nullptr;
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmW);
     if (has_res1) prefetch_tmap(&tmR);
+    if (has_res2) prefetch_tmap(&tmR2);
     if (ep.out32) prefetch_tmap(&tmO32);
     if (ep.out16) prefetch_tmap(&tmO16);
   }
@@ -281,10 +278,11 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const int t = tc.t0 + ms * 128;
           for (int c = 0; c < p.chunks_per_sub; ++c) {
             mbar_wait(&bars->e_empty[sl], eph ^ 1);
-            if (has_res1 && t < p.T) {
-              mbar_arrive_expect_tx(&bars->e_full[sl], kSlot32Bytes);
-              tma_load_3d(smE + sl * p.slot_bytes, &tmR, &bars->e_full[sl], tc.n_idx * p.n_out_tile + c * kEpiCols, t,
-                          tc.b);
+            if ((has_res1 || has_res2) && t < p.T) {
+              const int col = tc.n_idx * p.n_out_tile + c * kEpiCols;
+              mbar_arrive_expect_tx(&bars->e_full[sl], (has_res1 ? kSlot32Bytes : 0) + (has_res2 ? kSlot32Bytes : 0));
+              if (has_res1) tma_load_3d(smE + sl * p.slot_bytes, &tmR, &bars->e_full[sl], col, t, tc.b);
+              if (has_res2) tma_load_3d(smE + sl * p.slot_bytes + p.slot_r2_off, &tmR2, &bars->e_full[sl], col, t, tc.b);
             } else {
               mbar_arrive(&bars->e_full[sl]);
             }
@@ -300,10 +298,10 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const bool gate = ep.act == B200SVS_ACT_GATE;
     const int half_n = p.block_n >> 1;
     const bool leader = threadIdx.x == 4 * 32;
-    int it = 0, sl = 0, prev_sl = -1;
+    int it = 0, sl = 0, free_sl = 0, n_done = 0;
     uint32_t eph = 0;
     EpiCtx c;
-    c.ep = &ep; c.slot16_off = p.slot16_off; c.row = row; c.T = p.T; c.need32 = ep.out32 != nullptr;
+    c.ep = &ep; c.slot16_off = p.slot16_off; c.slot_r2_off = p.slot_r2_off; c.row = row; c.T = p.T; c.need32 = ep.out32 != nullptr;
     c.gate_off = half_n;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
       const int acc = it & 1;
@@ -346,10 +344,22 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               if (ep.out16) tma_store_3d(&tmO16, c.slot + p.slot16_off, c.ocol, tsub, tc.b);
             }
             tma_store_commit();
-            tma_store_wait_read<1>();              // every group but the newest has finished reading smem
-            if (prev_sl >= 0) mbar_arrive(&bars->e_empty[prev_sl]);
+            // keep `stores_in_flight` groups pending; the slot of the oldest completed one is recycled
+            switch (p.stores_in_flight) {
+              case 0: tma_store_wait_read<0>(); break;
+              case 1: tma_store_wait_read<1>(); break;
+              case 2: tma_store_wait_read<2>(); break;
+              case 3: tma_store_wait_read<3>(); break;
+              case 4: tma_store_wait_read<4>(); break;
+              case 5: tma_store_wait_read<5>(); break;
+              case 6: tma_store_wait_read<6>(); break;
+              default: tma_store_wait_read<7>(); break;
+            }
+            if (++n_done > p.stores_in_flight) {
+              mbar_arrive(&bars->e_empty[free_sl]);
+              if (++free_sl == p.n_slots) free_sl = 0;
+            }
           }
-          prev_sl = sl;
           if (++sl == p.n_slots) { sl = 0; eph ^= 1; }
         }
       }
@@ -422,26 +432,33 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   p.a_stage_bytes = p.a_boxes * p.a_box_rows * kRowBytes;
   p.w_stage_bytes = a->block_n * kRowBytes;
   const bool area32 = ep.res1 || ep.out32;
-  p.slot16_off = area32 ? kSlot32Bytes : 0;
+  p.slot_r2_off = ep.res2 ? (area32 ? kSlot32Bytes : 0) : 0;
+  B200SVS_REQUIRE(!ep.res2 || area32, "conv1d_tc: res2 needs res1 or out32");
+  p.slot16_off = (area32 ? kSlot32Bytes : 0) + (ep.res2 ? kSlot32Bytes : 0);
   p.slot_bytes = p.slot16_off + (ep.out16 ? kSlot16Bytes : 0);
-  p.n_slots = ep.res1 ? kMaxSlots : 2;
+  // shared memory: 2 activation stages, >= 3 weight stages (or all k-steps of a tile if fewer), then as many
+  // staging slots as fit (stores in flight + residual prefetch), the rest to weight stages
   const int budget = max_smem_optin() - 1024 - 1024;   // alignment slack + barriers
-  int fixed = kAStages * p.a_stage_bytes + p.n_slots * p.slot_bytes;
-  int w_stages = (budget - fixed) / p.w_stage_bytes;
-  while (w_stages < 3 && p.n_slots > 2) {   // trade residual prefetch depth for weight stages
-    --p.n_slots;
-    fixed = kAStages * p.a_stage_bytes + p.n_slots * p.slot_bytes;
-    w_stages = (budget - fixed) / p.w_stage_bytes;
-  }
+  const int ksteps = a->ntaps * p.nchunks;
+  int w_min = ksteps < 3 ? ksteps : 3;
+  if (w_min < 2) w_min = 2;
+  const int avail = budget - kAStages * p.a_stage_bytes;
+  int n_slots = (avail - w_min * p.w_stage_bytes) / p.slot_bytes;
+  if (n_slots > kMaxSlots) n_slots = kMaxSlots;
+  if (n_slots < 2) { n_slots = 2; }
+  int w_stages = (avail - n_slots * p.slot_bytes) / p.w_stage_bytes;
   if (w_stages > kMaxWStages) w_stages = kMaxWStages;
   B200SVS_REQUIRE(w_stages >= 2, "conv1d_tc: not enough shared memory (block_n=%d)", a->block_n);
+  p.n_slots = n_slots;
   p.w_stages = w_stages;
+  // with a residual, about half of the slots hold prefetched residual tiles, the other half are stores in flight
+  p.stores_in_flight = (ep.res1 || ep.res2) ? (n_slots - 1) / 2 : n_slots - 1;
   p.tmem_cols = next_pow2_cols(2 * p.msub * a->block_n);
   p.idesc = make_idesc_f16(128, a->block_n, a->x_dtype == B200SVS_DT_BF16);
   p.ep = ep;
 
   const int el16 = a->x_dtype == B200SVS_DT_BF16 ? 1 : 0;
-  CUtensorMap tmA, tmW, tmR, tmO32, tmO16;
+  CUtensorMap tmA, tmW, tmR, tmR2, tmO32, tmO16;
   {
     uint64_t dims[3] = {(uint64_t)a->Cin, (uint64_t)a->T, (uint64_t)a->B};
     uint64_t strides[2] = {(uint64_t)a->x_ld * 2, (uint64_t)a->T * a->x_ld * 2};
@@ -456,12 +473,17 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     int r = make_tmap(&tmW, el16, a->w, 2, dims, strides, box, 128);
     if (r) return r;
   }
-  tmR = tmA; tmO32 = tmA; tmO16 = tmA;
+  tmR = tmA; tmR2 = tmA; tmO32 = tmA; tmO16 = tmA;
   const uint32_t ebox[3] = {(uint32_t)kEpiCols, 128, 1};
   const uint64_t edims[3] = {(uint64_t)ep.n_valid, (uint64_t)a->T, (uint64_t)a->B};
   if (ep.res1) {
     uint64_t strides[2] = {(uint64_t)ep.res1_ld * 4, (uint64_t)a->T * ep.res1_ld * 4};
     int r = make_tmap(&tmR, 2, ep.res1, 3, edims, strides, ebox, 128);
+    if (r) return r;
+  }
+  if (ep.res2) {
+    uint64_t strides[2] = {(uint64_t)ep.res2_ld * 4, (uint64_t)a->T * ep.res2_ld * 4};
+    int r = make_tmap(&tmR2, 2, ep.res2, 3, edims, strides, ebox, 128);
     if (r) return r;
   }
   if (ep.out32) {
@@ -485,6 +507,6 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     configured = smem;
   }
   int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
-  conv1d_tc_kernel<<<grid, kTcThreads, smem, as_stream(stream)>>>(tmA, tmW, tmR, tmO32, tmO16, p);
+  conv1d_tc_kernel<<<grid, kTcThreads, smem, as_stream(stream)>>>(tmA, tmW, tmR, tmR2, tmO32, tmO16, p);
   return check_launch("conv1d_tc_kernel");
 }

@@ -134,6 +134,31 @@ def attention(qkv, out32, out16, rel_k, rel_v, lens, heads=2, window=4):
               _ptr(rel_k), _ptr(rel_v), _ptr(lens), B, T, c, heads, window, _stream())
 
 
+def attention_tc(qkv, out32, out16, rel_k, rel_v, lens, *, dtype, split=False, out16_split=False, ws=None, heads=2,
+                 window=4):
+    """Tensor-core attention: qkv fp32 [B,T,3C] -> out32 fp32 [B,T,C] and/or out16.  `split`: fp16 (hi, lo)
+    operands, three MMAs per product.  `ws`: optional dict reused across layers for the 16-bit operand copies."""
+    B, T, c3 = qkv.shape
+    c = c3 // 3
+    Tp = (T + 7) // 8 * 8
+    odt = torch.float16 if split else dtype
+    ws = ws if ws is not None else {}
+    key = (B, T, c, split, odt)
+    if ws.get("key") != key:
+        ws["key"] = key
+        ws["qk_hi"] = torch.empty(B, T, 2 * c, device=qkv.device, dtype=odt)
+        ws["vt_hi"] = torch.empty(B, c, Tp, device=qkv.device, dtype=odt)
+        ws["qk_lo"] = torch.empty_like(ws["qk_hi"]) if split else None
+        ws["vt_lo"] = torch.empty_like(ws["vt_hi"]) if split else None
+    code = dt_code(odt)
+    _lib.call("b200svs_attn_prep", _ptr(qkv), _btc(qkv, "qkv"), _ptr(ws["qk_hi"]), _ptr(ws["qk_lo"]), _ptr(ws["vt_hi"]),
+              _ptr(ws["vt_lo"]), code, B, T, Tp, c, _stream())
+    _lib.call("b200svs_attention_tc", _ptr(ws["qk_hi"]), _ptr(ws["qk_lo"]), _ptr(ws["vt_hi"]), _ptr(ws["vt_lo"]), code, Tp,
+              _ptr(out32), _btc(out32, "out32"), _ptr(out16), _btc(out16, "out16"),
+              0 if out16 is None else dt_code(out16.dtype), 1 if out16_split else 0, _ptr(rel_k), _ptr(rel_v),
+              _ptr(lens), B, T, c, heads, window, _stream())
+
+
 def layernorm(x, gamma, beta, lens, out32=None, out16=None, res=None, eps=1e-5):
     B, T, c = x.shape
     _lib.call("b200svs_layernorm", _ptr(x), _btc(x, "x"), _ptr(res), _btc(res, "res"), _ptr(gamma), _ptr(beta),

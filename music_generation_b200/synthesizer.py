@@ -231,22 +231,28 @@ class SynthesizerTrn(nn.Module):
         return P
 
     # ------------------------------------------------------------------ building blocks
-    def _encoder(self, layers, x32, x16, lens, f32):
+    def _encoder(self, layers, x32, x16, lens, f32, attn="f32"):
         """attentions.Encoder (VISinger/attentions.py:35-47), channels-last, in place on x32 (/x16).
-        x is masked on entry and after every LayerNorm; valid rows equal the reference's."""
+        x is masked on entry and after every LayerNorm; valid rows equal the reference's.
+        attn: "f32" = fp32 SIMT attention (phoneme level), "tc" = tensor-core attention with 16-bit
+        operands, "split" = tensor-core attention with fp16 (hi, lo) operands (F0 predictor)."""
         B, T, Cc = x32.shape
         dev = x32.device
         dt = self.operand_dtype
         qkv = torch.empty(B, T, 3 * Cc, device=dev, dtype=torch.float32)
-        att32 = torch.empty(B, T, Cc, device=dev, dtype=torch.float32)
+        att32 = torch.empty(B, T, Cc, device=dev, dtype=torch.float32) if f32 else None
         att16 = None if f32 else torch.empty(B, T, Cc, device=dev, dtype=dt)
         tmp = torch.empty(B, T, Cc, device=dev, dtype=torch.float32)
         hdt = torch.float32 if f32 else dt
         hid = torch.empty(B, T, self.filter_channels, device=dev, dtype=hdt)
+        ws = {}
         for e in layers:
             xin = x32 if f32 else x16
             ops.conv1d(e.qkv, xin, out32=qkv)
-            ops.attention(qkv, att32, att16, e.rel_k, e.rel_v, lens)
+            if attn == "f32":
+                ops.attention(qkv, att32, att16, e.rel_k, e.rel_v, lens)
+            else:
+                ops.attention_tc(qkv, att32, att16, e.rel_k, e.rel_v, lens, dtype=dt, split=(attn == "split"), ws=ws)
             ops.conv1d(e.o, att32 if f32 else att16, res1=x32, out32=tmp)
             ops.layernorm(tmp, e.ln1[0], e.ln1[1], lens, out32=x32, out16=x16)
             xin = x32 if f32 else x16
@@ -405,7 +411,7 @@ class SynthesizerTrn(nn.Module):
         xe16 = torch.empty(B, T, H, device=dev, dtype=dt)
         ops.add_pos_mask(h_lr, P["pos"], mlen, out32=xe32, out16=xe16)
         f0h = xe32.clone()
-        self._encoder(P["f0_enc"], f0h, None, mlen, True)
+        self._encoder(P["f0_enc"], f0h, None, mlen, True, attn="split")
         log_f0 = torch.empty(B, T, 1, device=dev, dtype=f32)
         ops.conv1d(P["f0_out"], f0h, lens=mlen, out32=log_f0)
         log_f0 = log_f0.view(B, T)
@@ -418,7 +424,7 @@ class SynthesizerTrn(nn.Module):
         m32 = torch.empty(B, T, H, device=dev, dtype=f32)
         m16 = torch.empty(B, T, H, device=dev, dtype=dt)
         ops.conv1d(P["mel_cond"], f0e16, res1=xe32, lens=mlen, out32=m32, out16=m16)
-        self._encoder(P["mel_enc"], m32, m16, mlen, False)
+        self._encoder(P["mel_enc"], m32, m16, mlen, False, attn="tc")
         mel32 = torch.empty(B, T, 80, device=dev, dtype=f32)
         ops.conv1d(P["mel_out"], m16, lens=mlen, out32=mel32)
         # FramePriorNetwork (frame_prior_network.py:31-41)

@@ -103,6 +103,23 @@ def attention(qkv, out32, out16, rel_k, rel_v, lens, heads=2, window=4):
     _store(out16, out)
 
 
+def attention_tc(qkv, out32, out16, rel_k, rel_v, lens, *, dtype, split=False, out16_split=False, ws=None, heads=2,
+                 window=4):
+    """Semantics of ops.attention_tc: 16-bit rounding of q,k,v in plain mode; split mode keeps ~fp32."""
+    q = qkv if split else qkv.to(dtype).float()
+    B, T, c3 = qkv.shape
+    tmp = torch.empty(B, T, c3 // 3)
+    attention(q, tmp, None, rel_k, rel_v, lens, heads, window)
+    _store(out32, tmp)
+    if out16 is not None:
+        if out16_split:
+            hi = tmp.half()
+            lo = (tmp - hi.float()).half()
+            out16.copy_(torch.cat([hi, lo, hi], -1))
+        else:
+            _store(out16, tmp)
+
+
 def layernorm(x, gamma, beta, lens, out32=None, out16=None, res=None, eps=1e-5):
     B, T, c = x.shape
     y = x if res is None else x + res
@@ -185,7 +202,7 @@ def conv_post_tanh(x16, w, out):
 def install(monkeypatch):
     """Route music_generation_b200.ops.* to the emulation above (CPU tests only)."""
     import music_generation_b200.synthesizer as syn
-    for name in ("conv1d", "attention", "layernorm", "text_embed", "duration_quantize", "lr_scan", "lr_gather",
+    for name in ("conv1d", "attention", "attention_tc", "layernorm", "text_embed", "duration_quantize", "lr_scan", "lr_gather",
                  "add_pos_mask", "f0_embed", "sample_prior", "conv_post_tanh"):
         monkeypatch.setattr(real_ops, name, globals()[name])
     monkeypatch.setattr(syn, "_require_cuda", lambda t: None)

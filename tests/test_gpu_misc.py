@@ -34,6 +34,45 @@ def test_attention_matches_reference_semantics(B, T, lens):
     assert max_abs(e32, r16.float().cpu()) < 4e-3
 
 
+@pytest.mark.parametrize("B,T,lens", [(2, 150, [150, 77]), (1, 64, [64]), (3, 200, [200, 1, 0]), (1, 3, [3]),
+                                      (2, 513, [513, 300]), (1, 1100, [1100])])
+@pytest.mark.parametrize("split", [False, True], ids=["plain", "split"])
+def test_attention_tc_matches_reference_semantics(B, T, lens, split):
+    """tcgen05 attention vs the fp32 semantics.  plain: fp16 operand rounding of q,k,v,p -> 4e-3;
+    split (hi,lo) operands -> fp32-class agreement."""
+    qkv = _rand(B, T, 576, seed=1)
+    rel_k, rel_v = _rand(9, 96, seed=2, scale=96 ** -0.5), _rand(9, 96, seed=3, scale=96 ** -0.5)
+    ln = torch.tensor(lens, dtype=torch.int32)
+    e32 = torch.empty(B, T, 192)
+    emu_ops.attention(qkv, e32, None, rel_k, rel_v, ln)
+    r32 = torch.full((B, T, 192), 7.0, device=DEV)
+    r16 = torch.full((B, T, 576 if split else 192), 7.0, device=DEV, dtype=torch.float16)
+    ops.attention_tc(qkv.to(DEV), r32, r16, rel_k.to(DEV), rel_v.to(DEV), ln.to(DEV), dtype=torch.float16, split=split,
+                     out16_split=split)
+    torch.cuda.synchronize()
+    tol = 2e-5 if split else 4e-3
+    assert max_abs(e32, r32.cpu()) < tol
+    if split:
+        hi, lo, hi2 = (r16[:, :, i * 192:(i + 1) * 192].float().cpu() for i in range(3))
+        assert torch.equal(hi, hi2)
+        assert max_abs(e32, hi + lo) < 2e-5
+    else:
+        assert max_abs(e32, r16.float().cpu()) < 6e-3
+
+
+def test_attention_tc_bf16():
+    B, T = 2, 300
+    qkv = _rand(B, T, 576, seed=4)
+    rel_k, rel_v = _rand(9, 96, seed=5, scale=96 ** -0.5), _rand(9, 96, seed=6, scale=96 ** -0.5)
+    ln = torch.tensor([300, 190], dtype=torch.int32)
+    e32 = torch.empty(B, T, 192)
+    emu_ops.attention(qkv, e32, None, rel_k, rel_v, ln)
+    r32 = torch.empty(B, T, 192, device=DEV)
+    ops.attention_tc(qkv.to(DEV), r32, None, rel_k.to(DEV), rel_v.to(DEV), ln.to(DEV), dtype=torch.bfloat16)
+    torch.cuda.synchronize()
+    assert max_abs(e32, r32.cpu()) < 3e-2
+
+
 def test_attention_agrees_with_oracle_mha():
     """Against the oracle's pad/view formulation (VISinger/attentions.py:148-243), not just the emulation."""
     from oracle import visinger_oracle as vo
