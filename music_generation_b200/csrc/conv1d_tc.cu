@@ -15,12 +15,12 @@
 // accumulator in place, and TMA stores write the fp32 and the 16-bit result (the latter with the next
 // layer's leaky-ReLU applied) fully coalesced; the tensor maps clip rows >= T and columns >= n_valid.
 //
-// Warp roles (256 threads, 1 CTA/SM, persistent over tiles):
+// Warp roles (384 threads, 1 CTA/SM, persistent over tiles):
 //   warp 0 lane 0 : TMA producer of the mainloop (activation ring, weight ring)
 //   warp 1 lane 0 : tcgen05.mma issuer (accumulators double-buffered in TMEM)
 //   warp 2        : TMEM alloc / dealloc
 //   warp 3 lane 0 : TMA producer of the epilogue staging slots (residual tiles)
-//   warps 4..7    : epilogue
+//   warps 4..11   : epilogue, two warpgroups taking alternate 32-column chunks
 //
 // Replaces: nn.Conv1d/ConvTranspose1d + surrounding pointwise ops of the reference
 // (VISinger/models_ae.py:327-346, modules.py:148-176,210-223,329-349, attentions.py:138-146,277-285).
@@ -37,7 +37,8 @@ constexpr int kMaxSlots = 8;
 constexpr int kEpiCols = 32;               // output columns per epilogue chunk
 constexpr int kSlot32Bytes = 128 * kEpiCols * 4;   // 16 KB: [128 rows][32 fp32], SWIZZLE_128B
 constexpr int kSlot16Bytes = 128 * kEpiCols * 2;   //  8 KB: [128 rows][32 x 16-bit], SWIZZLE_64B
-constexpr int kTcThreads = 256;
+constexpr int kEpiGroups = 1;               // epilogue warpgroups (4 warps each), chunks alternate between them
+constexpr int kTcThreads = 128 + kEpiGroups * 128;
 constexpr int kEpiThreads = 128;
 
 struct ConvTcParams {
@@ -50,6 +51,7 @@ struct ConvTcParams {
   int stores_in_flight;                    // TMA store groups left pending before a slot is recycled
   int chunks_per_sub, n_out_tile;          // output chunks per 128-row sub-tile; output columns per N tile
   int tmem_cols;
+  int ksub;                                // K=16 MMA steps per K chunk (4, or fewer when Cin < 64)
   uint32_t idesc;
   b200svs_epilogue ep;
 };
@@ -91,58 +93,67 @@ struct EpiCtx {
   int gate_off;           // GATE: packed-column distance between the tanh and the sigmoid half
   bool row_ok, row_live;
   bool need32;            // fp32 area is stored (out32 != NULL)
+  const float* bias_s;    // bias staged in shared memory (NULL: no bias)
 };
 
 // One chunk of 32 output columns for one row.  acc[] holds the raw accumulator bits (for GATE: acc =
-// tanh half, acc2 = sigmoid half).  Static indexing only: everything stays in registers.
-template <int ACT>
+// tanh half, acc2 = sigmoid half).  Static indexing only: everything stays in registers.  The bias lives
+// in shared memory (bias_s, indexed by packed column) and is read with broadcast 128-bit loads.
+template <int ACT, bool RES>
 __device__ __forceinline__ void epi_chunk(const EpiCtx& c, const uint32_t* acc, const uint32_t* acc2) {
   const b200svs_epilogue& ep = *c.ep;
   const float* gb = ep.gbias ? ep.gbias + static_cast<size_t>(c.b) * ep.gbias_ld : nullptr;
   const float s = c.row_live ? ep.scale : 0.0f;
-  const bool has_res1 = ep.res1 != nullptr;
-  const bool has_res2 = ep.res2 != nullptr;
+  const float alpha = ep.alpha;
+  const bool has_res1 = RES && ep.res1 != nullptr;
+  const bool has_res2 = RES && ep.res2 != nullptr;
+  const bool lre = ep.post_lrelu != 0;
+  const float slope = ep.post_slope;
+  const int odt = ep.out16_dtype;
   uint8_t* row32 = c.slot + c.row * 128;
   uint32_t p16[16];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     float v[4];
+    float4 bq = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c.bias_s) bq = *reinterpret_cast<const float4*>(c.bias_s + c.pcol + 4 * j);
+    v[0] = __uint_as_float(acc[4 * j]) + bq.x; v[1] = __uint_as_float(acc[4 * j + 1]) + bq.y;
+    v[2] = __uint_as_float(acc[4 * j + 2]) + bq.z; v[3] = __uint_as_float(acc[4 * j + 3]) + bq.w;
+    if (gb) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int k = 4 * j + i;
-      float x = __uint_as_float(acc[k]);
-      if (ACT == B200SVS_ACT_GATE) {
-        float y = __uint_as_float(acc2[k]);
-        if (ep.bias) { x += __ldg(ep.bias + c.pcol + k); y += __ldg(ep.bias + c.pcol + c.gate_off + k); }
-        if (gb) { x += __ldg(gb + c.pcol + k); y += __ldg(gb + c.pcol + c.gate_off + k); }
-        x = tanhf(x) * (1.0f / (1.0f + expf(-y)));
-      } else {
-        if (ep.bias) x += __ldg(ep.bias + c.pcol + k);
-        if (gb) x += __ldg(gb + c.pcol + k);
-        x = act_fn<ACT>(x);
+      for (int i = 0; i < 4; ++i) v[i] += __ldg(gb + c.pcol + 4 * j + i);
+    }
+    if (ACT == B200SVS_ACT_GATE) {
+      float4 b2 = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (c.bias_s) b2 = *reinterpret_cast<const float4*>(c.bias_s + c.pcol + c.gate_off + 4 * j);
+      float y[4] = {__uint_as_float(acc2[4 * j]) + b2.x, __uint_as_float(acc2[4 * j + 1]) + b2.y,
+                    __uint_as_float(acc2[4 * j + 2]) + b2.z, __uint_as_float(acc2[4 * j + 3]) + b2.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (gb) y[i] += __ldg(gb + c.pcol + c.gate_off + 4 * j + i);
+        v[i] = tanhf(v[i]) * (1.0f / (1.0f + expf(-y[i])));
       }
-      v[i] = x * ep.alpha;
+    } else {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) v[i] = act_fn<ACT>(v[i]);
     }
     const int phys = (j ^ (c.row & 7)) << 4;
-    if (has_res1) {
-      const float4 q = *reinterpret_cast<const float4*>(row32 + phys);
-      v[0] += q.x; v[1] += q.y; v[2] += q.z; v[3] += q.w;
-    }
+    float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (has_res1) r = *reinterpret_cast<const float4*>(row32 + phys);
     if (has_res2) {
       const float4 q = *reinterpret_cast<const float4*>(row32 + c.slot_r2_off + phys);
-      v[0] += q.x; v[1] += q.y; v[2] += q.z; v[3] += q.w;
+      r.x += q.x; r.y += q.y; r.z += q.z; r.w += q.w;
     }
-#pragma unroll
-    for (int i = 0; i < 4; ++i) v[i] *= s;
+    // (alpha * v + res1 + res2) * scale * mask
+    v[0] = fmaf(v[0], alpha, r.x) * s; v[1] = fmaf(v[1], alpha, r.y) * s;
+    v[2] = fmaf(v[2], alpha, r.z) * s; v[3] = fmaf(v[3], alpha, r.w) * s;
     if (c.need32) *reinterpret_cast<float4*>(row32 + phys) = make_float4(v[0], v[1], v[2], v[3]);
-    if (ep.out16) {
-      if (ep.post_lrelu) {
+    if (lre) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) v[i] = lrelu(v[i], ep.post_slope);
-      }
-      p16[2 * j] = pack16(v[0], v[1], ep.out16_dtype);
-      p16[2 * j + 1] = pack16(v[2], v[3], ep.out16_dtype);
+      for (int i = 0; i < 4; ++i) v[i] = fmaxf(v[i], v[i] * slope);     // leaky-ReLU, 0 < slope < 1
     }
+    p16[2 * j] = pack16(v[0], v[1], odt);
+    p16[2 * j + 1] = pack16(v[2], v[3], odt);
   }
   if (ep.out16) {
     uint8_t* row16 = c.slot + c.slot16_off + c.row * 64;
@@ -153,6 +164,20 @@ __device__ __forceinline__ void epi_chunk(const EpiCtx& c, const uint32_t* acc, 
           make_uint4(p16[4 * j], p16[4 * j + 1], p16[4 * j + 2], p16[4 * j + 3]);
   }
 }
+
+template <bool RES>
+__device__ __forceinline__ void epi_dispatch(const EpiCtx& c, int act, const uint32_t* r0, const uint32_t* r1) {
+  switch (act) {
+    case B200SVS_ACT_GATE: epi_chunk<B200SVS_ACT_GATE, RES>(c, r0, r1); break;
+    case B200SVS_ACT_RELU: epi_chunk<B200SVS_ACT_RELU, RES>(c, r0, r0); break;
+    case B200SVS_ACT_GELU: epi_chunk<B200SVS_ACT_GELU, RES>(c, r0, r0); break;
+    case B200SVS_ACT_SIGMOID: epi_chunk<B200SVS_ACT_SIGMOID, RES>(c, r0, r0); break;
+    case B200SVS_ACT_TANH: epi_chunk<B200SVS_ACT_TANH, RES>(c, r0, r0); break;
+    default: epi_chunk<B200SVS_ACT_NONE, RES>(c, r0, r0); break;
+  }
+}
+
+static_assert(sizeof(TcBarriers) <= 512, "barrier block must fit its 512-byte reservation");
 
 struct TileCoord {
   int n_idx, b, t0;
@@ -177,6 +202,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint8_t* smW = smA + kAStages * p.a_stage_bytes;
   uint8_t* smE = smW + p.w_stages * p.w_stage_bytes;
   TcBarriers* bars = reinterpret_cast<TcBarriers*>(smE + p.n_slots * p.slot_bytes);
+  float* bias_s = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);   // [cout_pad]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -195,7 +221,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kAStages; ++s) { mbar_init(&bars->a_full[s], 1); mbar_init(&bars->a_empty[s], 1); }
     for (int s = 0; s < p.w_stages; ++s) { mbar_init(&bars->w_full[s], 1); mbar_init(&bars->w_empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], 4); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], 4 * kEpiGroups); }
     for (int s = 0; s < p.n_slots; ++s) { mbar_init(&bars->e_full[s], 1); mbar_init(&bars->e_empty[s], 1); }
     fence_barrier_init();
   }
@@ -203,6 +229,8 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     tmem_alloc(&bars->tmem_base, p.tmem_cols);
     tmem_relinquish();
   }
+  if (p.ep.bias)
+    for (int i = threadIdx.x; i < p.cout_pad; i += kTcThreads) bias_s[i] = __ldg(p.ep.bias + i);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -236,36 +264,38 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // ------------------------------------------------------------ MMA issuer
-      int as = 0, ws = 0, it = 0;
-      uint32_t aph = 0, wph = 0;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-        const int acc = it & 1;
-        mbar_wait(&bars->tmem_empty[acc], ((it >> 1) & 1) ^ 1);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * acc_cols;
-        for (int ch = 0; ch < p.nchunks; ++ch) {
-          mbar_wait(&bars->a_full[as], aph);
-          const uint32_t sa = smem_u32(smA + as * p.a_stage_bytes);
-          for (int tap = 0; tap < p.ntaps; ++tap) {
-            mbar_wait(&bars->w_full[ws], wph);
-            tc_fence_after();
-            const uint64_t db = make_desc_k128(smem_u32(smW + ws * p.w_stage_bytes));
-            for (int ms = 0; ms < p.msub; ++ms) {
-              const uint64_t da = make_desc_k128(sa + (ms * 128 + tap * p.dil) * kRowBytes);
-#pragma unroll
-              for (int k = 0; k < kBlockK / 16; ++k)
-                umma_f16(d_tmem + ms * p.block_n, da + 2 * k, db + 2 * k, p.idesc, (ch | tap | k) != 0);
-            }
-            umma_commit(&bars->w_empty[ws]);
-            if (++ws == p.w_stages) { ws = 0; wph ^= 1; }
+    // -------------------------------------------------------------- MMA issuer (whole warp, convergent;
+    // one elected lane issues inside umma_*_warp)
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t smA_u = __shfl_sync(0xffffffffu, smem_u32(smA), 0);
+    const uint32_t smW_u = __shfl_sync(0xffffffffu, smem_u32(smW), 0);
+    const int ksub = p.ksub;          // K=16 steps per 64-channel chunk that hold real channels
+    int as = 0, ws = 0, it = 0;
+    uint32_t aph = 0, wph = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      mbar_wait(&bars->tmem_empty[acc], ((it >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_u + acc * acc_cols;
+      for (int ch = 0; ch < p.nchunks; ++ch) {
+        mbar_wait(&bars->a_full[as], aph);
+        const uint32_t sa = smA_u + as * p.a_stage_bytes;
+        for (int tap = 0; tap < p.ntaps; ++tap) {
+          mbar_wait(&bars->w_full[ws], wph);
+          tc_fence_after();
+          const uint64_t db = make_desc_k128(smW_u + ws * p.w_stage_bytes);
+          for (int ms = 0; ms < p.msub; ++ms) {
+            const uint64_t da = make_desc_k128(sa + (ms * 128 + tap * p.dil) * kRowBytes);
+            for (int k = 0; k < ksub; ++k)
+              umma_f16_warp(d_tmem + ms * p.block_n, da + 2 * k, db + 2 * k, p.idesc, (ch | tap | k) != 0);
           }
-          umma_commit(&bars->a_empty[as]);
-          if (++as == kAStages) { as = 0; aph ^= 1; }
+          umma_commit_warp(&bars->w_empty[ws]);
+          if (++ws == p.w_stages) { ws = 0; wph ^= 1; }
         }
-        umma_commit(&bars->tmem_full[acc]);
+        umma_commit_warp(&bars->a_empty[as]);
+        if (++as == kAStages) { as = 0; aph ^= 1; }
       }
+      umma_commit_warp(&bars->tmem_full[acc]);
     }
   } else if (warp == 3) {
     if (lane == 0) {
@@ -297,12 +327,15 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int row = q * 32 + lane;
     const bool gate = ep.act == B200SVS_ACT_GATE;
     const int half_n = p.block_n >> 1;
-    const bool leader = threadIdx.x == 4 * 32;
-    int it = 0, sl = 0, free_sl = 0, n_done = 0;
+    const int wg = (warp - 4) >> 2;                       // epilogue warpgroup: owns chunks i with i % kEpiGroups == wg
+    const bool leader = (threadIdx.x & 127) == 0;
+    int it = 0, sl = 0, n_done = 0, ci = 0;
+    int free_sl = wg % p.n_slots;                         // slot of this group's oldest un-recycled chunk
     uint32_t eph = 0;
     EpiCtx c;
     c.ep = &ep; c.slot16_off = p.slot16_off; c.slot_r2_off = p.slot_r2_off; c.row = row; c.T = p.T; c.need32 = ep.out32 != nullptr;
     c.gate_off = half_n;
+    c.bias_s = ep.bias ? bias_s : nullptr;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
       const int acc = it & 1;
       const TileCoord tc = tile_coord(p, tile);
@@ -316,7 +349,11 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         c.row_ok = c.t < p.T;
         c.row_live = c.t < len_b;
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * acc_cols + ms * p.block_n;
-        for (int ch = 0; ch < p.chunks_per_sub; ++ch) {
+        for (int ch = 0; ch < p.chunks_per_sub; ++ch, ++ci) {
+          if (ci % kEpiGroups != wg) {
+            if (++sl == p.n_slots) { sl = 0; eph ^= 1; }
+            continue;
+          }
           uint32_t r0[32], r1[32];
           const int pc = gate ? ch * kEpiCols : ch * kEpiCols;
           tmem_ld32_nowait(taddr + pc, r0);
@@ -327,17 +364,11 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           mbar_wait(&bars->e_full[sl], eph);
           tmem_ld_wait();
           if (tsub < p.T) {
-            switch (ep.act) {
-              case B200SVS_ACT_GATE: epi_chunk<B200SVS_ACT_GATE>(c, r0, r1); break;
-              case B200SVS_ACT_RELU: epi_chunk<B200SVS_ACT_RELU>(c, r0, r0); break;
-              case B200SVS_ACT_GELU: epi_chunk<B200SVS_ACT_GELU>(c, r0, r0); break;
-              case B200SVS_ACT_SIGMOID: epi_chunk<B200SVS_ACT_SIGMOID>(c, r0, r0); break;
-              case B200SVS_ACT_TANH: epi_chunk<B200SVS_ACT_TANH>(c, r0, r0); break;
-              default: epi_chunk<B200SVS_ACT_NONE>(c, r0, r0); break;
-            }
+            if (has_res1 || has_res2) epi_dispatch<true>(c, ep.act, r0, r1);
+            else epi_dispatch<false>(c, ep.act, r0, r1);
           }
           fence_proxy_async();
-          named_bar_sync(1, kEpiThreads);
+          named_bar_sync(1 + wg, kEpiThreads);
           if (leader) {
             if (tsub < p.T) {
               if (ep.out32) tma_store_3d(&tmO32, c.slot, c.ocol, tsub, tc.b);
@@ -357,7 +388,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
             if (++n_done > p.stores_in_flight) {
               mbar_arrive(&bars->e_empty[free_sl]);
-              if (++free_sl == p.n_slots) free_sl = 0;
+              free_sl = (free_sl + kEpiGroups) % p.n_slots;
             }
           }
           if (++sl == p.n_slots) { sl = 0; eph ^= 1; }
@@ -438,7 +469,8 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   p.slot_bytes = p.slot16_off + (ep.out16 ? kSlot16Bytes : 0);
   // shared memory: 2 activation stages, >= 3 weight stages (or all k-steps of a tile if fewer), then as many
   // staging slots as fit (stores in flight + residual prefetch), the rest to weight stages
-  const int budget = max_smem_optin() - 1024 - 1024;   // alignment slack + barriers
+  const int bias_bytes = ep.bias ? a->Cout_pad * 4 : 0;
+  const int budget = max_smem_optin() - 1024 - 1024 - bias_bytes;   // alignment slack + barriers + bias
   const int ksteps = a->ntaps * p.nchunks;
   int w_min = ksteps < 3 ? ksteps : 3;
   if (w_min < 2) w_min = 2;
@@ -452,8 +484,13 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   p.n_slots = n_slots;
   p.w_stages = w_stages;
   // with a residual, about half of the slots hold prefetched residual tiles, the other half are stores in flight
-  p.stores_in_flight = (ep.res1 || ep.res2) ? (n_slots - 1) / 2 : n_slots - 1;
+  // per epilogue group: chunk i's slot is needed again by chunk i + n_slots, so a group may keep at most
+  // (n_slots - 2) / 2 of its own store groups pending; with a residual half of that, the rest of the slots
+  // then hold prefetched residual tiles
+  p.stores_in_flight = (n_slots - 2) / kEpiGroups;
+  if (ep.res1 || ep.res2) p.stores_in_flight /= 2;
   p.tmem_cols = next_pow2_cols(2 * p.msub * a->block_n);
+  p.ksub = a->Cin >= kBlockK ? 4 : (a->Cin + 15) / 16;
   p.idesc = make_idesc_f16(128, a->block_n, a->x_dtype == B200SVS_DT_BF16);
   p.ep = ep;
 
@@ -498,7 +535,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   }
 
   const size_t smem = (size_t)kAStages * p.a_stage_bytes + (size_t)p.w_stages * p.w_stage_bytes +
-                      (size_t)p.n_slots * p.slot_bytes + sizeof(TcBarriers) + 1024;
+                      (size_t)p.n_slots * p.slot_bytes + 512 + bias_bytes + 1024;
   static size_t configured = 0;
   if (smem > configured) {
     int r = check_cuda(cudaFuncSetAttribute(conv1d_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
