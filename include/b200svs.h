@@ -45,7 +45,10 @@ enum {
   B200SVS_ACT_GATE = 5     /* tanh(a)*sigmoid(b): commons.fused_add_tanh_sigmoid_multiply (commons.py:100-107);
                               packed weight tile columns [0,N/2) = tanh half, [N/2,N) = sigmoid half */
 };
-enum { B200SVS_DT_F16 = 0, B200SVS_DT_BF16 = 1 };
+/* B200SVS_DT_F16_SPLIT (16-bit OUTPUTS only): the destination has 3x the columns, laid out [hi | lo | hi]
+ * with hi = fp16(v), lo = fp16(v - hi).  A conv whose weights are packed [w_hi | w_hi | w_lo] along Cin then
+ * computes x_hi.w_hi + x_lo.w_hi + x_hi.w_lo: tensor-core speed at fp32-class accuracy (F0 predictor). */
+enum { B200SVS_DT_F16 = 0, B200SVS_DT_BF16 = 1, B200SVS_DT_F16_SPLIT = 2 };
 
 /* Fused epilogue shared by the conv1d kernels.  For output row (b,t) and packed column c:
  *   v = acc + bias[c] + gbias[b*gbias_ld + c]

@@ -131,6 +131,7 @@ extern "C" int b200svs_conv1d_f32(const b200svs_conv_args* a, void* stream) {
   B200SVS_REQUIRE((reinterpret_cast<uintptr_t>(a->w) & 15) == 0, "conv1d_f32: w must be 16-B aligned");
   B200SVS_REQUIRE(a->ep.act != B200SVS_ACT_GATE, "conv1d_f32: GATE epilogue is tensor-core only");
   B200SVS_REQUIRE(a->ep.out32 || a->ep.out16, "conv1d_f32: no output");
+  B200SVS_REQUIRE(!a->ep.out16 || a->ep.out16_dtype != B200SVS_DT_F16_SPLIT, "conv1d_f32: split 16-bit output is tensor-core only");
   B200SVS_REQUIRE(a->ep.n_valid > 0 && a->ep.n_valid <= a->Cout_pad, "conv1d_f32: n_valid=%d", a->ep.n_valid);
   ConvF32Params p;
   p.x = static_cast<const float*>(a->x);

@@ -20,7 +20,7 @@
 //   warp 1 lane 0 : tcgen05.mma issuer (accumulators double-buffered in TMEM)
 //   warp 2        : TMEM alloc / dealloc
 //   warp 3 lane 0 : TMA producer of the epilogue staging slots (residual tiles)
-//   warps 4..11   : epilogue, two warpgroups taking alternate 32-column chunks
+//   warps 4..11   : epilogue; warp w and w+4 share a TMEM lane quadrant and split each 32-column chunk 16/16
 //
 // Replaces: nn.Conv1d/ConvTranspose1d + surrounding pointwise ops of the reference
 // (VISinger/models_ae.py:327-346, modules.py:148-176,210-223,329-349, attentions.py:138-146,277-285).
@@ -37,9 +37,8 @@ constexpr int kMaxSlots = 8;
 constexpr int kEpiCols = 32;               // output columns per epilogue chunk
 constexpr int kSlot32Bytes = 128 * kEpiCols * 4;   // 16 KB: [128 rows][32 fp32], SWIZZLE_128B
 constexpr int kSlot16Bytes = 128 * kEpiCols * 2;   //  8 KB: [128 rows][32 x 16-bit], SWIZZLE_64B
-constexpr int kEpiGroups = 1;               // epilogue warpgroups (4 warps each), chunks alternate between them
-constexpr int kTcThreads = 128 + kEpiGroups * 128;
-constexpr int kEpiThreads = 128;
+constexpr int kEpiThreads = 256;            // 8 epilogue warps
+constexpr int kTcThreads = 128 + kEpiThreads;
 
 struct ConvTcParams {
   int T, tiles_t, m_tiles, n_tiles, total_tiles;
@@ -84,96 +83,150 @@ __device__ __forceinline__ uint32_t pack16(float a, float b, int dtype) {
 
 struct EpiCtx {
   const b200svs_epilogue* ep;
-  uint8_t* slot;          // staging slot base (fp32 area); 16-bit area at slot + slot16_off
+  uint32_t slot;          // shared-space address of the staging slot (fp32 area); 16-bit area at + slot16_off
   int slot16_off, slot_r2_off;
   int row;                // row inside the 128-row sub-tile (= TMEM lane)
-  int b, t, T;            // batch index, global time row, rows per batch element
-  int pcol;               // first packed accumulator column of this chunk (bias / gbias index)
-  int ocol;               // first output column of this chunk
+  int half;               // which 16 of the chunk's 32 columns this thread owns (0 / 1)
+  int b;                  // batch index
+  int pcol;               // first packed accumulator column of this thread's 16 (bias / gbias index)
   int gate_off;           // GATE: packed-column distance between the tanh and the sigmoid half
-  bool row_ok, row_live;
+  bool row_live;
   bool need32;            // fp32 area is stored (out32 != NULL)
   const float* bias_s;    // bias staged in shared memory (NULL: no bias)
 };
 
-// One chunk of 32 output columns for one row.  acc[] holds the raw accumulator bits (for GATE: acc =
-// tanh half, acc2 = sigmoid half).  Static indexing only: everything stays in registers.  The bias lives
-// in shared memory (bias_s, indexed by packed column) and is read with broadcast 128-bit loads.
-template <int ACT, bool RES>
+__device__ __forceinline__ float4 lds128(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t a, float4 v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void sts128u(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+}
+template <bool BF>
+__device__ __forceinline__ uint32_t pack2(float a, float b) {
+  if (BF) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+  __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// 16 output columns of one row.  acc[] = raw accumulator bits (GATE: acc = tanh half, acc2 = sigmoid half).
+// Static indexing only (registers).  PLAIN: alpha == scale == 1, no sequence mask, no speaker bias - the
+// Generator's case - so the affine / mask arithmetic disappears.  BF: 16-bit output is bf16.  SPLIT: [hi|lo|hi].
+template <int ACT, bool RES, bool PLAIN, bool BF, bool SPLIT>
 __device__ __forceinline__ void epi_chunk(const EpiCtx& c, const uint32_t* acc, const uint32_t* acc2) {
   const b200svs_epilogue& ep = *c.ep;
-  const float* gb = ep.gbias ? ep.gbias + static_cast<size_t>(c.b) * ep.gbias_ld : nullptr;
+  const float* gb = (!PLAIN && ep.gbias) ? ep.gbias + static_cast<size_t>(c.b) * ep.gbias_ld : nullptr;
   const float s = c.row_live ? ep.scale : 0.0f;
   const float alpha = ep.alpha;
   const bool has_res1 = RES && ep.res1 != nullptr;
   const bool has_res2 = RES && ep.res2 != nullptr;
   const bool lre = ep.post_lrelu != 0;
   const float slope = ep.post_slope;
-  const int odt = ep.out16_dtype;
-  uint8_t* row32 = c.slot + c.row * 128;
-  uint32_t p16[16];
+  const uint32_t row32 = c.slot + c.row * 128;
+  uint32_t p16[8];
+  uint32_t l16[SPLIT ? 8 : 1];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
+  for (int jj = 0; jj < 4; ++jj) {
+    const int j = c.half * 4 + jj;                 // 16-byte chunk index inside the 128-byte fp32 row
     float v[4];
     float4 bq = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (c.bias_s) bq = *reinterpret_cast<const float4*>(c.bias_s + c.pcol + 4 * j);
-    v[0] = __uint_as_float(acc[4 * j]) + bq.x; v[1] = __uint_as_float(acc[4 * j + 1]) + bq.y;
-    v[2] = __uint_as_float(acc[4 * j + 2]) + bq.z; v[3] = __uint_as_float(acc[4 * j + 3]) + bq.w;
+    if (c.bias_s) bq = *reinterpret_cast<const float4*>(c.bias_s + c.pcol + 4 * jj);
+    v[0] = __uint_as_float(acc[4 * jj]) + bq.x; v[1] = __uint_as_float(acc[4 * jj + 1]) + bq.y;
+    v[2] = __uint_as_float(acc[4 * jj + 2]) + bq.z; v[3] = __uint_as_float(acc[4 * jj + 3]) + bq.w;
     if (gb) {
 #pragma unroll
-      for (int i = 0; i < 4; ++i) v[i] += __ldg(gb + c.pcol + 4 * j + i);
+      for (int i = 0; i < 4; ++i) v[i] += __ldg(gb + c.pcol + 4 * jj + i);
     }
     if (ACT == B200SVS_ACT_GATE) {
       float4 b2 = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (c.bias_s) b2 = *reinterpret_cast<const float4*>(c.bias_s + c.pcol + c.gate_off + 4 * j);
-      float y[4] = {__uint_as_float(acc2[4 * j]) + b2.x, __uint_as_float(acc2[4 * j + 1]) + b2.y,
-                    __uint_as_float(acc2[4 * j + 2]) + b2.z, __uint_as_float(acc2[4 * j + 3]) + b2.w};
+      if (c.bias_s) b2 = *reinterpret_cast<const float4*>(c.bias_s + c.pcol + c.gate_off + 4 * jj);
+      float y[4] = {__uint_as_float(acc2[4 * jj]) + b2.x, __uint_as_float(acc2[4 * jj + 1]) + b2.y,
+                    __uint_as_float(acc2[4 * jj + 2]) + b2.z, __uint_as_float(acc2[4 * jj + 3]) + b2.w};
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        if (gb) y[i] += __ldg(gb + c.pcol + c.gate_off + 4 * j + i);
+        if (gb) y[i] += __ldg(gb + c.pcol + c.gate_off + 4 * jj + i);
         v[i] = tanhf(v[i]) * (1.0f / (1.0f + expf(-y[i])));
       }
     } else {
 #pragma unroll
       for (int i = 0; i < 4; ++i) v[i] = act_fn<ACT>(v[i]);
     }
-    const int phys = (j ^ (c.row & 7)) << 4;
+    const uint32_t phys = (j ^ (c.row & 7)) << 4;
     float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (has_res1) r = *reinterpret_cast<const float4*>(row32 + phys);
+    if (has_res1) r = lds128(row32 + phys);
     if (has_res2) {
-      const float4 q = *reinterpret_cast<const float4*>(row32 + c.slot_r2_off + phys);
+      const float4 q = lds128(row32 + c.slot_r2_off + phys);
       r.x += q.x; r.y += q.y; r.z += q.z; r.w += q.w;
     }
-    // (alpha * v + res1 + res2) * scale * mask
-    v[0] = fmaf(v[0], alpha, r.x) * s; v[1] = fmaf(v[1], alpha, r.y) * s;
-    v[2] = fmaf(v[2], alpha, r.z) * s; v[3] = fmaf(v[3], alpha, r.w) * s;
-    if (c.need32) *reinterpret_cast<float4*>(row32 + phys) = make_float4(v[0], v[1], v[2], v[3]);
+    if (PLAIN) {
+      if (RES) { v[0] += r.x; v[1] += r.y; v[2] += r.z; v[3] += r.w; }
+    } else {   // (alpha * v + res1 + res2) * scale * mask
+      v[0] = fmaf(v[0], alpha, r.x) * s; v[1] = fmaf(v[1], alpha, r.y) * s;
+      v[2] = fmaf(v[2], alpha, r.z) * s; v[3] = fmaf(v[3], alpha, r.w) * s;
+    }
+    if (c.need32) sts128(row32 + phys, make_float4(v[0], v[1], v[2], v[3]));
     if (lre) {
 #pragma unroll
       for (int i = 0; i < 4; ++i) v[i] = fmaxf(v[i], v[i] * slope);     // leaky-ReLU, 0 < slope < 1
     }
-    p16[2 * j] = pack16(v[0], v[1], odt);
-    p16[2 * j + 1] = pack16(v[2], v[3], odt);
+    p16[2 * jj] = pack2<BF>(v[0], v[1]);
+    p16[2 * jj + 1] = pack2<BF>(v[2], v[3]);
+    if constexpr (SPLIT) {   // lo = v - hi, so that hi + lo == v to ~2^-22
+#pragma unroll
+      for (int i = 0; i < 4; ++i) v[i] -= __half2float(__float2half_rn(v[i]));
+      l16[2 * jj] = pack2<false>(v[0], v[1]);
+      l16[2 * jj + 1] = pack2<false>(v[2], v[3]);
+    }
   }
   if (ep.out16) {
-    uint8_t* row16 = c.slot + c.slot16_off + c.row * 64;
+    const uint32_t row16 = c.slot + c.slot16_off + c.row * 64;
     const int sw = (c.row >> 1) & 3;     // SWIZZLE_64B: 16-B chunk index ^= address bits [7:8]
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
-      *reinterpret_cast<uint4*>(row16 + ((j ^ sw) << 4)) =
-          make_uint4(p16[4 * j], p16[4 * j + 1], p16[4 * j + 2], p16[4 * j + 3]);
+    for (int jj = 0; jj < 2; ++jj) {
+      const uint32_t off = ((c.half * 2 + jj) ^ sw) << 4;
+      sts128u(row16 + off, p16[4 * jj], p16[4 * jj + 1], p16[4 * jj + 2], p16[4 * jj + 3]);
+      if constexpr (SPLIT) sts128u(row16 + kSlot16Bytes + off, l16[4 * jj], l16[4 * jj + 1], l16[4 * jj + 2], l16[4 * jj + 3]);
+    }
   }
 }
 
-template <bool RES>
-__device__ __forceinline__ void epi_dispatch(const EpiCtx& c, int act, const uint32_t* r0, const uint32_t* r1) {
+template <bool RES, bool BF>
+__device__ __forceinline__ void epi_dispatch2(const EpiCtx& c, int act, bool plain, bool split, const uint32_t* r0,
+                                              const uint32_t* r1) {
+  if (split) {   // host restricts split outputs to NONE / RELU, fp16
+    if (act == B200SVS_ACT_RELU) epi_chunk<B200SVS_ACT_RELU, RES, false, false, true>(c, r0, r0);
+    else epi_chunk<B200SVS_ACT_NONE, RES, false, false, true>(c, r0, r0);
+    return;
+  }
   switch (act) {
-    case B200SVS_ACT_GATE: epi_chunk<B200SVS_ACT_GATE, RES>(c, r0, r1); break;
-    case B200SVS_ACT_RELU: epi_chunk<B200SVS_ACT_RELU, RES>(c, r0, r0); break;
-    case B200SVS_ACT_GELU: epi_chunk<B200SVS_ACT_GELU, RES>(c, r0, r0); break;
-    case B200SVS_ACT_SIGMOID: epi_chunk<B200SVS_ACT_SIGMOID, RES>(c, r0, r0); break;
-    case B200SVS_ACT_TANH: epi_chunk<B200SVS_ACT_TANH, RES>(c, r0, r0); break;
-    default: epi_chunk<B200SVS_ACT_NONE, RES>(c, r0, r0); break;
+    case B200SVS_ACT_GATE: epi_chunk<B200SVS_ACT_GATE, RES, false, BF, false>(c, r0, r1); break;
+    case B200SVS_ACT_RELU: epi_chunk<B200SVS_ACT_RELU, RES, false, BF, false>(c, r0, r0); break;
+    case B200SVS_ACT_GELU: epi_chunk<B200SVS_ACT_GELU, RES, false, BF, false>(c, r0, r0); break;
+    case B200SVS_ACT_SIGMOID: epi_chunk<B200SVS_ACT_SIGMOID, RES, false, BF, false>(c, r0, r0); break;
+    case B200SVS_ACT_TANH: epi_chunk<B200SVS_ACT_TANH, RES, false, BF, false>(c, r0, r0); break;
+    default:
+      if (plain) epi_chunk<B200SVS_ACT_NONE, RES, true, BF, false>(c, r0, r0);
+      else epi_chunk<B200SVS_ACT_NONE, RES, false, BF, false>(c, r0, r0);
+      break;
+  }
+}
+__device__ __forceinline__ void epi_dispatch(const EpiCtx& c, int act, bool res, bool plain, const uint32_t* r0,
+                                             const uint32_t* r1) {
+  const bool split = c.ep->out16 && c.ep->out16_dtype == B200SVS_DT_F16_SPLIT;
+  const bool bf = c.ep->out16_dtype == B200SVS_DT_BF16;
+  if (res) {
+    if (bf) epi_dispatch2<true, true>(c, act, plain, split, r0, r1);
+    else epi_dispatch2<true, false>(c, act, plain, split, r0, r1);
+  } else {
+    if (bf) epi_dispatch2<false, true>(c, act, plain, split, r0, r1);
+    else epi_dispatch2<false, false>(c, act, plain, split, r0, r1);
   }
 }
 
@@ -221,7 +274,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kAStages; ++s) { mbar_init(&bars->a_full[s], 1); mbar_init(&bars->a_empty[s], 1); }
     for (int s = 0; s < p.w_stages; ++s) { mbar_init(&bars->w_full[s], 1); mbar_init(&bars->w_empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], 4 * kEpiGroups); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], kEpiThreads / 32); }
     for (int s = 0; s < p.n_slots; ++s) { mbar_init(&bars->e_full[s], 1); mbar_init(&bars->e_empty[s], 1); }
     fence_barrier_init();
   }
@@ -284,18 +337,23 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           mbar_wait(&bars->w_full[ws], wph);
           tc_fence_after();
           const uint64_t db = make_desc_k128(smW_u + ws * p.w_stage_bytes);
-          for (int ms = 0; ms < p.msub; ++ms) {
-            const uint64_t da = make_desc_k128(sa + (ms * 128 + tap * p.dil) * kRowBytes);
-            for (int k = 0; k < ksub; ++k)
-              umma_f16_warp(d_tmem + ms * p.block_n, da + 2 * k, db + 2 * k, p.idesc, (ch | tap | k) != 0);
+          if (elect_one()) {     // single-thread region: descriptors live in uniform registers
+            for (int ms = 0; ms < p.msub; ++ms) {
+              const uint64_t da = make_desc_k128(sa + (ms * 128 + tap * p.dil) * kRowBytes);
+              for (int k = 0; k < ksub; ++k)
+                umma_f16(d_tmem + ms * p.block_n, da + 2 * k, db + 2 * k, p.idesc, (ch | tap | k) != 0);
+            }
+            umma_commit(&bars->w_empty[ws]);
           }
-          umma_commit_warp(&bars->w_empty[ws]);
+          __syncwarp();
           if (++ws == p.w_stages) { ws = 0; wph ^= 1; }
         }
-        umma_commit_warp(&bars->a_empty[as]);
+        if (elect_one()) umma_commit(&bars->a_empty[as]);
+        __syncwarp();
         if (++as == kAStages) { as = 0; aph ^= 1; }
       }
-      umma_commit_warp(&bars->tmem_full[acc]);
+      if (elect_one()) umma_commit(&bars->tmem_full[acc]);
+      __syncwarp();
     }
   } else if (warp == 3) {
     if (lane == 0) {
@@ -322,20 +380,24 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else if (warp >= 4) {
-    // -------------------------------------------------------------- epilogue
+    // -------------------------------------------------------------- epilogue: 8 warps; warp w and w + 4 share
+    // TMEM lane quadrant w % 4 and split each 32-column chunk 16 / 16 (two warps per scheduler hide latency)
     const int q = warp & 3;
     const int row = q * 32 + lane;
+    const int half = (warp - 4) >> 2;
     const bool gate = ep.act == B200SVS_ACT_GATE;
     const int half_n = p.block_n >> 1;
-    const int wg = (warp - 4) >> 2;                       // epilogue warpgroup: owns chunks i with i % kEpiGroups == wg
-    const bool leader = (threadIdx.x & 127) == 0;
-    int it = 0, sl = 0, n_done = 0, ci = 0;
-    int free_sl = wg % p.n_slots;                         // slot of this group's oldest un-recycled chunk
+    const bool leader = threadIdx.x == 128;
+    const bool res = has_res1 || has_res2;
+    const bool plain = ep.alpha == 1.0f && ep.scale == 1.0f && ep.lens == nullptr && ep.gbias == nullptr;
+    int it = 0, sl = 0, n_done = 0, free_sl = 0;
     uint32_t eph = 0;
     EpiCtx c;
-    c.ep = &ep; c.slot16_off = p.slot16_off; c.slot_r2_off = p.slot_r2_off; c.row = row; c.T = p.T; c.need32 = ep.out32 != nullptr;
+    c.ep = &ep; c.slot16_off = p.slot16_off; c.slot_r2_off = p.slot_r2_off; c.row = row; c.half = half;
+    c.need32 = ep.out32 != nullptr;
     c.gate_off = half_n;
     c.bias_s = ep.bias ? bias_s : nullptr;
+    const uint32_t smE_u = smem_u32(smE);
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
       const int acc = it & 1;
       const TileCoord tc = tile_coord(p, tile);
@@ -345,34 +407,30 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       tc_fence_after();
       for (int ms = 0; ms < p.msub; ++ms) {
         const int tsub = tc.t0 + ms * 128;
-        c.t = tsub + row;
-        c.row_ok = c.t < p.T;
-        c.row_live = c.t < len_b;
+        c.row_live = tsub + row < len_b;
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * acc_cols + ms * p.block_n;
-        for (int ch = 0; ch < p.chunks_per_sub; ++ch, ++ci) {
-          if (ci % kEpiGroups != wg) {
-            if (++sl == p.n_slots) { sl = 0; eph ^= 1; }
-            continue;
-          }
-          uint32_t r0[32], r1[32];
-          const int pc = gate ? ch * kEpiCols : ch * kEpiCols;
-          tmem_ld32_nowait(taddr + pc, r0);
-          if (gate) tmem_ld32_nowait(taddr + half_n + pc, r1);
+        for (int ch = 0; ch < p.chunks_per_sub; ++ch) {
+          uint32_t r0[16], r1[16];
+          const int pc = ch * kEpiCols + half * 16;
+          tmem_ld16_nowait(taddr + pc, r0);
+          if (gate) tmem_ld16_nowait(taddr + half_n + pc, r1);
           c.pcol = tc.n_idx * p.block_n + pc;
-          c.ocol = tc.n_idx * p.n_out_tile + ch * kEpiCols;
-          c.slot = smE + sl * p.slot_bytes;
+          const int ocol = tc.n_idx * p.n_out_tile + ch * kEpiCols;
+          c.slot = smE_u + sl * p.slot_bytes;
           mbar_wait(&bars->e_full[sl], eph);
           tmem_ld_wait();
-          if (tsub < p.T) {
-            if (has_res1 || has_res2) epi_dispatch<true>(c, ep.act, r0, r1);
-            else epi_dispatch<false>(c, ep.act, r0, r1);
-          }
+          if (tsub < p.T) epi_dispatch(c, ep.act, res, plain, r0, r1);
           fence_proxy_async();
-          named_bar_sync(1 + wg, kEpiThreads);
+          named_bar_sync(1, kEpiThreads);
           if (leader) {
             if (tsub < p.T) {
-              if (ep.out32) tma_store_3d(&tmO32, c.slot, c.ocol, tsub, tc.b);
-              if (ep.out16) tma_store_3d(&tmO16, c.slot + p.slot16_off, c.ocol, tsub, tc.b);
+              uint8_t* slot = smE + sl * p.slot_bytes;
+              if (ep.out32) tma_store_3d(&tmO32, slot, ocol, tsub, tc.b);
+              if (ep.out16) tma_store_3d(&tmO16, slot + p.slot16_off, ocol, tsub, tc.b);
+              if (ep.out16 && ep.out16_dtype == B200SVS_DT_F16_SPLIT) {   // [hi | lo | hi]
+                tma_store_3d(&tmO16, slot + p.slot16_off + kSlot16Bytes, ep.n_valid + ocol, tsub, tc.b);
+                tma_store_3d(&tmO16, slot + p.slot16_off, 2 * ep.n_valid + ocol, tsub, tc.b);
+              }
             }
             tma_store_commit();
             // keep `stores_in_flight` groups pending; the slot of the oldest completed one is recycled
@@ -388,7 +446,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
             if (++n_done > p.stores_in_flight) {
               mbar_arrive(&bars->e_empty[free_sl]);
-              free_sl = (free_sl + kEpiGroups) % p.n_slots;
+              if (++free_sl == p.n_slots) free_sl = 0;
             }
           }
           if (++sl == p.n_slots) { sl = 0; eph ^= 1; }
@@ -466,7 +524,10 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   p.slot_r2_off = ep.res2 ? (area32 ? kSlot32Bytes : 0) : 0;
   B200SVS_REQUIRE(!ep.res2 || area32, "conv1d_tc: res2 needs res1 or out32");
   p.slot16_off = (area32 ? kSlot32Bytes : 0) + (ep.res2 ? kSlot32Bytes : 0);
-  p.slot_bytes = p.slot16_off + (ep.out16 ? kSlot16Bytes : 0);
+  const bool split16 = ep.out16 && ep.out16_dtype == B200SVS_DT_F16_SPLIT;
+  B200SVS_REQUIRE(!split16 || ep.act == B200SVS_ACT_NONE || ep.act == B200SVS_ACT_RELU, "conv1d_tc: split 16-bit output supports act NONE / RELU");
+  B200SVS_REQUIRE(!split16 || ep.n_valid % kEpiCols == 0, "conv1d_tc: split 16-bit output needs n_valid %% 32 == 0 (n_valid=%d)", ep.n_valid);
+  p.slot_bytes = p.slot16_off + (ep.out16 ? kSlot16Bytes : 0) + (split16 ? kSlot16Bytes : 0);
   // shared memory: 2 activation stages, >= 3 weight stages (or all k-steps of a tile if fewer), then as many
   // staging slots as fit (stores in flight + residual prefetch), the rest to weight stages
   const int bias_bytes = ep.bias ? a->Cout_pad * 4 : 0;
@@ -487,8 +548,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   // per epilogue group: chunk i's slot is needed again by chunk i + n_slots, so a group may keep at most
   // (n_slots - 2) / 2 of its own store groups pending; with a residual half of that, the rest of the slots
   // then hold prefetched residual tiles
-  p.stores_in_flight = (n_slots - 2) / kEpiGroups;
-  if (ep.res1 || ep.res2) p.stores_in_flight /= 2;
+  p.stores_in_flight = (ep.res1 || ep.res2) ? (n_slots - 1) / 2 : n_slots - 1;
   p.tmem_cols = next_pow2_cols(2 * p.msub * a->block_n);
   p.ksub = a->Cin >= kBlockK ? 4 : (a->Cin + 15) / 16;
   p.idesc = make_idesc_f16(128, a->block_n, a->x_dtype == B200SVS_DT_BF16);
@@ -530,7 +590,8 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   }
   if (ep.out16) {
     uint64_t strides[2] = {(uint64_t)ep.out16_ld * 2, (uint64_t)a->T * ep.out16_ld * 2};
-    int r = make_tmap(&tmO16, ep.out16_dtype == B200SVS_DT_BF16 ? 1 : 0, ep.out16, 3, edims, strides, ebox, 64);
+    uint64_t odims[3] = {(uint64_t)ep.n_valid * (ep.out16_dtype == B200SVS_DT_F16_SPLIT ? 3 : 1), (uint64_t)a->T, (uint64_t)a->B};
+    int r = make_tmap(&tmO16, ep.out16_dtype == B200SVS_DT_BF16 ? 1 : 0, ep.out16, 3, odims, strides, ebox, 64);
     if (r) return r;
   }
 

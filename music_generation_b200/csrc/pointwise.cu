@@ -10,6 +10,15 @@ __device__ __forceinline__ void store16(void* base, size_t idx, float v, int dty
   if (dtype == B200SVS_DT_BF16) reinterpret_cast<__nv_bfloat16*>(base)[idx] = __float2bfloat16_rn(v);
   else reinterpret_cast<__half*>(base)[idx] = __float2half_rn(v);
 }
+// 16-bit store of column c of a C-column row at `row_off`; B200SVS_DT_F16_SPLIT writes [hi | lo | hi]
+__device__ __forceinline__ void store16c(void* base, size_t row_off, int c, int C, float v, int dtype) {
+  if (dtype != B200SVS_DT_F16_SPLIT) { store16(base, row_off + c, v, dtype); return; }
+  __half* o = reinterpret_cast<__half*>(base) + row_off;
+  const __half hi = __float2half_rn(v);
+  o[c] = hi;
+  o[C + c] = __float2half_rn(v - __half2float(hi));
+  o[2 * C + c] = hi;
+}
 __device__ __forceinline__ float load16(const void* base, size_t idx, int dtype) {
   if (dtype == B200SVS_DT_BF16) return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(base)[idx]);
   return __half2float(reinterpret_cast<const __half*>(base)[idx]);
@@ -60,7 +69,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LnParams p) {
       float y = (v[i] - mean) * rstd * p.gamma[c] + p.beta[c];
       if (!live) y = 0.f;
       if (p.out32) p.out32[row * p.out32_ld + c] = y;
-      if (p.out16) store16(p.out16, row * p.out16_ld + c, y, p.out16_dtype);
+      if (p.out16) store16c(p.out16, row * p.out16_ld, c, p.C, y, p.out16_dtype);
     }
   }
 }
@@ -162,7 +171,7 @@ __global__ void add_pos_mask_kernel(const float* x, int x_ld, const float* pos, 
     float v = x[row * x_ld + c] + pos[static_cast<size_t>(t) * C + c];
     if (lens && t >= lens[b]) v = 0.f;
     if (out32) out32[row * out32_ld + c] = v;
-    if (out16) store16(out16, row * out16_ld + c, v, dt);
+    if (out16) store16c(out16, row * out16_ld, c, C, v, dt);
   }
 }
 
