@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libb200svs.so")
 CSRC_DIR = os.path.join(_HERE, "csrc")
 
 ACT_NONE, ACT_RELU, ACT_GELU, ACT_SIGMOID, ACT_TANH, ACT_GATE = range(6)
-DT_F16, DT_BF16 = 0, 1
+DT_F16, DT_BF16, DT_F16_SPLIT = 0, 1, 2
 
 
 class Epilogue(C.Structure):

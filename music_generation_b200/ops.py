@@ -24,6 +24,17 @@ def _ptr(t):
     return None if t is None else C.c_void_p(t.data_ptr())
 
 
+def out16_code(t, split16):
+    """dtype code of a 16-bit OUTPUT tensor; split16: fp16 [hi | lo | hi] with 3x the logical columns."""
+    if t is None:
+        return 0
+    if split16:
+        if t.dtype != torch.float16:
+            raise TypeError("split 16-bit outputs are fp16")
+        return _lib.DT_F16_SPLIT
+    return dt_code(t.dtype)
+
+
 def dt_code(dtype):
     if dtype == torch.float16:
         return DT_F16
@@ -47,7 +58,7 @@ def _btc(t, name):
 class PackedConv:
     """Device-resident packed weights of one convolution (see packer.py)."""
     __slots__ = ("w", "bias", "ntaps", "dil", "pad_left", "cin", "cin_pad", "cout", "cout_pad", "block_n",
-                 "gate", "f32", "n_out", "alg_macs_per_row", "tag")
+                 "gate", "f32", "n_out", "alg_macs_per_row", "tag", "out_scale")
 
     def __init__(self, w, bias, ntaps, dil, pad_left, cin, cin_pad, cout, cout_pad, block_n, gate, f32):
         self.w, self.bias, self.ntaps, self.dil, self.pad_left = w, bias, ntaps, dil, pad_left
@@ -58,6 +69,7 @@ class PackedConv:
         # form executes 1.5x of that, packer.pack_conv_transpose overrides it) - used by bench.py only
         self.alg_macs_per_row = cin * cout * ntaps
         self.tag = ""
+        self.out_scale = 1.0        # split-precision convs: power-of-two factor folded into the epilogue's alpha
 
     def to(self, device):
         self.w = self.w.to(device)
@@ -66,7 +78,7 @@ class PackedConv:
 
 
 def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, res2=None, lens=None,
-           out32=None, out16=None, post_lrelu=None, w_rows=None, n_valid=None):
+           out32=None, out16=None, post_lrelu=None, w_rows=None, n_valid=None, split16=False):
     """out = epilogue(conv(x, pc)).  See b200svs_epilogue in include/b200svs.h for the formula.
     `w_rows=(row0, nrows)` restricts the conv to a block of packed output channels (WN res/skip split)."""
     B, T, cin = x.shape
@@ -97,7 +109,7 @@ def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, 
     if gbias is not None:
         e.gbias, e.gbias_ld = gbias.data_ptr(), gbias.stride(0)
     e.act = ACT_GATE if pc.gate else act
-    e.alpha, e.scale = alpha, scale
+    e.alpha, e.scale = alpha * pc.out_scale, scale
     if res1 is not None:
         e.res1, e.res1_ld = res1.data_ptr(), _btc(res1, "res1")
     if res2 is not None:
@@ -108,7 +120,7 @@ def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, 
     if out32 is not None:
         e.out32, e.out32_ld = out32.data_ptr(), _btc(out32, "out32")
     if out16 is not None:
-        e.out16, e.out16_ld, e.out16_dtype = out16.data_ptr(), _btc(out16, "out16"), dt_code(out16.dtype)
+        e.out16, e.out16_ld, e.out16_dtype = out16.data_ptr(), _btc(out16, "out16"), out16_code(out16, split16)
     if post_lrelu is not None:
         e.post_lrelu, e.post_slope = 1, float(post_lrelu)
     e.n_valid = n_out if n_valid is None else n_valid
@@ -159,11 +171,11 @@ def attention_tc(qkv, out32, out16, rel_k, rel_v, lens, *, dtype, split=False, o
               _ptr(lens), B, T, c, heads, window, _stream())
 
 
-def layernorm(x, gamma, beta, lens, out32=None, out16=None, res=None, eps=1e-5):
+def layernorm(x, gamma, beta, lens, out32=None, out16=None, res=None, eps=1e-5, split16=False):
     B, T, c = x.shape
     _lib.call("b200svs_layernorm", _ptr(x), _btc(x, "x"), _ptr(res), _btc(res, "res"), _ptr(gamma), _ptr(beta),
               eps, _ptr(lens), _ptr(out32), _btc(out32, "out32"), _ptr(out16), _btc(out16, "out16"),
-              0 if out16 is None else dt_code(out16.dtype), B, T, c, _stream())
+              out16_code(out16, split16), B, T, c, _stream())
 
 
 def text_embed(phon, pitch, tone, dur, e_ph, e_pitch, e_tone, w_dur, b_dur, x_lengths, lens32, out):
@@ -189,11 +201,11 @@ def lr_gather(h, ends, mel32, out, index_out=None):
               _btc(out, "out"), _ptr(index_out), _stream())
 
 
-def add_pos_mask(x, pos, lens, out32=None, out16=None):
+def add_pos_mask(x, pos, lens, out32=None, out16=None, split16=False):
     B, T, c = x.shape
     _lib.call("b200svs_add_pos_mask", _ptr(x), _btc(x, "x"), _ptr(pos), _ptr(lens), _ptr(out32),
               _btc(out32, "out32"), _ptr(out16), _btc(out16, "out16"),
-              0 if out16 is None else dt_code(out16.dtype), B, T, c, _stream())
+              out16_code(out16, split16), B, T, c, _stream())
 
 
 def f0_embed(log_f0, coarse_in, table, lens, coarse_out, out32=None, out16=None):

@@ -46,9 +46,28 @@ def choose_block_n(cout):
 
 
 def pack_conv(weight, bias, *, dil=1, pad_left=None, dtype=torch.float16, f32=False, gate=False,
-              block_n=None):
-    """weight: [Cout, Cin, k] effective (weight-norm folded) Conv1d weight."""
+              block_n=None, split=False):
+    """weight: [Cout, Cin, k] effective (weight-norm folded) Conv1d weight.
+
+    split=True: split-precision tensor-core conv (F0 predictor).  The activation operand is the fp16
+    K-concatenation [x_hi | x_lo | x_hi] (3*Cin channels) and the weights are packed [w_hi | w_hi | w_lo],
+    so one conv computes x_hi.w_hi + x_lo.w_hi + x_hi.w_lo ~ x.w to 2^-22 with fp32 accumulation."""
     weight = weight.detach().float()
+    if split:
+        if f32 or gate:
+            raise ValueError("split packing is for plain tensor-core convs")
+        # The tensor cores flush fp16 subnormals, and w_lo ~ w * 2^-12 is subnormal for |w| < 0.25: scale the
+        # weights (and the bias) by a power of two so that max|w| sits just below 2^15; the epilogue's alpha
+        # undoes it exactly (act in {NONE, RELU} commutes with a positive scale).
+        import math
+        out_scale = 2.0 ** -math.floor(math.log2(32768.0 / max(float(weight.abs().max()), 1e-30)))
+        weight = weight / out_scale
+        if bias is not None:
+            bias = bias.detach().float() / out_scale
+        w_hi = weight.half().float()
+        w_lo = (weight - w_hi).half().float()
+        weight = torch.cat([w_hi, w_hi, w_lo], 1)
+        dtype = torch.float16
     cout, cin, k = weight.shape
     if pad_left is None:
         pad_left = (k * dil - dil) // 2          # commons.get_padding (VISinger/commons.py:14-15)
@@ -86,7 +105,11 @@ def pack_conv(weight, bias, *, dil=1, pad_left=None, dtype=torch.float16, f32=Fa
     if b is not None:
         bp = torch.zeros(cout_pad)
         bp[:cout] = b
-    return PackedConv(w.to(dtype).contiguous(), bp, k, dil, pad_left, cin, cin_pad, cout, cout_pad, bn, gate, False)
+    pc = PackedConv(w.to(dtype).contiguous(), bp, k, dil, pad_left, cin, cin_pad, cout, cout_pad, bn, gate, False)
+    if split:
+        pc.alg_macs_per_row = (cin // 3) * cout * k      # algorithmic (fp32-equivalent) MACs, not the 3x executed
+        pc.out_scale = out_scale
+    return pc
 
 
 def gate_order(hidden, block_n=128):

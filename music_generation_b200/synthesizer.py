@@ -38,7 +38,8 @@ class SynthesizerTrn(nn.Module):
                  n_heads, n_layers, kernel_size, p_dropout, resblock, resblock_kernel_sizes,
                  resblock_dilation_sizes, upsample_rates, upsample_initial_channel, upsample_kernel_sizes,
                  n_speakers=0, gin_channels=0, use_sdp=True, n_vocab_note=100, *, operand_dtype="fp16",
-                 max_position_embeddings=2000, generator_chunk_frames=32768, seed=1234, **kwargs):
+                 max_position_embeddings=2000, generator_chunk_frames=32768, f0_precision="split", seed=1234,
+                 **kwargs):
         super().__init__()
         if hidden_channels != 192 or n_heads != 2:
             raise ValueError("kernels are specialised for hidden_channels=192, n_heads=2 (ours_ae.json)")
@@ -53,6 +54,9 @@ class SynthesizerTrn(nn.Module):
         self.n_speakers, self.gin_channels, self.use_sdp = n_speakers, gin_channels, use_sdp
         self.operand_dtype = {"fp16": torch.float16, "bf16": torch.bfloat16}[operand_dtype]
         self.generator_chunk_frames = generator_chunk_frames
+        if f0_precision not in ("split", "fp32"):
+            raise ValueError("f0_precision must be 'split' (tensor cores, fp16 hi/lo operands) or 'fp32' (SIMT)")
+        self.f0_precision = f0_precision
         self.hop = 1
         for u in self.upsample_rates:
             self.hop *= u
@@ -95,17 +99,17 @@ class SynthesizerTrn(nn.Module):
         Bv = lambda p: sd.get(p + ".bias")
         P = {}
 
-        def enc(prefix, n_layers, f32):
+        def enc(prefix, n_layers, f32, split=False):
             layers = []
             for i in range(n_layers):
                 a, e = f"{prefix}.attn_layers.{i}", _Enc()
                 wqkv = torch.cat([W(f"{a}.conv_{n}") for n in "qkv"], 0)
                 bqkv = torch.cat([Bv(f"{a}.conv_{n}") for n in "qkv"], 0)
-                e.qkv = packer.pack_conv(wqkv, bqkv, dtype=dt, f32=f32).to(dev)
-                e.o = packer.pack_conv(W(a + ".conv_o"), Bv(a + ".conv_o"), dtype=dt, f32=f32).to(dev)
+                e.qkv = packer.pack_conv(wqkv, bqkv, dtype=dt, f32=f32, split=split).to(dev)
+                e.o = packer.pack_conv(W(a + ".conv_o"), Bv(a + ".conv_o"), dtype=dt, f32=f32, split=split).to(dev)
                 f = f"{prefix}.ffn_layers.{i}"
-                e.ffn1 = packer.pack_conv(W(f + ".conv_1"), Bv(f + ".conv_1"), dtype=dt, f32=f32).to(dev)
-                e.ffn2 = packer.pack_conv(W(f + ".conv_2"), Bv(f + ".conv_2"), dtype=dt, f32=f32).to(dev)
+                e.ffn1 = packer.pack_conv(W(f + ".conv_1"), Bv(f + ".conv_1"), dtype=dt, f32=f32, split=split).to(dev)
+                e.ffn2 = packer.pack_conv(W(f + ".conv_2"), Bv(f + ".conv_2"), dtype=dt, f32=f32, split=split).to(dev)
                 e.rel_k = sd[a + ".emb_rel_k"][0].contiguous().to(dev)
                 e.rel_v = sd[a + ".emb_rel_v"][0].contiguous().to(dev)
                 e.ln1 = (sd[f"{prefix}.norm_layers_1.{i}.gamma"].to(dev), sd[f"{prefix}.norm_layers_1.{i}.beta"].to(dev))
@@ -146,7 +150,9 @@ class SynthesizerTrn(nn.Module):
         P["dp_proj"] = conv(dp + ".proj", f32=True)
         tp = "text_post_net"
         P["pos"] = sd[tp + ".position_embeddings.weight"].contiguous().to(dev)
-        P["f0_enc"] = enc(tp + ".f0_predictor.encoder", 6, True)
+        f0_split = self.f0_precision == "split"
+        P["f0_enc"] = enc(tp + ".f0_predictor.encoder", 6, not f0_split, split=f0_split)
+        P["f0_mode"] = "split" if f0_split else "f32"
         P["f0_out"] = conv(tp + ".f0_predictor.output_layer", f32=True)
         P["f0_emb"] = sd[tp + ".f0_emb.weight"].contiguous().to(dev)
         P["mel_cond"] = conv(tp + ".mel_predict_net.condition_proj")
@@ -231,37 +237,46 @@ class SynthesizerTrn(nn.Module):
         return P
 
     # ------------------------------------------------------------------ building blocks
-    def _encoder(self, layers, x32, x16, lens, f32, attn="f32"):
+    def _encoder(self, layers, x32, x16, lens, mode):
         """attentions.Encoder (VISinger/attentions.py:35-47), channels-last, in place on x32 (/x16).
         x is masked on entry and after every LayerNorm; valid rows equal the reference's.
-        attn: "f32" = fp32 SIMT attention (phoneme level), "tc" = tensor-core attention with 16-bit
-        operands, "split" = tensor-core attention with fp16 (hi, lo) operands (F0 predictor)."""
+        mode "f32"  : fp32 SIMT convs + fp32 attention (phoneme level: durations are floor()ed bit-exactly)
+        mode "tc"   : tensor-core convs / attention with 16-bit operands (mel predictor); x16 = 16-bit copy of x32
+        mode "split": tensor cores with fp16 (hi, lo) split operands, fp32-class accuracy (F0 predictor, whose
+                      output is quantised by f0_to_coarse); x16 = [B,T,3C] fp16 hi|lo|hi copy of x32"""
         B, T, Cc = x32.shape
         dev = x32.device
         dt = self.operand_dtype
+        f32, split = mode == "f32", mode == "split"
         qkv = torch.empty(B, T, 3 * Cc, device=dev, dtype=torch.float32)
-        att32 = torch.empty(B, T, Cc, device=dev, dtype=torch.float32) if f32 else None
-        att16 = None if f32 else torch.empty(B, T, Cc, device=dev, dtype=dt)
         tmp = torch.empty(B, T, Cc, device=dev, dtype=torch.float32)
-        hdt = torch.float32 if f32 else dt
-        hid = torch.empty(B, T, self.filter_channels, device=dev, dtype=hdt)
+        F_ = self.filter_channels
+        if f32:
+            att = torch.empty(B, T, Cc, device=dev, dtype=torch.float32)
+            hid = torch.empty(B, T, F_, device=dev, dtype=torch.float32)
+        elif split:
+            att = torch.empty(B, T, 3 * Cc, device=dev, dtype=torch.float16)
+            hid = torch.empty(B, T, 3 * F_, device=dev, dtype=torch.float16)
+        else:
+            att = torch.empty(B, T, Cc, device=dev, dtype=dt)
+            hid = torch.empty(B, T, F_, device=dev, dtype=dt)
         ws = {}
         for e in layers:
             xin = x32 if f32 else x16
             ops.conv1d(e.qkv, xin, out32=qkv)
-            if attn == "f32":
-                ops.attention(qkv, att32, att16, e.rel_k, e.rel_v, lens)
+            if f32:
+                ops.attention(qkv, att, None, e.rel_k, e.rel_v, lens)
             else:
-                ops.attention_tc(qkv, att32, att16, e.rel_k, e.rel_v, lens, dtype=dt, split=(attn == "split"), ws=ws)
-            ops.conv1d(e.o, att32 if f32 else att16, res1=x32, out32=tmp)
-            ops.layernorm(tmp, e.ln1[0], e.ln1[1], lens, out32=x32, out16=x16)
+                ops.attention_tc(qkv, None, att, e.rel_k, e.rel_v, lens, dtype=dt, split=split, out16_split=split, ws=ws)
+            ops.conv1d(e.o, att, res1=x32, out32=tmp)
+            ops.layernorm(tmp, e.ln1[0], e.ln1[1], lens, out32=x32, out16=x16, split16=split)
             xin = x32 if f32 else x16
             if f32:
                 ops.conv1d(e.ffn1, xin, act=ACT_RELU, lens=lens, out32=hid)
             else:
-                ops.conv1d(e.ffn1, xin, act=ACT_RELU, lens=lens, out16=hid)
+                ops.conv1d(e.ffn1, xin, act=ACT_RELU, lens=lens, out16=hid, split16=split)
             ops.conv1d(e.ffn2, hid, res1=x32, lens=lens, out32=tmp)
-            ops.layernorm(tmp, e.ln2[0], e.ln2[1], lens, out32=x32, out16=x16)
+            ops.layernorm(tmp, e.ln2[0], e.ln2[1], lens, out32=x32, out16=x16, split16=split)
 
     def _wn(self, st, x32, x16, lens, out16, gcond=None):
         """modules.WN (VISinger/modules.py:148-176): x32/x16 hold the masked input and are updated in
@@ -367,7 +382,7 @@ class SynthesizerTrn(nn.Module):
         plen = torch.empty(B, device=dev, dtype=torch.int32)
         h = torch.empty(B, Pn, H, device=dev, dtype=f32)
         ops.text_embed(x, note_pitch_id, phone_shengdiao, note_duration, *P["emb"], *P["emb_dur"], x_lengths, plen, h)
-        self._encoder(P["text_enc"], h, None, plen, True)
+        self._encoder(P["text_enc"], h, None, plen, "f32")
 
         # 2. durations (models_ae.py:622-627)
         if ph_dur is None:
@@ -410,8 +425,15 @@ class SynthesizerTrn(nn.Module):
         xe32 = torch.empty(B, T, H, device=dev, dtype=f32)
         xe16 = torch.empty(B, T, H, device=dev, dtype=dt)
         ops.add_pos_mask(h_lr, P["pos"], mlen, out32=xe32, out16=xe16)
-        f0h = xe32.clone()
-        self._encoder(P["f0_enc"], f0h, None, mlen, True, attn="split")
+        # F0 predictor: tensor cores with fp16 (hi, lo) split operands (default), or fp32 SIMT (f0_precision="fp32")
+        f0h = torch.empty_like(xe32)
+        if P["f0_mode"] == "split":
+            f0s = torch.empty(B, T, 3 * H, device=dev, dtype=torch.float16)
+            ops.add_pos_mask(h_lr, P["pos"], mlen, out32=f0h, out16=f0s, split16=True)
+        else:
+            f0s = None
+            ops.add_pos_mask(h_lr, P["pos"], mlen, out32=f0h)
+        self._encoder(P["f0_enc"], f0h, f0s, mlen, P["f0_mode"])
         log_f0 = torch.empty(B, T, 1, device=dev, dtype=f32)
         ops.conv1d(P["f0_out"], f0h, lens=mlen, out32=log_f0)
         log_f0 = log_f0.view(B, T)
@@ -424,7 +446,7 @@ class SynthesizerTrn(nn.Module):
         m32 = torch.empty(B, T, H, device=dev, dtype=f32)
         m16 = torch.empty(B, T, H, device=dev, dtype=dt)
         ops.conv1d(P["mel_cond"], f0e16, res1=xe32, lens=mlen, out32=m32, out16=m16)
-        self._encoder(P["mel_enc"], m32, m16, mlen, False, attn="tc")
+        self._encoder(P["mel_enc"], m32, m16, mlen, "tc")
         mel32 = torch.empty(B, T, 80, device=dev, dtype=f32)
         ops.conv1d(P["mel_out"], m16, lens=mlen, out32=mel32)
         # FramePriorNetwork (frame_prior_network.py:31-41)

@@ -19,13 +19,19 @@ def _mask(lens, B, T):
     return (torch.arange(T).unsqueeze(0) < lens.to(torch.int64).unsqueeze(1)).to(torch.float32).unsqueeze(-1)
 
 
-def _store(dst, val):
-    if dst is not None:
+def _store(dst, val, split16=False):
+    if dst is None:
+        return
+    if split16:      # fp16 [hi | lo | hi]
+        hi = val.half()
+        lo = (val - hi.float()).half()
+        dst.copy_(torch.cat([hi, lo, hi], -1))
+    else:
         dst.copy_(val.to(dst.dtype))
 
 
 def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, res2=None, lens=None,
-           out32=None, out16=None, post_lrelu=None, w_rows=None, n_valid=None):
+           out32=None, out16=None, post_lrelu=None, w_rows=None, n_valid=None, split16=False):
     B, T, cin = x.shape
     assert cin == pc.cin
     xf = x.float()
@@ -62,7 +68,7 @@ def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, 
     elif act == ACT_TANH:
         y = torch.tanh(y)
     nv = n_valid if n_valid is not None else (pc.n_out if w_rows is None else w_rows[1])
-    y = y[:, :, :nv] * alpha
+    y = y[:, :, :nv] * (alpha * pc.out_scale)
     if res1 is not None:
         y = y + res1.float()[:, :, :nv]
     if res2 is not None:
@@ -75,7 +81,10 @@ def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, 
         out32[:, :, :nv] = y
     if out16 is not None:
         o = F.leaky_relu(y, post_lrelu) if post_lrelu is not None else y
-        out16[:, :, :nv] = o.to(out16.dtype)
+        if split16:
+            _store(out16, o, True)
+        else:
+            out16[:, :, :nv] = o.to(out16.dtype)
 
 
 def attention(qkv, out32, out16, rel_k, rel_v, lens, heads=2, window=4):
@@ -120,7 +129,7 @@ def attention_tc(qkv, out32, out16, rel_k, rel_v, lens, *, dtype, split=False, o
             _store(out16, tmp)
 
 
-def layernorm(x, gamma, beta, lens, out32=None, out16=None, res=None, eps=1e-5):
+def layernorm(x, gamma, beta, lens, out32=None, out16=None, res=None, eps=1e-5, split16=False):
     B, T, c = x.shape
     y = x if res is None else x + res
     y = F.layer_norm(y, (c,), gamma, beta, eps)
@@ -128,7 +137,7 @@ def layernorm(x, gamma, beta, lens, out32=None, out16=None, res=None, eps=1e-5):
     if m is not None:
         y = y * m
     _store(out32, y)
-    _store(out16, y)
+    _store(out16, y, split16)
 
 
 def text_embed(phon, pitch, tone, dur, e_ph, e_pitch, e_tone, w_dur, b_dur, x_lengths, lens32, out):
@@ -162,11 +171,11 @@ def lr_gather(h, ends, mel32, out, index_out=None):
         index_out.copy_(idx.to(torch.int32))
 
 
-def add_pos_mask(x, pos, lens, out32=None, out16=None):
+def add_pos_mask(x, pos, lens, out32=None, out16=None, split16=False):
     B, T, c = x.shape
     y = (x + pos[:T].unsqueeze(0)) * _mask(lens, B, T)
     _store(out32, y)
-    _store(out16, y)
+    _store(out16, y, split16)
 
 
 def f0_embed(log_f0, coarse_in, table, lens, coarse_out, out32=None, out16=None):

@@ -198,3 +198,34 @@ def test_bad_arguments_raise():
         ops.conv1d(pc, x[:, :, :96], out32=torch.zeros(1, 10, 192, device=DEV))
     with pytest.raises(TypeError):
         ops.conv1d(pc, x.bfloat16(), out32=torch.zeros(1, 10, 192, device=DEV))
+
+
+@pytest.mark.parametrize("cin,cout,k,act", [(192, 576, 1, ACT_NONE), (192, 768, 3, ACT_RELU), (768, 192, 3, ACT_NONE)])
+def test_conv1d_tc_split_precision(cin, cout, k, act):
+    """fp16 (hi, lo) split operands: x_hi.w_hi + x_lo.w_hi + x_hi.w_lo on the tensor cores must agree with an
+    fp32 convolution to fp32-class accuracy (F0 predictor path), and the [hi | lo | hi] output must re-compose."""
+    import torch.nn.functional as F
+    B, T = 2, 300
+    w, b = _rand(cout, cin, k, seed=40, scale=(cin * k) ** -0.5), _rand(cout, seed=41, scale=0.1)
+    x = _rand(B, T, cin, seed=42)
+    res = _rand(B, T, cout, seed=43)
+    lens = torch.tensor([300, 170], dtype=torch.int32)
+    ref = F.conv1d(x.double().transpose(1, 2), w.double(), b.double(), padding=k // 2).transpose(1, 2)
+    if act == ACT_RELU:
+        ref = torch.relu(ref)
+    ref = ((ref + res) * (torch.arange(T)[None, :, None] < lens[:, None, None])).float()
+    hi = x.half()
+    xs = torch.cat([hi, (x - hi.float()).half(), hi], -1).to(DEV)
+    pc = packer.pack_conv(w, b, split=True).to(DEV)
+    o32 = torch.empty(B, T, cout, device=DEV)
+    o16 = torch.empty(B, T, 3 * cout, device=DEV, dtype=torch.float16)
+    ops.conv1d(pc, xs, act=act, res1=res.to(DEV), lens=lens.to(DEV), out32=o32, out16=o16, split16=True)
+    torch.cuda.synchronize()
+    scale = float(ref.abs().max())
+    # operand quantisation contributes ~2e-7; the rest is the tensor core's truncating fp32 accumulate, measured
+    # (tools/diag_split.py) at <= 1.7e-7*|acc| per tcgen05.mma step and biased toward zero.  3*cin*k/16 steps.
+    steps = 3 * cin * k // 16
+    assert max_abs(ref, o32.cpu()) < (2e-6 + 2.5e-7 * steps) * max(scale, 1.0) / 4
+    h, l, h2 = (o16[:, :, i * cout:(i + 1) * cout].float().cpu() for i in range(3))
+    assert torch.equal(h, h2)
+    assert max_abs(o32.cpu(), h + l) < 2e-6 * max(scale, 1.0)

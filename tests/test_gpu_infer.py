@@ -94,6 +94,23 @@ def test_predicted_durations_are_bit_exact():
         assert torch.equal(got, want)
 
 
+def test_f0_split_precision_matches_fp32_path():
+    """The default F0 predictor (tensor cores, fp16 hi/lo split operands) against the fp32 SIMT path
+    (f0_precision="fp32"): log_f0 agrees to fp32-evaluation noise (tools/diag_f0.py: both are ~2e-6 rms from an
+    fp64 evaluation, the same as the oracle's own fp32 run) and the coarse buckets are identical."""
+    B, P, T = 2, 80, 800
+    inp = synthetic.make_inputs(B, P, seed=77, ragged=True)
+    ph_dur = synthetic.make_ph_dur(inp["x_lengths"], P, T, seed=77)
+    noise = torch.zeros(B, 192, int(ph_dur.sum(1).max()), device=DEV)
+    got = {}
+    for prec in ("split", "fp32"):
+        net, _ = build_model("ae", device=DEV, f0_precision=prec)
+        res = _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise)
+        got[prec] = (res[3].cpu(), net.last_aux["f0_coarse"].cpu())
+    assert max_abs(got["split"][0], got["fp32"][0]) < 4e-5
+    assert int((got["split"][1] != got["fp32"][1]).sum()) <= 1
+
+
 def test_batch_invariance_and_sharding_equivalence():
     """An utterance synthesised inside a batch equals the same utterance synthesised alone, bit for bit
     (no split-K over time, no cross-utterance reduction) - what makes G-GPU sharding exact."""
