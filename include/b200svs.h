@@ -106,6 +106,10 @@ int b200svs_check_device(void);
 
 /* tcgen05/TMEM/TMA implicit-GEMM conv, fp16|bf16 operands, fp32 accumulate */
 int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream);
+/* Diagnostic (tuning aid, not part of the data path): when dev_buf != NULL every following conv1d_tc launch
+ * writes per-tile clock64() stamps of its pipeline roles into dev_buf[grid][tiles_per_cta][16] (int64);
+ * NULL switches it off.  Slot meanings: tools/trace_conv.py. */
+int b200svs_conv1d_tc_set_trace(void* dev_buf, int32_t tiles_per_cta);
 /* fp32 SIMT conv (phoneme-level + F0 path where the float->int boundaries need fp32);
  * w packed [ntaps][Cin][Cout_pad] fp32 (Cout contiguous) */
 int b200svs_conv1d_f32(const b200svs_conv_args* a, void* stream);

@@ -15,15 +15,17 @@
 // accumulator in place, and TMA stores write the fp32 and the 16-bit result (the latter with the next
 // layer's leaky-ReLU applied) fully coalesced; the tensor maps clip rows >= T and columns >= n_valid.
 //
-// Warp roles (384 threads, 1 CTA/SM, persistent over tiles):
-//   warp 0 lane 0 : TMA producer of the mainloop (activation ring, weight ring)
+// Warp roles (416 threads, 1 CTA/SM, persistent over tiles):
+//   warp 0 lane 0 : TMA producer of the activation ring
 //   warp 1 lane 0 : tcgen05.mma issuer (accumulators double-buffered in TMEM)
-//   warp 2        : TMEM alloc / dealloc
+//   warp 2        : TMEM alloc / dealloc; lane 0 = TMA store thread (drains finished epilogue chunks)
 //   warp 3 lane 0 : TMA producer of the epilogue staging slots (residual tiles)
 //   warps 4..11   : epilogue; warp w and w+4 share a TMEM lane quadrant and split each 32-column chunk 16/16
+//   warp 12 lane 0: TMA producer of the weight ring
 //
 // Replaces: nn.Conv1d/ConvTranspose1d + surrounding pointwise ops of the reference
 // (VISinger/models_ae.py:327-346, modules.py:148-176,210-223,329-349, attentions.py:138-146,277-285).
+#include <cstdlib>
 #include "common.cuh"
 #include "api_internal.h"
 
@@ -31,20 +33,20 @@ namespace b200svs {
 
 constexpr int kBlockK = 64;
 constexpr int kRowBytes = kBlockK * 2;     // one K-chunk row of a 16-bit operand tile: 128 B
-constexpr int kAStages = 2;
+constexpr int kMaxAStages = 4;
 constexpr int kMaxWStages = 8;
 constexpr int kMaxSlots = 8;
 constexpr int kEpiCols = 32;               // output columns per epilogue chunk
 constexpr int kSlot32Bytes = 128 * kEpiCols * 4;   // 16 KB: [128 rows][32 fp32], SWIZZLE_128B
 constexpr int kSlot16Bytes = 128 * kEpiCols * 2;   //  8 KB: [128 rows][32 x 16-bit], SWIZZLE_64B
 constexpr int kEpiThreads = 256;            // 8 epilogue warps
-constexpr int kTcThreads = 128 + kEpiThreads;
+constexpr int kTcThreads = 128 + kEpiThreads + 32;   // + warp 12: weight-ring producer
 
 struct ConvTcParams {
   int T, tiles_t, m_tiles, n_tiles, total_tiles;
   int ntaps, nchunks, dil, pad_left, cout_pad, block_n, msub;
   int a_boxes, a_box_rows, a_stage_bytes;  // activation tile = a_boxes TMA boxes of a_box_rows rows
-  int w_stages, w_stage_bytes;
+  int a_stages, w_stages, w_stage_bytes;
   int n_slots, slot_bytes, slot16_off;     // epilogue staging slot: [fp32 area][res2 fp32 area][16-bit area]
   int slot_r2_off;                         // offset of the res2 area inside a slot (0 = none)
   int stores_in_flight;                    // TMA store groups left pending before a slot is recycled
@@ -52,14 +54,17 @@ struct ConvTcParams {
   int tmem_cols;
   int ksub;                                // K=16 MMA steps per K chunk (4, or fewer when Cin < 64)
   uint32_t idesc;
+  long long* trace;                        // diagnostic: [grid][trace_cap][16] clock64 stamps (NULL: off)
+  int trace_cap;
   b200svs_epilogue ep;
 };
 
 struct __align__(8) TcBarriers {
-  uint64_t a_full[kAStages], a_empty[kAStages];
+  uint64_t a_full[kMaxAStages], a_empty[kMaxAStages];
   uint64_t w_full[kMaxWStages], w_empty[kMaxWStages];
   uint64_t tmem_full[2], tmem_empty[2];
   uint64_t e_full[kMaxSlots], e_empty[kMaxSlots];
+  uint64_t s_ready[kMaxSlots];             // epilogue warps -> store thread: slot holds a finished chunk
   uint32_t tmem_base;
 };
 
@@ -197,40 +202,11 @@ __device__ __forceinline__ void epi_chunk(const EpiCtx& c, const uint32_t* acc, 
   }
 }
 
-template <bool RES, bool BF>
-__device__ __forceinline__ void epi_dispatch2(const EpiCtx& c, int act, bool plain, bool split, const uint32_t* r0,
-                                              const uint32_t* r1) {
-  if (split) {   // host restricts split outputs to NONE / RELU, fp16
-    if (act == B200SVS_ACT_RELU) epi_chunk<B200SVS_ACT_RELU, RES, false, false, true>(c, r0, r0);
-    else epi_chunk<B200SVS_ACT_NONE, RES, false, false, true>(c, r0, r0);
-    return;
-  }
-  switch (act) {
-    case B200SVS_ACT_GATE: epi_chunk<B200SVS_ACT_GATE, RES, false, BF, false>(c, r0, r1); break;
-    case B200SVS_ACT_RELU: epi_chunk<B200SVS_ACT_RELU, RES, false, BF, false>(c, r0, r0); break;
-    case B200SVS_ACT_GELU: epi_chunk<B200SVS_ACT_GELU, RES, false, BF, false>(c, r0, r0); break;
-    case B200SVS_ACT_SIGMOID: epi_chunk<B200SVS_ACT_SIGMOID, RES, false, BF, false>(c, r0, r0); break;
-    case B200SVS_ACT_TANH: epi_chunk<B200SVS_ACT_TANH, RES, false, BF, false>(c, r0, r0); break;
-    default:
-      if (plain) epi_chunk<B200SVS_ACT_NONE, RES, true, BF, false>(c, r0, r0);
-      else epi_chunk<B200SVS_ACT_NONE, RES, false, BF, false>(c, r0, r0);
-      break;
-  }
-}
-__device__ __forceinline__ void epi_dispatch(const EpiCtx& c, int act, bool res, bool plain, const uint32_t* r0,
-                                             const uint32_t* r1) {
-  const bool split = c.ep->out16 && c.ep->out16_dtype == B200SVS_DT_F16_SPLIT;
-  const bool bf = c.ep->out16_dtype == B200SVS_DT_BF16;
-  if (res) {
-    if (bf) epi_dispatch2<true, true>(c, act, plain, split, r0, r1);
-    else epi_dispatch2<true, false>(c, act, plain, split, r0, r1);
-  } else {
-    if (bf) epi_dispatch2<false, true>(c, act, plain, split, r0, r1);
-    else epi_dispatch2<false, false>(c, act, plain, split, r0, r1);
-  }
-}
-
 static_assert(sizeof(TcBarriers) <= 512, "barrier block must fit its 512-byte reservation");
+
+__device__ __forceinline__ void trace_stamp(const ConvTcParams& p, int it, int slot, long long v) {
+  if (p.trace && it < p.trace_cap) p.trace[(static_cast<size_t>(blockIdx.x) * p.trace_cap + it) * 16 + slot] = v;
+}
 
 struct TileCoord {
   int n_idx, b, t0;
@@ -244,6 +220,183 @@ __device__ __forceinline__ TileCoord tile_coord(const ConvTcParams& p, int tile)
   return c;
 }
 
+// The epilogue of one CTA: 8 warps; warp w and w + 4 share TMEM lane quadrant w % 4 and split each 32-column
+// chunk 16 / 16 (two warps per scheduler).  Everything that is constant for the launch is a template
+// parameter, so a chunk is straight-line code; the accumulators of chunk i + 1 are fetched from TMEM while
+// chunk i is processed.  Finished chunks are handed to the store thread through s_ready (no CTA barrier).
+template <int ACT, bool RES, bool PLAIN, bool BF, bool SPLIT>
+__device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
+                                              uint32_t smE_u, const float* bias_s) {
+  constexpr bool GATE = ACT == B200SVS_ACT_GATE;
+  const b200svs_epilogue& ep = p.ep;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = warp & 3;
+  const int row = q * 32 + lane;
+  const int half = (warp - 4) >> 2;
+  const int half_n = p.block_n >> 1;
+  const int acc_cols = p.msub * p.block_n;
+  const int cps = p.chunks_per_sub;
+  const int n_chunks = p.msub * cps;
+  const bool tracer = p.trace != nullptr && threadIdx.x == 128;
+  EpiCtx c;
+  c.ep = &ep; c.slot16_off = p.slot16_off; c.slot_r2_off = p.slot_r2_off; c.row = row; c.half = half;
+  c.need32 = ep.out32 != nullptr;
+  c.gate_off = half_n;
+  c.bias_s = ep.bias ? bias_s : nullptr;
+  int it = 0, sl = 0;
+  uint32_t eph = 0;
+  for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+    const int acc = it & 1;
+    const TileCoord tc = tile_coord(p, tile);
+    c.b = tc.b;
+    const int len_b = ep.lens ? __ldg(ep.lens + tc.b) : p.T;
+    mbar_wait(&bars->tmem_full[acc], (it >> 1) & 1);
+    tc_fence_after();
+    long long w_e = 0;
+    if (tracer) trace_stamp(p, it, 5, clock64());
+    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * acc_cols + half * 16;
+    uint32_t ra0[16], rb0[GATE ? 1 : 16], ra1[GATE ? 16 : 1];
+    auto fetch = [&](int ci, uint32_t* r0, uint32_t* r1) {
+      const int ms = ci >= cps ? 1 : 0;                  // msub <= 2
+      const uint32_t col = ms * p.block_n + (ci - ms * cps) * kEpiCols;
+      tmem_ld16_nowait(taddr + col, r0);
+      if (GATE) tmem_ld16_nowait(taddr + half_n + col, r1);
+    };
+    auto finish = [&](int ci, uint32_t* r0, uint32_t* r1) {
+      const int ms = ci >= cps ? 1 : 0;
+      const int ch = ci - ms * cps;
+      const int tsub = tc.t0 + ms * 128;
+      c.row_live = tsub + row < len_b;
+      c.pcol = tc.n_idx * p.block_n + ch * kEpiCols + half * 16;
+      c.slot = smE_u + sl * p.slot_bytes;
+      long long t0 = 0;
+      if (tracer) t0 = clock64();
+      mbar_wait(&bars->e_full[sl], eph);
+      if (tracer) w_e += clock64() - t0;
+      if (tsub < p.T) epi_chunk<ACT, RES, PLAIN, BF, SPLIT>(c, r0, r1);
+      fence_proxy_async();             // generic-proxy smem writes -> visible to the TMA store
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars->s_ready[sl]);
+      if (++sl == p.n_slots) { sl = 0; eph ^= 1; }
+    };
+    if constexpr (GATE) {              // two accumulator halves per chunk: no register room for a prefetch
+      for (int ci = 0; ci < n_chunks; ++ci) {
+        fetch(ci, ra0, ra1);
+        tmem_ld_wait16(ra0);
+        tmem_ld_wait16(ra1);
+        finish(ci, ra0, ra1);
+      }
+    } else {
+      fetch(0, ra0, ra1);
+      for (int ci = 0; ci < n_chunks; ci += 2) {
+        tmem_ld_wait16(ra0);
+        if (ci + 1 < n_chunks) fetch(ci + 1, rb0, ra1);
+        finish(ci, ra0, ra1);
+        if (ci + 1 < n_chunks) {
+          tmem_ld_wait16(rb0);
+          if (ci + 2 < n_chunks) fetch(ci + 2, ra0, ra1);
+          finish(ci + 1, rb0, ra1);
+        }
+      }
+    }
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+    if (tracer) { trace_stamp(p, it, 6, clock64()); trace_stamp(p, it, 7, w_e); }
+  }
+}
+
+template <bool RES, bool BF>
+__device__ __forceinline__ void epilogue_dispatch2(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
+                                                   uint32_t smE_u, const float* bias_s, bool plain, bool split) {
+  const int act = p.ep.act;
+  if (split) {   // host restricts split outputs to NONE / RELU, fp16
+    if (act == B200SVS_ACT_RELU) epilogue_loop<B200SVS_ACT_RELU, RES, false, false, true>(p, bars, tmem_base, smE_u, bias_s);
+    else epilogue_loop<B200SVS_ACT_NONE, RES, false, false, true>(p, bars, tmem_base, smE_u, bias_s);
+    return;
+  }
+  switch (act) {
+    case B200SVS_ACT_GATE: epilogue_loop<B200SVS_ACT_GATE, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s); break;
+    case B200SVS_ACT_RELU: epilogue_loop<B200SVS_ACT_RELU, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s); break;
+    case B200SVS_ACT_GELU: epilogue_loop<B200SVS_ACT_GELU, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s); break;
+    case B200SVS_ACT_SIGMOID: epilogue_loop<B200SVS_ACT_SIGMOID, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s); break;
+    case B200SVS_ACT_TANH: epilogue_loop<B200SVS_ACT_TANH, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s); break;
+    default:
+      if (plain) epilogue_loop<B200SVS_ACT_NONE, RES, true, BF, false>(p, bars, tmem_base, smE_u, bias_s);
+      else epilogue_loop<B200SVS_ACT_NONE, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s);
+      break;
+  }
+}
+__device__ __forceinline__ void epilogue_dispatch(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
+                                                  uint32_t smE_u, const float* bias_s) {
+  const b200svs_epilogue& ep = p.ep;
+  const bool res = ep.res1 != nullptr || ep.res2 != nullptr;
+  const bool plain = ep.alpha == 1.0f && ep.scale == 1.0f && ep.lens == nullptr && ep.gbias == nullptr;
+  const bool split = ep.out16 && ep.out16_dtype == B200SVS_DT_F16_SPLIT;
+  const bool bf = ep.out16 && ep.out16_dtype == B200SVS_DT_BF16;
+  if (res) {
+    if (bf) epilogue_dispatch2<true, true>(p, bars, tmem_base, smE_u, bias_s, plain, split);
+    else epilogue_dispatch2<true, false>(p, bars, tmem_base, smE_u, bias_s, plain, split);
+  } else {
+    if (bf) epilogue_dispatch2<false, true>(p, bars, tmem_base, smE_u, bias_s, plain, split);
+    else epilogue_dispatch2<false, false>(p, bars, tmem_base, smE_u, bias_s, plain, split);
+  }
+}
+
+// The tcgen05.mma issue loop of one CTA, run by a single thread.  KSUB = K=16 steps per 64-channel chunk
+// (0: runtime p.ksub); MSUB = 128-row sub-tiles per tile.  Descriptor arithmetic is done on the 14-bit
+// (address >> 4) field directly: every operand tile lies below 256 KB, so the adds never carry out of it.
+template <int MSUB, int KSUB>
+__device__ __forceinline__ void mma_issue_loop(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
+                                               uint32_t smA_u, uint32_t smW_u) {
+  const uint64_t descA0 = make_desc_k128(smA_u), descW0 = make_desc_k128(smW_u);
+  const uint32_t a_stage_d = static_cast<uint32_t>(p.a_stage_bytes) >> 4;
+  const uint32_t w_stage_d = static_cast<uint32_t>(p.w_stage_bytes) >> 4;
+  const uint32_t tap_d = static_cast<uint32_t>(p.dil * kRowBytes) >> 4;
+  constexpr uint32_t kSubD = (128 * kRowBytes) >> 4;       // next 128-row sub-tile of the activation stage
+  const int ksub = KSUB ? KSUB : p.ksub;
+  const int acc_cols = p.msub * p.block_n;
+  const uint32_t idesc = p.idesc;
+  int as = 0, ws = 0, it = 0;
+  uint32_t aph = 0, wph = 0;
+  for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+    const int acc = it & 1;
+    mbar_wait(&bars->tmem_empty[acc], ((it >> 1) & 1) ^ 1);
+    tc_fence_after();
+    trace_stamp(p, it, 2, clock64());
+    const uint32_t d_tmem = tmem_base + acc * acc_cols;
+    uint32_t accum = 0;
+    for (int ch = 0; ch < p.nchunks; ++ch) {
+      mbar_wait(&bars->a_full[as], aph);
+      if (ch == 0) trace_stamp(p, it, 3, clock64());
+      uint64_t da = descA0 + as * a_stage_d;
+      for (int tap = 0; tap < p.ntaps; ++tap) {
+        mbar_wait(&bars->w_full[ws], wph);
+        tc_fence_after();
+        const uint64_t db = descW0 + ws * w_stage_d;
+#pragma unroll
+        for (int ms = 0; ms < MSUB; ++ms) {
+          umma_f16(d_tmem + ms * p.block_n, da + ms * kSubD, db, idesc, accum);
+          if (KSUB) {
+#pragma unroll
+            for (int k = 1; k < KSUB; ++k) umma_f16(d_tmem + ms * p.block_n, da + ms * kSubD + 2 * k, db + 2 * k, idesc, 1u);
+          } else {
+            for (int k = 1; k < ksub; ++k) umma_f16(d_tmem + ms * p.block_n, da + ms * kSubD + 2 * k, db + 2 * k, idesc, 1u);
+          }
+        }
+        umma_commit(&bars->w_empty[ws]);
+        accum = 1;
+        da += tap_d;
+        if (++ws == p.w_stages) { ws = 0; wph ^= 1; }
+      }
+      umma_commit(&bars->a_empty[as]);
+      if (++as == p.a_stages) { as = 0; aph ^= 1; }
+    }
+    umma_commit(&bars->tmem_full[acc]);
+    trace_stamp(p, it, 4, clock64());
+  }
+}
+
 __global__ void __launch_bounds__(kTcThreads, 1)
 conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                  const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmR2,
@@ -252,7 +405,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smA = smem;
-  uint8_t* smW = smA + kAStages * p.a_stage_bytes;
+  uint8_t* smW = smA + p.a_stages * p.a_stage_bytes;
   uint8_t* smE = smW + p.w_stages * p.w_stage_bytes;
   TcBarriers* bars = reinterpret_cast<TcBarriers*>(smE + p.n_slots * p.slot_bytes);
   float* bias_s = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);   // [cout_pad]
@@ -272,10 +425,12 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (ep.out16) prefetch_tmap(&tmO16);
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < kAStages; ++s) { mbar_init(&bars->a_full[s], 1); mbar_init(&bars->a_empty[s], 1); }
+    for (int s = 0; s < p.a_stages; ++s) { mbar_init(&bars->a_full[s], 1); mbar_init(&bars->a_empty[s], 1); }
     for (int s = 0; s < p.w_stages; ++s) { mbar_init(&bars->w_full[s], 1); mbar_init(&bars->w_empty[s], 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], kEpiThreads / 32); }
-    for (int s = 0; s < p.n_slots; ++s) { mbar_init(&bars->e_full[s], 1); mbar_init(&bars->e_empty[s], 1); }
+    for (int s = 0; s < p.n_slots; ++s) {
+      mbar_init(&bars->e_full[s], 1); mbar_init(&bars->e_empty[s], 1); mbar_init(&bars->s_ready[s], kEpiThreads / 32);
+    }
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -288,73 +443,112 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
-  const int acc_cols = p.msub * p.block_n;
 
   if (warp == 0) {
     if (lane == 0) {
-      // ------------------------------------------------------------ mainloop TMA producer
-      int as = 0, ws = 0;
-      uint32_t aph = 0, wph = 0;
+      // ------------------------------------------------------------ activation-ring TMA producer (its own
+      // thread: the weight ring's back-pressure must not delay the prefetch of the next tiles' activations)
+      int as = 0, it = 0;
+      uint32_t aph = 0;
       const uint32_t a_tx = static_cast<uint32_t>(p.a_boxes) * p.a_box_rows * kRowBytes;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
         const TileCoord tc = tile_coord(p, tile);
         for (int ch = 0; ch < p.nchunks; ++ch) {
           mbar_wait(&bars->a_empty[as], aph ^ 1);
+          if (ch == 0) trace_stamp(p, it, 0, clock64());
           uint8_t* sa = smA + as * p.a_stage_bytes;
           mbar_arrive_expect_tx(&bars->a_full[as], a_tx);
           for (int bx = 0; bx < p.a_boxes; ++bx)
             tma_load_3d(sa + bx * p.a_box_rows * kRowBytes, &tmA, &bars->a_full[as], ch * kBlockK,
                         tc.t0 - p.pad_left + bx * p.a_box_rows, tc.b);
-          if (++as == kAStages) { as = 0; aph ^= 1; }
+          if (++as == p.a_stages) { as = 0; aph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 12) {
+    if (lane == 0) {
+      // ------------------------------------------------------------ weight-ring TMA producer
+      int ws = 0, it = 0;
+      uint32_t wph = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+        const int n_idx = tile / p.m_tiles;
+        for (int ch = 0; ch < p.nchunks; ++ch) {
           for (int tap = 0; tap < p.ntaps; ++tap) {
             mbar_wait(&bars->w_empty[ws], wph ^ 1);
             mbar_arrive_expect_tx(&bars->w_full[ws], p.w_stage_bytes);
             tma_load_2d(smW + ws * p.w_stage_bytes, &tmW, &bars->w_full[ws], ch * kBlockK,
-                        tap * p.cout_pad + tc.n_idx * p.block_n);
+                        tap * p.cout_pad + n_idx * p.block_n);
             if (++ws == p.w_stages) { ws = 0; wph ^= 1; }
           }
         }
+        trace_stamp(p, it, 1, clock64());
       }
     }
   } else if (warp == 1) {
-    // -------------------------------------------------------------- MMA issuer (whole warp, convergent;
-    // one elected lane issues inside umma_*_warp)
-    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
-    const uint32_t smA_u = __shfl_sync(0xffffffffu, smem_u32(smA), 0);
-    const uint32_t smW_u = __shfl_sync(0xffffffffu, smem_u32(smW), 0);
-    const int ksub = p.ksub;          // K=16 steps per 64-channel chunk that hold real channels
-    int as = 0, ws = 0, it = 0;
-    uint32_t aph = 0, wph = 0;
-    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-      const int acc = it & 1;
-      mbar_wait(&bars->tmem_empty[acc], ((it >> 1) & 1) ^ 1);
-      tc_fence_after();
-      const uint32_t d_tmem = tmem_u + acc * acc_cols;
-      for (int ch = 0; ch < p.nchunks; ++ch) {
-        mbar_wait(&bars->a_full[as], aph);
-        const uint32_t sa = smA_u + as * p.a_stage_bytes;
-        for (int tap = 0; tap < p.ntaps; ++tap) {
-          mbar_wait(&bars->w_full[ws], wph);
-          tc_fence_after();
-          const uint64_t db = make_desc_k128(smW_u + ws * p.w_stage_bytes);
-          if (elect_one()) {     // single-thread region: descriptors live in uniform registers
-            for (int ms = 0; ms < p.msub; ++ms) {
-              const uint64_t da = make_desc_k128(sa + (ms * 128 + tap * p.dil) * kRowBytes);
-              for (int k = 0; k < ksub; ++k)
-                umma_f16(d_tmem + ms * p.block_n, da + 2 * k, db + 2 * k, p.idesc, (ch | tap | k) != 0);
-            }
-            umma_commit(&bars->w_empty[ws]);
-          }
-          __syncwarp();
-          if (++ws == p.w_stages) { ws = 0; wph ^= 1; }
-        }
-        if (elect_one()) umma_commit(&bars->a_empty[as]);
-        __syncwarp();
-        if (++as == kAStages) { as = 0; aph ^= 1; }
+    // -------------------------------------------------------------- MMA issuer: one elected thread runs the
+    // whole loop (descriptors stay in uniform registers; MSUB / KSUB are compile-time so a tap is a straight
+    // run of UTCHMMAs with immediate descriptor offsets)
+    if (elect_one()) {
+      const uint32_t smA_u = smem_u32(smA), smW_u = smem_u32(smW);
+      if (p.msub == 2) {
+        if (p.ksub == 4) mma_issue_loop<2, 4>(p, bars, tmem_base, smA_u, smW_u);
+        else if (p.ksub == 2) mma_issue_loop<2, 2>(p, bars, tmem_base, smA_u, smW_u);
+        else mma_issue_loop<2, 0>(p, bars, tmem_base, smA_u, smW_u);
+      } else {
+        if (p.ksub == 4) mma_issue_loop<1, 4>(p, bars, tmem_base, smA_u, smW_u);
+        else mma_issue_loop<1, 0>(p, bars, tmem_base, smA_u, smW_u);
       }
-      if (elect_one()) umma_commit(&bars->tmem_full[acc]);
-      __syncwarp();
     }
+    __syncwarp();
+  } else if (warp == 2) {
+    if (lane == 0) {
+      // ------------------------------------------------------------ TMA store thread: drains finished chunks so
+      // the epilogue warps never meet at a CTA-wide barrier; keeps `stores_in_flight` bulk groups pending and
+      // recycles the slot of the oldest completed one
+      int sl = 0, n_done = 0, free_sl = 0;
+      uint32_t sph = 0;
+      const bool split16 = ep.out16 && ep.out16_dtype == B200SVS_DT_F16_SPLIT;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+        const TileCoord tc = tile_coord(p, tile);
+        for (int ms = 0; ms < p.msub; ++ms) {
+          const int tsub = tc.t0 + ms * 128;
+          for (int ch = 0; ch < p.chunks_per_sub; ++ch) {
+            mbar_wait(&bars->s_ready[sl], sph);
+            if (ms == 0 && ch == 0) trace_stamp(p, it, 8, clock64());
+            if (tsub < p.T) {
+              const int ocol = tc.n_idx * p.n_out_tile + ch * kEpiCols;
+              uint8_t* slot = smE + sl * p.slot_bytes;
+              if (ep.out32) tma_store_3d(&tmO32, slot, ocol, tsub, tc.b);
+              if (ep.out16) tma_store_3d(&tmO16, slot + p.slot16_off, ocol, tsub, tc.b);
+              if (split16) {   // [hi | lo | hi]
+                tma_store_3d(&tmO16, slot + p.slot16_off + kSlot16Bytes, ep.n_valid + ocol, tsub, tc.b);
+                tma_store_3d(&tmO16, slot + p.slot16_off, 2 * ep.n_valid + ocol, tsub, tc.b);
+              }
+            }
+            tma_store_commit();
+            switch (p.stores_in_flight) {
+              case 0: tma_store_wait_read<0>(); break;
+              case 1: tma_store_wait_read<1>(); break;
+              case 2: tma_store_wait_read<2>(); break;
+              case 3: tma_store_wait_read<3>(); break;
+              case 4: tma_store_wait_read<4>(); break;
+              case 5: tma_store_wait_read<5>(); break;
+              case 6: tma_store_wait_read<6>(); break;
+              default: tma_store_wait_read<7>(); break;
+            }
+            if (++n_done > p.stores_in_flight) {
+              mbar_arrive(&bars->e_empty[free_sl]);
+              if (++free_sl == p.n_slots) free_sl = 0;
+            }
+            if (++sl == p.n_slots) { sl = 0; sph ^= 1; }
+          }
+        }
+        trace_stamp(p, it, 9, clock64());
+      }
+      tma_store_wait_all<0>();
+    }
+    __syncwarp();
   } else if (warp == 3) {
     if (lane == 0) {
       // ------------------------------------------------------------ epilogue staging producer
@@ -379,84 +573,8 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
     }
-  } else if (warp >= 4) {
-    // -------------------------------------------------------------- epilogue: 8 warps; warp w and w + 4 share
-    // TMEM lane quadrant w % 4 and split each 32-column chunk 16 / 16 (two warps per scheduler hide latency)
-    const int q = warp & 3;
-    const int row = q * 32 + lane;
-    const int half = (warp - 4) >> 2;
-    const bool gate = ep.act == B200SVS_ACT_GATE;
-    const int half_n = p.block_n >> 1;
-    const bool leader = threadIdx.x == 128;
-    const bool res = has_res1 || has_res2;
-    const bool plain = ep.alpha == 1.0f && ep.scale == 1.0f && ep.lens == nullptr && ep.gbias == nullptr;
-    int it = 0, sl = 0, n_done = 0, free_sl = 0;
-    uint32_t eph = 0;
-    EpiCtx c;
-    c.ep = &ep; c.slot16_off = p.slot16_off; c.slot_r2_off = p.slot_r2_off; c.row = row; c.half = half;
-    c.need32 = ep.out32 != nullptr;
-    c.gate_off = half_n;
-    c.bias_s = ep.bias ? bias_s : nullptr;
-    const uint32_t smE_u = smem_u32(smE);
-    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-      const int acc = it & 1;
-      const TileCoord tc = tile_coord(p, tile);
-      c.b = tc.b;
-      const int len_b = ep.lens ? __ldg(ep.lens + tc.b) : p.T;
-      mbar_wait(&bars->tmem_full[acc], (it >> 1) & 1);
-      tc_fence_after();
-      for (int ms = 0; ms < p.msub; ++ms) {
-        const int tsub = tc.t0 + ms * 128;
-        c.row_live = tsub + row < len_b;
-        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * acc_cols + ms * p.block_n;
-        for (int ch = 0; ch < p.chunks_per_sub; ++ch) {
-          uint32_t r0[16], r1[16];
-          const int pc = ch * kEpiCols + half * 16;
-          tmem_ld16_nowait(taddr + pc, r0);
-          if (gate) tmem_ld16_nowait(taddr + half_n + pc, r1);
-          c.pcol = tc.n_idx * p.block_n + pc;
-          const int ocol = tc.n_idx * p.n_out_tile + ch * kEpiCols;
-          c.slot = smE_u + sl * p.slot_bytes;
-          mbar_wait(&bars->e_full[sl], eph);
-          tmem_ld_wait();
-          if (tsub < p.T) epi_dispatch(c, ep.act, res, plain, r0, r1);
-          fence_proxy_async();
-          named_bar_sync(1, kEpiThreads);
-          if (leader) {
-            if (tsub < p.T) {
-              uint8_t* slot = smE + sl * p.slot_bytes;
-              if (ep.out32) tma_store_3d(&tmO32, slot, ocol, tsub, tc.b);
-              if (ep.out16) tma_store_3d(&tmO16, slot + p.slot16_off, ocol, tsub, tc.b);
-              if (ep.out16 && ep.out16_dtype == B200SVS_DT_F16_SPLIT) {   // [hi | lo | hi]
-                tma_store_3d(&tmO16, slot + p.slot16_off + kSlot16Bytes, ep.n_valid + ocol, tsub, tc.b);
-                tma_store_3d(&tmO16, slot + p.slot16_off, 2 * ep.n_valid + ocol, tsub, tc.b);
-              }
-            }
-            tma_store_commit();
-            // keep `stores_in_flight` groups pending; the slot of the oldest completed one is recycled
-            switch (p.stores_in_flight) {
-              case 0: tma_store_wait_read<0>(); break;
-              case 1: tma_store_wait_read<1>(); break;
-              case 2: tma_store_wait_read<2>(); break;
-              case 3: tma_store_wait_read<3>(); break;
-              case 4: tma_store_wait_read<4>(); break;
-              case 5: tma_store_wait_read<5>(); break;
-              case 6: tma_store_wait_read<6>(); break;
-              default: tma_store_wait_read<7>(); break;
-            }
-            if (++n_done > p.stores_in_flight) {
-              mbar_arrive(&bars->e_empty[free_sl]);
-              if (++free_sl == p.n_slots) free_sl = 0;
-            }
-          }
-          if (++sl == p.n_slots) { sl = 0; eph ^= 1; }
-        }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
-    }
-    if (leader) tma_store_wait_all<0>();
+  } else if (warp >= 4 && warp < 12) {
+    epilogue_dispatch(p, bars, tmem_base, smem_u32(smE), bias_s);
   }
 
   tc_fence_before();
@@ -477,6 +595,14 @@ static int round_up_i(int x, int m) { return (x + m - 1) / m * m; }
 }  // namespace b200svs
 
 using namespace b200svs;
+
+static long long* g_trace = nullptr;
+static int g_trace_cap = 0;
+extern "C" int b200svs_conv1d_tc_set_trace(void* dev_buf, int tiles_per_cta) {
+  g_trace = static_cast<long long*>(dev_buf);
+  g_trace_cap = dev_buf ? tiles_per_cta : 0;
+  return 0;
+}
 
 extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   B200SVS_REQUIRE(a && a->x && a->w, "conv1d_tc: null argument");
@@ -535,7 +661,15 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   const int ksteps = a->ntaps * p.nchunks;
   int w_min = ksteps < 3 ? ksteps : 3;
   if (w_min < 2) w_min = 2;
-  const int avail = budget - kAStages * p.a_stage_bytes;
+  // as many activation stages (loads in flight) as leave room for the minimum of everything else
+  const bool has_res = ep.res1 || ep.res2;
+  const int min_slots = has_res ? 4 : 3;
+  int a_stages = kMaxAStages;
+  if (const char* e = getenv("B200SVS_TC_ASTAGES")) { int v = atoi(e); if (v >= 2 && v <= kMaxAStages) a_stages = v; }   // tuning knob
+  while (a_stages > 2 && budget - a_stages * p.a_stage_bytes - w_min * p.w_stage_bytes < min_slots * p.slot_bytes) --a_stages;
+  if (p.nchunks * ((p.total_tiles + num_sms() - 1) / num_sms()) < a_stages) a_stages = 2;
+  p.a_stages = a_stages;
+  const int avail = budget - a_stages * p.a_stage_bytes;
   int n_slots = (avail - w_min * p.w_stage_bytes) / p.slot_bytes;
   if (n_slots > kMaxSlots) n_slots = kMaxSlots;
   if (n_slots < 2) { n_slots = 2; }
@@ -544,15 +678,17 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   B200SVS_REQUIRE(w_stages >= 2, "conv1d_tc: not enough shared memory (block_n=%d)", a->block_n);
   p.n_slots = n_slots;
   p.w_stages = w_stages;
-  // with a residual, about half of the slots hold prefetched residual tiles, the other half are stores in flight
-  // per epilogue group: chunk i's slot is needed again by chunk i + n_slots, so a group may keep at most
-  // (n_slots - 2) / 2 of its own store groups pending; with a residual half of that, the rest of the slots
-  // then hold prefetched residual tiles
-  p.stores_in_flight = (ep.res1 || ep.res2) ? (n_slots - 1) / 2 : n_slots - 1;
+  // Slot recycling: after committing the store of chunk i the store thread waits until at most S bulk groups
+  // are still reading shared memory and frees the slot of chunk i - S.  wait_group.read only covers the smem
+  // read (fast), so S = 1 is enough to keep the store thread from blocking; a small S frees slots early, which
+  // gives the residual prefetch (and the epilogue's next write) a lead of n_slots - S - 1 chunks.
+  p.stores_in_flight = 1;
+  if (const char* e = getenv("B200SVS_TC_SIF")) { int v = atoi(e); if (v >= 0 && v <= n_slots - 2) p.stores_in_flight = v; }   // tuning knob
   p.tmem_cols = next_pow2_cols(2 * p.msub * a->block_n);
   p.ksub = a->Cin >= kBlockK ? 4 : (a->Cin + 15) / 16;
   p.idesc = make_idesc_f16(128, a->block_n, a->x_dtype == B200SVS_DT_BF16);
   p.ep = ep;
+  p.trace = g_trace; p.trace_cap = g_trace_cap;
 
   const int el16 = a->x_dtype == B200SVS_DT_BF16 ? 1 : 0;
   CUtensorMap tmA, tmW, tmR, tmR2, tmO32, tmO16;
@@ -595,7 +731,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     if (r) return r;
   }
 
-  const size_t smem = (size_t)kAStages * p.a_stage_bytes + (size_t)p.w_stages * p.w_stage_bytes +
+  const size_t smem = (size_t)p.a_stages * p.a_stage_bytes + (size_t)p.w_stages * p.w_stage_bytes +
                       (size_t)p.n_slots * p.slot_bytes + 512 + bias_bytes + 1024;
   static size_t configured = 0;
   if (smem > configured) {

@@ -1,0 +1,63 @@
+"""Per-tile pipeline timeline of conv1d_tc (diagnostic; GPU box).  Uses b200svs_conv1d_tc_set_trace.
+Stamp slots (clock64 of the CTA's SM):
+  0 producer: activation load of the tile issued     1 producer: last weight load of the tile issued
+  2 mma: accumulator free (tmem_empty)               3 mma: activation tile landed (a_full)
+  4 mma: last MMA + commit issued                    5 epilogue: accumulator ready (tmem_full)
+  6 epilogue: tile done (warp 4)                     7 epilogue: cycles waiting for staging slots (e_full)
+  8 store: first chunk of the tile ready             9 store: last chunk's store issued + slot recycled
+ 10 epilogue: cycles waiting for tcgen05.ld
+    python tools/trace_conv.py
+"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from music_generation_b200 import _lib, ops, packer
+
+DEV = "cuda"
+CAP = 64
+B, ROWS = 4, 524288            # rows at C=128 (Generator stage 1 of 4 x 2048 frames); scaled so bytes stay equal
+
+
+def run(C, k, dil, res):
+    T = ROWS * 128 // C // B
+    g = torch.Generator().manual_seed(0)
+    w = torch.randn(C, C, k, generator=g) * (C * k) ** -0.5
+    b = torch.randn(C, generator=g) * 0.1
+    pc = packer.pack_conv(w, b, dil=dil).to(DEV)
+    x = (torch.randn(B, T, C, generator=g)).half().to(DEV)
+    o16 = torch.empty(B, T, C, device=DEV, dtype=torch.float16)
+    kw = dict(out16=o16, post_lrelu=0.1)
+    if res:
+        r = torch.randn(B, T, C, device=DEV)
+        kw.update(res1=r, out32=r)
+    for _ in range(2):
+        ops.conv1d(pc, x, **kw)
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev[0].record(); ops.conv1d(pc, x, **kw); ev[1].record(); torch.cuda.synchronize()
+    us = ev[0].elapsed_time(ev[1]) * 1e3
+    buf = torch.zeros(148, CAP, 16, dtype=torch.int64, device=DEV)
+    _lib.call("b200svs_conv1d_tc_set_trace", buf.data_ptr(), CAP)
+    ops.conv1d(pc, x, **kw)
+    torch.cuda.synchronize()
+    _lib.call("b200svs_conv1d_tc_set_trace", None, 0)
+    t = buf.cpu().double()
+    n_it = int((t[0, :, 4] > 0).sum())
+    print(f"\nC={C} k={k} dil={dil} res={res}: {us:.1f} us, T={T}, tiles/CTA~{n_it}")
+    for cta in (0, 77):
+        tt = t[cta, :n_it]
+        base = tt[0, 0]
+        lo, hi = 4, n_it - 2          # steady state
+        per_tile = (tt[hi, 4] - tt[lo, 4]) / (hi - lo)
+        d = lambda a, b_: float((tt[lo:hi, a] - tt[lo:hi, b_]).mean())
+        print(f"  cta {cta}: cycles/tile {per_tile:.0f} | A issue->landed(mma sees) {d(3,0):.0f} | mma waits acc-free->A landed {d(3,2):.0f}"
+              f" | mma issue span {d(4,3):.0f} | mma done->epi start {d(5,4):.0f} | epi span {d(6,5):.0f}"
+              f" (slot wait {float(tt[lo:hi,7].mean()):.0f}, ld wait {float(tt[lo:hi,10].mean()):.0f})"
+              f" | store first->last {d(9,8):.0f} | epi done->store done {d(9,6):.0f}")
+        if cta == 0:
+            for i in range(3, 7):
+                print("     tile", i, [int(v - base) for v in tt[i, [0, 1, 2, 3, 4, 5, 6, 8, 9]]])
+
+
+for cfg in [(128, 3, 1, False), (128, 3, 1, True), (128, 11, 5, False), (64, 3, 1, False), (64, 7, 3, True), (32, 3, 1, False), (32, 11, 5, False), (32, 7, 1, True), (256, 3, 1, False)]:
+    run(*cfg)
