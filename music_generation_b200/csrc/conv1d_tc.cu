@@ -86,27 +86,13 @@ __device__ __forceinline__ uint32_t pack16(float a, float b, int dtype) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
-struct EpiCtx {
-  const b200svs_epilogue* ep;
-  uint32_t slot;          // shared-space address of the staging slot (fp32 area); 16-bit area at + slot16_off
-  int slot16_off, slot_r2_off;
-  int row;                // row inside the 128-row sub-tile (= TMEM lane)
-  int half;               // which 16 of the chunk's 32 columns this thread owns (0 / 1)
-  int b;                  // batch index
-  int pcol;               // first packed accumulator column of this thread's 16 (bias / gbias index)
-  int gate_off;           // GATE: packed-column distance between the tanh and the sigmoid half
-  bool row_live;
-  bool need32;            // fp32 area is stored (out32 != NULL)
-  const float* bias_s;    // bias staged in shared memory (NULL: no bias)
-};
-
 __device__ __forceinline__ float4 lds128(uint32_t a) {
   float4 v;
   asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
   return v;
 }
-__device__ __forceinline__ void sts128(uint32_t a, float4 v) {
-  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+__device__ __forceinline__ void sts128(uint32_t a, float x, float y, float z, float w) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
 }
 __device__ __forceinline__ void sts128u(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
@@ -119,87 +105,6 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
   }
   __half2 h = __floats2half2_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
-}
-
-// 16 output columns of one row.  acc[] = raw accumulator bits (GATE: acc = tanh half, acc2 = sigmoid half).
-// Static indexing only (registers).  PLAIN: alpha == scale == 1, no sequence mask, no speaker bias - the
-// Generator's case - so the affine / mask arithmetic disappears.  BF: 16-bit output is bf16.  SPLIT: [hi|lo|hi].
-template <int ACT, bool RES, bool PLAIN, bool BF, bool SPLIT>
-__device__ __forceinline__ void epi_chunk(const EpiCtx& c, const uint32_t* acc, const uint32_t* acc2) {
-  const b200svs_epilogue& ep = *c.ep;
-  const float* gb = (!PLAIN && ep.gbias) ? ep.gbias + static_cast<size_t>(c.b) * ep.gbias_ld : nullptr;
-  const float s = c.row_live ? ep.scale : 0.0f;
-  const float alpha = ep.alpha;
-  const bool has_res1 = RES && ep.res1 != nullptr;
-  const bool has_res2 = RES && ep.res2 != nullptr;
-  const bool lre = ep.post_lrelu != 0;
-  const float slope = ep.post_slope;
-  const uint32_t row32 = c.slot + c.row * 128;
-  uint32_t p16[8];
-  uint32_t l16[SPLIT ? 8 : 1];
-#pragma unroll
-  for (int jj = 0; jj < 4; ++jj) {
-    const int j = c.half * 4 + jj;                 // 16-byte chunk index inside the 128-byte fp32 row
-    float v[4];
-    float4 bq = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (c.bias_s) bq = *reinterpret_cast<const float4*>(c.bias_s + c.pcol + 4 * jj);
-    v[0] = __uint_as_float(acc[4 * jj]) + bq.x; v[1] = __uint_as_float(acc[4 * jj + 1]) + bq.y;
-    v[2] = __uint_as_float(acc[4 * jj + 2]) + bq.z; v[3] = __uint_as_float(acc[4 * jj + 3]) + bq.w;
-    if (gb) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) v[i] += __ldg(gb + c.pcol + 4 * jj + i);
-    }
-    if (ACT == B200SVS_ACT_GATE) {
-      float4 b2 = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (c.bias_s) b2 = *reinterpret_cast<const float4*>(c.bias_s + c.pcol + c.gate_off + 4 * jj);
-      float y[4] = {__uint_as_float(acc2[4 * jj]) + b2.x, __uint_as_float(acc2[4 * jj + 1]) + b2.y,
-                    __uint_as_float(acc2[4 * jj + 2]) + b2.z, __uint_as_float(acc2[4 * jj + 3]) + b2.w};
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        if (gb) y[i] += __ldg(gb + c.pcol + c.gate_off + 4 * jj + i);
-        v[i] = tanhf(v[i]) * (1.0f / (1.0f + expf(-y[i])));
-      }
-    } else {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) v[i] = act_fn<ACT>(v[i]);
-    }
-    const uint32_t phys = (j ^ (c.row & 7)) << 4;
-    float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (has_res1) r = lds128(row32 + phys);
-    if (has_res2) {
-      const float4 q = lds128(row32 + c.slot_r2_off + phys);
-      r.x += q.x; r.y += q.y; r.z += q.z; r.w += q.w;
-    }
-    if (PLAIN) {
-      if (RES) { v[0] += r.x; v[1] += r.y; v[2] += r.z; v[3] += r.w; }
-    } else {   // (alpha * v + res1 + res2) * scale * mask
-      v[0] = fmaf(v[0], alpha, r.x) * s; v[1] = fmaf(v[1], alpha, r.y) * s;
-      v[2] = fmaf(v[2], alpha, r.z) * s; v[3] = fmaf(v[3], alpha, r.w) * s;
-    }
-    if (c.need32) sts128(row32 + phys, make_float4(v[0], v[1], v[2], v[3]));
-    if (lre) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) v[i] = fmaxf(v[i], v[i] * slope);     // leaky-ReLU, 0 < slope < 1
-    }
-    p16[2 * jj] = pack2<BF>(v[0], v[1]);
-    p16[2 * jj + 1] = pack2<BF>(v[2], v[3]);
-    if constexpr (SPLIT) {   // lo = v - hi, so that hi + lo == v to ~2^-22
-#pragma unroll
-      for (int i = 0; i < 4; ++i) v[i] -= __half2float(__float2half_rn(v[i]));
-      l16[2 * jj] = pack2<false>(v[0], v[1]);
-      l16[2 * jj + 1] = pack2<false>(v[2], v[3]);
-    }
-  }
-  if (ep.out16) {
-    const uint32_t row16 = c.slot + c.slot16_off + c.row * 64;
-    const int sw = (c.row >> 1) & 3;     // SWIZZLE_64B: 16-B chunk index ^= address bits [7:8]
-#pragma unroll
-    for (int jj = 0; jj < 2; ++jj) {
-      const uint32_t off = ((c.half * 2 + jj) ^ sw) << 4;
-      sts128u(row16 + off, p16[4 * jj], p16[4 * jj + 1], p16[4 * jj + 2], p16[4 * jj + 3]);
-      if constexpr (SPLIT) sts128u(row16 + kSlot16Bytes + off, l16[4 * jj], l16[4 * jj + 1], l16[4 * jj + 2], l16[4 * jj + 3]);
-    }
-  }
 }
 
 static_assert(sizeof(TcBarriers) <= 512, "barrier block must fit its 512-byte reservation");
@@ -221,80 +126,158 @@ __device__ __forceinline__ TileCoord tile_coord(const ConvTcParams& p, int tile)
 }
 
 // The epilogue of one CTA: 8 warps; warp w and w + 4 share TMEM lane quadrant w % 4 and split each 32-column
-// chunk 16 / 16 (two warps per scheduler).  Everything that is constant for the launch is a template
-// parameter, so a chunk is straight-line code; the accumulators of chunk i + 1 are fetched from TMEM while
-// chunk i is processed.  Finished chunks are handed to the store thread through s_ready (no CTA barrier).
-template <int ACT, bool RES, bool PLAIN, bool BF, bool SPLIT>
+// chunk 16 / 16 (two warps per scheduler).  One thread owns 16 output columns of one time row per chunk.
+// Everything constant for the launch is a template parameter or lives in a register (swizzled staging
+// offsets, slopes), so a chunk is straight-line code; the accumulators of chunk i + 1 are fetched from TMEM
+// while chunk i is processed.  Finished chunks are handed to the store thread through s_ready (no CTA barrier).
+//   RES: 0 none, 1 res1 only, 2 res2 (+ res1 if present).  PLAIN: alpha == scale == 1, no sequence mask, no
+//   speaker bias (the Generator's case).  BF: 16-bit output is bf16.  SPLIT: fp16 [hi | lo | hi] output.
+template <int ACT, int RES, bool PLAIN, bool BF, bool SPLIT>
 __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
-                                              uint32_t smE_u, const float* bias_s) {
+                                              uint32_t smE_u, uint32_t bias_u) {
   constexpr bool GATE = ACT == B200SVS_ACT_GATE;
   const b200svs_epilogue& ep = p.ep;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q = warp & 3;
   const int row = q * 32 + lane;
   const int half = (warp - 4) >> 2;
-  const int half_n = p.block_n >> 1;
-  const int acc_cols = p.msub * p.block_n;
+  const int block_n = p.block_n, half_n = p.block_n >> 1;
+  const int acc_cols = p.msub * block_n;
   const int cps = p.chunks_per_sub;
   const int n_chunks = p.msub * cps;
-  const bool tracer = p.trace != nullptr && threadIdx.x == 128;
-  EpiCtx c;
-  c.ep = &ep; c.slot16_off = p.slot16_off; c.slot_r2_off = p.slot_r2_off; c.row = row; c.half = half;
-  c.need32 = ep.out32 != nullptr;
-  c.gate_off = half_n;
-  c.bias_s = ep.bias ? bias_s : nullptr;
+  const int n_slots = p.n_slots, slot_bytes = p.slot_bytes;
+  const bool need32 = ep.out32 != nullptr, has16 = ep.out16 != nullptr;
+  const bool has_res1 = ep.res1 != nullptr;
+  const float slope = ep.post_lrelu ? ep.post_slope : 1.0f;     // max(v, v * 1) == v: no branch for "no lrelu"
+  const float alpha = ep.alpha;
+  const float* gbias = PLAIN ? nullptr : ep.gbias;
+  // this thread's 16-byte cells inside a staging slot (fp32 area SWIZZLE_128B, 16-bit area SWIZZLE_64B)
+  uint32_t off32[4], off16[2];
+#pragma unroll
+  for (int jj = 0; jj < 4; ++jj) off32[jj] = row * 128 + (((half * 4 + jj) ^ (row & 7)) << 4);
+#pragma unroll
+  for (int jj = 0; jj < 2; ++jj) off16[jj] = p.slot16_off + row * 64 + (((half * 2 + jj) ^ ((row >> 1) & 3)) << 4);
+  const uint32_t r2_off = p.slot_r2_off;
+
+  auto process = [&](const uint32_t* a0, const uint32_t* a1, uint32_t slot_u, int pcol, int b, float s) {
+    float v[16];
+    const uint32_t ba = bias_u + pcol * 4;
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) {
+      const float4 bq = lds128(ba + 16 * jj);
+      v[4 * jj] = __uint_as_float(a0[4 * jj]) + bq.x; v[4 * jj + 1] = __uint_as_float(a0[4 * jj + 1]) + bq.y;
+      v[4 * jj + 2] = __uint_as_float(a0[4 * jj + 2]) + bq.z; v[4 * jj + 3] = __uint_as_float(a0[4 * jj + 3]) + bq.w;
+    }
+    if constexpr (!PLAIN) {
+      if (gbias) {
+        const float* gb = gbias + static_cast<size_t>(b) * ep.gbias_ld + pcol;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] += __ldg(gb + i);
+      }
+    }
+    if constexpr (GATE) {
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) {
+        const float4 bq = lds128(ba + half_n * 4 + 16 * jj);
+        float y[4] = {__uint_as_float(a1[4 * jj]) + bq.x, __uint_as_float(a1[4 * jj + 1]) + bq.y,
+                      __uint_as_float(a1[4 * jj + 2]) + bq.z, __uint_as_float(a1[4 * jj + 3]) + bq.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          if (gbias) y[i] += __ldg(gbias + static_cast<size_t>(b) * ep.gbias_ld + pcol + half_n + 4 * jj + i);
+          v[4 * jj + i] = tanhf(v[4 * jj + i]) * (1.0f / (1.0f + expf(-y[i])));
+        }
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] = act_fn<ACT>(v[i]);
+    }
+    if constexpr (RES != 0) {
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) {
+        float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (RES == 1 || has_res1) r = lds128(slot_u + off32[jj]);
+        if constexpr (RES == 2) {
+          const float4 q2 = lds128(slot_u + r2_off + off32[jj]);
+          r.x += q2.x; r.y += q2.y; r.z += q2.z; r.w += q2.w;
+        }
+        if constexpr (PLAIN) {
+          v[4 * jj] += r.x; v[4 * jj + 1] += r.y; v[4 * jj + 2] += r.z; v[4 * jj + 3] += r.w;
+        } else {   // (alpha * v + res1 + res2) * scale * mask
+          v[4 * jj] = fmaf(v[4 * jj], alpha, r.x) * s; v[4 * jj + 1] = fmaf(v[4 * jj + 1], alpha, r.y) * s;
+          v[4 * jj + 2] = fmaf(v[4 * jj + 2], alpha, r.z) * s; v[4 * jj + 3] = fmaf(v[4 * jj + 3], alpha, r.w) * s;
+        }
+      }
+    } else if constexpr (!PLAIN) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] = fmaf(v[i], alpha, 0.0f) * s;
+    }
+    if (need32) {
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) sts128(slot_u + off32[jj], v[4 * jj], v[4 * jj + 1], v[4 * jj + 2], v[4 * jj + 3]);
+    }
+    if (has16) {
+      uint32_t p16[8];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], v[i] * slope);     // leaky-ReLU, 0 < slope <= 1
+#pragma unroll
+      for (int i = 0; i < 8; ++i) p16[i] = pack2<BF>(v[2 * i], v[2 * i + 1]);
+      sts128u(slot_u + off16[0], p16[0], p16[1], p16[2], p16[3]);
+      sts128u(slot_u + off16[1], p16[4], p16[5], p16[6], p16[7]);
+      if constexpr (SPLIT) {   // lo = v - hi, so that hi + lo == v to ~2^-22
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] -= __half2float(__float2half_rn(v[i]));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) p16[i] = pack2<false>(v[2 * i], v[2 * i + 1]);
+        sts128u(slot_u + kSlot16Bytes + off16[0], p16[0], p16[1], p16[2], p16[3]);
+        sts128u(slot_u + kSlot16Bytes + off16[1], p16[4], p16[5], p16[6], p16[7]);
+      }
+    }
+  };
+
   int it = 0, sl = 0;
   uint32_t eph = 0;
   for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
     const int acc = it & 1;
     const TileCoord tc = tile_coord(p, tile);
-    c.b = tc.b;
     const int len_b = ep.lens ? __ldg(ep.lens + tc.b) : p.T;
+    const int pcol0 = tc.n_idx * block_n + half * 16;
     mbar_wait(&bars->tmem_full[acc], (it >> 1) & 1);
     tc_fence_after();
-    long long w_e = 0;
-    if (tracer) trace_stamp(p, it, 5, clock64());
+    if (threadIdx.x == 128) trace_stamp(p, it, 5, clock64());
     const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * acc_cols + half * 16;
     uint32_t ra0[16], rb0[GATE ? 1 : 16], ra1[GATE ? 16 : 1];
-    auto fetch = [&](int ci, uint32_t* r0, uint32_t* r1) {
-      const int ms = ci >= cps ? 1 : 0;                  // msub <= 2
-      const uint32_t col = ms * p.block_n + (ci - ms * cps) * kEpiCols;
-      tmem_ld16_nowait(taddr + col, r0);
-      if (GATE) tmem_ld16_nowait(taddr + half_n + col, r1);
-    };
-    auto finish = [&](int ci, uint32_t* r0, uint32_t* r1) {
+    // chunk ci: sub-tile ms = ci / cps, column chunk ch = ci % cps (msub <= 2)
+    auto finish = [&](int ci, const uint32_t* r0, const uint32_t* r1) {
       const int ms = ci >= cps ? 1 : 0;
-      const int ch = ci - ms * cps;
+      const int ch = ci - (ms ? cps : 0);
       const int tsub = tc.t0 + ms * 128;
-      c.row_live = tsub + row < len_b;
-      c.pcol = tc.n_idx * p.block_n + ch * kEpiCols + half * 16;
-      c.slot = smE_u + sl * p.slot_bytes;
-      long long t0 = 0;
-      if (tracer) t0 = clock64();
+      const float s = tsub + row < len_b ? ep.scale : 0.0f;
       mbar_wait(&bars->e_full[sl], eph);
-      if (tracer) w_e += clock64() - t0;
-      if (tsub < p.T) epi_chunk<ACT, RES, PLAIN, BF, SPLIT>(c, r0, r1);
+      if (tsub < p.T) process(r0, r1, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, tc.b, s);
       fence_proxy_async();             // generic-proxy smem writes -> visible to the TMA store
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars->s_ready[sl]);
-      if (++sl == p.n_slots) { sl = 0; eph ^= 1; }
+      if (++sl == n_slots) { sl = 0; eph ^= 1; }
     };
     if constexpr (GATE) {              // two accumulator halves per chunk: no register room for a prefetch
       for (int ci = 0; ci < n_chunks; ++ci) {
-        fetch(ci, ra0, ra1);
+        const int ms = ci >= cps ? 1 : 0;
+        const uint32_t col = ms * block_n + (ci - (ms ? cps : 0)) * kEpiCols;
+        tmem_ld16_nowait(taddr + col, ra0);
+        tmem_ld16_nowait(taddr + half_n + col, ra1);
         tmem_ld_wait16(ra0);
         tmem_ld_wait16(ra1);
         finish(ci, ra0, ra1);
       }
-    } else {
-      fetch(0, ra0, ra1);
+    } else {                           // block_n == cps * 32: chunk ci sits at TMEM column ci * 32
+      tmem_ld16_nowait(taddr, ra0);
       for (int ci = 0; ci < n_chunks; ci += 2) {
         tmem_ld_wait16(ra0);
-        if (ci + 1 < n_chunks) fetch(ci + 1, rb0, ra1);
+        if (ci + 1 < n_chunks) tmem_ld16_nowait(taddr + (ci + 1) * kEpiCols, rb0);
         finish(ci, ra0, ra1);
         if (ci + 1 < n_chunks) {
           tmem_ld_wait16(rb0);
-          if (ci + 2 < n_chunks) fetch(ci + 2, ra0, ra1);
+          if (ci + 2 < n_chunks) tmem_ld16_nowait(taddr + (ci + 2) * kEpiCols, ra0);
           finish(ci + 1, rb0, ra1);
         }
       }
@@ -302,13 +285,13 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
     tc_fence_before();
     __syncwarp();
     if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
-    if (tracer) { trace_stamp(p, it, 6, clock64()); trace_stamp(p, it, 7, w_e); }
+    if (threadIdx.x == 128) trace_stamp(p, it, 6, clock64());
   }
 }
 
-template <bool RES, bool BF>
+template <int RES, bool BF>
 __device__ __forceinline__ void epilogue_dispatch2(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
-                                                   uint32_t smE_u, const float* bias_s, bool plain, bool split) {
+                                                   uint32_t smE_u, uint32_t bias_s, bool plain, bool split) {
   const int act = p.ep.act;
   if (split) {   // host restricts split outputs to NONE / RELU, fp16
     if (act == B200SVS_ACT_RELU) epilogue_loop<B200SVS_ACT_RELU, RES, false, false, true>(p, bars, tmem_base, smE_u, bias_s);
@@ -328,18 +311,21 @@ __device__ __forceinline__ void epilogue_dispatch2(const ConvTcParams& p, TcBarr
   }
 }
 __device__ __forceinline__ void epilogue_dispatch(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
-                                                  uint32_t smE_u, const float* bias_s) {
+                                                  uint32_t smE_u, uint32_t bias_s) {
   const b200svs_epilogue& ep = p.ep;
-  const bool res = ep.res1 != nullptr || ep.res2 != nullptr;
+  const int res = ep.res2 != nullptr ? 2 : (ep.res1 != nullptr ? 1 : 0);
   const bool plain = ep.alpha == 1.0f && ep.scale == 1.0f && ep.lens == nullptr && ep.gbias == nullptr;
   const bool split = ep.out16 && ep.out16_dtype == B200SVS_DT_F16_SPLIT;
   const bool bf = ep.out16 && ep.out16_dtype == B200SVS_DT_BF16;
-  if (res) {
-    if (bf) epilogue_dispatch2<true, true>(p, bars, tmem_base, smE_u, bias_s, plain, split);
-    else epilogue_dispatch2<true, false>(p, bars, tmem_base, smE_u, bias_s, plain, split);
+  if (res == 2) {
+    if (bf) epilogue_dispatch2<2, true>(p, bars, tmem_base, smE_u, bias_s, plain, split);
+    else epilogue_dispatch2<2, false>(p, bars, tmem_base, smE_u, bias_s, plain, split);
+  } else if (res == 1) {
+    if (bf) epilogue_dispatch2<1, true>(p, bars, tmem_base, smE_u, bias_s, plain, split);
+    else epilogue_dispatch2<1, false>(p, bars, tmem_base, smE_u, bias_s, plain, split);
   } else {
-    if (bf) epilogue_dispatch2<false, true>(p, bars, tmem_base, smE_u, bias_s, plain, split);
-    else epilogue_dispatch2<false, false>(p, bars, tmem_base, smE_u, bias_s, plain, split);
+    if (bf) epilogue_dispatch2<0, true>(p, bars, tmem_base, smE_u, bias_s, plain, split);
+    else epilogue_dispatch2<0, false>(p, bars, tmem_base, smE_u, bias_s, plain, split);
   }
 }
 
@@ -437,8 +423,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     tmem_alloc(&bars->tmem_base, p.tmem_cols);
     tmem_relinquish();
   }
-  if (p.ep.bias)
-    for (int i = threadIdx.x; i < p.cout_pad; i += kTcThreads) bias_s[i] = __ldg(p.ep.bias + i);
+  for (int i = threadIdx.x; i < p.cout_pad; i += kTcThreads) bias_s[i] = p.ep.bias ? __ldg(p.ep.bias + i) : 0.0f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -574,7 +559,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else if (warp >= 4 && warp < 12) {
-    epilogue_dispatch(p, bars, tmem_base, smem_u32(smE), bias_s);
+    epilogue_dispatch(p, bars, tmem_base, smem_u32(smE), smem_u32(bias_s));
   }
 
   tc_fence_before();
@@ -656,7 +641,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   p.slot_bytes = p.slot16_off + (ep.out16 ? kSlot16Bytes : 0) + (split16 ? kSlot16Bytes : 0);
   // shared memory: 2 activation stages, >= 3 weight stages (or all k-steps of a tile if fewer), then as many
   // staging slots as fit (stores in flight + residual prefetch), the rest to weight stages
-  const int bias_bytes = ep.bias ? a->Cout_pad * 4 : 0;
+  const int bias_bytes = a->Cout_pad * 4;     // staged bias (zeros when there is none)
   const int budget = max_smem_optin() - 1024 - 1024 - bias_bytes;   // alignment slack + barriers + bias
   const int ksteps = a->ntaps * p.nchunks;
   int w_min = ksteps < 3 ? ksteps : 3;
