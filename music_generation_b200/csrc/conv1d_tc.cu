@@ -43,7 +43,7 @@ constexpr int kEpiThreads = 256;            // 8 epilogue warps
 constexpr int kTcThreads = 128 + kEpiThreads + 32;   // + warp 12: weight-ring producer
 
 struct ConvTcParams {
-  int T, tiles_t, m_tiles, n_tiles, total_tiles;
+  int T, batch, tiles_t, m_tiles, n_tiles, total_tiles;
   int ntaps, nchunks, dil, pad_left, cout_pad, block_n, msub;
   int a_boxes, a_box_rows, a_stage_bytes;  // activation tile = a_boxes TMA boxes of a_box_rows rows
   int a_stages, w_stages, w_stage_bytes;
@@ -113,17 +113,29 @@ __device__ __forceinline__ void trace_stamp(const ConvTcParams& p, int it, int s
   if (p.trace && it < p.trace_cap) p.trace[(static_cast<size_t>(blockIdx.x) * p.trace_cap + it) * 16 + slot] = v;
 }
 
-struct TileCoord {
-  int n_idx, b, t0;
+// Walks this CTA's tiles (tile = blockIdx.x + i * gridDim.x, ordered [n_idx][b][time tile]) without the two
+// integer divisions per tile a direct decode costs every role.
+struct TileIter {
+  int tile, n_idx, b, tt, d_b, d_t;
+  __device__ __forceinline__ explicit TileIter(const ConvTcParams& p) {
+    tile = blockIdx.x;
+    n_idx = tile / p.m_tiles;
+    const int m = tile - n_idx * p.m_tiles;
+    b = m / p.tiles_t;
+    tt = m - b * p.tiles_t;
+    d_b = gridDim.x / p.tiles_t;
+    d_t = gridDim.x - d_b * p.tiles_t;
+  }
+  __device__ __forceinline__ bool valid(const ConvTcParams& p) const { return tile < p.total_tiles; }
+  __device__ __forceinline__ int t0(const ConvTcParams& p) const { return tt * (128 * p.msub); }
+  __device__ __forceinline__ void next(const ConvTcParams& p) {
+    tile += gridDim.x;
+    tt += d_t;
+    b += d_b;
+    if (tt >= p.tiles_t) { tt -= p.tiles_t; ++b; }
+    while (b >= p.batch) { b -= p.batch; ++n_idx; }
+  }
 };
-__device__ __forceinline__ TileCoord tile_coord(const ConvTcParams& p, int tile) {
-  TileCoord c;
-  c.n_idx = tile / p.m_tiles;
-  const int m = tile - c.n_idx * p.m_tiles;
-  c.b = m / p.tiles_t;
-  c.t0 = (m - c.b * p.tiles_t) * (128 * p.msub);
-  return c;
-}
 
 // The epilogue of one CTA: 8 warps; warp w and w + 4 share TMEM lane quadrant w % 4 and split each 32-column
 // chunk 16 / 16 (two warps per scheduler).  One thread owns 16 output columns of one time row per chunk.
@@ -236,11 +248,11 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
 
   int it = 0, sl = 0;
   uint32_t eph = 0;
-  for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+  for (TileIter ti(p); ti.valid(p); ti.next(p), ++it) {
     const int acc = it & 1;
-    const TileCoord tc = tile_coord(p, tile);
-    const int len_b = ep.lens ? __ldg(ep.lens + tc.b) : p.T;
-    const int pcol0 = tc.n_idx * block_n + half * 16;
+    const int tile_b = ti.b, tile_t0 = ti.t0(p);
+    const int len_b = ep.lens ? __ldg(ep.lens + tile_b) : p.T;
+    const int pcol0 = ti.n_idx * block_n + half * 16;
     mbar_wait(&bars->tmem_full[acc], (it >> 1) & 1);
     tc_fence_after();
     if (threadIdx.x == 128) trace_stamp(p, it, 5, clock64());
@@ -250,10 +262,10 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
     auto finish = [&](int ci, const uint32_t* r0, const uint32_t* r1) {
       const int ms = ci >= cps ? 1 : 0;
       const int ch = ci - (ms ? cps : 0);
-      const int tsub = tc.t0 + ms * 128;
+      const int tsub = tile_t0 + ms * 128;
       const float s = tsub + row < len_b ? ep.scale : 0.0f;
       mbar_wait(&bars->e_full[sl], eph);
-      if (tsub < p.T) process(r0, r1, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, tc.b, s);
+      if (tsub < p.T) process(r0, r1, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, tile_b, s);
       fence_proxy_async();             // generic-proxy smem writes -> visible to the TMA store
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars->s_ready[sl]);
@@ -436,8 +448,8 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int as = 0, it = 0;
       uint32_t aph = 0;
       const uint32_t a_tx = static_cast<uint32_t>(p.a_boxes) * p.a_box_rows * kRowBytes;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-        const TileCoord tc = tile_coord(p, tile);
+      for (TileIter ti(p); ti.valid(p); ti.next(p), ++it) {
+        const int tile_t0 = ti.t0(p);
         for (int ch = 0; ch < p.nchunks; ++ch) {
           mbar_wait(&bars->a_empty[as], aph ^ 1);
           if (ch == 0) trace_stamp(p, it, 0, clock64());
@@ -445,7 +457,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           mbar_arrive_expect_tx(&bars->a_full[as], a_tx);
           for (int bx = 0; bx < p.a_boxes; ++bx)
             tma_load_3d(sa + bx * p.a_box_rows * kRowBytes, &tmA, &bars->a_full[as], ch * kBlockK,
-                        tc.t0 - p.pad_left + bx * p.a_box_rows, tc.b);
+                        tile_t0 - p.pad_left + bx * p.a_box_rows, ti.b);
           if (++as == p.a_stages) { as = 0; aph ^= 1; }
         }
       }
@@ -455,8 +467,8 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       // ------------------------------------------------------------ weight-ring TMA producer
       int ws = 0, it = 0;
       uint32_t wph = 0;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-        const int n_idx = tile / p.m_tiles;
+      for (TileIter ti(p); ti.valid(p); ti.next(p), ++it) {
+        const int n_idx = ti.n_idx;
         for (int ch = 0; ch < p.nchunks; ++ch) {
           for (int tap = 0; tap < p.ntaps; ++tap) {
             mbar_wait(&bars->w_empty[ws], wph ^ 1);
@@ -494,10 +506,10 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t sph = 0;
       const bool split16 = ep.out16 && ep.out16_dtype == B200SVS_DT_F16_SPLIT;
       int it = 0;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-        const TileCoord tc = tile_coord(p, tile);
+      for (TileIter ti(p); ti.valid(p); ti.next(p), ++it) {
+        const TileIter& tc = ti;
         for (int ms = 0; ms < p.msub; ++ms) {
-          const int tsub = tc.t0 + ms * 128;
+          const int tsub = ti.t0(p) + ms * 128;
           for (int ch = 0; ch < p.chunks_per_sub; ++ch) {
             mbar_wait(&bars->s_ready[sl], sph);
             if (ms == 0 && ch == 0) trace_stamp(p, it, 8, clock64());
@@ -539,10 +551,10 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       // ------------------------------------------------------------ epilogue staging producer
       int sl = 0;
       uint32_t eph = 0;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-        const TileCoord tc = tile_coord(p, tile);
+      for (TileIter ti(p); ti.valid(p); ti.next(p)) {
+        const TileIter& tc = ti;
         for (int ms = 0; ms < p.msub; ++ms) {
-          const int t = tc.t0 + ms * 128;
+          const int t = ti.t0(p) + ms * 128;
           for (int c = 0; c < p.chunks_per_sub; ++c) {
             mbar_wait(&bars->e_empty[sl], eph ^ 1);
             if ((has_res1 || has_res2) && t < p.T) {
@@ -612,7 +624,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   B200SVS_REQUIRE(ep.n_valid > 0 && ep.n_valid <= n_tiles * n_out_tile, "conv1d_tc: n_valid=%d", ep.n_valid);
 
   ConvTcParams p;
-  p.T = a->T;
+  p.T = a->T; p.batch = a->B;
   p.ntaps = a->ntaps; p.nchunks = (a->Cin + kBlockK - 1) / kBlockK;
   p.dil = a->dil; p.pad_left = a->pad_left; p.cout_pad = a->Cout_pad; p.block_n = a->block_n;
   p.n_tiles = n_tiles; p.n_out_tile = n_out_tile;

@@ -32,11 +32,16 @@ def _round_up(x, m):
 
 
 def choose_block_n(cout):
-    """N tile of the tensor-core conv: a multiple of 32 (epilogue chunk), <= 256.  128 is preferred
-    for wide layers: TMEM then holds 2 x 2 accumulators and the kernel runs 256-row tiles in which
-    every weight tile feeds two MMAs (conv1d_tc.cu)."""
+    """N tile of the tensor-core conv: a multiple of 32 (epilogue chunk), <= 256.
+    256 when it divides cout: an N=256 MMA reads 12 KB of shared memory per 128 cycles and runs at ~94 % of the
+    tensor peak, an N=128 one needs 8 KB per 64 cycles - all of the SM's shared-memory bandwidth - and measures
+    79-126 cycles next to the TMA / epilogue traffic (tools/trace_conv.py bn).  Otherwise 128 is preferred for
+    wide layers: TMEM then holds 2 x 2 accumulators and the kernel runs 256-row tiles in which every weight
+    tile feeds two MMAs (conv1d_tc.cu)."""
     if cout <= 128:
         return _round_up(cout, 32)
+    if cout % 256 == 0:
+        return 256
     best = None
     for bn in (128, 192, 160, 224, 256):
         pad = _round_up(cout, bn)

@@ -18,12 +18,12 @@ CAP = 64
 B, ROWS = 4, 524288            # rows at C=128 (Generator stage 1 of 4 x 2048 frames); scaled so bytes stay equal
 
 
-def run(C, k, dil, res):
+def run(C, k, dil, res, block_n=None):
     T = ROWS * 128 // C // B
     g = torch.Generator().manual_seed(0)
     w = torch.randn(C, C, k, generator=g) * (C * k) ** -0.5
     b = torch.randn(C, generator=g) * 0.1
-    pc = packer.pack_conv(w, b, dil=dil).to(DEV)
+    pc = packer.pack_conv(w, b, dil=dil, block_n=block_n).to(DEV)
     x = (torch.randn(B, T, C, generator=g)).half().to(DEV)
     o16 = torch.empty(B, T, C, device=DEV, dtype=torch.float16)
     kw = dict(out16=o16, post_lrelu=0.1)
@@ -43,7 +43,7 @@ def run(C, k, dil, res):
     _lib.call("b200svs_conv1d_tc_set_trace", None, 0)
     t = buf.cpu().double()
     n_it = int((t[0, :, 4] > 0).sum())
-    print(f"\nC={C} k={k} dil={dil} res={res}: {us:.1f} us, T={T}, tiles/CTA~{n_it}")
+    print(f"\nC={C} k={k} dil={dil} res={res} block_n={pc.block_n}: {us:.1f} us, T={T}, tiles/CTA~{n_it}")
     for cta in (0, 77):
         tt = t[cta, :n_it]
         base = tt[0, 0]
@@ -59,5 +59,7 @@ def run(C, k, dil, res):
                 print("     tile", i, [int(v - base) for v in tt[i, [0, 1, 2, 3, 4, 5, 6, 8, 9]]])
 
 
-for cfg in [(128, 3, 1, False), (128, 3, 1, True), (128, 11, 5, False), (64, 3, 1, False), (64, 7, 3, True), (32, 3, 1, False), (32, 11, 5, False), (32, 7, 1, True), (256, 3, 1, False)]:
+import sys as _s
+cfgs = [(256, 3, 1, False, 128), (256, 3, 1, False, 256), (256, 11, 1, False, 128), (256, 11, 1, False, 256), (256, 7, 1, True, 128), (256, 7, 1, True, 256)] if len(_s.argv) > 1 and _s.argv[1] == 'bn' else None
+for cfg in cfgs or [(128, 3, 1, False), (128, 3, 1, True), (128, 11, 5, False), (64, 3, 1, False), (64, 7, 3, True), (32, 3, 1, False), (32, 11, 5, False), (32, 7, 1, True), (256, 3, 1, False)]:
     run(*cfg)
