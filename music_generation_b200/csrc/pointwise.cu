@@ -233,42 +233,70 @@ __global__ void __launch_bounds__(256) sample_prior_kernel(const float* stats, i
 }
 
 // ------------------------------------------------------------------ conv_post (C -> 1, k taps) + tanh
-// One thread per output sample; each tap is a dot product over C contiguous 16-bit channels
-// (128-bit loads); weights live in shared memory.  Memory-bound: reads k*C*2 B per sample through L1.
-__global__ void __launch_bounds__(256) conv_post_tanh_kernel(const void* x, int dt, int x_ld, const float* w, int B,
-                                                             int L, int C, int ktaps, float* out) {
-  extern __shared__ float ws[];   // [ktaps][C]
+// A block owns kPostTile consecutive output samples of one utterance.  Every input row (C contiguous 16-bit
+// channels, 128-bit loads) is read ONCE: its thread forms the k partial dot products row . w[tap] and leaves
+// them in shared memory; after a barrier each output sample sums its k partials (tap j of sample t is the
+// partial j of row t + j - pad) and applies tanh.  Weights are broadcast reads from shared memory.
+constexpr int kPostTile = 256;
+constexpr int kPostMaxTaps = 16;
+constexpr int kPostMaxC = 64;
+template <bool BF>
+__global__ void __launch_bounds__(kPostTile) conv_post_tanh_kernel(const void* x, int x_ld, const float* w, int B, int L,
+                                                                    int C, int ktaps, int tiles_per_row, float* out) {
+  extern __shared__ float smem_post[];
+  float* ws = smem_post;                               // [ktaps][C]
+  float* part = ws + ktaps * C;                        // [ktaps][kPostTile + kPostMaxTaps]
+  constexpr int kStride = kPostTile + kPostMaxTaps;
   for (int i = threadIdx.x; i < ktaps * C; i += blockDim.x) ws[i] = w[i];
   __syncthreads();
-  const long long n = static_cast<long long>(B) * L;
   const int pad = ktaps / 2;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int b = static_cast<int>(i / L), t = static_cast<int>(i - static_cast<long long>(b) * L);
-    float acc = 0.f;
-    for (int k = 0; k < ktaps; ++k) {
-      const int tt = t + k - pad;
-      if (tt < 0 || tt >= L) continue;
-      const size_t base = (static_cast<size_t>(b) * L + tt) * x_ld;
-      const float* wk = ws + k * C;
-      for (int c = 0; c < C; c += 8) {
-        const uint4 q = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(x) + base + c);
+  const int b = blockIdx.x / tiles_per_row;
+  const int t0 = (blockIdx.x - b * tiles_per_row) * kPostTile;
+  const int rows = kPostTile + ktaps - 1;
+  const uint16_t* xb = reinterpret_cast<const uint16_t*>(x) + static_cast<size_t>(b) * L * x_ld;
+  for (int r = threadIdx.x; r < rows; r += kPostTile) {
+    const int t = t0 - pad + r;
+    float acc[kPostMaxTaps];
+#pragma unroll
+    for (int k = 0; k < kPostMaxTaps; ++k) acc[k] = 0.f;
+    if (t >= 0 && t < L) {
+      const uint4* src = reinterpret_cast<const uint4*>(xb + static_cast<size_t>(t) * x_ld);
+      for (int c8 = 0; c8 < C / 8; ++c8) {
+        const uint4 q = __ldg(src + c8);
         const uint32_t u[4] = {q.x, q.y, q.z, q.w};
+        float xv[8];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          float lo, hi;
-          if (dt == B200SVS_DT_BF16) {
-            lo = __uint_as_float(u[j] << 16); hi = __uint_as_float(u[j] & 0xFFFF0000u);
+          if (BF) {
+            xv[2 * j] = __uint_as_float(u[j] << 16); xv[2 * j + 1] = __uint_as_float(u[j] & 0xFFFF0000u);
           } else {
-            const __half2 h2 = *reinterpret_cast<const __half2*>(&u[j]);
-            lo = __low2float(h2); hi = __high2float(h2);
+            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&u[j]));
+            xv[2 * j] = f.x; xv[2 * j + 1] = f.y;
           }
-          acc = fmaf(lo, wk[c + 2 * j], acc);
-          acc = fmaf(hi, wk[c + 2 * j + 1], acc);
+        }
+#pragma unroll
+        for (int k = 0; k < kPostMaxTaps; ++k) {
+          if (k < ktaps) {
+            const float4 w0 = *reinterpret_cast<const float4*>(ws + k * C + c8 * 8);
+            const float4 w1 = *reinterpret_cast<const float4*>(ws + k * C + c8 * 8 + 4);
+            float a = acc[k];
+            a = fmaf(xv[0], w0.x, a); a = fmaf(xv[1], w0.y, a); a = fmaf(xv[2], w0.z, a); a = fmaf(xv[3], w0.w, a);
+            a = fmaf(xv[4], w1.x, a); a = fmaf(xv[5], w1.y, a); a = fmaf(xv[6], w1.z, a); a = fmaf(xv[7], w1.w, a);
+            acc[k] = a;
+          }
         }
       }
     }
-    out[i] = tanhf(acc);
+#pragma unroll
+    for (int k = 0; k < kPostMaxTaps; ++k)
+      if (k < ktaps) part[k * kStride + r] = acc[k];
+  }
+  __syncthreads();
+  const int t = t0 + threadIdx.x;
+  if (t < L) {
+    float v = 0.f;
+    for (int k = 0; k < ktaps; ++k) v += part[k * kStride + threadIdx.x + k];     // same tap order as a direct conv
+    out[static_cast<size_t>(b) * L + t] = tanhf(v);
   }
 }
 
@@ -404,9 +432,15 @@ int b200svs_conv_post_tanh(const void* x, int32_t x_dtype, int32_t x_ld, const f
   B200SVS_REQUIRE(x && w && out && B > 0 && L > 0, "conv_post_tanh: bad argument");
   B200SVS_REQUIRE(C % 8 == 0 && x_ld % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0,
                   "conv_post_tanh: C=%d ld=%d must be multiples of 8, x 16-B aligned", C, x_ld);
-  const long long n = static_cast<long long>(B) * L;
-  conv_post_tanh_kernel<<<grid_1d(n, 256, num_sms() * 32), 256, ktaps * C * sizeof(float), as_stream(stream)>>>(
-      x, x_dtype, x_ld, w, B, L, C, ktaps, out);
+  B200SVS_REQUIRE(ktaps >= 1 && ktaps <= kPostMaxTaps && C <= kPostMaxC, "conv_post_tanh: ktaps=%d (<= %d), C=%d (<= %d)",
+                  ktaps, kPostMaxTaps, C, kPostMaxC);
+  const int tiles_per_row = (L + kPostTile - 1) / kPostTile;
+  const size_t smem = (static_cast<size_t>(ktaps) * C + static_cast<size_t>(ktaps) * (kPostTile + kPostMaxTaps)) * sizeof(float);
+  const unsigned grid = static_cast<unsigned>(B) * tiles_per_row;
+  if (x_dtype == B200SVS_DT_BF16)
+    conv_post_tanh_kernel<true><<<grid, kPostTile, smem, as_stream(stream)>>>(x, x_ld, w, B, L, C, ktaps, tiles_per_row, out);
+  else
+    conv_post_tanh_kernel<false><<<grid, kPostTile, smem, as_stream(stream)>>>(x, x_ld, w, B, L, C, ktaps, tiles_per_row, out);
   return check_launch("conv_post_tanh_kernel");
 }
 

@@ -38,8 +38,8 @@ class SynthesizerTrn(nn.Module):
                  n_heads, n_layers, kernel_size, p_dropout, resblock, resblock_kernel_sizes,
                  resblock_dilation_sizes, upsample_rates, upsample_initial_channel, upsample_kernel_sizes,
                  n_speakers=0, gin_channels=0, use_sdp=True, n_vocab_note=100, *, operand_dtype="fp16",
-                 max_position_embeddings=2000, generator_chunk_frames=32768, f0_precision="split", seed=1234,
-                 **kwargs):
+                 max_position_embeddings=2000, generator_chunk_frames=32768, f0_precision="split",
+                 text_precision="split", seed=1234, **kwargs):
         super().__init__()
         if hidden_channels != 192 or n_heads != 2:
             raise ValueError("kernels are specialised for hidden_channels=192, n_heads=2 (ours_ae.json)")
@@ -57,6 +57,9 @@ class SynthesizerTrn(nn.Module):
         if f0_precision not in ("split", "fp32"):
             raise ValueError("f0_precision must be 'split' (tensor cores, fp16 hi/lo operands) or 'fp32' (SIMT)")
         self.f0_precision = f0_precision
+        if text_precision not in ("split", "fp32"):
+            raise ValueError("text_precision must be 'split' or 'fp32'")
+        self.text_precision = text_precision
         self.hop = 1
         for u in self.upsample_rates:
             self.hop *= u
@@ -143,7 +146,9 @@ class SynthesizerTrn(nn.Module):
                          ("emb_phoneme.weight", "emb_note_pitch.weight", "emb_phone_shengdiao.weight"))
         P["emb_dur"] = (sd[te + ".emb_note_duration.weight"].reshape(-1).contiguous().to(dev),
                         sd[te + ".emb_note_duration.bias"].contiguous().to(dev))
-        P["text_enc"] = enc(te + ".encoder", self.n_layers, True)
+        t_split = self.text_precision == "split"
+        P["text_enc"] = enc(te + ".encoder", self.n_layers, not t_split, split=t_split)
+        P["text_mode"] = "split" if t_split else "f32"
         dp = "duration_predictor"
         P["dp"] = [(conv(f"{dp}.conv_{i}", f32=True), sd[f"{dp}.norm_{i}.gamma"].to(dev), sd[f"{dp}.norm_{i}.beta"].to(dev))
                    for i in (1, 2, 3)]
@@ -382,7 +387,11 @@ class SynthesizerTrn(nn.Module):
         plen = torch.empty(B, device=dev, dtype=torch.int32)
         h = torch.empty(B, Pn, H, device=dev, dtype=f32)
         ops.text_embed(x, note_pitch_id, phone_shengdiao, note_duration, *P["emb"], *P["emb_dur"], x_lengths, plen, h)
-        self._encoder(P["text_enc"], h, None, plen, "f32")
+        hs = None
+        if P["text_mode"] == "split":     # fp16 (hi, lo) split copy for the tensor-core path: (h + 0) * mask == h
+            hs = torch.empty(B, Pn, 3 * H, device=dev, dtype=torch.float16)
+            ops.add_pos_mask(h, torch.zeros(Pn, H, device=dev, dtype=f32), plen, out16=hs, split16=True)
+        self._encoder(P["text_enc"], h, hs, plen, P["text_mode"])
 
         # 2. durations (models_ae.py:622-627)
         if ph_dur is None:
