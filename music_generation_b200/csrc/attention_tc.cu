@@ -4,14 +4,17 @@
 // [B,H,T,T] scores:
 //   S = (Q K^T)/sqrt(d) + band(q.rel_k) ; masked_fill(key >= len, -1e4) ; P = softmax(S)
 //   O = P V + sum_{|r|<=w} P[i,i+r] rel_v[r]
-// One CTA = 128 query rows of one (batch, head); thread r owns query row r = TMEM lane r.
-// Per 64-key tile:  TMA(K_j) -> tcgen05.mma S = Q.K_j^T (TMEM, 64 cols) -> softmax in registers
-// (online max/sum, fp32) -> P written to shared memory as the next MMA's A operand (SWIZZLE_128B,
-// K-major) -> tcgen05.mma PV = P.V_j (TMEM, 96 cols) -> O = O*alpha + PV in registers.
+// One CTA = 128 query rows of one (batch, head), warp-specialised and software-pipelined over 64-key tiles:
+//   warps 0-3 : softmax (thread r owns query row r = TMEM lane r): S_j from TMEM -> online max/sum (fp32,
+//               log2 domain, ex2.approx) -> P_j to shared memory as the PV MMA's A operand (SWIZZLE_128B,
+//               K-major); folds PV_{j-1} into the register accumulator O (O = O*alpha + PV)
+//   warp 4    : tcgen05.mma issuer (one elected thread): S_{j+1} = Q.K_{j+1}^T is issued while the softmax
+//               warps work on S_j (S double-buffered in TMEM), PV_j = P_j.V_j as soon as P_j is published
+//   warp 5    : TMA loader (K double-buffered, V single-buffered)
 // V is consumed K-major from a transposed copy V^T [B,C,T] written by attn_prep_kernel.
 //
-// SPLIT mode (F0 predictor, whose output is quantised by f0_to_coarse: SURVEY.md 7.3-C): every
-// operand is an fp16 (hi, lo) pair with x = hi + lo to ~2^-22, and every product is three MMAs
+// SPLIT mode (phoneme encoder and F0 predictor, whose outputs cross float->int boundaries):
+// every operand is an fp16 (hi, lo) pair with x = hi + lo to ~2^-22, and every product is three MMAs
 // (hi.hi + hi.lo + lo.hi) accumulated in fp32 - tensor-core speed at fp32-class accuracy.
 #include "common.cuh"
 #include "api_internal.h"
@@ -27,6 +30,8 @@ constexpr int kQChunkBytes = kTQ * 128;   // 16 KB  [128 rows][64 x 16-bit]
 constexpr int kKChunkBytes = kTK * 128;   //  8 KB
 constexpr int kVBytes = kHD * 128;        // 12 KB  [96 d rows][64 keys]
 constexpr int kPBytes = kTQ * 128;        // 16 KB  [128 q rows][64 keys]
+constexpr int kAttnThreads = kTQ + 64;    // 4 softmax warps + MMA warp + TMA warp
+constexpr float kLog2e = 1.4426950408889634f;
 
 struct AttnTcParams {
   const void* qk_hi; const void* qk_lo; int qk_ld;   // [B,T,2C] 16-bit (q | k)
@@ -38,7 +43,11 @@ struct AttnTcParams {
 };
 
 struct __align__(8) AttnBars {
-  uint64_t qbar, kbar, vbar, sbar, obar;
+  uint64_t qbar;
+  uint64_t k_full[2], k_empty[2];
+  uint64_t v_full, v_empty;
+  uint64_t s_full[2], s_free[2];     // S_j in TMEM ready / read out by the softmax warps
+  uint64_t p_full, o_full;           // P_j published in shared memory / PV_j complete in TMEM
   uint32_t tmem_base;
 };
 
@@ -58,34 +67,40 @@ __device__ __forceinline__ float rt16(float a, int dtype) {   // round trip thro
   if (dtype == B200SVS_DT_BF16) return __bfloat162float(__float2bfloat16_rn(a));
   return __half2float(__float2half_rn(a));
 }
+__device__ __forceinline__ float ex2f(float x) {              // 2^x, 2 ulp; ex2(-inf) = 0
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 template <bool SPLIT>
-__global__ void __launch_bounds__(kTQ, SPLIT ? 1 : 2)
+__global__ void __launch_bounds__(kAttnThreads, SPLIT ? 1 : 2)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant__ CUtensorMap tmKh,
                     const __grid_constant__ CUtensorMap tmVh, const __grid_constant__ CUtensorMap tmQl,
                     const __grid_constant__ CUtensorMap tmKl, const __grid_constant__ CUtensorMap tmVl,
                     const AttnTcParams p) {
   constexpr int NP = SPLIT ? 2 : 1;
+  constexpr int kKStage = NP * 2 * kKChunkBytes;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smQ = smem;                                   // [NP][2 chunks][16 KB]
-  uint8_t* smK = smQ + NP * 2 * kQChunkBytes;            // [NP][2 chunks][8 KB]
-  uint8_t* smV = smK + NP * 2 * kKChunkBytes;            // [NP][12 KB]
+  uint8_t* smK = smQ + NP * 2 * kQChunkBytes;            // [2 stages][NP][2 chunks][8 KB]
+  uint8_t* smV = smK + 2 * kKStage;                      // [NP][12 KB]
   uint8_t* smP = smV + NP * kVBytes;                     // [NP][16 KB]
-  float* qrel = reinterpret_cast<float*>(smP + NP * kPBytes);   // [128][9]
-  float* band = qrel + kTQ * kNR;                               // [128][9]
+  float* qrel = reinterpret_cast<float*>(smP + NP * kPBytes);   // [128][9]  (q/sqrt(d)).rel_k * log2(e)
+  float* band = qrel + kTQ * kNR;                               // [128][9]  band scores (log2 domain)
   AttnBars* bars = reinterpret_cast<AttnBars*>(band + kTQ * kNR);
 
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q0 = blockIdx.x * kTQ, h = blockIdx.y, b = blockIdx.z;
   const int len = p.lens ? min(__ldg(p.lens + b), p.T) : p.T;
   const int dt = SPLIT ? B200SVS_DT_F16 : p.dtype;
-  const int t = q0 + tid;
+  const int t = q0 + tid;                                // query row of a softmax thread
   const size_t orow = static_cast<size_t>(b) * p.T + t;
   const int oc = h * kHD;
 
   if (q0 >= len) {   // whole tile is padding: zeros (the reference's values there are masked by every consumer)
-    if (t < p.T) {
+    if (tid < kTQ && t < p.T) {
       for (int c = 0; c < kHD; ++c) {
         if (p.out32) p.out32[orow * p.out32_ld + oc + c] = 0.f;
         if (p.out16) {
@@ -99,245 +114,304 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
   }
 
   if (tid == 0) {
-    mbar_init(&bars->qbar, 1); mbar_init(&bars->kbar, 1); mbar_init(&bars->vbar, 1);
-    mbar_init(&bars->sbar, 1); mbar_init(&bars->obar, 1);
+    mbar_init(&bars->qbar, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bars->k_full[i], 1); mbar_init(&bars->k_empty[i], 1);
+      mbar_init(&bars->s_full[i], 1); mbar_init(&bars->s_free[i], kTQ / 32);
+    }
+    mbar_init(&bars->v_full, 1); mbar_init(&bars->v_empty, 1);
+    mbar_init(&bars->p_full, kTQ / 32); mbar_init(&bars->o_full, 1);
     fence_barrier_init();
     prefetch_tmap(&tmQh); prefetch_tmap(&tmKh); prefetch_tmap(&tmVh);
   }
-  if (warp == 0) {
+  if (warp == 4) {
     tmem_alloc(&bars->tmem_base, 256);
     tmem_relinquish();
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_s = bars->tmem_base;          // S : 64 columns
-  const uint32_t tmem_o = tmem_s + 64;              // PV: 96 columns
+  const uint32_t tmem_s = bars->tmem_base;          // S : 2 x 64 columns
+  const uint32_t tmem_o = tmem_s + 2 * kTK;         // PV: 96 columns
   const int n_kt = (len + kTK - 1) / kTK;
 
-  auto load_k = [&](int j) {
-    mbar_arrive_expect_tx(&bars->kbar, NP * 2 * kKChunkBytes);
-    for (int c = 0; c < 2; ++c) {
-      tma_load_3d(smK + c * kKChunkBytes, &tmKh, &bars->kbar, p.C + oc + c * 64, j * kTK, b);
-      if (SPLIT) tma_load_3d(smK + (2 + c) * kKChunkBytes, &tmKl, &bars->kbar, p.C + oc + c * 64, j * kTK, b);
-    }
-  };
-  auto load_v = [&](int j) {
-    mbar_arrive_expect_tx(&bars->vbar, NP * kVBytes);
-    tma_load_3d(smV, &tmVh, &bars->vbar, j * kTK, oc, b);
-    if (SPLIT) tma_load_3d(smV + kVBytes, &tmVl, &bars->vbar, j * kTK, oc, b);
-  };
-  if (tid == 0) {
-    mbar_arrive_expect_tx(&bars->qbar, NP * 2 * kQChunkBytes);
-    for (int c = 0; c < 2; ++c) {
-      tma_load_3d(smQ + c * kQChunkBytes, &tmQh, &bars->qbar, oc + c * 64, q0, b);
-      if (SPLIT) tma_load_3d(smQ + (2 + c) * kQChunkBytes, &tmQl, &bars->qbar, oc + c * 64, q0, b);
-    }
-    load_k(0);
-    load_v(0);
-  }
-
-  // (q_i / sqrt(d)) . rel_k[w] for the 9 band offsets; q read back from global (16-bit hi [+ lo])
-  const float scale = rsqrtf(static_cast<float>(kHD));
-  {
-    float a[kNR];
-#pragma unroll
-    for (int w = 0; w < kNR; ++w) a[w] = 0.f;
-    if (t < p.T) {
-      const size_t qi = orow * p.qk_ld + oc;
-      for (int c = 0; c < kHD; ++c) {
-        float qv = ld16f(p.qk_hi, qi + c, dt);
-        if (SPLIT) qv += ld16f(p.qk_lo, qi + c, dt);
-#pragma unroll
-        for (int w = 0; w < kNR; ++w) a[w] = fmaf(qv, __ldg(p.rel_k + w * kHD + c), a[w]);
+  if (warp == 5) {
+    if (lane == 0) {
+      // ------------------------------------------------------------ TMA loader: Q, K0, then (K_{j+1}, V_j)
+      auto load_k = [&](int j) {
+        const int st = j & 1;
+        mbar_wait(&bars->k_empty[st], ((j >> 1) & 1) ^ 1);
+        uint8_t* dst = smK + st * kKStage;
+        mbar_arrive_expect_tx(&bars->k_full[st], kKStage);
+        for (int c = 0; c < 2; ++c) {
+          tma_load_3d(dst + c * kKChunkBytes, &tmKh, &bars->k_full[st], p.C + oc + c * 64, j * kTK, b);
+          if (SPLIT) tma_load_3d(dst + (2 + c) * kKChunkBytes, &tmKl, &bars->k_full[st], p.C + oc + c * 64, j * kTK, b);
+        }
+      };
+      mbar_arrive_expect_tx(&bars->qbar, NP * 2 * kQChunkBytes);
+      for (int c = 0; c < 2; ++c) {
+        tma_load_3d(smQ + c * kQChunkBytes, &tmQh, &bars->qbar, oc + c * 64, q0, b);
+        if (SPLIT) tma_load_3d(smQ + (2 + c) * kQChunkBytes, &tmQl, &bars->qbar, oc + c * 64, q0, b);
+      }
+      load_k(0);
+      for (int j = 0; j < n_kt; ++j) {
+        if (j + 1 < n_kt) load_k(j + 1);
+        mbar_wait(&bars->v_empty, (j & 1) ^ 1);
+        mbar_arrive_expect_tx(&bars->v_full, NP * kVBytes);
+        tma_load_3d(smV, &tmVh, &bars->v_full, j * kTK, oc, b);
+        if (SPLIT) tma_load_3d(smV + kVBytes, &tmVl, &bars->v_full, j * kTK, oc, b);
       }
     }
+  } else if (warp == 4) {
+    if (elect_one()) {
+      // ------------------------------------------------------------ MMA issuer
+      const uint32_t idesc_s = make_idesc_f16(128, kTK, dt == B200SVS_DT_BF16);
+      const uint32_t idesc_o = make_idesc_f16(128, kHD, dt == B200SVS_DT_BF16);
+      const uint32_t q_u = smem_u32(smQ), k_u = smem_u32(smK), v_u = smem_u32(smV), p_u = smem_u32(smP);
+      auto issue_s = [&](int j) {      // S_j = Q . K_j^T  (d = 96 = 64 + 32)
+        const int st = j & 1;
+        mbar_wait(&bars->k_full[st], (j >> 1) & 1);
+        mbar_wait(&bars->s_free[st], ((j >> 1) & 1) ^ 1);
+        tc_fence_after();
+        uint32_t accum = 0;
 #pragma unroll
-    for (int w = 0; w < kNR; ++w) {
-      qrel[tid * kNR + w] = a[w] * scale;
-      band[tid * kNR + w] = -INFINITY;
-    }
-  }
-
-  const uint32_t idesc_s = make_idesc_f16(128, kTK, dt == B200SVS_DT_BF16);
-  const uint32_t idesc_o = make_idesc_f16(128, kHD, dt == B200SVS_DT_BF16);
-  float m_run = -INFINITY, l_run = 0.f;
-  float o[kHD];
+        for (int c = 0; c < 2; ++c) {
 #pragma unroll
-  for (int c = 0; c < kHD; ++c) o[c] = 0.f;
-
-  for (int j = 0; j < n_kt; ++j) {
-    const int k0 = j * kTK;
-    const uint32_t ph = j & 1;
-    if (tid == 0) {
-      if (j == 0) mbar_wait(&bars->qbar, 0);
-      mbar_wait(&bars->kbar, ph);
-      tc_fence_after();
-      bool first = true;
+          for (int pr = 0; pr < (SPLIT ? 3 : 1); ++pr) {
+            const int pa = pr == 2 ? 1 : 0, pb = pr == 1 ? 1 : 0;       // (hi,hi) (hi,lo) (lo,hi)
+            const uint64_t da = make_desc_k128(q_u + (pa * 2 + c) * kQChunkBytes);
+            const uint64_t db = make_desc_k128(k_u + st * kKStage + (pb * 2 + c) * kKChunkBytes);
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        const int ks = c == 0 ? 4 : 2;     // d = 96 = 64 + 32
-        for (int pr = 0; pr < (SPLIT ? 3 : 1); ++pr) {
-          const int pa = pr == 2 ? 1 : 0, pb = pr == 1 ? 1 : 0;       // (hi,hi) (hi,lo) (lo,hi)
-          const uint64_t da = make_desc_k128(smem_u32(smQ + (pa * 2 + c) * kQChunkBytes));
-          const uint64_t db = make_desc_k128(smem_u32(smK + (pb * 2 + c) * kKChunkBytes));
-          for (int k = 0; k < ks; ++k) {
-            umma_f16(tmem_s, da + 2 * k, db + 2 * k, idesc_s, first ? 0u : 1u);
-            first = false;
+            for (int k = 0; k < (c == 0 ? 4 : 2); ++k) {
+              umma_f16(tmem_s + st * kTK, da + 2 * k, db + 2 * k, idesc_s, accum);
+              accum = 1;
+            }
           }
         }
-      }
-      umma_commit(&bars->sbar);
-    }
-    mbar_wait(&bars->sbar, ph);
-    tc_fence_after();
-    if (tid == 0 && j + 1 < n_kt) load_k(j + 1);      // K buffer is free: S MMAs have completed
-
-    // ---- softmax over this tile's 64 keys (row = thread)
-    float s[kTK];
-    {
-      uint32_t r[32];
-      const uint32_t ta = tmem_s + (static_cast<uint32_t>(warp * 32) << 16);
-      tmem_ld32_nowait(ta, r);
-      tmem_ld_wait();
+        umma_commit(&bars->s_full[st]);
+        umma_commit(&bars->k_empty[st]);
+      };
+      mbar_wait(&bars->qbar, 0);
+      issue_s(0);
+      for (int j = 0; j < n_kt; ++j) {
+        if (j + 1 < n_kt) issue_s(j + 1);
+        mbar_wait(&bars->p_full, j & 1);
+        mbar_wait(&bars->v_full, j & 1);
+        tc_fence_after();
+        uint32_t accum = 0;
 #pragma unroll
-      for (int e = 0; e < 32; ++e) s[e] = __uint_as_float(r[e]) * scale;
-      tmem_ld32_nowait(ta + 32, r);
-      tmem_ld_wait();
+        for (int pr = 0; pr < (SPLIT ? 3 : 1); ++pr) {
+          const int pa = pr == 2 ? 1 : 0, pb = pr == 1 ? 1 : 0;
+          const uint64_t da = make_desc_k128(p_u + pa * kPBytes);
+          const uint64_t db = make_desc_k128(v_u + pb * kVBytes);
 #pragma unroll
-      for (int e = 0; e < 32; ++e) s[32 + e] = __uint_as_float(r[e]) * scale;
-    }
-    const bool near_diag = (k0 <= q0 + kTQ - 1 + kWin) && (k0 + kTK - 1 >= q0 - kWin);
-    const bool tail = k0 + kTK > len;
-    if (near_diag) {
-#pragma unroll
-      for (int e = 0; e < kTK; ++e) {
-        const int d = k0 + e - t + kWin;
-        if (d >= 0 && d < kNR) s[e] += qrel[tid * kNR + d];
+          for (int k = 0; k < kTK / 16; ++k) {
+            umma_f16(tmem_o, da + 2 * k, db + 2 * k, idesc_o, accum);
+            accum = 1;
+          }
+        }
+        umma_commit(&bars->o_full);
+        umma_commit(&bars->v_empty);
       }
     }
-    if (tail) {
+    __syncwarp();
+  } else {
+    // ---------------------------------------------------------------- softmax warps (tid < 128)
+    const float scale2 = rsqrtf(static_cast<float>(kHD)) * kLog2e;     // scores live in the log2 domain
+    {   // (q_i / sqrt(d)) . rel_k[w] for the 9 band offsets; q read back from global (16-bit hi [+ lo])
+      float a[kNR];
 #pragma unroll
-      for (int e = 0; e < kTK; ++e) {
-        const int key = k0 + e;
-        if (key >= len) s[e] = -1e4f;             // masked_fill(mask == 0, -1e4)
-        if (key >= p.T) s[e] = -INFINITY;          // beyond the tensor: not a key at all
-      }
-    }
-    if (near_diag) {
+      for (int w = 0; w < kNR; ++w) a[w] = 0.f;
+      if (t < p.T) {
+        const size_t qi = orow * p.qk_ld + oc;
+        for (int c = 0; c < kHD; ++c) {
+          float qv = ld16f(p.qk_hi, qi + c, dt);
+          if (SPLIT) qv += ld16f(p.qk_lo, qi + c, dt);
 #pragma unroll
-      for (int e = 0; e < kTK; ++e) {
-        const int d = k0 + e - t + kWin;
-        if (d >= 0 && d < kNR && k0 + e < p.T) band[tid * kNR + d] = s[e];
-      }
-    }
-    float mx = s[0];
-#pragma unroll
-    for (int e = 1; e < kTK; ++e) mx = fmaxf(mx, s[e]);
-    const float m_new = fmaxf(m_run, mx);
-    const float alpha = (m_run == -INFINITY) ? 0.f : expf(m_run - m_new);
-    float sum = 0.f;
-    uint8_t* prow = smP + tid * 128;
-#pragma unroll
-    for (int c8 = 0; c8 < 8; ++c8) {
-      float pv[8];
-#pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const float x = s[c8 * 8 + e];
-        pv[e] = (x == -INFINITY) ? 0.f : (SPLIT ? expf(x - m_new) : __expf(x - m_new));
-        sum += pv[e];
-      }
-      const int phys = (c8 ^ (tid & 7)) << 4;
-      *reinterpret_cast<uint4*>(prow + phys) =
-          make_uint4(pk16(pv[0], pv[1], dt), pk16(pv[2], pv[3], dt), pk16(pv[4], pv[5], dt), pk16(pv[6], pv[7], dt));
-      if (SPLIT) {
-#pragma unroll
-        for (int e = 0; e < 8; ++e) pv[e] -= rt16(pv[e], dt);
-        *reinterpret_cast<uint4*>(prow + kPBytes + phys) =
-            make_uint4(pk16(pv[0], pv[1], dt), pk16(pv[2], pv[3], dt), pk16(pv[4], pv[5], dt), pk16(pv[6], pv[7], dt));
-      }
-    }
-    l_run = l_run * alpha + sum;
-    m_run = m_new;
-    fence_proxy_async();
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      mbar_wait(&bars->vbar, ph);
-      tc_fence_after();
-      bool first = true;
-      for (int pr = 0; pr < (SPLIT ? 3 : 1); ++pr) {
-        const int pa = pr == 2 ? 1 : 0, pb = pr == 1 ? 1 : 0;
-        const uint64_t da = make_desc_k128(smem_u32(smP + pa * kPBytes));
-        const uint64_t db = make_desc_k128(smem_u32(smV + pb * kVBytes));
-        for (int k = 0; k < kTK / 16; ++k) {
-          umma_f16(tmem_o, da + 2 * k, db + 2 * k, idesc_o, first ? 0u : 1u);
-          first = false;
+          for (int w = 0; w < kNR; ++w) a[w] = fmaf(qv, __ldg(p.rel_k + w * kHD + c), a[w]);
         }
       }
-      umma_commit(&bars->obar);
+#pragma unroll
+      for (int w = 0; w < kNR; ++w) {
+        qrel[tid * kNR + w] = a[w] * scale2;
+        band[tid * kNR + w] = -INFINITY;
+      }
     }
-    mbar_wait(&bars->obar, ph);
-    tc_fence_after();
-    if (tid == 0 && j + 1 < n_kt) load_v(j + 1);      // V and P buffers are free: PV MMAs have completed
-    {
-      const uint32_t ta = tmem_o + (static_cast<uint32_t>(warp * 32) << 16);
+    float m_run = -INFINITY, l_run = 0.f, alpha_prev = 0.f;
+    float o[kHD];
+#pragma unroll
+    for (int c = 0; c < kHD; ++c) o[c] = 0.f;
+    const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
+    auto fold = [&](float alpha) {       // O = O * alpha + PV  (PV: 96 TMEM columns)
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
         uint32_t r[32];
-        tmem_ld32_nowait(ta + c * 32, r);
+        tmem_ld32_nowait(tmem_o + lane_off + c * 32, r);
         tmem_ld_wait();
 #pragma unroll
         for (int e = 0; e < 32; ++e) o[c * 32 + e] = fmaf(o[c * 32 + e], alpha, __uint_as_float(r[e]));
       }
+    };
+
+    for (int j = 0; j < n_kt; ++j) {
+      const int k0 = j * kTK;
+      const int sb = j & 1;
+      mbar_wait(&bars->s_full[sb], (j >> 1) & 1);
+      tc_fence_after();
+      const uint32_t ta = tmem_s + sb * kTK + lane_off;
+      const bool near_diag = (k0 <= q0 + kTQ - 1 + kWin) && (k0 + kTK - 1 >= q0 - kWin);
+      const bool tail = k0 + kTK > len;
+      const bool slow = near_diag || tail;             // CTA-uniform
+      // score of key k0 + e with the band bias and the masks applied (slow tiles only)
+      auto adjust = [&](uint32_t raw, int e) -> float {
+        float x = __uint_as_float(raw) * scale2;
+        const int d = k0 + e - t + kWin;
+        if (d >= 0 && d < kNR) x += qrel[tid * kNR + d];
+        const int key = k0 + e;
+        if (key >= len) x = -1e4f * kLog2e;            // masked_fill(mask == 0, -1e4)
+        if (key >= p.T) x = -INFINITY;                 // beyond the tensor: not a key at all
+        return x;
+      };
+      // ---- pass 1: row maximum.  Rolled loops over 8-column groups (the next group's TMEM load is in flight
+      // while the current one is reduced): a fully unrolled 64-key body thrashes the instruction cache.
+      float mx = -INFINITY;
+      {
+        uint32_t ra[8], rb[8];
+        tmem_ld8_nowait(ta, ra);
+#pragma unroll 1
+        for (int g = 0; g < kTK / 8; g += 2) {
+          tmem_ld_wait8(ra);
+          tmem_ld8_nowait(ta + (g + 1) * 8, rb);
+          if (slow) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) mx = fmaxf(mx, adjust(ra[e], g * 8 + e));
+          } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) mx = fmaxf(mx, __uint_as_float(ra[e]));
+          }
+          tmem_ld_wait8(rb);
+          if (g + 2 < kTK / 8) tmem_ld8_nowait(ta + (g + 2) * 8, ra);
+          if (slow) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) mx = fmaxf(mx, adjust(rb[e], (g + 1) * 8 + e));
+          } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) mx = fmaxf(mx, __uint_as_float(rb[e]));
+          }
+        }
+      }
+      if (!slow) mx *= scale2;                         // scale2 > 0 commutes with max
+      const float m_new = fmaxf(m_run, mx);
+      const float alpha = (m_run == -INFINITY) ? 0.f : ex2f(m_run - m_new);
+      // ---- PV_{j-1} has to be folded into O (and the P buffer released by its MMAs) before P_j is written
+      if (j > 0) {
+        mbar_wait(&bars->o_full, (j - 1) & 1);
+        tc_fence_after();
+        fold(alpha_prev);
+      }
+      // ---- pass 2: P = 2^(S - m), row sum, publish P as the A operand of the PV MMA
+      float sum = 0.f;
+      uint8_t* prow = smP + tid * 128;
+      auto emit = [&](const uint32_t* r, int g) {      // 8 keys -> one 16-byte cell of the P row
+        float pv[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          float x;
+          if (slow) {
+            const int ee = g * 8 + e;
+            x = adjust(r[e], ee);
+            const int d = k0 + ee - t + kWin;
+            if (near_diag && d >= 0 && d < kNR && k0 + ee < p.T) band[tid * kNR + d] = x;
+            x -= m_new;
+          } else {
+            x = fmaf(__uint_as_float(r[e]), scale2, -m_new);
+          }
+          pv[e] = ex2f(x);                              // ex2(-inf) = 0
+          sum += pv[e];
+        }
+        const int phys = (g ^ (tid & 7)) << 4;
+        *reinterpret_cast<uint4*>(prow + phys) =
+            make_uint4(pk16(pv[0], pv[1], dt), pk16(pv[2], pv[3], dt), pk16(pv[4], pv[5], dt), pk16(pv[6], pv[7], dt));
+        if (SPLIT) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) pv[e] -= rt16(pv[e], dt);
+          *reinterpret_cast<uint4*>(prow + kPBytes + phys) =
+              make_uint4(pk16(pv[0], pv[1], dt), pk16(pv[2], pv[3], dt), pk16(pv[4], pv[5], dt), pk16(pv[6], pv[7], dt));
+        }
+      };
+      {
+        uint32_t ra[8], rb[8];
+        tmem_ld8_nowait(ta, ra);
+#pragma unroll 1
+        for (int g = 0; g < kTK / 8; g += 2) {
+          tmem_ld_wait8(ra);
+          tmem_ld8_nowait(ta + (g + 1) * 8, rb);
+          emit(ra, g);
+          tmem_ld_wait8(rb);
+          if (g + 2 < kTK / 8) tmem_ld8_nowait(ta + (g + 2) * 8, ra);
+          emit(rb, g + 1);
+        }
+      }
+      l_run = l_run * alpha + sum;
+      m_run = m_new;
+      alpha_prev = alpha;
+      fence_proxy_async();               // P (generic-proxy stores) -> visible to the tensor core
+      tc_fence_before();                 // S_j and PV_{j-1} reads are complete
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&bars->s_free[sb]);
+        mbar_arrive(&bars->p_full);
+      }
+    }
+    mbar_wait(&bars->o_full, (n_kt - 1) & 1);
+    tc_fence_after();
+    fold(alpha_prev);
+
+    // ---- relative-value band term, normalisation, stores
+    const bool live = t < len;
+    if (t < p.T) {
+      if (live) {
+#pragma unroll
+        for (int w = 0; w < kNR; ++w) {
+          const float sv = band[tid * kNR + w];
+          if (sv == -INFINITY) continue;
+          const float pw = ex2f(sv - m_run);
+#pragma unroll
+          for (int c = 0; c < kHD; ++c) o[c] = fmaf(pw, __ldg(p.rel_v + w * kHD + c), o[c]);
+        }
+      }
+      const float invl = live ? 1.0f / l_run : 0.f;
+#pragma unroll
+      for (int c = 0; c < kHD; ++c) o[c] = live ? o[c] * invl : 0.f;
+      if (p.out32) {
+        float* op = p.out32 + orow * p.out32_ld + oc;
+#pragma unroll
+        for (int c = 0; c < kHD; c += 4) *reinterpret_cast<float4*>(op + c) = make_float4(o[c], o[c + 1], o[c + 2], o[c + 3]);
+      }
+      if (p.out16) {
+        uint16_t* op = reinterpret_cast<uint16_t*>(p.out16) + orow * p.out16_ld + oc;
+        const int odt = p.out16_split ? B200SVS_DT_F16 : p.out16_dtype;
+#pragma unroll
+        for (int c = 0; c < kHD; c += 8) {
+          const uint4 hi = make_uint4(pk16(o[c], o[c + 1], odt), pk16(o[c + 2], o[c + 3], odt), pk16(o[c + 4], o[c + 5], odt),
+                                      pk16(o[c + 6], o[c + 7], odt));
+          *reinterpret_cast<uint4*>(op + c) = hi;
+          if (p.out16_split) {
+            float lo[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) lo[e] = o[c + e] - rt16(o[c + e], odt);
+            *reinterpret_cast<uint4*>(op + p.C + c) =
+                make_uint4(pk16(lo[0], lo[1], odt), pk16(lo[2], lo[3], odt), pk16(lo[4], lo[5], odt), pk16(lo[6], lo[7], odt));
+            *reinterpret_cast<uint4*>(op + 2 * p.C + c) = hi;
+          }
+        }
+      }
     }
     tc_fence_before();
   }
 
-  // ---- relative-value band term, normalisation, stores
-  const bool live = t < len;
-  if (t < p.T) {
-    if (live) {
-#pragma unroll
-      for (int w = 0; w < kNR; ++w) {
-        const float sv = band[tid * kNR + w];
-        if (sv == -INFINITY) continue;
-        const float pw = SPLIT ? expf(sv - m_run) : __expf(sv - m_run);
-#pragma unroll
-        for (int c = 0; c < kHD; ++c) o[c] = fmaf(pw, __ldg(p.rel_v + w * kHD + c), o[c]);
-      }
-    }
-    const float invl = live ? 1.0f / l_run : 0.f;
-#pragma unroll
-    for (int c = 0; c < kHD; ++c) o[c] = live ? o[c] * invl : 0.f;
-    if (p.out32) {
-      float* op = p.out32 + orow * p.out32_ld + oc;
-#pragma unroll
-      for (int c = 0; c < kHD; c += 4) *reinterpret_cast<float4*>(op + c) = make_float4(o[c], o[c + 1], o[c + 2], o[c + 3]);
-    }
-    if (p.out16) {
-      uint16_t* op = reinterpret_cast<uint16_t*>(p.out16) + orow * p.out16_ld + oc;
-      const int odt = p.out16_split ? B200SVS_DT_F16 : p.out16_dtype;
-#pragma unroll
-      for (int c = 0; c < kHD; c += 8) {
-        const uint4 hi = make_uint4(pk16(o[c], o[c + 1], odt), pk16(o[c + 2], o[c + 3], odt), pk16(o[c + 4], o[c + 5], odt),
-                                    pk16(o[c + 6], o[c + 7], odt));
-        *reinterpret_cast<uint4*>(op + c) = hi;
-        if (p.out16_split) {
-          float lo[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) lo[e] = o[c + e] - rt16(o[c + e], odt);
-          *reinterpret_cast<uint4*>(op + p.C + c) =
-              make_uint4(pk16(lo[0], lo[1], odt), pk16(lo[2], lo[3], odt), pk16(lo[4], lo[5], odt), pk16(lo[6], lo[7], odt));
-          *reinterpret_cast<uint4*>(op + 2 * p.C + c) = hi;
-        }
-      }
-    }
-  }
-
-  tc_fence_before();
   __syncthreads();
-  if (warp == 0) {
+  if (warp == 4) {
     tc_fence_after();
     tmem_dealloc(bars->tmem_base, 256);
   }
@@ -440,7 +514,7 @@ extern "C" int b200svs_attention_tc(const void* qk_hi, const void* qk_lo, const 
   p.out16_split = out16_split; p.rel_k = rel_k; p.rel_v = rel_v; p.lens = lens;
   p.B = B; p.T = T; p.C = C; p.H = H; p.dtype = dtype;
   const int np = split ? 2 : 1;
-  const size_t smem = (size_t)np * (2 * kQChunkBytes + 2 * kKChunkBytes + kVBytes + kPBytes) + 2 * kTQ * kNR * sizeof(float) +
+  const size_t smem = (size_t)np * (2 * kQChunkBytes + 4 * kKChunkBytes + kVBytes + kPBytes) + 2 * kTQ * kNR * sizeof(float) +
                       sizeof(AttnBars) + 1024;
   dim3 grid((T + kTQ - 1) / kTQ, H, B);
   if (split) {
@@ -450,7 +524,7 @@ extern "C" int b200svs_attention_tc(const void* qk_hi, const void* qk_lo, const 
       if (r) return r;
       cfg = true;
     }
-    attention_tc_kernel<true><<<grid, kTQ, smem, as_stream(stream)>>>(tmQ[0], tmK[0], tmV[0], tmQ[1], tmK[1], tmV[1], p);
+    attention_tc_kernel<true><<<grid, kAttnThreads, smem, as_stream(stream)>>>(tmQ[0], tmK[0], tmV[0], tmQ[1], tmK[1], tmV[1], p);
   } else {
     static bool cfg = false;
     if (!cfg) {
@@ -458,7 +532,7 @@ extern "C" int b200svs_attention_tc(const void* qk_hi, const void* qk_lo, const 
       if (r) return r;
       cfg = true;
     }
-    attention_tc_kernel<false><<<grid, kTQ, smem, as_stream(stream)>>>(tmQ[0], tmK[0], tmV[0], tmQ[1], tmK[1], tmV[1], p);
+    attention_tc_kernel<false><<<grid, kAttnThreads, smem, as_stream(stream)>>>(tmQ[0], tmK[0], tmV[0], tmQ[1], tmK[1], tmV[1], p);
   }
   return check_launch("attention_tc_kernel");
 }
