@@ -53,9 +53,9 @@ enum { B200SVS_DT_F16 = 0, B200SVS_DT_BF16 = 1, B200SVS_DT_F16_SPLIT = 2 };
 /* Fused epilogue shared by the conv1d kernels.  For output row (b,t) and packed column c:
  *   v = acc + bias[c] + gbias[b*gbias_ld + c]
  *   v = act(v)                                   (GATE halves the column count)
- *   v = alpha*v + res1[b,t,c'] + res2[b,t,c']    (c' = output column)
+ *   v = alpha*v + res1[b,t,c'] + res2[b,t,c'] + res16[b,t,c']    (c' = output column)
  *   v = v*scale;  v *= (t < lens[b])             (lens == NULL: no mask)
- *   out32[b,t,c'] = v;  out16[b,t,c'] = cvt16(post_lrelu ? lrelu(v, post_slope) : v)
+ *   out32[b,t,c'] = v;  out16r[b,t,c'] = cvt16(v);  out16[b,t,c'] = cvt16(post_lrelu ? lrelu(v, post_slope) : v)
  * Columns c' >= n_valid are not stored by conv1d_f32; conv1d_tc stores through TMA, which clips at
  * 16-byte granularity: columns up to the next multiple of 4 (fp32) / 8 (16-bit) may be written with the
  * zero-padded channels' values, so out32_ld / out16_ld must cover that rounding.  out32 may alias res1
@@ -81,6 +81,12 @@ typedef struct b200svs_epilogue {
   int32_t post_lrelu;
   float post_slope;
   int32_t n_valid;
+  /* conv1d_tc only (act NONE, non-split): 16-bit residual stream.  res16 is added like res1 (same 16-bit type
+   * as the operands); out16r receives cvt16(v) WITHOUT the post-activation and may alias res16. */
+  const void* res16;
+  int32_t res16_ld;
+  void* out16r;
+  int32_t out16r_ld;
 } b200svs_epilogue;
 
 /* 1-D convolution over time as an implicit GEMM (replaces nn.Conv1d / ConvTranspose1d + the pointwise

@@ -25,6 +25,8 @@ class Epilogue(C.Structure):
         ("out32", C.c_void_p), ("out32_ld", C.c_int32),
         ("out16", C.c_void_p), ("out16_ld", C.c_int32), ("out16_dtype", C.c_int32),
         ("post_lrelu", C.c_int32), ("post_slope", C.c_float), ("n_valid", C.c_int32),
+        ("res16", C.c_void_p), ("res16_ld", C.c_int32),
+        ("out16r", C.c_void_p), ("out16r_ld", C.c_int32),
     ]
 
 

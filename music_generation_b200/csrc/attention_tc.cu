@@ -89,7 +89,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
   uint8_t* smP = smV + NP * kVBytes;                     // [NP][16 KB]
   float* qrel = reinterpret_cast<float*>(smP + NP * kPBytes);   // [128][9]  (q/sqrt(d)).rel_k * log2(e)
   float* band = qrel + kTQ * kNR;                               // [128][9]  band scores (log2 domain)
-  AttnBars* bars = reinterpret_cast<AttnBars*>(band + kTQ * kNR);
+  float* relk_s = band + kTQ * kNR;                             // [9][96]
+  float* relv_s = relk_s + kNR * kHD;                           // [9][96]
+  AttnBars* bars = reinterpret_cast<AttnBars*>(relv_s + kNR * kHD);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q0 = blockIdx.x * kTQ, h = blockIdx.y, b = blockIdx.z;
@@ -127,6 +129,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
   if (warp == 4) {
     tmem_alloc(&bars->tmem_base, 256);
     tmem_relinquish();
+  }
+  for (int i = tid; i < kNR * kHD; i += kAttnThreads) {
+    relk_s[i] = __ldg(p.rel_k + i);
+    relv_s[i] = __ldg(p.rel_v + i);
   }
   tc_fence_before();
   __syncthreads();
@@ -218,22 +224,49 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
   } else {
     // ---------------------------------------------------------------- softmax warps (tid < 128)
     const float scale2 = rsqrtf(static_cast<float>(kHD)) * kLog2e;     // scores live in the log2 domain
-    {   // (q_i / sqrt(d)) . rel_k[w] for the 9 band offsets; q read back from global (16-bit hi [+ lo])
+    {   // (q_i / sqrt(d)) . rel_k[w] for the 9 band offsets; q read from the TMA-loaded (swizzled) Q tile
       float a[kNR];
 #pragma unroll
       for (int w = 0; w < kNR; ++w) a[w] = 0.f;
-      if (t < p.T) {
-        const size_t qi = orow * p.qk_ld + oc;
-        for (int c = 0; c < kHD; ++c) {
-          float qv = ld16f(p.qk_hi, qi + c, dt);
-          if (SPLIT) qv += ld16f(p.qk_lo, qi + c, dt);
+      mbar_wait(&bars->qbar, 0);
+#pragma unroll 1
+      for (int cell = 0; cell < kHD / 8; ++cell) {      // 12 cells of 8 channels: chunk 0 holds d 0..63, chunk 1 d 64..95
+        const int c = cell >> 3, jc = cell & 7;
+        const uint8_t* src = smQ + c * kQChunkBytes + tid * 128 + ((jc ^ (tid & 7)) << 4);
+        const uint4 qh = *reinterpret_cast<const uint4*>(src);
+        const uint32_t uh[4] = {qh.x, qh.y, qh.z, qh.w};
+        float qv[8];
 #pragma unroll
-          for (int w = 0; w < kNR; ++w) a[w] = fmaf(qv, __ldg(p.rel_k + w * kHD + c), a[w]);
+        for (int e = 0; e < 4; ++e) {
+          if (dt == B200SVS_DT_BF16) {
+            qv[2 * e] = __uint_as_float(uh[e] << 16); qv[2 * e + 1] = __uint_as_float(uh[e] & 0xFFFF0000u);
+          } else {
+            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&uh[e]));
+            qv[2 * e] = f.x; qv[2 * e + 1] = f.y;
+          }
+        }
+        if (SPLIT) {
+          const uint4 ql = *reinterpret_cast<const uint4*>(src + 2 * kQChunkBytes);
+          const uint32_t ul[4] = {ql.x, ql.y, ql.z, ql.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&ul[e]));
+            qv[2 * e] += f.x; qv[2 * e + 1] += f.y;
+          }
+        }
+#pragma unroll
+        for (int w = 0; w < kNR; ++w) {
+          const float4 k0v = *reinterpret_cast<const float4*>(relk_s + w * kHD + cell * 8);
+          const float4 k1v = *reinterpret_cast<const float4*>(relk_s + w * kHD + cell * 8 + 4);
+          float x = a[w];
+          x = fmaf(qv[0], k0v.x, x); x = fmaf(qv[1], k0v.y, x); x = fmaf(qv[2], k0v.z, x); x = fmaf(qv[3], k0v.w, x);
+          x = fmaf(qv[4], k1v.x, x); x = fmaf(qv[5], k1v.y, x); x = fmaf(qv[6], k1v.z, x); x = fmaf(qv[7], k1v.w, x);
+          a[w] = x;
         }
       }
 #pragma unroll
       for (int w = 0; w < kNR; ++w) {
-        qrel[tid * kNR + w] = a[w] * scale2;
+        qrel[tid * kNR + w] = (t < p.T) ? a[w] * scale2 : 0.f;
         band[tid * kNR + w] = -INFINITY;
       }
     }
@@ -371,13 +404,17 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
     const bool live = t < len;
     if (t < p.T) {
       if (live) {
-#pragma unroll
+#pragma unroll 1
         for (int w = 0; w < kNR; ++w) {
           const float sv = band[tid * kNR + w];
           if (sv == -INFINITY) continue;
           const float pw = ex2f(sv - m_run);
 #pragma unroll
-          for (int c = 0; c < kHD; ++c) o[c] = fmaf(pw, __ldg(p.rel_v + w * kHD + c), o[c]);
+          for (int c = 0; c < kHD; c += 4) {
+            const float4 rv = *reinterpret_cast<const float4*>(relv_s + w * kHD + c);
+            o[c] = fmaf(pw, rv.x, o[c]); o[c + 1] = fmaf(pw, rv.y, o[c + 1]);
+            o[c + 2] = fmaf(pw, rv.z, o[c + 2]); o[c + 3] = fmaf(pw, rv.w, o[c + 3]);
+          }
         }
       }
       const float invl = live ? 1.0f / l_run : 0.f;
@@ -514,7 +551,7 @@ extern "C" int b200svs_attention_tc(const void* qk_hi, const void* qk_lo, const 
   p.out16_split = out16_split; p.rel_k = rel_k; p.rel_v = rel_v; p.lens = lens;
   p.B = B; p.T = T; p.C = C; p.H = H; p.dtype = dtype;
   const int np = split ? 2 : 1;
-  const size_t smem = (size_t)np * (2 * kQChunkBytes + 4 * kKChunkBytes + kVBytes + kPBytes) + 2 * kTQ * kNR * sizeof(float) +
+  const size_t smem = (size_t)np * (2 * kQChunkBytes + 4 * kKChunkBytes + kVBytes + kPBytes) + 2 * kTQ * kNR * sizeof(float) + 2 * kNR * kHD * sizeof(float) +
                       sizeof(AttnBars) + 1024;
   dim3 grid((T + kTQ - 1) / kTQ, H, B);
   if (split) {

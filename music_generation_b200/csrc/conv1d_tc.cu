@@ -49,6 +49,7 @@ struct ConvTcParams {
   int a_stages, w_stages, w_stage_bytes;
   int n_slots, slot_bytes, slot16_off;     // epilogue staging slot: [fp32 area][res2 fp32 area][16-bit area]
   int slot_r2_off;                         // offset of the res2 area inside a slot (0 = none)
+  int slot_raw_off;                        // offset of the raw 16-bit area (res16 in / out16r out) inside a slot
   int stores_in_flight;                    // TMA store groups left pending before a slot is recycled
   int chunks_per_sub, n_out_tile;          // output chunks per 128-row sub-tile; output columns per N tile
   int tmem_cols;
@@ -144,7 +145,7 @@ struct TileIter {
 // while chunk i is processed.  Finished chunks are handed to the store thread through s_ready (no CTA barrier).
 //   RES: 0 none, 1 res1 only, 2 res2 (+ res1 if present).  PLAIN: alpha == scale == 1, no sequence mask, no
 //   speaker bias (the Generator's case).  BF: 16-bit output is bf16.  SPLIT: fp16 [hi | lo | hi] output.
-template <int ACT, int RES, bool PLAIN, bool BF, bool SPLIT>
+template <int ACT, int RES, bool PLAIN, bool BF, bool SPLIT, bool R16 = false>
 __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
                                               uint32_t smE_u, uint32_t bias_u) {
   constexpr bool GATE = ACT == B200SVS_ACT_GATE;
@@ -170,6 +171,9 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
 #pragma unroll
   for (int jj = 0; jj < 2; ++jj) off16[jj] = p.slot16_off + row * 64 + (((half * 2 + jj) ^ ((row >> 1) & 3)) << 4);
   const uint32_t r2_off = p.slot_r2_off;
+  // raw 16-bit area (R16): residual in, un-activated result out, same cells as the activated 16-bit copy
+  const uint32_t raw_delta = static_cast<uint32_t>(p.slot_raw_off - p.slot16_off);
+  const bool has_res16 = R16 && ep.res16 != nullptr, has_out16r = R16 && ep.out16r != nullptr;
 
   auto process = [&](const uint32_t* a0, const uint32_t* a1, uint32_t slot_u, int pcol, int b, float s) {
     float v[16];
@@ -203,11 +207,33 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
 #pragma unroll
       for (int i = 0; i < 16; ++i) v[i] = act_fn<ACT>(v[i]);
     }
+    float r16v[R16 ? 16 : 1];
+    if constexpr (R16) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) r16v[i] = 0.f;
+      if (has_res16) {
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+          const float4 q = lds128(slot_u + raw_delta + off16[jj]);
+          const uint32_t u[4] = {__float_as_uint(q.x), __float_as_uint(q.y), __float_as_uint(q.z), __float_as_uint(q.w)};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            if (BF) {
+              r16v[8 * jj + 2 * e] = __uint_as_float(u[e] << 16); r16v[8 * jj + 2 * e + 1] = __uint_as_float(u[e] & 0xFFFF0000u);
+            } else {
+              const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&u[e]));
+              r16v[8 * jj + 2 * e] = f.x; r16v[8 * jj + 2 * e + 1] = f.y;
+            }
+          }
+        }
+      }
+    }
     if constexpr (RES != 0) {
 #pragma unroll
       for (int jj = 0; jj < 4; ++jj) {
         float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
         if (RES == 1 || has_res1) r = lds128(slot_u + off32[jj]);
+        if constexpr (R16) { r.x += r16v[4 * jj]; r.y += r16v[4 * jj + 1]; r.z += r16v[4 * jj + 2]; r.w += r16v[4 * jj + 3]; }
         if constexpr (RES == 2) {
           const float4 q2 = lds128(slot_u + r2_off + off32[jj]);
           r.x += q2.x; r.y += q2.y; r.z += q2.z; r.w += q2.w;
@@ -219,6 +245,9 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
           v[4 * jj + 2] = fmaf(v[4 * jj + 2], alpha, r.z) * s; v[4 * jj + 3] = fmaf(v[4 * jj + 3], alpha, r.w) * s;
         }
       }
+    } else if constexpr (R16) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] = PLAIN ? v[i] + r16v[i] : fmaf(v[i], alpha, r16v[i]) * s;
     } else if constexpr (!PLAIN) {
 #pragma unroll
       for (int i = 0; i < 16; ++i) v[i] = fmaf(v[i], alpha, 0.0f) * s;
@@ -226,6 +255,15 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
     if (need32) {
 #pragma unroll
       for (int jj = 0; jj < 4; ++jj) sts128(slot_u + off32[jj], v[4 * jj], v[4 * jj + 1], v[4 * jj + 2], v[4 * jj + 3]);
+    }
+    if constexpr (R16) {
+      if (has_out16r) {
+        uint32_t p16[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) p16[i] = pack2<BF>(v[2 * i], v[2 * i + 1]);
+        sts128u(slot_u + raw_delta + off16[0], p16[0], p16[1], p16[2], p16[3]);
+        sts128u(slot_u + raw_delta + off16[1], p16[4], p16[5], p16[6], p16[7]);
+      }
     }
     if (has16) {
       uint32_t p16[8];
@@ -305,6 +343,13 @@ template <int RES, bool BF>
 __device__ __forceinline__ void epilogue_dispatch2(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
                                                    uint32_t smE_u, uint32_t bias_s, bool plain, bool split) {
   const int act = p.ep.act;
+  if (p.ep.res16 || p.ep.out16r) {   // 16-bit residual stream: host restricts it to act NONE, non-split, RES in {0, 2}
+    if (RES == 1) return;
+    constexpr int R = RES == 1 ? 0 : RES;
+    if (plain) epilogue_loop<B200SVS_ACT_NONE, R, true, BF, false, true>(p, bars, tmem_base, smE_u, bias_s);
+    else epilogue_loop<B200SVS_ACT_NONE, R, false, BF, false, true>(p, bars, tmem_base, smE_u, bias_s);
+    return;
+  }
   if (split) {   // host restricts split outputs to NONE / RELU, fp16
     if (act == B200SVS_ACT_RELU) epilogue_loop<B200SVS_ACT_RELU, RES, false, false, true>(p, bars, tmem_base, smE_u, bias_s);
     else epilogue_loop<B200SVS_ACT_NONE, RES, false, false, true>(p, bars, tmem_base, smE_u, bias_s);
@@ -399,7 +444,8 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                  const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmR2,
                  const __grid_constant__ CUtensorMap tmO32,
-                 const __grid_constant__ CUtensorMap tmO16, const ConvTcParams p) {
+                 const __grid_constant__ CUtensorMap tmO16, const __grid_constant__ CUtensorMap tmR16,
+                 const __grid_constant__ CUtensorMap tmO16r, const ConvTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smA = smem;
@@ -421,6 +467,8 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (has_res2) prefetch_tmap(&tmR2);
     if (ep.out32) prefetch_tmap(&tmO32);
     if (ep.out16) prefetch_tmap(&tmO16);
+    if (ep.res16) prefetch_tmap(&tmR16);
+    if (ep.out16r) prefetch_tmap(&tmO16r);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < p.a_stages; ++s) { mbar_init(&bars->a_full[s], 1); mbar_init(&bars->a_empty[s], 1); }
@@ -518,6 +566,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               uint8_t* slot = smE + sl * p.slot_bytes;
               if (ep.out32) tma_store_3d(&tmO32, slot, ocol, tsub, tc.b);
               if (ep.out16) tma_store_3d(&tmO16, slot + p.slot16_off, ocol, tsub, tc.b);
+              if (ep.out16r) tma_store_3d(&tmO16r, slot + p.slot_raw_off, ocol, tsub, tc.b);
               if (split16) {   // [hi | lo | hi]
                 tma_store_3d(&tmO16, slot + p.slot16_off + kSlot16Bytes, ep.n_valid + ocol, tsub, tc.b);
                 tma_store_3d(&tmO16, slot + p.slot16_off, 2 * ep.n_valid + ocol, tsub, tc.b);
@@ -557,9 +606,11 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const int t = ti.t0(p) + ms * 128;
           for (int c = 0; c < p.chunks_per_sub; ++c) {
             mbar_wait(&bars->e_empty[sl], eph ^ 1);
-            if ((has_res1 || has_res2) && t < p.T) {
+            if ((has_res1 || has_res2 || ep.res16) && t < p.T) {
               const int col = tc.n_idx * p.n_out_tile + c * kEpiCols;
-              mbar_arrive_expect_tx(&bars->e_full[sl], (has_res1 ? kSlot32Bytes : 0) + (has_res2 ? kSlot32Bytes : 0));
+              mbar_arrive_expect_tx(&bars->e_full[sl], (has_res1 ? kSlot32Bytes : 0) + (has_res2 ? kSlot32Bytes : 0) +
+                                                           (ep.res16 ? kSlot16Bytes : 0));
+              if (ep.res16) tma_load_3d(smE + sl * p.slot_bytes + p.slot_raw_off, &tmR16, &bars->e_full[sl], col, t, tc.b);
               if (has_res1) tma_load_3d(smE + sl * p.slot_bytes, &tmR, &bars->e_full[sl], col, t, tc.b);
               if (has_res2) tma_load_3d(smE + sl * p.slot_bytes + p.slot_r2_off, &tmR2, &bars->e_full[sl], col, t, tc.b);
             } else {
@@ -614,7 +665,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   const b200svs_epilogue& ep = a->ep;
   const bool gate = ep.act == B200SVS_ACT_GATE;
   B200SVS_REQUIRE(!gate || a->block_n % 64 == 0, "conv1d_tc: GATE needs block_n %% 64 == 0");
-  B200SVS_REQUIRE(ep.out32 || ep.out16, "conv1d_tc: no output");
+  B200SVS_REQUIRE(ep.out32 || ep.out16 || ep.out16r, "conv1d_tc: no output");
   B200SVS_REQUIRE(!ep.out32 || (ep.out32_ld % 4 == 0 && (reinterpret_cast<uintptr_t>(ep.out32) & 15) == 0), "conv1d_tc: out32 alignment");
   B200SVS_REQUIRE(!ep.out16 || (ep.out16_ld % 8 == 0 && (reinterpret_cast<uintptr_t>(ep.out16) & 15) == 0), "conv1d_tc: out16 alignment");
   B200SVS_REQUIRE(!ep.res1 || (ep.res1_ld % 4 == 0 && (reinterpret_cast<uintptr_t>(ep.res1) & 15) == 0), "conv1d_tc: res1 alignment");
@@ -645,12 +696,17 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   p.w_stage_bytes = a->block_n * kRowBytes;
   const bool area32 = ep.res1 || ep.out32;
   p.slot_r2_off = ep.res2 ? (area32 ? kSlot32Bytes : 0) : 0;
-  B200SVS_REQUIRE(!ep.res2 || area32, "conv1d_tc: res2 needs res1 or out32");
   p.slot16_off = (area32 ? kSlot32Bytes : 0) + (ep.res2 ? kSlot32Bytes : 0);
   const bool split16 = ep.out16 && ep.out16_dtype == B200SVS_DT_F16_SPLIT;
   B200SVS_REQUIRE(!split16 || ep.act == B200SVS_ACT_NONE || ep.act == B200SVS_ACT_RELU, "conv1d_tc: split 16-bit output supports act NONE / RELU");
   B200SVS_REQUIRE(!split16 || ep.n_valid % kEpiCols == 0, "conv1d_tc: split 16-bit output needs n_valid %% 32 == 0 (n_valid=%d)", ep.n_valid);
-  p.slot_bytes = p.slot16_off + (ep.out16 ? kSlot16Bytes : 0) + (split16 ? kSlot16Bytes : 0);
+  const bool raw16 = ep.res16 || ep.out16r;
+  B200SVS_REQUIRE(!raw16 || (ep.act == B200SVS_ACT_NONE && !split16 && !ep.res1),
+                  "conv1d_tc: res16 / out16r need act NONE, a non-split output and no fp32 res1");
+  B200SVS_REQUIRE(!ep.res16 || (ep.res16_ld % 8 == 0 && (reinterpret_cast<uintptr_t>(ep.res16) & 15) == 0), "conv1d_tc: res16 alignment");
+  B200SVS_REQUIRE(!ep.out16r || (ep.out16r_ld % 8 == 0 && (reinterpret_cast<uintptr_t>(ep.out16r) & 15) == 0), "conv1d_tc: out16r alignment");
+  p.slot_raw_off = p.slot16_off + (ep.out16 ? kSlot16Bytes : 0) + (split16 ? kSlot16Bytes : 0);
+  p.slot_bytes = p.slot_raw_off + (raw16 ? kSlot16Bytes : 0);
   // shared memory: 2 activation stages, >= 3 weight stages (or all k-steps of a tile if fewer), then as many
   // staging slots as fit (stores in flight + residual prefetch), the rest to weight stages
   const int bias_bytes = a->Cout_pad * 4;     // staged bias (zeros when there is none)
@@ -659,7 +715,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   int w_min = ksteps < 3 ? ksteps : 3;
   if (w_min < 2) w_min = 2;
   // as many activation stages (loads in flight) as leave room for the minimum of everything else
-  const bool has_res = ep.res1 || ep.res2;
+  const bool has_res = ep.res1 || ep.res2 || ep.res16;
   const int min_slots = has_res ? 4 : 3;
   int a_stages = kMaxAStages;
   if (const char* e = getenv("B200SVS_TC_ASTAGES")) { int v = atoi(e); if (v >= 2 && v <= kMaxAStages) a_stages = v; }   // tuning knob
@@ -688,7 +744,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   p.trace = g_trace; p.trace_cap = g_trace_cap;
 
   const int el16 = a->x_dtype == B200SVS_DT_BF16 ? 1 : 0;
-  CUtensorMap tmA, tmW, tmR, tmR2, tmO32, tmO16;
+  CUtensorMap tmA, tmW, tmR, tmR2, tmO32, tmO16, tmR16, tmO16r;
   {
     uint64_t dims[3] = {(uint64_t)a->Cin, (uint64_t)a->T, (uint64_t)a->B};
     uint64_t strides[2] = {(uint64_t)a->x_ld * 2, (uint64_t)a->T * a->x_ld * 2};
@@ -703,7 +759,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     int r = make_tmap(&tmW, el16, a->w, 2, dims, strides, box, 128);
     if (r) return r;
   }
-  tmR = tmA; tmR2 = tmA; tmO32 = tmA; tmO16 = tmA;
+  tmR = tmA; tmR2 = tmA; tmO32 = tmA; tmO16 = tmA; tmR16 = tmA; tmO16r = tmA;
   const uint32_t ebox[3] = {(uint32_t)kEpiCols, 128, 1};
   const uint64_t edims[3] = {(uint64_t)ep.n_valid, (uint64_t)a->T, (uint64_t)a->B};
   if (ep.res1) {
@@ -728,6 +784,17 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     if (r) return r;
   }
 
+  if (ep.res16) {
+    uint64_t strides[2] = {(uint64_t)ep.res16_ld * 2, (uint64_t)a->T * ep.res16_ld * 2};
+    int r = make_tmap(&tmR16, el16, ep.res16, 3, edims, strides, ebox, 64);
+    if (r) return r;
+  }
+  if (ep.out16r) {
+    uint64_t strides[2] = {(uint64_t)ep.out16r_ld * 2, (uint64_t)a->T * ep.out16r_ld * 2};
+    int r = make_tmap(&tmO16r, el16, ep.out16r, 3, edims, strides, ebox, 64);
+    if (r) return r;
+  }
+
   const size_t smem = (size_t)p.a_stages * p.a_stage_bytes + (size_t)p.w_stages * p.w_stage_bytes +
                       (size_t)p.n_slots * p.slot_bytes + 512 + bias_bytes + 1024;
   static size_t configured = 0;
@@ -738,6 +805,6 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     configured = smem;
   }
   int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
-  conv1d_tc_kernel<<<grid, kTcThreads, smem, as_stream(stream)>>>(tmA, tmW, tmR, tmR2, tmO32, tmO16, p);
+  conv1d_tc_kernel<<<grid, kTcThreads, smem, as_stream(stream)>>>(tmA, tmW, tmR, tmR2, tmO32, tmO16, tmR16, tmO16r, p);
   return check_launch("conv1d_tc_kernel");
 }

@@ -78,7 +78,8 @@ class PackedConv:
 
 
 def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, res2=None, lens=None,
-           out32=None, out16=None, post_lrelu=None, w_rows=None, n_valid=None, split16=False):
+           out32=None, out16=None, post_lrelu=None, w_rows=None, n_valid=None, split16=False, res16=None,
+           out16r=None):
     """out = epilogue(conv(x, pc)).  See b200svs_epilogue in include/b200svs.h for the formula.
     `w_rows=(row0, nrows)` restricts the conv to a block of packed output channels (WN res/skip split)."""
     B, T, cin = x.shape
@@ -123,6 +124,10 @@ def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, 
         e.out16, e.out16_ld, e.out16_dtype = out16.data_ptr(), _btc(out16, "out16"), out16_code(out16, split16)
     if post_lrelu is not None:
         e.post_lrelu, e.post_slope = 1, float(post_lrelu)
+    if res16 is not None:      # 16-bit residual input (same dtype as the operands), added like res1
+        e.res16, e.res16_ld = res16.data_ptr(), _btc(res16, "res16")
+    if out16r is not None:     # 16-bit copy of the result WITHOUT the post-activation (may alias res16)
+        e.out16r, e.out16r_ld = out16r.data_ptr(), _btc(out16r, "out16r")
     e.n_valid = n_out if n_valid is None else n_valid
     if _lib.PROFILE is not None:
         frac = 1.0 if w_rows is None else w_rows[1] / pc.cout_pad

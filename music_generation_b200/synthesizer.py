@@ -39,7 +39,7 @@ class SynthesizerTrn(nn.Module):
                  resblock_dilation_sizes, upsample_rates, upsample_initial_channel, upsample_kernel_sizes,
                  n_speakers=0, gin_channels=0, use_sdp=True, n_vocab_note=100, *, operand_dtype="fp16",
                  max_position_embeddings=2000, generator_chunk_frames=32768, f0_precision="split",
-                 text_precision="split", seed=1234, **kwargs):
+                 text_precision="split", generator_residual="fp16", seed=1234, **kwargs):
         super().__init__()
         if hidden_channels != 192 or n_heads != 2:
             raise ValueError("kernels are specialised for hidden_channels=192, n_heads=2 (ours_ae.json)")
@@ -60,6 +60,9 @@ class SynthesizerTrn(nn.Module):
         if text_precision not in ("split", "fp32"):
             raise ValueError("text_precision must be 'split' or 'fp32'")
         self.text_precision = text_precision
+        if generator_residual not in ("fp16", "fp32"):
+            raise ValueError("generator_residual must be 'fp16' (16-bit residual stream; fp16 operand mode only) or 'fp32'")
+        self.generator_residual = generator_residual
         self.hop = 1
         for u in self.upsample_rates:
             self.hop *= u
@@ -322,46 +325,61 @@ class SynthesizerTrn(nn.Module):
         ops.conv1d(P["g_pre"], x16, gbias=gbias, out16=cur16, post_lrelu=LRELU_SLOPE)
         L = T
         n_st = len(self.upsample_rates)
+        r16 = self.generator_residual == "fp16" and dt == torch.float16
         for i, u in enumerate(self.upsample_rates):
             ch = up0 // (2 ** (i + 1))
             Lo = L * u
-            x32 = torch.empty(B, Lo, ch, device=dev, dtype=torch.float32)
+            # stage residual stream: fp32 (x32) or, by default in fp16 mode, 16-bit (xr16: HBM traffic of a
+            # ResBlock pair drops from 16 to 12 bytes per element); xl16 = leaky-ReLU'd copy the convs consume
+            x32 = None if r16 else torch.empty(B, Lo, ch, device=dev, dtype=torch.float32)
+            xr16 = torch.empty(B, Lo, ch, device=dev, dtype=dt) if r16 else None
             xl16 = torch.empty(B, Lo, ch, device=dev, dtype=dt)
             # ConvTranspose1d as a 3-tap conv writing the [B, L, u*ch] view of [B, L*u, ch]
-            ops.conv1d(P["g_ups"][i], cur16, out32=x32.view(B, L, u * ch), out16=xl16.view(B, L, u * ch),
-                       post_lrelu=LRELU_SLOPE)
-            c32 = torch.empty_like(x32)
+            if r16:
+                ops.conv1d(P["g_ups"][i], cur16, out16r=xr16.view(B, L, u * ch), out16=xl16.view(B, L, u * ch),
+                           post_lrelu=LRELU_SLOPE)
+            else:
+                ops.conv1d(P["g_ups"][i], cur16, out32=x32.view(B, L, u * ch), out16=xl16.view(B, L, u * ch),
+                           post_lrelu=LRELU_SLOPE)
+            c32 = None if r16 else torch.empty_like(x32)
+            cr16 = torch.empty_like(xl16) if r16 else None
             cl16 = torch.empty_like(xl16)
             t16 = torch.empty_like(xl16)
-            mrf = torch.empty_like(x32)
+            mrf = torch.empty(B, Lo, ch, device=dev, dtype=torch.float32)
             nxt16 = torch.empty_like(xl16)
             nk = len(P["g_rb"][i])
             next_slope = LRELU_SLOPE if i < n_st - 1 else 0.01      # F.leaky_relu default (models_ae.py:342)
             for j, pairs in enumerate(P["g_rb"][i]):
-                src32, src16 = x32, xl16
+                src32, srcr, src16 = x32, xr16, xl16
                 for m, (c1, c2) in enumerate(pairs):
                     last = m == len(pairs) - 1
                     kw = {}
                     if last:
-                        # MRF: xs = sum_j resblock_j(x); x = xs / num_kernels (models_ae.py:335-341)
+                        # MRF: xs = sum_j resblock_j(x); x = xs / num_kernels (models_ae.py:335-341); fp32 accumulator
                         if j > 0:
                             kw["res2"] = mrf
                         if j < nk - 1:
                             kw.update(out32=mrf)
                         else:
                             kw.update(scale=1.0 / nk, out16=nxt16, post_lrelu=next_slope)
+                    elif r16:
+                        kw.update(out16r=cr16, out16=cl16, post_lrelu=LRELU_SLOPE)
                     else:
                         kw.update(out32=c32, out16=cl16, post_lrelu=LRELU_SLOPE)
+                    if r16:
+                        kw["res16"] = srcr
+                    else:
+                        kw["res1"] = src32
                     if c2 is not None:      # ResBlock1 (modules.py:210-223)
                         ops.conv1d(c1, src16, out16=t16, post_lrelu=LRELU_SLOPE)
-                        ops.conv1d(c2, t16, res1=src32, **kw)
-                        src32, src16 = c32, cl16
+                        ops.conv1d(c2, t16, **kw)
+                        src32, srcr, src16 = c32, cr16, cl16
                     else:                   # ResBlock2 (modules.py:243-252): ping-pong the 16-bit stream,
                         dst16 = t16 if src16 is cl16 else cl16      # the conv reads halo rows of its input
                         if "out16" in kw and not last:
                             kw["out16"] = dst16
-                        ops.conv1d(c1, src16, res1=src32, **kw)
-                        src32, src16 = c32, dst16
+                        ops.conv1d(c1, src16, **kw)
+                        src32, srcr, src16 = c32, cr16, dst16
             cur16, L = nxt16, Lo
         ops.conv_post_tanh(cur16, P["g_post"], out.view(B, L))
 

@@ -31,7 +31,8 @@ def _store(dst, val, split16=False):
 
 
 def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, res2=None, lens=None,
-           out32=None, out16=None, post_lrelu=None, w_rows=None, n_valid=None, split16=False):
+           out32=None, out16=None, post_lrelu=None, w_rows=None, n_valid=None, split16=False, res16=None,
+           out16r=None):
     B, T, cin = x.shape
     assert cin == pc.cin
     xf = x.float()
@@ -73,12 +74,16 @@ def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, 
         y = y + res1.float()[:, :, :nv]
     if res2 is not None:
         y = y + res2.float()[:, :, :nv]
+    if res16 is not None:
+        y = y + res16.float()[:, :, :nv]
     y = y * scale
     m = _mask(lens, B, T)
     if m is not None:
         y = y * m
     if out32 is not None:
         out32[:, :, :nv] = y
+    if out16r is not None:
+        out16r[:, :, :nv] = y.to(out16r.dtype)
     if out16 is not None:
         o = F.leaky_relu(y, post_lrelu) if post_lrelu is not None else y
         if split16:

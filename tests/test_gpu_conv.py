@@ -229,3 +229,29 @@ def test_conv1d_tc_split_precision(cin, cout, k, act):
     h, l, h2 = (o16[:, :, i * cout:(i + 1) * cout].float().cpu() for i in range(3))
     assert torch.equal(h, h2)
     assert max_abs(o32.cpu(), h + l) < 2e-6 * max(scale, 1.0)
+
+
+@pytest.mark.parametrize("cout,k,dil,with_res2,scale", [(128, 3, 1, False, 1.0), (32, 7, 3, True, 1.0), (64, 11, 5, True, 1.0 / 3)])
+def test_conv1d_tc_16bit_residual_stream(cout, k, dil, with_res2, scale):
+    """res16 (16-bit residual in) + out16r (un-activated 16-bit copy out, in place over res16) + activated out16:
+    the Generator's 16-bit residual stream."""
+    import torch.nn.functional as F
+    B, T, cin = 2, 700, cout
+    w, b = _rand(cout, cin, k, seed=50, scale=(cin * k) ** -0.5), _rand(cout, seed=51, scale=0.1)
+    x = _rand(B, T, cin, seed=52).half()
+    r16 = _rand(B, T, cout, seed=53).half()
+    r2 = _rand(B, T, cout, seed=54) if with_res2 else None
+    ref = F.conv1d(x.float().transpose(1, 2), w.half().float(), b, padding=dil * (k // 2), dilation=dil).transpose(1, 2)
+    ref = ref + r16.float() + (r2 if with_res2 else 0.0)
+    ref = ref * scale
+    pc = packer.pack_conv(w, b, dil=dil).to(DEV)
+    raw = r16.clone().to(DEV)                      # updated in place
+    act16 = torch.empty(B, T, cout, device=DEV, dtype=torch.float16)
+    o32 = torch.empty(B, T, cout, device=DEV) if with_res2 else None
+    ops.conv1d(pc, x.to(DEV), res16=raw, out16r=raw, out16=act16, post_lrelu=0.1, out32=o32,
+               res2=None if r2 is None else r2.to(DEV), scale=scale)
+    torch.cuda.synchronize()
+    assert max_abs(ref.half().float(), raw.float().cpu()) < 4e-3
+    assert max_abs(F.leaky_relu(ref, 0.1).half().float(), act16.float().cpu()) < 4e-3
+    if with_res2:
+        assert max_abs(ref, o32.cpu()) < 2e-3
