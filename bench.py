@@ -58,9 +58,20 @@ def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         d = json.load(open(p))
-        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sustained=d["bf16_tflops_sustained"],
-                    src="MEASURED_PEAKS.json")
-    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, src="fallback (B200_PROFILING.md)")
+        return dict(hbm=d["hbm_gbs"], hbm_gbs=d["hbm_gbs"], tf_burst=d["bf16_tflops"],
+                    tf_sustained=d["bf16_tflops_sustained"], src="MEASURED_PEAKS.json")
+    return dict(hbm=6650.0, hbm_gbs=6650.0, tf_burst=1590.0, tf_sustained=1400.0, src="fallback (B200_PROFILING.md)")
+
+
+def load_traffic(workload):
+    """DRAM bytes per conv1d_tc launch (dram__bytes_read.sum + dram__bytes_write.sum averaged over the launches of one
+    step) from the committed ncu pass of this workload (profiles/conv1d_tc_dram.json, written by
+    tools/ncu_dram_summary.py); None when no capture of this workload is committed."""
+    p = os.path.join(ROOT, "profiles", "conv1d_tc_dram.json")
+    if not os.path.exists(p):
+        return None
+    d = json.load(open(p))
+    return d if d.get("workload") == workload else None
 
 
 class ClockSampler:
@@ -238,6 +249,12 @@ def run_gpu_arm(args, rank, local_rank, world):
     sampler.start()
     ms_total, launches = timed(step_device, args.steps)
     clocks = sampler.stop()
+    if args.ncu_range:        # one extra step inside a cudaProfiler range (ncu --profile-from-start off); not timed
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        step_device()
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
     for _ in range(2):
         step_e2e()
     ms_e2e, _ = timed(step_e2e, args.steps)
@@ -260,24 +277,34 @@ def run_gpu_arm(args, rank, local_rank, world):
         prof, _lib.PROFILE = _lib.PROFILE, None
         step_ms = ev0.elapsed_time(ev1)
         agg = {}
-        for kind, tag, flops, a, b in prof:
+        hbm_t = hbm_b = 0.0       # launches that are HBM-bound by their algorithmic intensity
+        for kind, tag, flops, a, b, nbytes in prof:
             t = a.elapsed_time(b)
             key = (kind, tag)
-            f, tt, n = agg.get(key, (0.0, 0.0, 0))
-            agg[key] = (f + flops, tt + t, n + 1)
+            f, tt, n, by = agg.get(key, (0.0, 0.0, 0, 0.0))
+            agg[key] = (f + flops, tt + t, n + 1, by + nbytes)
         tc_f = sum(v[0] for k, v in agg.items() if k[0] == "conv1d_tc")
         tc_t = sum(v[1] for k, v in agg.items() if k[0] == "conv1d_tc")
         tc_n = sum(v[2] for k, v in agg.items() if k[0] == "conv1d_tc")
         peaks = load_peaks()
         ach = tc_f / (tc_t * 1e-3) / 1e12 if tc_t > 0 else 0.0
+        tc_b = sum(v[3] for k, v in agg.items() if k[0] == "conv1d_tc")
+        traffic = load_traffic(f"svs_v5_infer_{utts}x{audio_seconds(frames):.0f}s")
         roofline = {"bound": "tensor", "kernel": "conv1d_tc_kernel", "achieved": ach, "peak": peaks["tf_sustained"],
-                    "unit": "TFLOP/s", "frac": ach / peaks["tf_sustained"], "traffic": None,
+                    "unit": "TFLOP/s", "frac": ach / peaks["tf_sustained"],
+                    "traffic": None if traffic is None else traffic["dram_bytes_per_launch"],
+                    "traffic_source": None if traffic is None else traffic["source"],
+                    "alg_bytes_per_launch": tc_b / max(tc_n, 1),
+                    "hbm_view": {"achieved": tc_b / (tc_t * 1e-3) / 1e9 if tc_t > 0 else 0.0, "peak": peaks["hbm_gbs"],
+                                 "unit": "GB/s", "frac": (tc_b / (tc_t * 1e-3) / 1e9) / peaks["hbm_gbs"] if tc_t > 0 else 0.0,
+                                 "how": "algorithmic HBM bytes of the same launches / the same durations"},
                     "peak_source": peaks["src"] + " (bf16 sustained: kernel timed inside a long step)",
                     "launches_per_step": tc_n, "alg_tflop_per_step": tc_f / 1e12,
                     "avg_launch_ms": tc_t / max(tc_n, 1), "share_of_step": tc_t / step_ms,
                     "how": "sum of algorithmic conv FLOPs / sum of CUDA-event launch durations, instrumented step"}
         extra["stages_ms"] = {f"{k[0]}:{k[1] or 'untagged'}": {"ms": round(v[1], 3), "launches": v[2],
-                                                              "tflops": round(v[0] / max(v[1], 1e-9) / 1e9, 1)}
+                                                              "tflops": round(v[0] / max(v[1], 1e-9) / 1e9, 1),
+                                                              "alg_gbs": round(v[3] / max(v[1], 1e-9) / 1e6, 1)}
                               for k, v in sorted(agg.items())}
         extra["instrumented_step_ms"] = step_ms
         extra["step_tflops"] = mflop_per_frame(frames) * 1e6 * utts * frames / (ms_step * 1e-3) / 1e12
@@ -322,6 +349,8 @@ def main():
     ap.add_argument("--frames", type=int, default=FRAMES)
     ap.add_argument("--phones", type=int, default=PHONES)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ncu-range", action="store_true",
+                    help="run one extra, untimed step inside cudaProfilerStart/Stop (for ncu --profile-from-start off)")
     args = ap.parse_args()
 
     world = int(os.environ.get("WORLD_SIZE", "1"))

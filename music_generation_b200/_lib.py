@@ -111,7 +111,7 @@ LAUNCHES = 0
 
 
 # bench.py's instrumented pass: when PROFILE is a list every call appends
-# (entry point, tag, algorithmic flops, start event, end event); NEXT_META is set by ops.conv1d
+# (entry point, tag, algorithmic flops, start event, end event, algorithmic HBM bytes); NEXT_META is set by ops.conv1d
 PROFILE = None
 NEXT_META = None
 
@@ -127,6 +127,6 @@ def call(name, *args):
     ev0.record()
     check(getattr(lib(), name)(*args), name)
     ev1.record()
-    tag, flops = NEXT_META or ("", 0.0)
+    tag, flops, nbytes = NEXT_META or ("", 0.0, 0.0)
     NEXT_META = None
-    PROFILE.append((name.replace("b200svs_", ""), tag, flops, ev0, ev1))
+    PROFILE.append((name.replace("b200svs_", ""), tag, flops, ev0, ev1, nbytes))

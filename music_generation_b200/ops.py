@@ -131,7 +131,12 @@ def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, 
     e.n_valid = n_out if n_valid is None else n_valid
     if _lib.PROFILE is not None:
         frac = 1.0 if w_rows is None else w_rows[1] / pc.cout_pad
-        _lib.NEXT_META = (pc.tag, 2.0 * B * T * pc.alg_macs_per_row * frac)
+        n = float(B) * T * e.n_valid
+        xb = x.element_size()
+        nbytes = (float(B) * T * cin * xb + w.numel() * w.element_size()
+                  + n * (4 * (res1 is not None) + 4 * (res2 is not None) + 2 * (res16 is not None) + 4 * (out32 is not None)
+                         + 2 * (out16r is not None) + (6 if split16 else 2) * (out16 is not None)))
+        _lib.NEXT_META = (pc.tag, 2.0 * B * T * pc.alg_macs_per_row * frac, nbytes)
     if pc.f32:
         if x.dtype != torch.float32:
             raise TypeError("fp32 conv needs fp32 activations")
