@@ -221,6 +221,19 @@ def run_gpu_arm(args, rank, local_rank, world):
         host_wave.copy_(res[0], non_blocking=True)
         return res
 
+    # song driver: the same utterances as the lines of one song - one ragged batch, peak-normalised,
+    # int16, concatenated on the device; only the int16 song crosses PCIe
+    from music_generation_b200 import pipeline
+    syn = pipeline.Synthesiser(net)
+    host_lines = [(host["x"][b], host["note_pitch_id"][b], host["note_duration"][b], host["phone_shengdiao"][b])
+                  for b in range(utts)]
+    host_song = torch.empty(pipeline.LEAD_IN + utts * n_samples, dtype=torch.int16).pin_memory()
+
+    def step_song():
+        song = syn.syn_song(host_lines, ph_dur=host["ph_dur"].to(dev, non_blocking=True))
+        host_song.copy_(song, non_blocking=True)
+        return song
+
     def barrier():
         if world > 1:
             dist.barrier()
@@ -258,6 +271,8 @@ def run_gpu_arm(args, rank, local_rank, world):
     for _ in range(2):
         step_e2e()
     ms_e2e, _ = timed(step_e2e, args.steps)
+    step_song()
+    ms_song, _ = timed(step_song, args.steps)
 
     ms_step = ms_total / args.steps
     audio_per_step = audio_seconds(utts * frames) * world
@@ -329,6 +344,10 @@ def run_gpu_arm(args, rank, local_rank, world):
                 "per_gpu": value / world,
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                         "ms_per_step": ms_e2e / args.steps},
+                "e2e_song": {"value": audio_per_step / (ms_song / args.steps / 1e3), "unit": UNIT,
+                             "d2h_bytes_per_step": host_song.numel() * 2, "ms_per_step": ms_song / args.steps,
+                             "what": "pipeline.Synthesiser.syn_song: host id tensors -> one ragged batch -> infer -> "
+                                     "device peak-normalise / int16 / concatenate -> int16 song to pinned host memory"},
                 "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline}
         line.update(extra)
         print(json.dumps(line), flush=True)

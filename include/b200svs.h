@@ -200,6 +200,17 @@ int b200svs_btc_to_bct(const float* in_btc, int32_t in_ld, int32_t B, int32_t C,
 int b200svs_probe_rowshift(const void* a_f16, const void* b_f16, float* out, int32_t rows_a, int32_t shift,
                            int32_t base_offset_mode, void* stream);
 
+/* Song assembly: what the reference does on the host after every per-line infer()
+ * (pipline_inference_svs_v5.py:134-139,225-243,241-258; pipline_inference_svs_v6_multispeaker.py:240-258), on a
+ * ragged batch in HBM: for line i (utterance order[i], or i when order == NULL) the valid samples
+ * o[b, 0 : mel_len[b]*hop] are peak-normalised twice (audio *= 32767 / max(0.01, max|audio|), fp32), truncated to
+ * int16 and written at song[lead_in + offsets[i] ...]; song[0 : lead_in] = 0 (the 0.2 s = 4410-sample lead-in).
+ * legacy_scalar: 0 = NumPy >= 2 scalar semantics (32767/peak in fp32), 1 = NumPy < 2 (fp64 then rounded).
+ * peak_ws: n_lines uint32 of scratch; scales_out (nullable): [n_lines][2] the two factors, for parity checks. */
+int b200svs_song_assemble(const float* o, int64_t o_ld, const int64_t* mel_len, const int32_t* order,
+                          const int64_t* offsets, int32_t n_lines, int32_t hop, int32_t lead_in, int32_t legacy_scalar,
+                          uint32_t* peak_ws, int16_t* song, float* scales_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -248,3 +248,13 @@ def bct_to_btc(x_bct, out32=None, out16=None, lens=None):
 def btc_to_bct(x_btc, out_bct):
     B, T, c = x_btc.shape
     _lib.call("b200svs_btc_to_bct", _ptr(x_btc), _btc(x_btc, "x"), B, c, T, _ptr(out_bct), _stream())
+
+
+def song_assemble(o, mel_len, offsets, song, *, order=None, hop=256, lead_in=4410, legacy_scalar=False, scales_out=None):
+    """Peak-normalise (twice, as the reference's driver does), truncate to int16 and concatenate the valid samples of
+    every line of a ragged batch (b200svs_song_assemble).  o: [B,1,S] fp32; mel_len: [B] int64; offsets: [n] int64
+    start sample of each line in the song (without the lead-in); order: [n] int32 utterance index per line."""
+    n = offsets.numel()
+    ws = torch.empty(n, device=o.device, dtype=torch.int32)
+    _lib.call("b200svs_song_assemble", _ptr(o), o.stride(0), _ptr(mel_len), _ptr(order), _ptr(offsets), n, hop, lead_in,
+              1 if legacy_scalar else 0, _ptr(ws), _ptr(song), _ptr(scales_out), _stream())

@@ -2,7 +2,7 @@
 # GPU bring-up: every test file in its own process so one faulting kernel cannot hide the others.
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > gpurun_out/gpu.txt 2>&1
-for f in test_gpu_misc test_gpu_conv test_gpu_infer; do
+for f in test_gpu_misc test_gpu_conv test_gpu_infer test_gpu_song; do
   timeout 900 python -m pytest tests/$f.py -q -m gpu --timeout 300 -p no:cacheprovider > gpurun_out/$f.log 2>&1
   echo "$f exit $?" >> gpurun_out/summary.txt
   tail -5 gpurun_out/$f.log
