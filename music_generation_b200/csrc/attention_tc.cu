@@ -5,17 +5,19 @@
 //   S = (Q K^T)/sqrt(d) + band(q.rel_k) ; masked_fill(key >= len, -1e4) ; P = softmax(S)
 //   O = P V + sum_{|r|<=w} P[i,i+r] rel_v[r]
 // One CTA = 128 query rows of one (batch, head), warp-specialised and software-pipelined over 64-key tiles:
-//   warps 0-3 : softmax (thread r owns query row r = TMEM lane r): S_j from TMEM -> online max/sum (fp32,
+//   warps 0-7 : softmax (warps q and q+4 own query rows 32q..32q+31 = TMEM lanes, and split the 64 key columns and
+//               the 96 O columns between them): S_j from TMEM -> online max/sum (fp32,
 //               log2 domain, ex2.approx) -> P_j to shared memory as the PV MMA's A operand (SWIZZLE_128B,
 //               K-major); folds PV_{j-1} into the register accumulator O (O = O*alpha + PV)
-//   warp 4    : tcgen05.mma issuer (one elected thread): S_{j+1} = Q.K_{j+1}^T is issued while the softmax
+//   warp 8    : tcgen05.mma issuer (one elected thread): S_{j+1} = Q.K_{j+1}^T is issued while the softmax
 //               warps work on S_j (S double-buffered in TMEM), PV_j = P_j.V_j as soon as P_j is published
-//   warp 5    : TMA loader (K double-buffered, V single-buffered)
+//   warp 9    : TMA loader (K double-buffered, V single-buffered)
 // V is consumed K-major from a transposed copy V^T [B,C,T] written by attn_prep_kernel.
 //
 // SPLIT mode (phoneme encoder and F0 predictor, whose outputs cross float->int boundaries):
 // every operand is an fp16 (hi, lo) pair with x = hi + lo to ~2^-22, and every product is three MMAs
 // (hi.hi + hi.lo + lo.hi) accumulated in fp32 - tensor-core speed at fp32-class accuracy.
+#include <type_traits>
 #include "common.cuh"
 #include "api_internal.h"
 
@@ -30,7 +32,9 @@ constexpr int kQChunkBytes = kTQ * 128;   // 16 KB  [128 rows][64 x 16-bit]
 constexpr int kKChunkBytes = kTK * 128;   //  8 KB
 constexpr int kVBytes = kHD * 128;        // 12 KB  [96 d rows][64 keys]
 constexpr int kPBytes = kTQ * 128;        // 16 KB  [128 q rows][64 keys]
-constexpr int kAttnThreads = kTQ + 64;    // 4 softmax warps + MMA warp + TMA warp
+constexpr int kSoftWarps = 8;              // two per scheduler: warp w and w + 4 share query rows, split the columns
+constexpr int kAttnThreads = kSoftWarps * 32 + 64;    // softmax warps + MMA warp + TMA warp
+constexpr int kMmaWarp = kSoftWarps, kTmaWarp = kSoftWarps + 1;
 constexpr float kLog2e = 1.4426950408889634f;
 
 struct AttnTcParams {
@@ -91,17 +95,19 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
   float* band = qrel + kTQ * kNR;                               // [128][9]  band scores (log2 domain)
   float* relk_s = band + kTQ * kNR;                             // [9][96]
   float* relv_s = relk_s + kNR * kHD;                           // [9][96]
-  AttnBars* bars = reinterpret_cast<AttnBars*>(relv_s + kNR * kHD);
+  float* pmax = relv_s + kNR * kHD;                             // [2 S buffers][2 halves][128] partial row maxima
+  float* lsum = pmax + 4 * kTQ;                                 // [2 halves][128] partial row sums
+  AttnBars* bars = reinterpret_cast<AttnBars*>(lsum + 2 * kTQ);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q0 = blockIdx.x * kTQ, h = blockIdx.y, b = blockIdx.z;
   const int len = p.lens ? min(__ldg(p.lens + b), p.T) : p.T;
   const int dt = SPLIT ? B200SVS_DT_F16 : p.dtype;
-  const int t = q0 + tid;                                // query row of a softmax thread
-  const size_t orow = static_cast<size_t>(b) * p.T + t;
   const int oc = h * kHD;
 
   if (q0 >= len) {   // whole tile is padding: zeros (the reference's values there are masked by every consumer)
+    const int t = q0 + tid;
+    const size_t orow = static_cast<size_t>(b) * p.T + t;
     if (tid < kTQ && t < p.T) {
       for (int c = 0; c < kHD; ++c) {
         if (p.out32) p.out32[orow * p.out32_ld + oc + c] = 0.f;
@@ -119,14 +125,14 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
     mbar_init(&bars->qbar, 1);
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bars->k_full[i], 1); mbar_init(&bars->k_empty[i], 1);
-      mbar_init(&bars->s_full[i], 1); mbar_init(&bars->s_free[i], kTQ / 32);
+      mbar_init(&bars->s_full[i], 1); mbar_init(&bars->s_free[i], kSoftWarps);
     }
     mbar_init(&bars->v_full, 1); mbar_init(&bars->v_empty, 1);
-    mbar_init(&bars->p_full, kTQ / 32); mbar_init(&bars->o_full, 1);
+    mbar_init(&bars->p_full, kSoftWarps); mbar_init(&bars->o_full, 1);
     fence_barrier_init();
     prefetch_tmap(&tmQh); prefetch_tmap(&tmKh); prefetch_tmap(&tmVh);
   }
-  if (warp == 4) {
+  if (warp == kMmaWarp) {
     tmem_alloc(&bars->tmem_base, 256);
     tmem_relinquish();
   }
@@ -141,7 +147,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
   const uint32_t tmem_o = tmem_s + 2 * kTK;         // PV: 96 columns
   const int n_kt = (len + kTK - 1) / kTK;
 
-  if (warp == 5) {
+  if (warp == kTmaWarp) {
     if (lane == 0) {
       // ------------------------------------------------------------ TMA loader: Q, K0, then (K_{j+1}, V_j)
       auto load_k = [&](int j) {
@@ -168,7 +174,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
         if (SPLIT) tma_load_3d(smV + kVBytes, &tmVl, &bars->v_full, j * kTK, oc, b);
       }
     }
-  } else if (warp == 4) {
+  } else if (warp == kMmaWarp) {
     if (elect_one()) {
       // ------------------------------------------------------------ MMA issuer
       const uint32_t idesc_s = make_idesc_f16(128, kTK, dt == B200SVS_DT_BF16);
@@ -222,17 +228,25 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
     }
     __syncwarp();
   } else {
-    // ---------------------------------------------------------------- softmax warps (tid < 128)
+    // ---------------------------------------------------------------- softmax warps 0-7 (256 threads)
+    // Thread (row, half): query row `row` = TMEM lane, key columns [32*half, 32*half+32) of every S tile and
+    // O columns [48*half, 48*half+48).  Warps q and q+4 own the same rows; they exchange the row maximum once
+    // per tile through shared memory (named barrier 1+q, 64 threads) and the row sums once at the end.
+    const int q = warp & 3, half = warp >> 2;
+    const int row = q * 32 + lane;
+    const int t = q0 + row;
+    const size_t orow = static_cast<size_t>(b) * p.T + t;
     const float scale2 = rsqrtf(static_cast<float>(kHD)) * kLog2e;     // scores live in the log2 domain
-    {   // (q_i / sqrt(d)) . rel_k[w] for the 9 band offsets; q read from the TMA-loaded (swizzled) Q tile
-      float a[kNR];
+    {   // (q_i / sqrt(d)) . rel_k[w]: half 0 computes band offsets 0..4, half 1 offsets 5..8
+      const int w0 = half ? 5 : 0, nw = half ? 4 : 5;
+      float a[5];
 #pragma unroll
-      for (int w = 0; w < kNR; ++w) a[w] = 0.f;
+      for (int w = 0; w < 5; ++w) a[w] = 0.f;
       mbar_wait(&bars->qbar, 0);
 #pragma unroll 1
       for (int cell = 0; cell < kHD / 8; ++cell) {      // 12 cells of 8 channels: chunk 0 holds d 0..63, chunk 1 d 64..95
         const int c = cell >> 3, jc = cell & 7;
-        const uint8_t* src = smQ + c * kQChunkBytes + tid * 128 + ((jc ^ (tid & 7)) << 4);
+        const uint8_t* src = smQ + c * kQChunkBytes + row * 128 + ((jc ^ (row & 7)) << 4);
         const uint4 qh = *reinterpret_cast<const uint4*>(src);
         const uint32_t uh[4] = {qh.x, qh.y, qh.z, qh.w};
         float qv[8];
@@ -255,34 +269,40 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
           }
         }
 #pragma unroll
-        for (int w = 0; w < kNR; ++w) {
-          const float4 k0v = *reinterpret_cast<const float4*>(relk_s + w * kHD + cell * 8);
-          const float4 k1v = *reinterpret_cast<const float4*>(relk_s + w * kHD + cell * 8 + 4);
-          float x = a[w];
-          x = fmaf(qv[0], k0v.x, x); x = fmaf(qv[1], k0v.y, x); x = fmaf(qv[2], k0v.z, x); x = fmaf(qv[3], k0v.w, x);
-          x = fmaf(qv[4], k1v.x, x); x = fmaf(qv[5], k1v.y, x); x = fmaf(qv[6], k1v.z, x); x = fmaf(qv[7], k1v.w, x);
-          a[w] = x;
+        for (int w = 0; w < 5; ++w) {
+          if (w < nw) {
+            const float4 k0v = *reinterpret_cast<const float4*>(relk_s + (w0 + w) * kHD + cell * 8);
+            const float4 k1v = *reinterpret_cast<const float4*>(relk_s + (w0 + w) * kHD + cell * 8 + 4);
+            float x = a[w];
+            x = fmaf(qv[0], k0v.x, x); x = fmaf(qv[1], k0v.y, x); x = fmaf(qv[2], k0v.z, x); x = fmaf(qv[3], k0v.w, x);
+            x = fmaf(qv[4], k1v.x, x); x = fmaf(qv[5], k1v.y, x); x = fmaf(qv[6], k1v.z, x); x = fmaf(qv[7], k1v.w, x);
+            a[w] = x;
+          }
         }
       }
 #pragma unroll
-      for (int w = 0; w < kNR; ++w) {
-        qrel[tid * kNR + w] = (t < p.T) ? a[w] * scale2 : 0.f;
-        band[tid * kNR + w] = -INFINITY;
+      for (int w = 0; w < 5; ++w) {
+        if (w < nw) {
+          qrel[row * kNR + w0 + w] = (t < p.T) ? a[w] * scale2 : 0.f;
+          band[row * kNR + w0 + w] = -INFINITY;
+        }
       }
+      named_bar_sync(1 + q, 64);         // both halves' band offsets are in place
     }
-    float m_run = -INFINITY, l_run = 0.f, alpha_prev = 0.f;
-    float o[kHD];
+    float m_run = -INFINITY, l_run = 0.f, alpha_prev = 0.f;    // l_run: partial row sum over this thread's key columns
+    constexpr int kOC = kHD / 2;                               // 48 O columns per thread
+    float o[kOC];
 #pragma unroll
-    for (int c = 0; c < kHD; ++c) o[c] = 0.f;
-    const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
-    auto fold = [&](float alpha) {       // O = O * alpha + PV  (PV: 96 TMEM columns)
+    for (int c = 0; c < kOC; ++c) o[c] = 0.f;
+    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    auto fold = [&](float alpha) {       // O = O * alpha + PV  (this thread's 48 of the 96 PV columns)
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        uint32_t r[32];
-        tmem_ld32_nowait(tmem_o + lane_off + c * 32, r);
-        tmem_ld_wait();
+        uint32_t r[16];
+        tmem_ld16_nowait(tmem_o + lane_off + half * kOC + c * 16, r);
+        tmem_ld_wait16(r);
 #pragma unroll
-        for (int e = 0; e < 32; ++e) o[c * 32 + e] = fmaf(o[c * 32 + e], alpha, __uint_as_float(r[e]));
+        for (int e = 0; e < 16; ++e) o[c * 16 + e] = fmaf(o[c * 16 + e], alpha, __uint_as_float(r[e]));
       }
     };
 
@@ -291,28 +311,28 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
       const int sb = j & 1;
       mbar_wait(&bars->s_full[sb], (j >> 1) & 1);
       tc_fence_after();
-      const uint32_t ta = tmem_s + sb * kTK + lane_off;
+      const uint32_t ta = tmem_s + sb * kTK + lane_off + half * 32;      // this thread's 32 key columns
+      const int kb = k0 + half * 32;                                       // first key of those columns
       const bool near_diag = (k0 <= q0 + kTQ - 1 + kWin) && (k0 + kTK - 1 >= q0 - kWin);
       const bool tail = k0 + kTK > len;
       const bool slow = near_diag || tail;             // CTA-uniform
-      // score of key k0 + e with the band bias and the masks applied (slow tiles only)
+      // score of key kb + e with the band bias and the masks applied (slow tiles only)
       auto adjust = [&](uint32_t raw, int e) -> float {
         float x = __uint_as_float(raw) * scale2;
-        const int d = k0 + e - t + kWin;
-        if (d >= 0 && d < kNR) x += qrel[tid * kNR + d];
-        const int key = k0 + e;
+        const int key = kb + e;
+        const int d = key - t + kWin;
+        if (d >= 0 && d < kNR) x += qrel[row * kNR + d];
         if (key >= len) x = -1e4f * kLog2e;            // masked_fill(mask == 0, -1e4)
         if (key >= p.T) x = -INFINITY;                 // beyond the tensor: not a key at all
         return x;
       };
-      // ---- pass 1: row maximum.  Rolled loops over 8-column groups (the next group's TMEM load is in flight
-      // while the current one is reduced): a fully unrolled 64-key body thrashes the instruction cache.
+      // ---- pass 1: row maximum over this thread's 32 keys, then over the pair
       float mx = -INFINITY;
       {
         uint32_t ra[8], rb[8];
         tmem_ld8_nowait(ta, ra);
 #pragma unroll 1
-        for (int g = 0; g < kTK / 8; g += 2) {
+        for (int g = 0; g < 4; g += 2) {
           tmem_ld_wait8(ra);
           tmem_ld8_nowait(ta + (g + 1) * 8, rb);
           if (slow) {
@@ -323,7 +343,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
             for (int e = 0; e < 8; ++e) mx = fmaxf(mx, __uint_as_float(ra[e]));
           }
           tmem_ld_wait8(rb);
-          if (g + 2 < kTK / 8) tmem_ld8_nowait(ta + (g + 2) * 8, ra);
+          if (g + 2 < 4) tmem_ld8_nowait(ta + (g + 2) * 8, ra);
           if (slow) {
 #pragma unroll
             for (int e = 0; e < 8; ++e) mx = fmaxf(mx, adjust(rb[e], (g + 1) * 8 + e));
@@ -334,6 +354,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
         }
       }
       if (!slow) mx *= scale2;                         // scale2 > 0 commutes with max
+      pmax[(sb * 2 + half) * kTQ + row] = mx;
+      named_bar_sync(1 + q, 64);
+      mx = fmaxf(mx, pmax[(sb * 2 + (half ^ 1)) * kTQ + row]);
       const float m_new = fmaxf(m_run, mx);
       const float alpha = (m_run == -INFINITY) ? 0.f : ex2f(m_run - m_new);
       // ---- PV_{j-1} has to be folded into O (and the P buffer released by its MMAs) before P_j is written
@@ -342,19 +365,20 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
         tc_fence_after();
         fold(alpha_prev);
       }
-      // ---- pass 2: P = 2^(S - m), row sum, publish P as the A operand of the PV MMA
+      // ---- pass 2: P = 2^(S - m), partial row sum, publish P as the A operand of the PV MMA
       float sum = 0.f;
-      uint8_t* prow = smP + tid * 128;
-      auto emit = [&](const uint32_t* r, int g) {      // 8 keys -> one 16-byte cell of the P row
+      uint8_t* prow = smP + row * 128;
+      auto emit = [&](const uint32_t* r, int g, auto slow_c) {      // 8 keys -> one 16-byte cell of the P row
+        constexpr bool kSlow = decltype(slow_c)::value;
         float pv[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
           float x;
-          if (slow) {
+          if constexpr (kSlow) {
             const int ee = g * 8 + e;
             x = adjust(r[e], ee);
-            const int d = k0 + ee - t + kWin;
-            if (near_diag && d >= 0 && d < kNR && k0 + ee < p.T) band[tid * kNR + d] = x;
+            const int d = kb + ee - t + kWin;
+            if (near_diag && d >= 0 && d < kNR && kb + ee < p.T) band[row * kNR + d] = x;
             x -= m_new;
           } else {
             x = fmaf(__uint_as_float(r[e]), scale2, -m_new);
@@ -362,7 +386,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
           pv[e] = ex2f(x);                              // ex2(-inf) = 0
           sum += pv[e];
         }
-        const int phys = (g ^ (tid & 7)) << 4;
+        const int phys = ((half * 4 + g) ^ (row & 7)) << 4;
         *reinterpret_cast<uint4*>(prow + phys) =
             make_uint4(pk16(pv[0], pv[1], dt), pk16(pv[2], pv[3], dt), pk16(pv[4], pv[5], dt), pk16(pv[6], pv[7], dt));
         if (SPLIT) {
@@ -376,13 +400,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
         uint32_t ra[8], rb[8];
         tmem_ld8_nowait(ta, ra);
 #pragma unroll 1
-        for (int g = 0; g < kTK / 8; g += 2) {
+        for (int g = 0; g < 4; g += 2) {
           tmem_ld_wait8(ra);
           tmem_ld8_nowait(ta + (g + 1) * 8, rb);
-          emit(ra, g);
+          if (slow) emit(ra, g, std::true_type{}); else emit(ra, g, std::false_type{});
           tmem_ld_wait8(rb);
-          if (g + 2 < kTK / 8) tmem_ld8_nowait(ta + (g + 2) * 8, ra);
-          emit(rb, g + 1);
+          if (g + 2 < 4) tmem_ld8_nowait(ta + (g + 2) * 8, ra);
+          if (slow) emit(rb, g + 1, std::true_type{}); else emit(rb, g + 1, std::false_type{});
         }
       }
       l_run = l_run * alpha + sum;
@@ -400,36 +424,40 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
     tc_fence_after();
     fold(alpha_prev);
 
-    // ---- relative-value band term, normalisation, stores
+    // ---- row sum over both halves, relative-value band term, normalisation, stores
+    lsum[half * kTQ + row] = l_run;
+    named_bar_sync(1 + q, 64);
+    const float l_tot = l_run + lsum[(half ^ 1) * kTQ + row];
     const bool live = t < len;
+    const int oc = h * kHD + half * kOC;
     if (t < p.T) {
       if (live) {
 #pragma unroll 1
         for (int w = 0; w < kNR; ++w) {
-          const float sv = band[tid * kNR + w];
+          const float sv = band[row * kNR + w];
           if (sv == -INFINITY) continue;
           const float pw = ex2f(sv - m_run);
 #pragma unroll
-          for (int c = 0; c < kHD; c += 4) {
-            const float4 rv = *reinterpret_cast<const float4*>(relv_s + w * kHD + c);
+          for (int c = 0; c < kOC; c += 4) {
+            const float4 rv = *reinterpret_cast<const float4*>(relv_s + w * kHD + half * kOC + c);
             o[c] = fmaf(pw, rv.x, o[c]); o[c + 1] = fmaf(pw, rv.y, o[c + 1]);
             o[c + 2] = fmaf(pw, rv.z, o[c + 2]); o[c + 3] = fmaf(pw, rv.w, o[c + 3]);
           }
         }
       }
-      const float invl = live ? 1.0f / l_run : 0.f;
+      const float invl = live ? 1.0f / l_tot : 0.f;
 #pragma unroll
-      for (int c = 0; c < kHD; ++c) o[c] = live ? o[c] * invl : 0.f;
+      for (int c = 0; c < kOC; ++c) o[c] = live ? o[c] * invl : 0.f;
       if (p.out32) {
         float* op = p.out32 + orow * p.out32_ld + oc;
 #pragma unroll
-        for (int c = 0; c < kHD; c += 4) *reinterpret_cast<float4*>(op + c) = make_float4(o[c], o[c + 1], o[c + 2], o[c + 3]);
+        for (int c = 0; c < kOC; c += 4) *reinterpret_cast<float4*>(op + c) = make_float4(o[c], o[c + 1], o[c + 2], o[c + 3]);
       }
       if (p.out16) {
         uint16_t* op = reinterpret_cast<uint16_t*>(p.out16) + orow * p.out16_ld + oc;
         const int odt = p.out16_split ? B200SVS_DT_F16 : p.out16_dtype;
 #pragma unroll
-        for (int c = 0; c < kHD; c += 8) {
+        for (int c = 0; c < kOC; c += 8) {
           const uint4 hi = make_uint4(pk16(o[c], o[c + 1], odt), pk16(o[c + 2], o[c + 3], odt), pk16(o[c + 4], o[c + 5], odt),
                                       pk16(o[c + 6], o[c + 7], odt));
           *reinterpret_cast<uint4*>(op + c) = hi;
@@ -448,7 +476,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
   }
 
   __syncthreads();
-  if (warp == 4) {
+  if (warp == kMmaWarp) {
     tc_fence_after();
     tmem_dealloc(bars->tmem_base, 256);
   }
@@ -551,7 +579,7 @@ extern "C" int b200svs_attention_tc(const void* qk_hi, const void* qk_lo, const 
   p.out16_split = out16_split; p.rel_k = rel_k; p.rel_v = rel_v; p.lens = lens;
   p.B = B; p.T = T; p.C = C; p.H = H; p.dtype = dtype;
   const int np = split ? 2 : 1;
-  const size_t smem = (size_t)np * (2 * kQChunkBytes + 4 * kKChunkBytes + kVBytes + kPBytes) + 2 * kTQ * kNR * sizeof(float) + 2 * kNR * kHD * sizeof(float) +
+  const size_t smem = (size_t)np * (2 * kQChunkBytes + 4 * kKChunkBytes + kVBytes + kPBytes) + 2 * kTQ * kNR * sizeof(float) + 2 * kNR * kHD * sizeof(float) + 6 * kTQ * sizeof(float) +
                       sizeof(AttnBars) + 1024;
   dim3 grid((T + kTQ - 1) / kTQ, H, B);
   if (split) {
