@@ -94,6 +94,28 @@ def test_predicted_durations_are_bit_exact():
         assert torch.equal(got, want)
 
 
+@pytest.mark.parametrize("kw,snr_min", [
+    ({"generator_residual": "fp32"}, SNR_DB_TOL),                           # fp32 residual stream in the Generator
+    ({"f0_precision": "fp32", "text_precision": "fp32"}, SNR_DB_TOL),       # fp32 SIMT encoders
+    ({"operand_dtype": "bf16"}, 34.0),                                      # bf16 operands (8-bit mantissa): reported, looser
+], ids=["residual_fp32", "encoders_fp32", "bf16"])
+def test_infer_option_paths_against_golden(kw, snr_min):
+    """The non-default constructor paths stay within tolerance of the reference's golden output."""
+    name = "ae_phdur_b2"
+    g = load_golden(name)
+    variant, inp, ph_dur, seed = case_inputs(name)
+    net, _ = build_model(variant, device=DEV, **kw)
+    noise = synthetic.make_noise(inp["x"].shape[0], 192, int(g["T"]), seed=seed)
+    res = _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise.to(DEV))
+    o = res[0].cpu()
+    s = snr_db(g["o"], o)
+    print(f"{kw}: snr {s:.2f} dB max_abs {max_abs(g['o'], o):.2e}")
+    assert torch.equal(res[1].cpu(), g["y_mask"])
+    assert s >= snr_min, s
+    if "operand_dtype" not in kw:
+        assert max_abs(g["o"], o) <= MAX_ABS_TOL
+
+
 def test_f0_split_precision_matches_fp32_path():
     """The default F0 predictor (tensor cores, fp16 hi/lo split operands) against the fp32 SIMT path
     (f0_precision="fp32"): log_f0 agrees to fp32-evaluation noise (tools/diag_f0.py: both are ~2e-6 rms from an
