@@ -89,7 +89,7 @@ def pack_conv(weight, bias, *, dil=1, pad_left=None, dtype=torch.float16, f32=Fa
     cin_pad = _round_up(cin, 64)
     if gate:
         half = cout // 2
-        bn = block_n or 128
+        bn = block_n or gate_block_n(half)
         hb = bn // 2
         if half % hb:
             raise ValueError(f"gate packing needs hidden {half} divisible by {hb}")
@@ -117,8 +117,14 @@ def pack_conv(weight, bias, *, dil=1, pad_left=None, dtype=torch.float16, f32=Fa
     return pc
 
 
-def gate_order(hidden, block_n=128):
+def gate_block_n(hidden):
+    """N tile of a gated conv: 192 (two tiles for hidden 192, N=192 MMAs) when hidden splits into 96-wide halves, else 128."""
+    return 192 if hidden % 96 == 0 else 128
+
+
+def gate_order(hidden, block_n=None):
     """Packed column order of a gated [tanh | sigmoid] 2*hidden conv (also used for cond biases)."""
+    block_n = block_n or gate_block_n(hidden)
     hb = block_n // 2
     order = []
     for n in range(hidden // hb):
