@@ -15,7 +15,7 @@ import math
 import torch
 from torch import nn
 
-from . import ops, packer, params
+from . import _lib, ops, packer, params
 from .ops import ACT_GELU, ACT_NONE, ACT_RELU, ACT_SIGMOID
 
 LRELU_SLOPE = 0.1   # VISinger/modules.py:17
@@ -39,7 +39,7 @@ class SynthesizerTrn(nn.Module):
                  resblock_dilation_sizes, upsample_rates, upsample_initial_channel, upsample_kernel_sizes,
                  n_speakers=0, gin_channels=0, use_sdp=True, n_vocab_note=100, *, operand_dtype="fp16",
                  max_position_embeddings=2000, generator_chunk_frames=32768, f0_precision="split",
-                 text_precision="split", generator_residual="fp16", seed=1234, **kwargs):
+                 text_precision="split", generator_residual="fp16", cuda_graphs=False, seed=1234, **kwargs):
         super().__init__()
         if hidden_channels != 192 or n_heads != 2:
             raise ValueError("kernels are specialised for hidden_channels=192, n_heads=2 (ours_ae.json)")
@@ -63,6 +63,11 @@ class SynthesizerTrn(nn.Module):
         if generator_residual not in ("fp16", "fp32"):
             raise ValueError("generator_residual must be 'fp16' (16-bit residual stream; fp16 operand mode only) or 'fp32'")
         self.generator_residual = generator_residual
+        # launch-bound (small) calls: replay the frame-level part of infer from a CUDA graph keyed by its shapes
+        self.cuda_graphs = bool(cuda_graphs)
+        self.cuda_graph_max_frames = 32768
+        self.cuda_graph_cache = 8
+        self._graphs = {}
         self.hop = 1
         for u in self.upsample_rates:
             self.hop *= u
@@ -79,10 +84,12 @@ class SynthesizerTrn(nn.Module):
     # ------------------------------------------------------------------ nn.Module plumbing
     def _apply(self, fn, *a, **k):
         self._packed = None
+        self._graphs = {}
         return super()._apply(fn, *a, **k)
 
     def load_state_dict(self, state_dict, strict=True, **k):
         self._packed = None
+        self._graphs = {}
         # tolerate a position table enlarged for T > 2000
         kp = "text_post_net.position_embeddings.weight"
         if kp in state_dict and state_dict[kp].shape != self.text_post_net.position_embeddings.weight.shape:
@@ -383,6 +390,28 @@ class SynthesizerTrn(nn.Module):
             cur16, L = nxt16, Lo
         ops.conv_post_tanh(cur16, P["g_post"], out.view(B, L))
 
+    def _graphed(self, fn, args, shape_key):
+        """Run fn(*args) through a cached CUDA graph.  args: tensors or None; the graph owns static copies of them and
+        of its outputs, results are cloned so that a later replay cannot overwrite what the caller holds."""
+        key = shape_key + tuple(None if a is None else (tuple(a.shape), str(a.dtype)) for a in args)
+        ent = self._graphs.get(key)
+        if ent is None:
+            static = tuple(None if a is None else a.clone() for a in args)
+            fn(*static)                               # eager warm-up: lazy one-time host setup must not be captured
+            torch.cuda.synchronize()
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr):
+                outs, faux = fn(*static)
+            if len(self._graphs) >= self.cuda_graph_cache:
+                self._graphs.pop(next(iter(self._graphs)))
+            ent = self._graphs[key] = (gr, static, outs, faux)
+        gr, static, outs, faux = ent
+        for s_, a in zip(static, args):
+            if a is not None:
+                s_.copy_(a)
+        gr.replay()
+        return tuple(None if o_ is None else o_.clone() for o_ in outs), {k: v.clone() for k, v in faux.items()}
+
     # ------------------------------------------------------------------ the public entry point
     @torch.no_grad()
     def infer(self, x, x_lengths, note_pitch_id, note_duration, phone_shengdiao, ph_dur=None, lf0=None, sid=None,
@@ -442,117 +471,133 @@ class SynthesizerTrn(nn.Module):
             # the reference fails here too: position table has 2000 rows (text_post_net.py:26,69-72)
             raise RuntimeError(f"The size of tensor a ({T}) must match the size of tensor b ({n_pos}) at "
                                f"non-singleton dimension 1 (frames exceed the position table)")
-        h_lr = torch.empty(B, T, H, device=dev, dtype=f32)
-        lr_index = torch.empty(B, T, device=dev, dtype=torch.int32)
-        ops.lr_gather(h, ends, mlen, h_lr, lr_index)
-        aux["lr_index"] = lr_index
         y_mask = (torch.arange(T, device=dev).unsqueeze(0) < mel_len.unsqueeze(1)).unsqueeze(1).to(x.dtype)
-
-        # 4. TextPostNet (ext_modules/text_post_net.py:64-94)
-        xe32 = torch.empty(B, T, H, device=dev, dtype=f32)
-        xe16 = torch.empty(B, T, H, device=dev, dtype=dt)
-        ops.add_pos_mask(h_lr, P["pos"], mlen, out32=xe32, out16=xe16)
-        # F0 predictor: tensor cores with fp16 (hi, lo) split operands (default), or fp32 SIMT (f0_precision="fp32")
-        f0h = torch.empty_like(xe32)
-        if P["f0_mode"] == "split":
-            f0s = torch.empty(B, T, 3 * H, device=dev, dtype=torch.float16)
-            ops.add_pos_mask(h_lr, P["pos"], mlen, out32=f0h, out16=f0s, split16=True)
-        else:
-            f0s = None
-            ops.add_pos_mask(h_lr, P["pos"], mlen, out32=f0h)
-        self._encoder(P["f0_enc"], f0h, f0s, mlen, P["f0_mode"])
-        log_f0 = torch.empty(B, T, 1, device=dev, dtype=f32)
-        ops.conv1d(P["f0_out"], f0h, lens=mlen, out32=log_f0)
-        log_f0 = log_f0.view(B, T)
-        coarse = torch.empty(B, T, device=dev, dtype=torch.int64)
-        f0e16 = torch.empty(B, T, H, device=dev, dtype=dt)
-        cin = None if f0_score is None else f0_score.to(device=dev, dtype=torch.int64).contiguous()
-        ops.f0_embed(log_f0, cin, P["f0_emb"], mlen, coarse, out16=f0e16)
-        aux["f0_coarse"] = coarse
-        # MelPredictNetwork (mel_predict_network.py:37-45)
-        m32 = torch.empty(B, T, H, device=dev, dtype=f32)
-        m16 = torch.empty(B, T, H, device=dev, dtype=dt)
-        ops.conv1d(P["mel_cond"], f0e16, res1=xe32, lens=mlen, out32=m32, out16=m16)
-        self._encoder(P["mel_enc"], m32, m16, mlen, "tc")
-        mel32 = torch.empty(B, T, 80, device=dev, dtype=f32)
-        ops.conv1d(P["mel_out"], m16, lens=mlen, out32=mel32)
-        # FramePriorNetwork (frame_prior_network.py:31-41)
-        fp_a = torch.empty(B, T, 80, device=dev, dtype=dt)
-        ops.conv1d(P["fp_cond"], f0e16, res1=mel32, lens=mlen, out16=fp_a)
-        src = fp_a
-        for pc in P["fp"]:
-            dst = torch.empty(B, T, H, device=dev, dtype=dt)
-            ops.conv1d(pc, src, act=ACT_GELU, lens=mlen, out16=dst)
-            src = dst
-        stats = torch.empty(B, T, 2 * self.inter_channels, device=dev, dtype=f32)
-        ops.conv1d(P["proj"], src, lens=mlen, out32=stats)
         Ci = self.inter_channels
 
-        # 5. z_p = m_p + noise * exp(logs_p) * noise_scale (models_ae.py:643)
-        if noise is None:
-            noise = torch.randn(B, Ci, T, device=dev, dtype=f32)
-        noise = noise.to(device=dev, dtype=f32).contiguous()
-        zp32 = torch.empty(B, T, Ci, device=dev, dtype=f32)
-        z16 = torch.empty(B, T, Ci, device=dev, dtype=dt)
-        ops.sample_prior(stats, noise, float(noise_scale), zp32=zp32, zp16=z16)
-        z32 = zp32.clone()
+        def frame_level(h, ends, mlen, noise, g, f0_score):
+            """Everything after the host learns T: ~95 % of the launches.  Pure device work on its arguments (no host
+            sync), so it can be captured in a CUDA graph."""
+            faux = {}
+            h_lr = torch.empty(B, T, H, device=dev, dtype=f32)
+            lr_index = torch.empty(B, T, device=dev, dtype=torch.int32)
+            ops.lr_gather(h, ends, mlen, h_lr, lr_index)
+            faux["lr_index"] = lr_index
 
-        # speaker conditioning (optional; WN.cond_layer modules.py:152-159, Generator.cond models_ae.py:329-330)
-        g_btc = None
-        if g is not None:
-            if not self.gin_channels:
-                raise ValueError("model was built with gin_channels=0")
-            g_btc = g.to(device=dev, dtype=f32).reshape(B, 1, self.gin_channels).contiguous()
+            # 4. TextPostNet (ext_modules/text_post_net.py:64-94)
+            xe32 = torch.empty(B, T, H, device=dev, dtype=f32)
+            xe16 = torch.empty(B, T, H, device=dev, dtype=dt)
+            ops.add_pos_mask(h_lr, P["pos"], mlen, out32=xe32, out16=xe16)
+            # F0 predictor: tensor cores with fp16 (hi, lo) split operands (default), or fp32 SIMT (f0_precision="fp32")
+            f0h = torch.empty_like(xe32)
+            if P["f0_mode"] == "split":
+                f0s = torch.empty(B, T, 3 * H, device=dev, dtype=torch.float16)
+                ops.add_pos_mask(h_lr, P["pos"], mlen, out32=f0h, out16=f0s, split16=True)
+            else:
+                f0s = None
+                ops.add_pos_mask(h_lr, P["pos"], mlen, out32=f0h)
+            self._encoder(P["f0_enc"], f0h, f0s, mlen, P["f0_mode"])
+            log_f0 = torch.empty(B, T, 1, device=dev, dtype=f32)
+            ops.conv1d(P["f0_out"], f0h, lens=mlen, out32=log_f0)
+            log_f0 = log_f0.view(B, T)
+            coarse = torch.empty(B, T, device=dev, dtype=torch.int64)
+            f0e16 = torch.empty(B, T, H, device=dev, dtype=dt)
+            cin = None if f0_score is None else f0_score.to(device=dev, dtype=torch.int64).contiguous()
+            ops.f0_embed(log_f0, cin, P["f0_emb"], mlen, coarse, out16=f0e16)
+            faux["f0_coarse"] = coarse
+            # MelPredictNetwork (mel_predict_network.py:37-45)
+            m32 = torch.empty(B, T, H, device=dev, dtype=f32)
+            m16 = torch.empty(B, T, H, device=dev, dtype=dt)
+            ops.conv1d(P["mel_cond"], f0e16, res1=xe32, lens=mlen, out32=m32, out16=m16)
+            self._encoder(P["mel_enc"], m32, m16, mlen, "tc")
+            mel32 = torch.empty(B, T, 80, device=dev, dtype=f32)
+            ops.conv1d(P["mel_out"], m16, lens=mlen, out32=mel32)
+            # FramePriorNetwork (frame_prior_network.py:31-41)
+            fp_a = torch.empty(B, T, 80, device=dev, dtype=dt)
+            ops.conv1d(P["fp_cond"], f0e16, res1=mel32, lens=mlen, out16=fp_a)
+            src = fp_a
+            for pc in P["fp"]:
+                dst = torch.empty(B, T, H, device=dev, dtype=dt)
+                ops.conv1d(pc, src, act=ACT_GELU, lens=mlen, out16=dst)
+                src = dst
+            stats = torch.empty(B, T, 2 * self.inter_channels, device=dev, dtype=f32)
+            ops.conv1d(P["proj"], src, lens=mlen, out32=stats)
+            Ci = self.inter_channels
 
-        def cond_of(st):
-            if g_btc is None:
-                return None
-            out = torch.empty(B, 1, st["cond"].cout, device=dev, dtype=f32)
-            ops.conv1d(st["cond"], g_btc, out32=out)
-            return out.view(B, -1)
+            # 5. z_p = m_p + noise * exp(logs_p) * noise_scale (models_ae.py:643)
+            if noise is None:
+                noise = torch.randn(B, Ci, T, device=dev, dtype=f32)
+            noise = noise.to(device=dev, dtype=f32).contiguous()
+            zp32 = torch.empty(B, T, Ci, device=dev, dtype=f32)
+            z16 = torch.empty(B, T, Ci, device=dev, dtype=dt)
+            ops.sample_prior(stats, noise, float(noise_scale), zp32=zp32, zp16=z16)
+            z32 = zp32.clone()
 
-        # 6. reverse flow (models_ae.py:246-253; modules.py:329-349), Flips folded into the weights
-        half = Ci // 2
-        hx32 = torch.empty(B, T, H, device=dev, dtype=f32)
-        hx16 = torch.empty(B, T, H, device=dev, dtype=dt)
-        wo16 = torch.empty(B, T, H, device=dev, dtype=dt)
-        for fl in P["flow"]:
-            io, oo = fl["in_off"], fl["out_off"]
-            ops.conv1d(fl["pre"], z16[:, :, io:io + half], lens=mlen, out32=hx32, out16=hx16)
-            self._wn(fl["wn"], hx32, hx16, mlen, wo16, cond_of(fl["wn"]))
-            ops.conv1d(fl["post"], wo16, alpha=-1.0, res1=z32[:, :, oo:oo + half], lens=mlen,
-                       out32=z32[:, :, oo:oo + half], out16=z16[:, :, oo:oo + half])
+            # speaker conditioning (optional; WN.cond_layer modules.py:152-159, Generator.cond models_ae.py:329-330)
+            g_btc = None
+            if g is not None:
+                if not self.gin_channels:
+                    raise ValueError("model was built with gin_channels=0")
+                g_btc = g.to(device=dev, dtype=f32).reshape(B, 1, self.gin_channels).contiguous()
 
-        # 7. SpecDecoder + spec_proj (ae only; spec_decoder.py:41-46, models_ae.py:647-648)
-        gen_g = None
-        if g_btc is not None:
-            gg = torch.empty(B, 1, self.upsample_initial_channel, device=dev, dtype=f32)
-            ops.conv1d(P["g_cond"], g_btc, out32=gg)
-            gen_g = gg.view(B, -1)
-        Tg = T if max_len is None else min(T, int(max_len))
-        if self.variant == "ae":
-            ops.conv1d(P["sd_pre"], z16, lens=mlen, out32=hx32, out16=hx16)
-            self._wn(P["sd_wn"], hx32, hx16, mlen, wo16, cond_of(P["sd_wn"]))
-            sc_ld = 576
-            spec32 = torch.empty(B, T, sc_ld, device=dev, dtype=f32)
-            spec16 = torch.empty(B, T, sc_ld, device=dev, dtype=dt)
-            sc = self.spec_channels
-            ops.conv1d(P["sd_proj"], wo16, lens=mlen, out32=spec32[:, :, :sc], out16=spec16[:, :, :sc])
-            gin16 = torch.empty(B, T, Ci, device=dev, dtype=dt)
-            ops.conv1d(P["spec_proj"], spec16[:, :, :sc], lens=mlen, out16=gin16)
-            gen_in = gin16
+            def cond_of(st):
+                if g_btc is None:
+                    return None
+                out = torch.empty(B, 1, st["cond"].cout, device=dev, dtype=f32)
+                ops.conv1d(st["cond"], g_btc, out32=out)
+                return out.view(B, -1)
+
+            # 6. reverse flow (models_ae.py:246-253; modules.py:329-349), Flips folded into the weights
+            half = Ci // 2
+            hx32 = torch.empty(B, T, H, device=dev, dtype=f32)
+            hx16 = torch.empty(B, T, H, device=dev, dtype=dt)
+            wo16 = torch.empty(B, T, H, device=dev, dtype=dt)
+            for fl in P["flow"]:
+                io, oo = fl["in_off"], fl["out_off"]
+                ops.conv1d(fl["pre"], z16[:, :, io:io + half], lens=mlen, out32=hx32, out16=hx16)
+                self._wn(fl["wn"], hx32, hx16, mlen, wo16, cond_of(fl["wn"]))
+                ops.conv1d(fl["post"], wo16, alpha=-1.0, res1=z32[:, :, oo:oo + half], lens=mlen,
+                           out32=z32[:, :, oo:oo + half], out16=z16[:, :, oo:oo + half])
+
+            # 7. SpecDecoder + spec_proj (ae only; spec_decoder.py:41-46, models_ae.py:647-648)
+            gen_g = None
+            if g_btc is not None:
+                gg = torch.empty(B, 1, self.upsample_initial_channel, device=dev, dtype=f32)
+                ops.conv1d(P["g_cond"], g_btc, out32=gg)
+                gen_g = gg.view(B, -1)
+            Tg = T if max_len is None else min(T, int(max_len))
+            if self.variant == "ae":
+                ops.conv1d(P["sd_pre"], z16, lens=mlen, out32=hx32, out16=hx16)
+                self._wn(P["sd_wn"], hx32, hx16, mlen, wo16, cond_of(P["sd_wn"]))
+                sc_ld = 576
+                spec32 = torch.empty(B, T, sc_ld, device=dev, dtype=f32)
+                spec16 = torch.empty(B, T, sc_ld, device=dev, dtype=dt)
+                sc = self.spec_channels
+                ops.conv1d(P["sd_proj"], wo16, lens=mlen, out32=spec32[:, :, :sc], out16=spec16[:, :, :sc])
+                gin16 = torch.empty(B, T, Ci, device=dev, dtype=dt)
+                ops.conv1d(P["spec_proj"], spec16[:, :, :sc], lens=mlen, out16=gin16)
+                gen_in = gin16
+            else:
+                gen_in = z16          # z is already masked ((x1 - m) * mask; x0 masked upstream)
+            if Tg != T:
+                gen_in = gen_in[:, :Tg].contiguous()
+
+            # 8. Generator
+            o = self._generator(gen_in, gen_g)
+
+            spec = spec32[:, :, :sc] if self.variant == "ae" else None
+            return (o, z32, zp32, stats, log_f0, spec, mel32), faux
+
+        args = (h, ends, mlen, noise, g, f0_score)
+        if self.cuda_graphs and B * T <= self.cuda_graph_max_frames and _lib.PROFILE is None:
+            outs, faux = self._graphed(frame_level, args, (B, Pn, T, float(noise_scale), max_len, str(x.dtype)))
         else:
-            gen_in = z16          # z is already masked ((x1 - m) * mask; x0 masked upstream)
-        if Tg != T:
-            gen_in = gen_in[:, :Tg].contiguous()
-
-        # 8. Generator
-        o = self._generator(gen_in, gen_g)
-
+            outs, faux = frame_level(*args)
+        aux.update(faux)
+        o, z32, zp32, stats, log_f0, spec, mel32 = outs
         bct = lambda t: t.transpose(1, 2)
         m_p, logs_p = bct(stats[:, :, :Ci]), bct(stats[:, :, Ci:])
         if lf0 is not None:
             log_f0 = lf0
         if self.variant == "ae":
-            return o, y_mask, (bct(z32), bct(zp32), m_p, logs_p), log_f0, bct(spec32[:, :, :sc]), bct(mel32)
+            return o, y_mask, (bct(z32), bct(zp32), m_p, logs_p), log_f0, bct(spec), bct(mel32)
         return o, y_mask, (bct(z32), bct(zp32), m_p, logs_p), log_f0, bct(mel32)
