@@ -48,23 +48,42 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                : "memory");
 }
+// try_wait with a suspend-time hint: the hardware parks the thread until the phase completes or ~kMbarSuspendNs
+// pass, instead of returning every ~35 ns - the role threads and idle epilogue warps otherwise spend as many issue
+// slots polling as the CTA spends on real work.
+#ifndef B200SVS_MBAR_SUSPEND_NS
+#define B200SVS_MBAR_SUSPEND_NS 2000
+#endif
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
       "selp.u32 %0, 1, 0, p;\n\t}\n"
       : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(B200SVS_MBAR_SUSPEND_NS)
       : "memory");
   return ok != 0;
 }
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// Blocks until the phase with `parity` completes.  A wait that lasts longer than 4 s of wall clock is a protocol
+// bug: trap instead of hanging the GPU.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
   uint32_t spins = 0;
+  unsigned long long t0 = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > B200SVS_SPIN_LIMIT) {
-      printf("b200svs: mbarrier timeout block %d thread %d\n", blockIdx.x, threadIdx.x);
-      __trap();
+    if ((++spins & 0xff) == 0) {
+      const unsigned long long now = global_timer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 4000000000ull) {
+        printf("b200svs: mbarrier timeout block %d thread %d\n", blockIdx.x, threadIdx.x);
+        __trap();
+      }
     }
   }
 }
