@@ -51,6 +51,8 @@ struct ConvTcParams {
   int slot_r2_off;                         // offset of the res2 area inside a slot (0 = none)
   int slot_raw_off;                        // offset of the raw 16-bit area (res16 in / out16r out) inside a slot
   int stores_in_flight;                    // TMA store groups left pending before a slot is recycled
+  int w_resident;                          // all weight tiles stay in shared memory (w_stages = taps x K chunks)
+  int peek;                                // MMA thread peeks the next tile's barriers before the last tap
   int chunks_per_sub, n_out_tile;          // output chunks per 128-row sub-tile; output columns per N tile
   int tmem_cols;
   int ksub;                                // K=16 MMA steps per K chunk (4, or fewer when Cin < 64)
@@ -389,7 +391,7 @@ __device__ __forceinline__ void epilogue_dispatch(const ConvTcParams& p, TcBarri
 // The tcgen05.mma issue loop of one CTA, run by a single thread.  KSUB = K=16 steps per 64-channel chunk
 // (0: runtime p.ksub); MSUB = 128-row sub-tiles per tile.  Descriptor arithmetic is done on the 14-bit
 // (address >> 4) field directly: every operand tile lies below 256 KB, so the adds never carry out of it.
-template <int MSUB, int KSUB>
+template <int MSUB, int KSUB, bool WRES>
 __device__ __forceinline__ void mma_issue_loop(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
                                                uint32_t smA_u, uint32_t smW_u) {
   const uint64_t descA0 = make_desc_k128(smA_u), descW0 = make_desc_k128(smW_u);
@@ -402,21 +404,39 @@ __device__ __forceinline__ void mma_issue_loop(const ConvTcParams& p, TcBarriers
   const uint32_t idesc = p.idesc;
   int as = 0, ws = 0, it = 0;
   uint32_t aph = 0, wph = 0;
+  if (WRES) {            // every weight tile of the conv is resident: one wait for the whole kernel
+    mbar_wait(&bars->w_full[0], 0);
+    tc_fence_after();
+  }
+  // The waits of tile i+1 (accumulator drained, first activation chunk landed) are peeked before the last tap
+  // of tile i is issued, while the tensor pipe still has a tap's worth of MMAs queued: in a tensor-bound conv
+  // both barriers completed long ago and only their latency is left, which otherwise drains the MMA queue at
+  // every tile boundary.  A failed peek falls back to the blocking wait in its usual place.
+  bool peeked = false;
   for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
     const int acc = it & 1;
-    mbar_wait(&bars->tmem_empty[acc], ((it >> 1) & 1) ^ 1);
+    if (!peeked) mbar_wait(&bars->tmem_empty[acc], ((it >> 1) & 1) ^ 1);
     tc_fence_after();
     trace_stamp(p, it, 2, clock64());
     const uint32_t d_tmem = tmem_base + acc * acc_cols;
     uint32_t accum = 0;
     for (int ch = 0; ch < p.nchunks; ++ch) {
-      mbar_wait(&bars->a_full[as], aph);
+      if (!(peeked && ch == 0)) mbar_wait(&bars->a_full[as], aph);
       if (ch == 0) trace_stamp(p, it, 3, clock64());
       uint64_t da = descA0 + as * a_stage_d;
+      const bool last_ch = ch == p.nchunks - 1;
       for (int tap = 0; tap < p.ntaps; ++tap) {
-        mbar_wait(&bars->w_full[ws], wph);
-        tc_fence_after();
-        const uint64_t db = descW0 + ws * w_stage_d;
+        if (!WRES) {
+          mbar_wait(&bars->w_full[ws], wph);
+          tc_fence_after();
+        }
+        if (last_ch && tap == p.ntaps - 1) {
+          const int as_n = as + 1 == p.a_stages ? 0 : as + 1;
+          const uint32_t aph_n = as + 1 == p.a_stages ? aph ^ 1 : aph;
+          peeked = p.peek && tile + static_cast<int>(gridDim.x) < p.total_tiles &&
+                   mbar_test(&bars->tmem_empty[acc ^ 1], (((it + 1) >> 1) & 1) ^ 1) && mbar_test(&bars->a_full[as_n], aph_n);
+        }
+        const uint64_t db = descW0 + (WRES ? static_cast<uint32_t>(ch * p.ntaps + tap) : static_cast<uint32_t>(ws)) * w_stage_d;
 #pragma unroll
         for (int ms = 0; ms < MSUB; ++ms) {
           umma_f16(d_tmem + ms * p.block_n, da + ms * kSubD, db, idesc, accum);
@@ -427,10 +447,12 @@ __device__ __forceinline__ void mma_issue_loop(const ConvTcParams& p, TcBarriers
             for (int k = 1; k < ksub; ++k) umma_f16(d_tmem + ms * p.block_n, da + ms * kSubD + 2 * k, db + 2 * k, idesc, 1u);
           }
         }
-        umma_commit(&bars->w_empty[ws]);
         accum = 1;
         da += tap_d;
-        if (++ws == p.w_stages) { ws = 0; wph ^= 1; }
+        if (!WRES) {
+          umma_commit(&bars->w_empty[ws]);
+          if (++ws == p.w_stages) { ws = 0; wph ^= 1; }
+        }
       }
       umma_commit(&bars->a_empty[as]);
       if (++as == p.a_stages) { as = 0; aph ^= 1; }
@@ -472,7 +494,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < p.a_stages; ++s) { mbar_init(&bars->a_full[s], 1); mbar_init(&bars->a_empty[s], 1); }
-    for (int s = 0; s < p.w_stages; ++s) { mbar_init(&bars->w_full[s], 1); mbar_init(&bars->w_empty[s], 1); }
+    for (int s = 0; s < (p.w_resident ? 1 : p.w_stages); ++s) { mbar_init(&bars->w_full[s], 1); mbar_init(&bars->w_empty[s], 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], kEpiThreads / 32); }
     for (int s = 0; s < p.n_slots; ++s) {
       mbar_init(&bars->e_full[s], 1); mbar_init(&bars->e_empty[s], 1); mbar_init(&bars->s_ready[s], kEpiThreads / 32);
@@ -515,7 +537,14 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       // ------------------------------------------------------------ weight-ring TMA producer
       int ws = 0, it = 0;
       uint32_t wph = 0;
-      for (TileIter ti(p); ti.valid(p); ti.next(p), ++it) {
+      if (p.w_resident) {        // the whole conv's weights (one N tile) fit: loaded once, never recycled
+        const int ksteps = p.nchunks * p.ntaps;
+        mbar_arrive_expect_tx(&bars->w_full[0], static_cast<uint32_t>(ksteps) * p.w_stage_bytes);
+        for (int ch = 0; ch < p.nchunks; ++ch)
+          for (int tap = 0; tap < p.ntaps; ++tap)
+            tma_load_2d(smW + (ch * p.ntaps + tap) * p.w_stage_bytes, &tmW, &bars->w_full[0], ch * kBlockK, tap * p.cout_pad);
+      }
+      for (TileIter ti(p); !p.w_resident && ti.valid(p); ti.next(p), ++it) {
         const int n_idx = ti.n_idx;
         for (int ch = 0; ch < p.nchunks; ++ch) {
           for (int tap = 0; tap < p.ntaps; ++tap) {
@@ -535,13 +564,22 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // run of UTCHMMAs with immediate descriptor offsets)
     if (elect_one()) {
       const uint32_t smA_u = smem_u32(smA), smW_u = smem_u32(smW);
-      if (p.msub == 2) {
-        if (p.ksub == 4) mma_issue_loop<2, 4>(p, bars, tmem_base, smA_u, smW_u);
-        else if (p.ksub == 2) mma_issue_loop<2, 2>(p, bars, tmem_base, smA_u, smW_u);
-        else mma_issue_loop<2, 0>(p, bars, tmem_base, smA_u, smW_u);
+      if (p.w_resident) {
+        if (p.msub == 2) {
+          if (p.ksub == 4) mma_issue_loop<2, 4, true>(p, bars, tmem_base, smA_u, smW_u);
+          else if (p.ksub == 2) mma_issue_loop<2, 2, true>(p, bars, tmem_base, smA_u, smW_u);
+          else mma_issue_loop<2, 0, true>(p, bars, tmem_base, smA_u, smW_u);
+        } else {
+          if (p.ksub == 4) mma_issue_loop<1, 4, true>(p, bars, tmem_base, smA_u, smW_u);
+          else mma_issue_loop<1, 0, true>(p, bars, tmem_base, smA_u, smW_u);
+        }
+      } else if (p.msub == 2) {
+        if (p.ksub == 4) mma_issue_loop<2, 4, false>(p, bars, tmem_base, smA_u, smW_u);
+        else if (p.ksub == 2) mma_issue_loop<2, 2, false>(p, bars, tmem_base, smA_u, smW_u);
+        else mma_issue_loop<2, 0, false>(p, bars, tmem_base, smA_u, smW_u);
       } else {
-        if (p.ksub == 4) mma_issue_loop<1, 4>(p, bars, tmem_base, smA_u, smW_u);
-        else mma_issue_loop<1, 0>(p, bars, tmem_base, smA_u, smW_u);
+        if (p.ksub == 4) mma_issue_loop<1, 4, false>(p, bars, tmem_base, smA_u, smW_u);
+        else mma_issue_loop<1, 0, false>(p, bars, tmem_base, smA_u, smW_u);
       }
     }
     __syncwarp();
@@ -717,6 +755,15 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   // as many activation stages (loads in flight) as leave room for the minimum of everything else
   const bool has_res = ep.res1 || ep.res2 || ep.res16;
   const int min_slots = has_res ? 4 : 3;
+  // Resident weights: with one N tile and taps x K-chunks x block_n x 128 B small enough (the 32- and 64-channel
+  // Generator stages, k = 3 at 128 channels) the weights are loaded once per CTA instead of once per tile, and the
+  // MMA thread's tap loop loses its per-tap wait and commit.
+  static const int wres_on = [] { const char* e = getenv("B200SVS_TC_WRES"); return e ? atoi(e) : 1; }();
+  static const int peek_on = [] { const char* e = getenv("B200SVS_TC_PEEK"); return e ? atoi(e) : 1; }();
+  p.peek = peek_on;
+  p.w_resident = wres_on && n_tiles == 1 &&
+                 budget - ksteps * p.w_stage_bytes - 2 * p.a_stage_bytes >= min_slots * p.slot_bytes;
+  if (p.w_resident) w_min = ksteps;
   int a_stages = kMaxAStages;
   if (const char* e = getenv("B200SVS_TC_ASTAGES")) { int v = atoi(e); if (v >= 2 && v <= kMaxAStages) a_stages = v; }   // tuning knob
   while (a_stages > 2 && budget - a_stages * p.a_stage_bytes - w_min * p.w_stage_bytes < min_slots * p.slot_bytes) --a_stages;
@@ -728,7 +775,8 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   if (n_slots < 2) { n_slots = 2; }
   int w_stages = (avail - n_slots * p.slot_bytes) / p.w_stage_bytes;
   if (w_stages > kMaxWStages) w_stages = kMaxWStages;
-  B200SVS_REQUIRE(w_stages >= 2, "conv1d_tc: not enough shared memory (block_n=%d)", a->block_n);
+  if (p.w_resident) w_stages = ksteps;
+  B200SVS_REQUIRE(w_stages >= 2 || p.w_resident, "conv1d_tc: not enough shared memory (block_n=%d)", a->block_n);
   p.n_slots = n_slots;
   p.w_stages = w_stages;
   // Slot recycling: after committing the store of chunk i the store thread waits until at most S bulk groups

@@ -27,7 +27,10 @@ def run(C, k, dil, res, block_n=None):
     x = (torch.randn(B, T, C, generator=g)).half().to(DEV)
     o16 = torch.empty(B, T, C, device=DEV, dtype=torch.float16)
     kw = dict(out16=o16, post_lrelu=0.1)
-    if res:
+    if res == 2:       # the Generator's 16-bit residual stream: res16 in, raw out16r in place, activated out16
+        r = torch.randn(B, T, C, device=DEV).half()
+        kw.update(res16=r, out16r=r)
+    elif res:
         r = torch.randn(B, T, C, device=DEV)
         kw.update(res1=r, out32=r)
     for _ in range(2):
@@ -44,6 +47,15 @@ def run(C, k, dil, res, block_n=None):
     t = buf.cpu().double()
     n_it = int((t[0, :, 4] > 0).sum())
     print(f"\nC={C} k={k} dil={dil} res={res} block_n={pc.block_n}: {us:.1f} us, T={T}, tiles/CTA~{n_it}")
+    if COMPACT:
+        tt = t[:, 4:n_it - 2]
+        per = float(((tt[:, -1, 4] - tt[:, 0, 4]) / (tt.shape[1] - 1)).mean())
+        mma = float((tt[:, :, 4] - tt[:, :, 3]).mean()); epi = float((tt[:, :, 6] - tt[:, :, 5]).mean())
+        n_mma = 2 * k * C // 16
+        bytes_tile = 256 * C * (8 if res == 2 else 16 if res else 4)
+        print(f"   cycles/tile {per:.0f} | mma span {mma:.0f} ({mma / n_mma:.0f}/MMA x {n_mma}) | epi span {epi:.0f} | "
+              f"slot wait {float(tt[:, :, 7].mean()):.0f} | hbm floor(24B/clk) {bytes_tile / 24:.0f} | alg {B * T * C * (bytes_tile / 256 / C) / us / 1e3:.0f} GB/s")
+        return
     for cta in (0, 77):
         tt = t[cta, :n_it]
         base = tt[0, 0]
@@ -54,12 +66,18 @@ def run(C, k, dil, res, block_n=None):
               f" | mma issue span {d(4,3):.0f} | mma done->epi start {d(5,4):.0f} | epi span {d(6,5):.0f}"
               f" (slot wait {float(tt[lo:hi,7].mean()):.0f}, ld wait {float(tt[lo:hi,10].mean()):.0f})"
               f" | store first->last {d(9,8):.0f} | epi done->store done {d(9,6):.0f}")
+        print(f"     prev last-MMA-issue -> acc free {float((tt[lo+1:hi+1, 2] - tt[lo:hi, 4]).mean()):.0f}")
         if cta == 0:
             for i in range(3, 7):
                 print("     tile", i, [int(v - base) for v in tt[i, [0, 1, 2, 3, 4, 5, 6, 8, 9]]])
 
 
 import sys as _s
+COMPACT = len(_s.argv) > 1 and _s.argv[1] == 'gen'
 cfgs = [(256, 3, 1, False, 128), (256, 3, 1, False, 256), (256, 11, 1, False, 128), (256, 11, 1, False, 256), (256, 7, 1, True, 128), (256, 7, 1, True, 256)] if len(_s.argv) > 1 and _s.argv[1] == 'bn' else None
+if len(_s.argv) > 1 and _s.argv[1] == 'gap':
+    cfgs = [(32, 11, 1, False), (64, 7, 1, False), (128, 11, 1, False), (32, 3, 1, False)]
+if COMPACT:
+    cfgs = [(C, k, 1, r) for C in (128, 64, 32) for k in (3, 7, 11) for r in (False, 2)]
 for cfg in cfgs or [(128, 3, 1, False), (128, 3, 1, True), (128, 11, 5, False), (64, 3, 1, False), (64, 7, 3, True), (32, 3, 1, False), (32, 11, 5, False), (32, 7, 1, True), (256, 3, 1, False)]:
     run(*cfg)
