@@ -273,6 +273,13 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n, bool bf16) {
          (uint32_t(m >> 4) << 24);
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// wait: blocks until every grid this one depends on has completed and its memory is visible (no-op when the
+// kernel was launched without the programmatic-serialization attribute).  launch_dependents: the dependent grid
+// may be scheduled once every CTA of this grid has executed it (or exited).
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---------------------------------------------------------------- math
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + __expf(-x)); }
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }

@@ -36,6 +36,7 @@ constexpr int kRowBytes = kBlockK * 2;     // one K-chunk row of a 16-bit operan
 constexpr int kMaxAStages = 4;
 constexpr int kMaxWStages = 8;
 constexpr int kMaxSlots = 8;
+constexpr int kMaxAcc = 4;               // TMEM accumulator ring (2 or 4 buffers)
 constexpr int kEpiCols = 32;               // output columns per epilogue chunk
 constexpr int kSlot32Bytes = 128 * kEpiCols * 4;   // 16 KB: [128 rows][32 fp32], SWIZZLE_128B
 constexpr int kSlot16Bytes = 128 * kEpiCols * 2;   //  8 KB: [128 rows][32 x 16-bit], SWIZZLE_64B
@@ -51,7 +52,9 @@ struct ConvTcParams {
   int slot_r2_off;                         // offset of the res2 area inside a slot (0 = none)
   int slot_raw_off;                        // offset of the raw 16-bit area (res16 in / out16r out) inside a slot
   int stores_in_flight;                    // TMA store groups left pending before a slot is recycled
+  int acc_shift;                           // log2 of the accumulator ring depth (1 or 2)
   int w_resident;                          // all weight tiles stay in shared memory (w_stages = taps x K chunks)
+  int xpre;                                // epilogue prefetches the next tile's first TMEM chunk
   int peek;                                // MMA thread peeks the next tile's barriers before the last tap
   int chunks_per_sub, n_out_tile;          // output chunks per 128-row sub-tile; output columns per N tile
   int tmem_cols;
@@ -65,7 +68,7 @@ struct ConvTcParams {
 struct __align__(8) TcBarriers {
   uint64_t a_full[kMaxAStages], a_empty[kMaxAStages];
   uint64_t w_full[kMaxWStages], w_empty[kMaxWStages];
-  uint64_t tmem_full[2], tmem_empty[2];
+  uint64_t tmem_full[kMaxAcc], tmem_empty[kMaxAcc];
   uint64_t e_full[kMaxSlots], e_empty[kMaxSlots];
   uint64_t s_ready[kMaxSlots];             // epilogue warps -> store thread: slot holds a finished chunk
   uint32_t tmem_base;
@@ -158,6 +161,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
   const int half = (warp - 4) >> 2;
   const int block_n = p.block_n, half_n = p.block_n >> 1;
   const int acc_cols = p.msub * block_n;
+  const int acc_shift = p.acc_shift, acc_mask = (1 << p.acc_shift) - 1;
   const int cps = p.chunks_per_sub;
   const int n_chunks = p.msub * cps;
   const int n_slots = p.n_slots, slot_bytes = p.slot_bytes;
@@ -288,16 +292,20 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
 
   int it = 0, sl = 0;
   uint32_t eph = 0;
+  const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + half * 16;
+  uint32_t ra0[16], rb0[GATE ? 1 : 16], ra1[GATE ? 16 : 1];
+  bool pre = false;                    // ra0 already holds the in-flight load of this tile's first chunk
   for (TileIter ti(p); ti.valid(p); ti.next(p), ++it) {
-    const int acc = it & 1;
+    const int acc = it & acc_mask;
     const int tile_b = ti.b, tile_t0 = ti.t0(p);
     const int len_b = ep.lens ? __ldg(ep.lens + tile_b) : p.T;
     const int pcol0 = ti.n_idx * block_n + half * 16;
-    mbar_wait(&bars->tmem_full[acc], (it >> 1) & 1);
-    tc_fence_after();
+    if (!pre) {
+      mbar_wait(&bars->tmem_full[acc], (it >> acc_shift) & 1);
+      tc_fence_after();
+    }
     if (threadIdx.x == 128) trace_stamp(p, it, 5, clock64());
-    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * acc_cols + half * 16;
-    uint32_t ra0[16], rb0[GATE ? 1 : 16], ra1[GATE ? 16 : 1];
+    const uint32_t taddr = taddr0 + acc * acc_cols;
     // chunk ci: sub-tile ms = ci / cps, column chunk ch = ci % cps (msub <= 2)
     auto finish = [&](int ci, const uint32_t* r0, const uint32_t* r1) {
       const int ms = ci >= cps ? 1 : 0;
@@ -322,14 +330,24 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
         finish(ci, ra0, ra1);
       }
     } else {                           // block_n == cps * 32: chunk ci sits at TMEM column ci * 32
-      tmem_ld16_nowait(taddr, ra0);
+      if (!pre) tmem_ld16_nowait(taddr, ra0);
+      pre = false;
       for (int ci = 0; ci < n_chunks; ci += 2) {
         tmem_ld_wait16(ra0);
         if (ci + 1 < n_chunks) tmem_ld16_nowait(taddr + (ci + 1) * kEpiCols, rb0);
         finish(ci, ra0, ra1);
         if (ci + 1 < n_chunks) {
           tmem_ld_wait16(rb0);
-          if (ci + 2 < n_chunks) tmem_ld16_nowait(taddr + (ci + 2) * kEpiCols, ra0);
+          if (ci + 2 < n_chunks) {
+            tmem_ld16_nowait(taddr + (ci + 2) * kEpiCols, ra0);
+          } else if (p.xpre && ti.tile + static_cast<int>(gridDim.x) < p.total_tiles &&
+                     mbar_test(&bars->tmem_full[(it + 1) & acc_mask], ((it + 1) >> acc_shift) & 1)) {
+            // the next tile's accumulator is already complete (the usual case when the epilogue is the slower
+            // side): start fetching its first chunk under the last chunk of this tile
+            tc_fence_after();
+            tmem_ld16_nowait(taddr0 + ((it + 1) & acc_mask) * acc_cols, ra0);
+            pre = true;
+          }
           finish(ci + 1, rb0, ra1);
         }
       }
@@ -401,6 +419,7 @@ __device__ __forceinline__ void mma_issue_loop(const ConvTcParams& p, TcBarriers
   constexpr uint32_t kSubD = (128 * kRowBytes) >> 4;       // next 128-row sub-tile of the activation stage
   const int ksub = KSUB ? KSUB : p.ksub;
   const int acc_cols = p.msub * p.block_n;
+  const int acc_shift = p.acc_shift, acc_mask = (1 << p.acc_shift) - 1;
   const uint32_t idesc = p.idesc;
   int as = 0, ws = 0, it = 0;
   uint32_t aph = 0, wph = 0;
@@ -414,8 +433,8 @@ __device__ __forceinline__ void mma_issue_loop(const ConvTcParams& p, TcBarriers
   // every tile boundary.  A failed peek falls back to the blocking wait in its usual place.
   bool peeked = false;
   for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-    const int acc = it & 1;
-    if (!peeked) mbar_wait(&bars->tmem_empty[acc], ((it >> 1) & 1) ^ 1);
+    const int acc = it & acc_mask;
+    if (!peeked) mbar_wait(&bars->tmem_empty[acc], ((it >> acc_shift) & 1) ^ 1);
     tc_fence_after();
     trace_stamp(p, it, 2, clock64());
     const uint32_t d_tmem = tmem_base + acc * acc_cols;
@@ -434,7 +453,7 @@ __device__ __forceinline__ void mma_issue_loop(const ConvTcParams& p, TcBarriers
           const int as_n = as + 1 == p.a_stages ? 0 : as + 1;
           const uint32_t aph_n = as + 1 == p.a_stages ? aph ^ 1 : aph;
           peeked = p.peek && tile + static_cast<int>(gridDim.x) < p.total_tiles &&
-                   mbar_test(&bars->tmem_empty[acc ^ 1], (((it + 1) >> 1) & 1) ^ 1) && mbar_test(&bars->a_full[as_n], aph_n);
+                   mbar_test(&bars->tmem_empty[(it + 1) & acc_mask], (((it + 1) >> acc_shift) & 1) ^ 1) && mbar_test(&bars->a_full[as_n], aph_n);
         }
         const uint64_t db = descW0 + (WRES ? static_cast<uint32_t>(ch * p.ntaps + tap) : static_cast<uint32_t>(ws)) * w_stage_d;
 #pragma unroll
@@ -495,7 +514,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < p.a_stages; ++s) { mbar_init(&bars->a_full[s], 1); mbar_init(&bars->a_empty[s], 1); }
     for (int s = 0; s < (p.w_resident ? 1 : p.w_stages); ++s) { mbar_init(&bars->w_full[s], 1); mbar_init(&bars->w_empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], kEpiThreads / 32); }
+    for (int s = 0; s < kMaxAcc; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], kEpiThreads / 32); }
     for (int s = 0; s < p.n_slots; ++s) {
       mbar_init(&bars->e_full[s], 1); mbar_init(&bars->e_empty[s], 1); mbar_init(&bars->s_ready[s], kEpiThreads / 32);
     }
@@ -510,9 +529,15 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
+  // Programmatic dependent launch: this CTA's setup (barriers, TMEM, bias, tensor-map prefetch, and below the
+  // resident-weight loads, none of which read what the previous kernel writes) ran while the previous kernel of
+  // the stream was still draining; let the next kernel's CTAs be scheduled as soon as ours exit.  Every thread
+  // that reads or writes activations waits for the previous grid to complete and flush first.
+  griddep_launch_dependents();
 
   if (warp == 0) {
     if (lane == 0) {
+      griddep_wait();
       // ------------------------------------------------------------ activation-ring TMA producer (its own
       // thread: the weight ring's back-pressure must not delay the prefetch of the next tiles' activations)
       int as = 0, it = 0;
@@ -588,6 +613,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       // ------------------------------------------------------------ TMA store thread: drains finished chunks so
       // the epilogue warps never meet at a CTA-wide barrier; keeps `stores_in_flight` bulk groups pending and
       // recycles the slot of the oldest completed one
+      griddep_wait();
       int sl = 0, n_done = 0, free_sl = 0;
       uint32_t sph = 0;
       const bool split16 = ep.out16 && ep.out16_dtype == B200SVS_DT_F16_SPLIT;
@@ -636,6 +662,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp == 3) {
     if (lane == 0) {
       // ------------------------------------------------------------ epilogue staging producer
+      griddep_wait();
       int sl = 0;
       uint32_t eph = 0;
       for (TileIter ti(p); ti.valid(p); ti.next(p)) {
@@ -660,6 +687,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else if (warp >= 4 && warp < 12) {
+    griddep_wait();
     epilogue_dispatch(p, bars, tmem_base, smem_u32(smE), smem_u32(bias_s));
   }
 
@@ -761,6 +789,8 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   static const int wres_on = [] { const char* e = getenv("B200SVS_TC_WRES"); return e ? atoi(e) : 1; }();
   static const int peek_on = [] { const char* e = getenv("B200SVS_TC_PEEK"); return e ? atoi(e) : 1; }();
   p.peek = peek_on;
+  static const int xpre_on = [] { const char* e = getenv("B200SVS_TC_XPRE"); return e ? atoi(e) : 1; }();
+  p.xpre = xpre_on;
   p.w_resident = wres_on && n_tiles == 1 &&
                  budget - ksteps * p.w_stage_bytes - 2 * p.a_stage_bytes >= min_slots * p.slot_bytes;
   if (p.w_resident) w_min = ksteps;
@@ -785,7 +815,11 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   // gives the residual prefetch (and the epilogue's next write) a lead of n_slots - S - 1 chunks.
   p.stores_in_flight = 1;
   if (const char* e = getenv("B200SVS_TC_SIF")) { int v = atoi(e); if (v >= 0 && v <= n_slots - 2) p.stores_in_flight = v; }   // tuning knob
-  p.tmem_cols = next_pow2_cols(2 * p.msub * a->block_n);
+  // accumulator ring: 4 buffers when TMEM has room (block_n <= 64 with 256-row tiles) - the MMA of tile i+1 then
+  // no longer waits for the epilogue of tile i-1, which left the epilogue idle ~25 % of a short (k = 3) tile
+  static const int acc4_on = [] { const char* e = getenv("B200SVS_TC_ACC4"); return e ? atoi(e) : 1; }();
+  p.acc_shift = (acc4_on && 4 * p.msub * a->block_n <= 512) ? 2 : 1;
+  p.tmem_cols = next_pow2_cols((1 << p.acc_shift) * p.msub * a->block_n);
   p.ksub = a->Cin >= kBlockK ? 4 : (a->Cin + 15) / 16;
   p.idesc = make_idesc_f16(128, a->block_n, a->x_dtype == B200SVS_DT_BF16);
   p.ep = ep;
@@ -853,6 +887,15 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     configured = smem;
   }
   int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
-  conv1d_tc_kernel<<<grid, kTcThreads, smem, as_stream(stream)>>>(tmA, tmW, tmR, tmR2, tmO32, tmO16, tmR16, tmO16r, p);
-  return check_launch("conv1d_tc_kernel");
+  // launched with programmatic stream serialization (PDL): the kernel may start while its predecessor in the
+  // stream drains; it orders itself with griddepcontrol.wait (B200SVS_PDL=0 restores full serialization)
+  static const int pdl_on = [] { const char* e = getenv("B200SVS_PDL"); return e ? atoi(e) : 1; }();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kTcThreads); cfg.dynamicSmemBytes = smem; cfg.stream = as_stream(stream);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_on ? 1 : 0;
+  return check_cuda(cudaLaunchKernelEx(&cfg, conv1d_tc_kernel, tmA, tmW, tmR, tmR2, tmO32, tmO16, tmR16, tmO16r, p),
+                    "conv1d_tc_kernel launch");
 }

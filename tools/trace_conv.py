@@ -75,6 +75,8 @@ def run(C, k, dil, res, block_n=None):
 import sys as _s
 COMPACT = len(_s.argv) > 1 and _s.argv[1] == 'gen'
 cfgs = [(256, 3, 1, False, 128), (256, 3, 1, False, 256), (256, 11, 1, False, 128), (256, 11, 1, False, 256), (256, 7, 1, True, 128), (256, 7, 1, True, 256)] if len(_s.argv) > 1 and _s.argv[1] == 'bn' else None
+if len(_s.argv) > 1 and _s.argv[1] == 'hbm':
+    cfgs = [(32, 3, 1, False), (32, 3, 1, 2), (64, 3, 1, False), (64, 3, 1, 2)]
 if len(_s.argv) > 1 and _s.argv[1] == 'gap':
     cfgs = [(32, 11, 1, False), (64, 7, 1, False), (128, 11, 1, False), (32, 3, 1, False)]
 if COMPACT:
