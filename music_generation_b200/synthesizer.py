@@ -39,7 +39,8 @@ class SynthesizerTrn(nn.Module):
                  resblock_dilation_sizes, upsample_rates, upsample_initial_channel, upsample_kernel_sizes,
                  n_speakers=0, gin_channels=0, use_sdp=True, n_vocab_note=100, *, operand_dtype="fp16",
                  max_position_embeddings=2000, generator_chunk_frames=32768, f0_precision="split",
-                 text_precision="split", generator_residual="fp16", cuda_graphs=False, seed=1234, **kwargs):
+                 text_precision="split", generator_residual="fp16", cuda_graphs=False, fuse_spec_proj=False,
+                 seed=1234, **kwargs):
         super().__init__()
         if hidden_channels != 192 or n_heads != 2:
             raise ValueError("kernels are specialised for hidden_channels=192, n_heads=2 (ours_ae.json)")
@@ -63,6 +64,10 @@ class SynthesizerTrn(nn.Module):
         if generator_residual not in ("fp16", "fp32"):
             raise ValueError("generator_residual must be 'fp16' (16-bit residual stream; fp16 operand mode only) or 'fp32'")
         self.generator_residual = generator_residual
+        # every call site of the reference discards spec_predict; with fuse_spec_proj=True the two
+        # 513-wide 1x1 convs SpecDecoder.proj -> spec_proj collapse into one 192x192 conv (see _pack) and infer
+        # returns None in spec_predict's place.  Off by default: the result tuple then matches the reference's.
+        self.fuse_spec_proj = bool(fuse_spec_proj)
         # launch-bound (small) calls: replay the frame-level part of infer from a CUDA graph keyed by its shapes
         self.cuda_graphs = bool(cuda_graphs)
         self.cuda_graph_max_frames = 32768
@@ -202,6 +207,12 @@ class SynthesizerTrn(nn.Module):
             P["sd_wn"] = wn_stack("spec_decoder.enc")
             P["sd_proj"] = conv("spec_decoder.proj")
             P["spec_proj"] = conv("spec_proj")
+            # spec_proj(proj(x) * m) * m == m * (W2 W1 x + W2 b1 + b2) for a 0/1 frame mask m
+            # (ext_modules/spec_decoder.py:41-46, models_ae.py:647-650): one masked 1x1 conv
+            w1, b1 = W("spec_decoder.proj")[:, :, 0], Bv("spec_decoder.proj")
+            w2, b2 = W("spec_proj")[:, :, 0], Bv("spec_proj")
+            P["sd_fused"] = packer.pack_conv((w2.double() @ w1.double()).float().unsqueeze(-1),
+                                             (w2.double() @ b1.double() + b2.double()).float(), dtype=dt).to(dev)
         # generator
         d = "decoder"
         P["g_pre"] = conv(d + ".conv_pre")
@@ -240,7 +251,8 @@ class SynthesizerTrn(nn.Module):
         for key, name in (("text_enc", "text"), ("dp", "text"), ("dp_proj", "text"), ("f0_enc", "f0"), ("f0_out", "f0"),
                           ("mel_cond", "mel"), ("mel_enc", "mel"), ("mel_out", "mel"), ("fp_cond", "prior"),
                           ("fp", "prior"), ("proj", "prior"), ("flow", "flow"), ("sd_pre", "specdec"),
-                          ("sd_wn", "specdec"), ("sd_proj", "specdec"), ("spec_proj", "specdec"), ("g_pre", "gen_pre"),
+                          ("sd_wn", "specdec"), ("sd_proj", "specdec"), ("spec_proj", "specdec"), ("sd_fused", "specdec"),
+                          ("g_pre", "gen_pre"),
                           ("g_cond", "gen_pre")):
             if key in P and P[key] is not None:
                 tag(P[key], name)
@@ -568,13 +580,16 @@ class SynthesizerTrn(nn.Module):
             if self.variant == "ae":
                 ops.conv1d(P["sd_pre"], z16, lens=mlen, out32=hx32, out16=hx16)
                 self._wn(P["sd_wn"], hx32, hx16, mlen, wo16, cond_of(P["sd_wn"]))
-                sc_ld = 576
-                spec32 = torch.empty(B, T, sc_ld, device=dev, dtype=f32)
-                spec16 = torch.empty(B, T, sc_ld, device=dev, dtype=dt)
-                sc = self.spec_channels
-                ops.conv1d(P["sd_proj"], wo16, lens=mlen, out32=spec32[:, :, :sc], out16=spec16[:, :, :sc])
                 gin16 = torch.empty(B, T, Ci, device=dev, dtype=dt)
-                ops.conv1d(P["spec_proj"], spec16[:, :, :sc], lens=mlen, out16=gin16)
+                spec32, sc = None, self.spec_channels
+                if self.fuse_spec_proj:
+                    ops.conv1d(P["sd_fused"], wo16, lens=mlen, out16=gin16)
+                else:
+                    sc_ld = 576
+                    spec32 = torch.empty(B, T, sc_ld, device=dev, dtype=f32)
+                    spec16 = torch.empty(B, T, sc_ld, device=dev, dtype=dt)
+                    ops.conv1d(P["sd_proj"], wo16, lens=mlen, out32=spec32[:, :, :sc], out16=spec16[:, :, :sc])
+                    ops.conv1d(P["spec_proj"], spec16[:, :, :sc], lens=mlen, out16=gin16)
                 gen_in = gin16
             else:
                 gen_in = z16          # z is already masked ((x1 - m) * mask; x0 masked upstream)
@@ -584,7 +599,7 @@ class SynthesizerTrn(nn.Module):
             # 8. Generator
             o = self._generator(gen_in, gen_g)
 
-            spec = spec32[:, :, :sc] if self.variant == "ae" else None
+            spec = spec32[:, :, :sc] if self.variant == "ae" and spec32 is not None else None
             return (o, z32, zp32, stats, log_f0, spec, mel32), faux
 
         args = (h, ends, mlen, noise, g, f0_score)
@@ -599,5 +614,5 @@ class SynthesizerTrn(nn.Module):
         if lf0 is not None:
             log_f0 = lf0
         if self.variant == "ae":
-            return o, y_mask, (bct(z32), bct(zp32), m_p, logs_p), log_f0, bct(spec), bct(mel32)
+            return o, y_mask, (bct(z32), bct(zp32), m_p, logs_p), log_f0, None if spec is None else bct(spec), bct(mel32)
         return o, y_mask, (bct(z32), bct(zp32), m_p, logs_p), log_f0, bct(mel32)

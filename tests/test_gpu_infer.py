@@ -98,7 +98,8 @@ def test_predicted_durations_are_bit_exact():
     ({"generator_residual": "fp32"}, SNR_DB_TOL),                           # fp32 residual stream in the Generator
     ({"f0_precision": "fp32", "text_precision": "fp32"}, SNR_DB_TOL),       # fp32 SIMT encoders
     ({"operand_dtype": "bf16"}, 34.0),                                      # bf16 operands (8-bit mantissa): reported, looser
-], ids=["residual_fp32", "encoders_fp32", "bf16"])
+    ({"fuse_spec_proj": True}, SNR_DB_TOL),                                 # SpecDecoder.proj -> spec_proj as one conv
+], ids=["residual_fp32", "encoders_fp32", "bf16", "fused_spec_proj"])
 def test_infer_option_paths_against_golden(kw, snr_min):
     """The non-default constructor paths stay within tolerance of the reference's golden output."""
     name = "ae_phdur_b2"
@@ -112,6 +113,7 @@ def test_infer_option_paths_against_golden(kw, snr_min):
     print(f"{kw}: snr {s:.2f} dB max_abs {max_abs(g['o'], o):.2e}")
     assert torch.equal(res[1].cpu(), g["y_mask"])
     assert s >= snr_min, s
+    assert (res[4] is None) == bool(kw.get("fuse_spec_proj"))              # spec_predict is the price of the fusion
     if "operand_dtype" not in kw:
         assert max_abs(g["o"], o) <= MAX_ABS_TOL
 

@@ -131,6 +131,24 @@ def test_max_len_and_lf0_quirks(monkeypatch):
     assert snr_db(ref[0], out[0]) >= SNR_DB_TOL
 
 
+def test_fused_spec_proj_equals_two_convs(monkeypatch):
+    """fuse_spec_proj=True: spec_proj(proj(x) * m) * m as one masked 192x192 conv; spec_predict is None,
+    every other result is unchanged (ragged batch: the frame mask has to commute exactly)."""
+    _emu(monkeypatch)
+    inp = synthetic.make_inputs(2, 6, seed=21, ragged=True)
+    ph_dur = synthetic.make_ph_dur(inp["x_lengths"], 6, 20, seed=21)
+    noise = synthetic.make_noise(2, 192, int(ph_dur.sum(1).max()), seed=21)
+    outs = []
+    for fused in (False, True):
+        net, _ = build_model("ae", fuse_spec_proj=fused)
+        outs.append(net.infer(inp["x"], inp["x_lengths"], inp["note_pitch_id"], inp["note_duration"],
+                              inp["phone_shengdiao"], ph_dur=ph_dur, noise=noise))
+    a, b = outs
+    assert a[4] is not None and b[4] is None
+    assert torch.equal(a[1], b[1]) and torch.equal(a[2][0], b[2][0]) and torch.equal(a[5], b[5])
+    assert snr_db(a[0], b[0]) >= 50.0 and max_abs(a[0], b[0]) <= MAX_ABS_TOL      # two 16-bit roundings apart
+
+
 def test_frames_beyond_position_table_raise(monkeypatch):
     _emu(monkeypatch)
     net, _ = build_model("ae")
