@@ -54,6 +54,7 @@ struct ConvTcParams {
   int stores_in_flight;                    // TMA store groups left pending before a slot is recycled
   int acc_shift;                           // log2 of the accumulator ring depth (1 or 2)
   int w_resident;                          // all weight tiles stay in shared memory (w_stages = taps x K chunks)
+  int epi_alt;                             // epilogue warp pairs take alternate chunks (32 columns each)
   int xpre;                                // epilogue prefetches the next tile's first TMEM chunk
   int peek;                                // MMA thread peeks the next tile's barriers before the last tap
   int chunks_per_sub, n_out_tile;          // output chunks per 128-row sub-tile; output columns per N tile
@@ -150,7 +151,9 @@ struct TileIter {
 // while chunk i is processed.  Finished chunks are handed to the store thread through s_ready (no CTA barrier).
 //   RES: 0 none, 1 res1 only, 2 res2 (+ res1 if present).  PLAIN: alpha == scale == 1, no sequence mask, no
 //   speaker bias (the Generator's case).  BF: 16-bit output is bf16.  SPLIT: fp16 [hi | lo | hi] output.
-template <int ACT, int RES, bool PLAIN, bool BF, bool SPLIT, bool R16 = false>
+//   ALT: warp w and w + 4 take alternate 32-column chunks (even / odd) and do all 32 columns of theirs, instead of
+//   splitting every chunk 16 / 16: half as many slot waits, fences, barrier arrivals and loop trips per byte.
+template <int ACT, int RES, bool PLAIN, bool BF, bool SPLIT, bool R16 = false, bool ALT = false>
 __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
                                               uint32_t smE_u, uint32_t bias_u) {
   constexpr bool GATE = ACT == B200SVS_ACT_GATE;
@@ -171,17 +174,22 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
   const float alpha = ep.alpha;
   const float* gbias = PLAIN ? nullptr : ep.gbias;
   // this thread's 16-byte cells inside a staging slot (fp32 area SWIZZLE_128B, 16-bit area SWIZZLE_64B)
-  uint32_t off32[4], off16[2];
+  constexpr int NH = ALT ? 2 : 1;      // column halves this thread handles
+  uint32_t off32[NH][4], off16[NH][2];
 #pragma unroll
-  for (int jj = 0; jj < 4; ++jj) off32[jj] = row * 128 + (((half * 4 + jj) ^ (row & 7)) << 4);
+  for (int h = 0; h < NH; ++h) {
+    const int hh = ALT ? h : half;
 #pragma unroll
-  for (int jj = 0; jj < 2; ++jj) off16[jj] = p.slot16_off + row * 64 + (((half * 2 + jj) ^ ((row >> 1) & 3)) << 4);
+    for (int jj = 0; jj < 4; ++jj) off32[h][jj] = row * 128 + (((hh * 4 + jj) ^ (row & 7)) << 4);
+#pragma unroll
+    for (int jj = 0; jj < 2; ++jj) off16[h][jj] = p.slot16_off + row * 64 + (((hh * 2 + jj) ^ ((row >> 1) & 3)) << 4);
+  }
   const uint32_t r2_off = p.slot_r2_off;
   // raw 16-bit area (R16): residual in, un-activated result out, same cells as the activated 16-bit copy
   const uint32_t raw_delta = static_cast<uint32_t>(p.slot_raw_off - p.slot16_off);
   const bool has_res16 = R16 && ep.res16 != nullptr, has_out16r = R16 && ep.out16r != nullptr;
 
-  auto process = [&](const uint32_t* a0, const uint32_t* a1, uint32_t slot_u, int pcol, int b, float s) {
+  auto process = [&](const uint32_t* a0, const uint32_t* a1, uint32_t slot_u, int pcol, int b, float s, int h) {
     float v[16];
     const uint32_t ba = bias_u + pcol * 4;
 #pragma unroll
@@ -220,7 +228,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
       if (has_res16) {
 #pragma unroll
         for (int jj = 0; jj < 2; ++jj) {
-          const float4 q = lds128(slot_u + raw_delta + off16[jj]);
+          const float4 q = lds128(slot_u + raw_delta + off16[h][jj]);
           const uint32_t u[4] = {__float_as_uint(q.x), __float_as_uint(q.y), __float_as_uint(q.z), __float_as_uint(q.w)};
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
@@ -238,10 +246,10 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
 #pragma unroll
       for (int jj = 0; jj < 4; ++jj) {
         float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (RES == 1 || has_res1) r = lds128(slot_u + off32[jj]);
+        if (RES == 1 || has_res1) r = lds128(slot_u + off32[h][jj]);
         if constexpr (R16) { r.x += r16v[4 * jj]; r.y += r16v[4 * jj + 1]; r.z += r16v[4 * jj + 2]; r.w += r16v[4 * jj + 3]; }
         if constexpr (RES == 2) {
-          const float4 q2 = lds128(slot_u + r2_off + off32[jj]);
+          const float4 q2 = lds128(slot_u + r2_off + off32[h][jj]);
           r.x += q2.x; r.y += q2.y; r.z += q2.z; r.w += q2.w;
         }
         if constexpr (PLAIN) {
@@ -260,15 +268,15 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
     }
     if (need32) {
 #pragma unroll
-      for (int jj = 0; jj < 4; ++jj) sts128(slot_u + off32[jj], v[4 * jj], v[4 * jj + 1], v[4 * jj + 2], v[4 * jj + 3]);
+      for (int jj = 0; jj < 4; ++jj) sts128(slot_u + off32[h][jj], v[4 * jj], v[4 * jj + 1], v[4 * jj + 2], v[4 * jj + 3]);
     }
     if constexpr (R16) {
       if (has_out16r) {
         uint32_t p16[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) p16[i] = pack2<BF>(v[2 * i], v[2 * i + 1]);
-        sts128u(slot_u + raw_delta + off16[0], p16[0], p16[1], p16[2], p16[3]);
-        sts128u(slot_u + raw_delta + off16[1], p16[4], p16[5], p16[6], p16[7]);
+        sts128u(slot_u + raw_delta + off16[h][0], p16[0], p16[1], p16[2], p16[3]);
+        sts128u(slot_u + raw_delta + off16[h][1], p16[4], p16[5], p16[6], p16[7]);
       }
     }
     if (has16) {
@@ -277,18 +285,78 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
       for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], v[i] * slope);     // leaky-ReLU, 0 < slope <= 1
 #pragma unroll
       for (int i = 0; i < 8; ++i) p16[i] = pack2<BF>(v[2 * i], v[2 * i + 1]);
-      sts128u(slot_u + off16[0], p16[0], p16[1], p16[2], p16[3]);
-      sts128u(slot_u + off16[1], p16[4], p16[5], p16[6], p16[7]);
+      sts128u(slot_u + off16[h][0], p16[0], p16[1], p16[2], p16[3]);
+      sts128u(slot_u + off16[h][1], p16[4], p16[5], p16[6], p16[7]);
       if constexpr (SPLIT) {   // lo = v - hi, so that hi + lo == v to ~2^-22
 #pragma unroll
         for (int i = 0; i < 16; ++i) v[i] -= __half2float(__float2half_rn(v[i]));
 #pragma unroll
         for (int i = 0; i < 8; ++i) p16[i] = pack2<false>(v[2 * i], v[2 * i + 1]);
-        sts128u(slot_u + kSlot16Bytes + off16[0], p16[0], p16[1], p16[2], p16[3]);
-        sts128u(slot_u + kSlot16Bytes + off16[1], p16[4], p16[5], p16[6], p16[7]);
+        sts128u(slot_u + kSlot16Bytes + off16[h][0], p16[0], p16[1], p16[2], p16[3]);
+        sts128u(slot_u + kSlot16Bytes + off16[h][1], p16[4], p16[5], p16[6], p16[7]);
       }
     }
   };
+
+  if constexpr (ALT) {                 // n_chunks is even (host): this warp's chunks are grp, grp + 2, ...
+    const int grp = half;
+    int it = 0, sl = grp;
+    uint32_t eph = 0;
+    const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    uint32_t ra[32];
+    bool pre = false;                  // ra already holds the in-flight load of this tile's first chunk
+    for (TileIter ti(p); ti.valid(p); ti.next(p), ++it) {
+      const int acc = it & acc_mask;
+      const int tile_b = ti.b, tile_t0 = ti.t0(p);
+      const int len_b = ep.lens ? __ldg(ep.lens + tile_b) : p.T;
+      const int pcol0 = ti.n_idx * block_n;
+      const uint32_t taddr = taddr0 + acc * acc_cols;
+      if (!pre) {
+        mbar_wait(&bars->tmem_full[acc], (it >> acc_shift) & 1);
+        tc_fence_after();
+        tmem_ld16_nowait(taddr + grp * kEpiCols, ra);
+        tmem_ld16_nowait(taddr + grp * kEpiCols + 16, ra + 16);
+      }
+      pre = false;
+      if (threadIdx.x == 128) trace_stamp(p, it, 5, clock64());
+      for (int ci = grp; ci < n_chunks; ci += 2) {
+        const int ms = ci >= cps ? 1 : 0;
+        const int ch = ci - (ms ? cps : 0);
+        const int tsub = tile_t0 + ms * 128;
+        const float s = tsub + row < len_b ? ep.scale : 0.0f;
+        mbar_wait(&bars->e_full[sl], eph);
+        tmem_ld_wait16(ra);
+        tmem_ld_wait16(ra + 16);
+        if (tsub < p.T) {
+          const uint32_t slot_u = smE_u + sl * slot_bytes;
+          process(ra, ra, slot_u, pcol0 + ch * kEpiCols, tile_b, s, 0);
+          process(ra + 16, ra, slot_u, pcol0 + ch * kEpiCols + 16, tile_b, s, 1);
+        }
+        // the accumulators of this warp's next chunk are fetched under the fence / barrier traffic below
+        if (ci + 2 < n_chunks) {
+          tmem_ld16_nowait(taddr + (ci + 2) * kEpiCols, ra);
+          tmem_ld16_nowait(taddr + (ci + 2) * kEpiCols + 16, ra + 16);
+        } else if (p.xpre && ti.tile + static_cast<int>(gridDim.x) < p.total_tiles &&
+                   mbar_test(&bars->tmem_full[(it + 1) & acc_mask], ((it + 1) >> acc_shift) & 1)) {
+          tc_fence_after();
+          const uint32_t tn = taddr0 + ((it + 1) & acc_mask) * acc_cols + grp * kEpiCols;
+          tmem_ld16_nowait(tn, ra);
+          tmem_ld16_nowait(tn + 16, ra + 16);
+          pre = true;
+        }
+        fence_proxy_async();             // generic-proxy smem writes -> visible to the TMA store
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->s_ready[sl]);
+        sl += 2;
+        if (sl >= n_slots) { sl -= n_slots; eph ^= 1; }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+      if (threadIdx.x == 128) trace_stamp(p, it, 6, clock64());
+    }
+    return;
+  }
 
   int it = 0, sl = 0;
   uint32_t eph = 0;
@@ -313,7 +381,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
       const int tsub = tile_t0 + ms * 128;
       const float s = tsub + row < len_b ? ep.scale : 0.0f;
       mbar_wait(&bars->e_full[sl], eph);
-      if (tsub < p.T) process(r0, r1, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, tile_b, s);
+      if (tsub < p.T) process(r0, r1, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, tile_b, s, 0);
       fence_proxy_async();             // generic-proxy smem writes -> visible to the TMA store
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars->s_ready[sl]);
@@ -366,6 +434,11 @@ __device__ __forceinline__ void epilogue_dispatch2(const ConvTcParams& p, TcBarr
   if (p.ep.res16 || p.ep.out16r) {   // 16-bit residual stream: host restricts it to act NONE, non-split, RES in {0, 2}
     if (RES == 1) return;
     constexpr int R = RES == 1 ? 0 : RES;
+    if (R == 0 && p.epi_alt) {       // no residual to stage (the upsampling convs): alternate-chunk epilogue
+      if (plain) epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, true, true>(p, bars, tmem_base, smE_u, bias_s);
+      else epilogue_loop<B200SVS_ACT_NONE, 0, false, BF, false, true, true>(p, bars, tmem_base, smE_u, bias_s);
+      return;
+    }
     if (plain) epilogue_loop<B200SVS_ACT_NONE, R, true, BF, false, true>(p, bars, tmem_base, smE_u, bias_s);
     else epilogue_loop<B200SVS_ACT_NONE, R, false, BF, false, true>(p, bars, tmem_base, smE_u, bias_s);
     return;
@@ -382,7 +455,8 @@ __device__ __forceinline__ void epilogue_dispatch2(const ConvTcParams& p, TcBarr
     case B200SVS_ACT_SIGMOID: epilogue_loop<B200SVS_ACT_SIGMOID, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s); break;
     case B200SVS_ACT_TANH: epilogue_loop<B200SVS_ACT_TANH, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s); break;
     default:
-      if (plain) epilogue_loop<B200SVS_ACT_NONE, RES, true, BF, false>(p, bars, tmem_base, smE_u, bias_s);
+      if (RES == 0 && plain && p.epi_alt) epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, false, true>(p, bars, tmem_base, smE_u, bias_s);
+      else if (plain) epilogue_loop<B200SVS_ACT_NONE, RES, true, BF, false>(p, bars, tmem_base, smE_u, bias_s);
       else epilogue_loop<B200SVS_ACT_NONE, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s);
       break;
   }
@@ -516,7 +590,8 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int s = 0; s < (p.w_resident ? 1 : p.w_stages); ++s) { mbar_init(&bars->w_full[s], 1); mbar_init(&bars->w_empty[s], 1); }
     for (int s = 0; s < kMaxAcc; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], kEpiThreads / 32); }
     for (int s = 0; s < p.n_slots; ++s) {
-      mbar_init(&bars->e_full[s], 1); mbar_init(&bars->e_empty[s], 1); mbar_init(&bars->s_ready[s], kEpiThreads / 32);
+      mbar_init(&bars->e_full[s], 1); mbar_init(&bars->e_empty[s], 1);
+      mbar_init(&bars->s_ready[s], p.epi_alt ? kEpiThreads / 64 : kEpiThreads / 32);
     }
     fence_barrier_init();
   }
@@ -796,7 +871,12 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   if (p.w_resident) w_min = ksteps;
   int a_stages = kMaxAStages;
   if (const char* e = getenv("B200SVS_TC_ASTAGES")) { int v = atoi(e); if (v >= 2 && v <= kMaxAStages) a_stages = v; }   // tuning knob
-  while (a_stages > 2 && budget - a_stages * p.a_stage_bytes - w_min * p.w_stage_bytes < min_slots * p.slot_bytes) --a_stages;
+  // a conv with a staged residual wants depth in the slot ring first (the residual of chunk c is requested when
+  // slot c mod n_slots is recycled: 4 slots give it a lead of ~1 chunk, under the HBM latency): 6 slots before a
+  // third / fourth activation stage (measured: C=32 k=3 conv2 99 -> 92 us, C=64 91.5 vs 93.8, C=128 97 vs 101)
+  static const int slots_pref = [] { const char* e = getenv("B200SVS_TC_SLOTS"); return e ? atoi(e) : 6; }();
+  const int want_slots = has_res && slots_pref > min_slots ? slots_pref : min_slots;
+  while (a_stages > 2 && budget - a_stages * p.a_stage_bytes - w_min * p.w_stage_bytes < want_slots * p.slot_bytes) --a_stages;
   if (p.nchunks * ((p.total_tiles + num_sms() - 1) / num_sms()) < a_stages) a_stages = 2;
   p.a_stages = a_stages;
   const int avail = budget - a_stages * p.a_stage_bytes;
@@ -821,6 +901,14 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   p.acc_shift = (acc4_on && 4 * p.msub * a->block_n <= 512) ? 2 : 1;
   p.tmem_cols = next_pow2_cols((1 << p.acc_shift) * p.msub * a->block_n);
   p.ksub = a->Cin >= kBlockK ? 4 : (a->Cin + 15) / 16;
+  {   // alternate-chunk epilogue for convs without a residual input (act NONE): measured -4..-7 % on the k=3 conv1
+      // launches; with a staged residual it is slower (two slots held at once halve the residual prefetch lead)
+    static const int alt_on = [] { const char* e = getenv("B200SVS_TC_ALT"); return e ? atoi(e) : 1; }();
+    const bool plain = ep.alpha == 1.0f && ep.scale == 1.0f && ep.lens == nullptr && ep.gbias == nullptr;
+    const int res = ep.res2 ? 2 : (ep.res1 ? 1 : 0);
+    p.epi_alt = alt_on && ep.act == B200SVS_ACT_NONE && !split16 && (p.msub * p.chunks_per_sub) % 2 == 0 &&
+                !has_res && (raw16 || plain);
+  }
   p.idesc = make_idesc_f16(128, a->block_n, a->x_dtype == B200SVS_DT_BF16);
   p.ep = ep;
   p.trace = g_trace; p.trace_cap = g_trace_cap;
