@@ -194,7 +194,7 @@ def run_gpu_arm(args, rank, local_rank, world):
     utts, frames, phones = args.utts, args.frames, args.phones
     positions = max(2000, frames)
     net = models_ae.SynthesizerTrn(100, 513, 48, **HP, max_position_embeddings=positions,
-                                   operand_dtype=args.dtype).eval()
+                                   operand_dtype=args.dtype, **json.loads(args.model_kw)).eval()
     sd = synthetic.apply_recipe({k: v.clone() for k, v in net.state_dict().items()}, positions=positions)
     net.load_state_dict(sd)
     net = net.to(dev)
@@ -368,6 +368,8 @@ def main():
     ap.add_argument("--frames", type=int, default=FRAMES)
     ap.add_argument("--phones", type=int, default=PHONES)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--model-kw", default="{}", help='JSON of extra SynthesizerTrn keyword arguments for A/B runs, '
+                    'e.g. \'{"generator_mrf": "fp32"}\' (the default line uses none)')
     ap.add_argument("--ncu-range", action="store_true",
                     help="run one extra, untimed step inside cudaProfilerStart/Stop (for ncu --profile-from-start off)")
     args = ap.parse_args()

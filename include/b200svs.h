@@ -87,6 +87,9 @@ typedef struct b200svs_epilogue {
   int32_t res16_ld;
   void* out16r;
   int32_t out16r_ld;
+  /* conv1d_tc only: res2 points to a 16-bit tensor of the operand type instead of fp32 (the Generator's MRF sum
+   * `xs += resblock_j(x)`, models_ae.py:335-341, kept as a 16-bit stream; same restrictions as res16). */
+  int32_t res2_is16;
 } b200svs_epilogue;
 
 /* 1-D convolution over time as an implicit GEMM (replaces nn.Conv1d / ConvTranspose1d + the pointwise

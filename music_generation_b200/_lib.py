@@ -27,6 +27,7 @@ class Epilogue(C.Structure):
         ("post_lrelu", C.c_int32), ("post_slope", C.c_float), ("n_valid", C.c_int32),
         ("res16", C.c_void_p), ("res16_ld", C.c_int32),
         ("out16r", C.c_void_p), ("out16r_ld", C.c_int32),
+        ("res2_is16", C.c_int32),
     ]
 
 

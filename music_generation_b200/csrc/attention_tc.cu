@@ -78,7 +78,10 @@ __device__ __forceinline__ float ex2f(float x) {              // 2^x, 2 ulp; ex2
 }
 
 template <bool SPLIT>
-__global__ void __launch_bounds__(kAttnThreads, SPLIT ? 1 : 2)
+#ifndef B200SVS_ATTN_MINB_PLAIN
+#define B200SVS_ATTN_MINB_PLAIN 2
+#endif
+__global__ void __launch_bounds__(kAttnThreads, SPLIT ? 1 : B200SVS_ATTN_MINB_PLAIN)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant__ CUtensorMap tmKh,
                     const __grid_constant__ CUtensorMap tmVh, const __grid_constant__ CUtensorMap tmQl,
                     const __grid_constant__ CUtensorMap tmKl, const __grid_constant__ CUtensorMap tmVl,

@@ -188,6 +188,8 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
   // raw 16-bit area (R16): residual in, un-activated result out, same cells as the activated 16-bit copy
   const uint32_t raw_delta = static_cast<uint32_t>(p.slot_raw_off - p.slot16_off);
   const bool has_res16 = R16 && ep.res16 != nullptr, has_out16r = R16 && ep.out16r != nullptr;
+  const bool has_r2h = R16 && ep.res2 != nullptr && ep.res2_is16;      // 16-bit res2 (MRF stream), own slot area
+  const uint32_t r2h_delta = static_cast<uint32_t>(p.slot_r2_off - p.slot16_off);
 
   auto process = [&](const uint32_t* a0, const uint32_t* a1, uint32_t slot_u, int pcol, int b, float s, int h) {
     float v[16];
@@ -225,10 +227,10 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
     if constexpr (R16) {
 #pragma unroll
       for (int i = 0; i < 16; ++i) r16v[i] = 0.f;
-      if (has_res16) {
+      if (has_r2h) {
 #pragma unroll
         for (int jj = 0; jj < 2; ++jj) {
-          const float4 q = lds128(slot_u + raw_delta + off16[h][jj]);
+          const float4 q = lds128(slot_u + r2h_delta + off16[h][jj]);
           const uint32_t u[4] = {__float_as_uint(q.x), __float_as_uint(q.y), __float_as_uint(q.z), __float_as_uint(q.w)};
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
@@ -237,6 +239,22 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
             } else {
               const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&u[e]));
               r16v[8 * jj + 2 * e] = f.x; r16v[8 * jj + 2 * e + 1] = f.y;
+            }
+          }
+        }
+      }
+      if (has_res16) {
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+          const float4 q = lds128(slot_u + raw_delta + off16[h][jj]);
+          const uint32_t u[4] = {__float_as_uint(q.x), __float_as_uint(q.y), __float_as_uint(q.z), __float_as_uint(q.w)};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            if (BF) {
+              r16v[8 * jj + 2 * e] += __uint_as_float(u[e] << 16); r16v[8 * jj + 2 * e + 1] += __uint_as_float(u[e] & 0xFFFF0000u);
+            } else {
+              const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&u[e]));
+              r16v[8 * jj + 2 * e] += f.x; r16v[8 * jj + 2 * e + 1] += f.y;
             }
           }
         }
@@ -431,7 +449,7 @@ template <int RES, bool BF>
 __device__ __forceinline__ void epilogue_dispatch2(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
                                                    uint32_t smE_u, uint32_t bias_s, bool plain, bool split) {
   const int act = p.ep.act;
-  if (p.ep.res16 || p.ep.out16r) {   // 16-bit residual stream: host restricts it to act NONE, non-split, RES in {0, 2}
+  if (p.ep.res16 || p.ep.out16r || (p.ep.res2 && p.ep.res2_is16)) {   // 16-bit residual stream: host restricts it to act NONE, non-split, RES in {0, 2}
     if (RES == 1) return;
     constexpr int R = RES == 1 ? 0 : RES;
     if (R == 0 && p.epi_alt) {       // no residual to stage (the upsampling convs): alternate-chunk epilogue
@@ -464,7 +482,7 @@ __device__ __forceinline__ void epilogue_dispatch2(const ConvTcParams& p, TcBarr
 __device__ __forceinline__ void epilogue_dispatch(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
                                                   uint32_t smE_u, uint32_t bias_s) {
   const b200svs_epilogue& ep = p.ep;
-  const int res = ep.res2 != nullptr ? 2 : (ep.res1 != nullptr ? 1 : 0);
+  const int res = (ep.res2 != nullptr && !ep.res2_is16) ? 2 : (ep.res1 != nullptr ? 1 : 0);   // a 16-bit res2 rides the R16 path
   const bool plain = ep.alpha == 1.0f && ep.scale == 1.0f && ep.lens == nullptr && ep.gbias == nullptr;
   const bool split = ep.out16 && ep.out16_dtype == B200SVS_DT_F16_SPLIT;
   const bool bf = ep.out16 && ep.out16_dtype == B200SVS_DT_BF16;
@@ -748,7 +766,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_wait(&bars->e_empty[sl], eph ^ 1);
             if ((has_res1 || has_res2 || ep.res16) && t < p.T) {
               const int col = tc.n_idx * p.n_out_tile + c * kEpiCols;
-              mbar_arrive_expect_tx(&bars->e_full[sl], (has_res1 ? kSlot32Bytes : 0) + (has_res2 ? kSlot32Bytes : 0) +
+              mbar_arrive_expect_tx(&bars->e_full[sl], (has_res1 ? kSlot32Bytes : 0) + (has_res2 ? (ep.res2_is16 ? kSlot16Bytes : kSlot32Bytes) : 0) +
                                                            (ep.res16 ? kSlot16Bytes : 0));
               if (ep.res16) tma_load_3d(smE + sl * p.slot_bytes + p.slot_raw_off, &tmR16, &bars->e_full[sl], col, t, tc.b);
               if (has_res1) tma_load_3d(smE + sl * p.slot_bytes, &tmR, &bars->e_full[sl], col, t, tc.b);
@@ -810,7 +828,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   B200SVS_REQUIRE(!ep.out32 || (ep.out32_ld % 4 == 0 && (reinterpret_cast<uintptr_t>(ep.out32) & 15) == 0), "conv1d_tc: out32 alignment");
   B200SVS_REQUIRE(!ep.out16 || (ep.out16_ld % 8 == 0 && (reinterpret_cast<uintptr_t>(ep.out16) & 15) == 0), "conv1d_tc: out16 alignment");
   B200SVS_REQUIRE(!ep.res1 || (ep.res1_ld % 4 == 0 && (reinterpret_cast<uintptr_t>(ep.res1) & 15) == 0), "conv1d_tc: res1 alignment");
-  B200SVS_REQUIRE(!ep.res2 || (ep.res2_ld % 4 == 0 && (reinterpret_cast<uintptr_t>(ep.res2) & 15) == 0), "conv1d_tc: res2 alignment");
+  B200SVS_REQUIRE(!ep.res2 || (ep.res2_ld % (ep.res2_is16 ? 8 : 4) == 0 && (reinterpret_cast<uintptr_t>(ep.res2) & 15) == 0), "conv1d_tc: res2 alignment");
   const int n_tiles = a->Cout_pad / a->block_n;
   const int n_out_tile = gate ? a->block_n / 2 : a->block_n;
   B200SVS_REQUIRE(ep.n_valid > 0 && ep.n_valid <= n_tiles * n_out_tile, "conv1d_tc: n_valid=%d", ep.n_valid);
@@ -836,18 +854,20 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   p.a_stage_bytes = p.a_boxes * p.a_box_rows * kRowBytes;
   p.w_stage_bytes = a->block_n * kRowBytes;
   const bool area32 = ep.res1 || ep.out32;
-  p.slot_r2_off = ep.res2 ? (area32 ? kSlot32Bytes : 0) : 0;
-  p.slot16_off = (area32 ? kSlot32Bytes : 0) + (ep.res2 ? kSlot32Bytes : 0);
+  const bool res2_f32 = ep.res2 && !ep.res2_is16, res2_h = ep.res2 && ep.res2_is16;
+  p.slot_r2_off = res2_f32 ? (area32 ? kSlot32Bytes : 0) : 0;
+  p.slot16_off = (area32 ? kSlot32Bytes : 0) + (res2_f32 ? kSlot32Bytes : 0);
   const bool split16 = ep.out16 && ep.out16_dtype == B200SVS_DT_F16_SPLIT;
   B200SVS_REQUIRE(!split16 || ep.act == B200SVS_ACT_NONE || ep.act == B200SVS_ACT_RELU, "conv1d_tc: split 16-bit output supports act NONE / RELU");
   B200SVS_REQUIRE(!split16 || ep.n_valid % kEpiCols == 0, "conv1d_tc: split 16-bit output needs n_valid %% 32 == 0 (n_valid=%d)", ep.n_valid);
-  const bool raw16 = ep.res16 || ep.out16r;
+  const bool raw16 = ep.res16 || ep.out16r || res2_h;
   B200SVS_REQUIRE(!raw16 || (ep.act == B200SVS_ACT_NONE && !split16 && !ep.res1),
-                  "conv1d_tc: res16 / out16r need act NONE, a non-split output and no fp32 res1");
+                  "conv1d_tc: res16 / out16r / 16-bit res2 need act NONE, a non-split output and no fp32 res1");
   B200SVS_REQUIRE(!ep.res16 || (ep.res16_ld % 8 == 0 && (reinterpret_cast<uintptr_t>(ep.res16) & 15) == 0), "conv1d_tc: res16 alignment");
   B200SVS_REQUIRE(!ep.out16r || (ep.out16r_ld % 8 == 0 && (reinterpret_cast<uintptr_t>(ep.out16r) & 15) == 0), "conv1d_tc: out16r alignment");
   p.slot_raw_off = p.slot16_off + (ep.out16 ? kSlot16Bytes : 0) + (split16 ? kSlot16Bytes : 0);
-  p.slot_bytes = p.slot_raw_off + (raw16 ? kSlot16Bytes : 0);
+  p.slot_bytes = p.slot_raw_off + ((ep.res16 || ep.out16r) ? kSlot16Bytes : 0);
+  if (res2_h) { p.slot_r2_off = p.slot_bytes; p.slot_bytes += kSlot16Bytes; }     // 16-bit res2 tile: its own area
   // shared memory: 2 activation stages, >= 3 weight stages (or all k-steps of a tile if fewer), then as many
   // staging slots as fit (stores in flight + residual prefetch), the rest to weight stages
   const int bias_bytes = a->Cout_pad * 4;     // staged bias (zeros when there is none)
@@ -937,7 +957,11 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     int r = make_tmap(&tmR, 2, ep.res1, 3, edims, strides, ebox, 128);
     if (r) return r;
   }
-  if (ep.res2) {
+  if (ep.res2 && ep.res2_is16) {
+    uint64_t strides[2] = {(uint64_t)ep.res2_ld * 2, (uint64_t)a->T * ep.res2_ld * 2};
+    int r = make_tmap(&tmR2, el16, ep.res2, 3, edims, strides, ebox, 64);
+    if (r) return r;
+  } else if (ep.res2) {
     uint64_t strides[2] = {(uint64_t)ep.res2_ld * 4, (uint64_t)a->T * ep.res2_ld * 4};
     int r = make_tmap(&tmR2, 2, ep.res2, 3, edims, strides, ebox, 128);
     if (r) return r;

@@ -115,6 +115,7 @@ def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, 
         e.res1, e.res1_ld = res1.data_ptr(), _btc(res1, "res1")
     if res2 is not None:
         e.res2, e.res2_ld = res2.data_ptr(), _btc(res2, "res2")
+        e.res2_is16 = 0 if res2.dtype == torch.float32 else 1      # 16-bit MRF stream (operand dtype)
     if lens is not None:
         e.lens = lens.data_ptr()
     e.lens_div = 1
@@ -134,7 +135,7 @@ def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, 
         n = float(B) * T * e.n_valid
         xb = x.element_size()
         nbytes = (float(B) * T * cin * xb + w.numel() * w.element_size()
-                  + n * (4 * (res1 is not None) + 4 * (res2 is not None) + 2 * (res16 is not None) + 4 * (out32 is not None)
+                  + n * (4 * (res1 is not None) + (0 if res2 is None else res2.element_size()) + 2 * (res16 is not None) + 4 * (out32 is not None)
                          + 2 * (out16r is not None) + (6 if split16 else 2) * (out16 is not None)))
         _lib.NEXT_META = (pc.tag, 2.0 * B * T * pc.alg_macs_per_row * frac, nbytes)
     if pc.f32:

@@ -39,7 +39,8 @@ class SynthesizerTrn(nn.Module):
                  resblock_dilation_sizes, upsample_rates, upsample_initial_channel, upsample_kernel_sizes,
                  n_speakers=0, gin_channels=0, use_sdp=True, n_vocab_note=100, *, operand_dtype="fp16",
                  max_position_embeddings=2000, generator_chunk_frames=32768, f0_precision="split",
-                 text_precision="split", generator_residual="fp16", cuda_graphs=False, fuse_spec_proj=False,
+                 text_precision="split", generator_residual="fp16", generator_mrf="fp16", cuda_graphs=False,
+                 fuse_spec_proj=False,
                  seed=1234, **kwargs):
         super().__init__()
         if hidden_channels != 192 or n_heads != 2:
@@ -64,6 +65,10 @@ class SynthesizerTrn(nn.Module):
         if generator_residual not in ("fp16", "fp32"):
             raise ValueError("generator_residual must be 'fp16' (16-bit residual stream; fp16 operand mode only) or 'fp32'")
         self.generator_residual = generator_residual
+        if generator_mrf not in ("fp16", "fp32"):
+            raise ValueError("generator_mrf must be 'fp16' (the MRF sum xs += resblock_j(x) as a 16-bit stream; only "
+                             "with generator_residual='fp16') or 'fp32'")
+        self.generator_mrf = generator_mrf
         # every call site of the reference discards spec_predict; with fuse_spec_proj=True the two
         # 513-wide 1x1 convs SpecDecoder.proj -> spec_proj collapse into one 192x192 conv (see _pack) and infer
         # returns None in spec_predict's place.  Off by default: the result tuple then matches the reference's.
@@ -364,7 +369,10 @@ class SynthesizerTrn(nn.Module):
             cr16 = torch.empty_like(xl16) if r16 else None
             cl16 = torch.empty_like(xl16)
             t16 = torch.empty_like(xl16)
-            mrf = torch.empty(B, Lo, ch, device=dev, dtype=torch.float32)
+            # MRF accumulator xs (models_ae.py:335-341): 16-bit in the 16-bit-residual mode (16 -> 8 B per element
+            # of MRF traffic), else fp32
+            mrf16 = r16 and self.generator_mrf == "fp16"
+            mrf = torch.empty(B, Lo, ch, device=dev, dtype=dt if mrf16 else torch.float32)
             nxt16 = torch.empty_like(xl16)
             nk = len(P["g_rb"][i])
             next_slope = LRELU_SLOPE if i < n_st - 1 else 0.01      # F.leaky_relu default (models_ae.py:342)
@@ -374,11 +382,11 @@ class SynthesizerTrn(nn.Module):
                     last = m == len(pairs) - 1
                     kw = {}
                     if last:
-                        # MRF: xs = sum_j resblock_j(x); x = xs / num_kernels (models_ae.py:335-341); fp32 accumulator
+                        # MRF: xs = sum_j resblock_j(x); x = xs / num_kernels (models_ae.py:335-341)
                         if j > 0:
                             kw["res2"] = mrf
                         if j < nk - 1:
-                            kw.update(out32=mrf)
+                            kw.update(out16r=mrf) if mrf16 else kw.update(out32=mrf)
                         else:
                             kw.update(scale=1.0 / nk, out16=nxt16, post_lrelu=next_slope)
                     elif r16:

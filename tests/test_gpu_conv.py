@@ -255,3 +255,28 @@ def test_conv1d_tc_16bit_residual_stream(cout, k, dil, with_res2, scale):
     assert max_abs(F.leaky_relu(ref, 0.1).half().float(), act16.float().cpu()) < 4e-3
     if with_res2:
         assert max_abs(ref, o32.cpu()) < 2e-3
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cout,k,dil,scale", [(32, 3, 1, 1.0), (64, 7, 1, 1.0 / 3.0), (128, 11, 1, 1.0 / 3.0), (256, 3, 1, 1.0)])
+def test_conv1d_tc_16bit_mrf_stream(cout, k, dil, scale):
+    """res2 as a 16-bit tensor (b200svs_epilogue.res2_is16): the MRF sum xs += resblock_j(x) kept as a 16-bit
+    stream - accumulate in place (res2 in, out16r out over the same buffer) and the final scaled, activated out16."""
+    import torch.nn.functional as F
+    B, T, cin = 2, 700, cout
+    w, b = _rand(cout, cin, k, seed=60, scale=(cin * k) ** -0.5), _rand(cout, seed=61, scale=0.1)
+    x = _rand(B, T, cin, seed=62).half()
+    r16 = _rand(B, T, cout, seed=63).half()
+    mrf = _rand(B, T, cout, seed=64).half()
+    ref = F.conv1d(x.float().transpose(1, 2), w.half().float(), b, padding=dil * (k // 2), dilation=dil).transpose(1, 2)
+    ref = (ref + r16.float() + mrf.float()) * scale
+    pc = packer.pack_conv(w, b, dil=dil).to(DEV)
+    # j = 1: xs += resblock_1(x), in place
+    acc = mrf.clone().to(DEV)
+    ops.conv1d(pc, x.to(DEV), res16=r16.to(DEV), res2=acc, out16r=acc, scale=scale)
+    # j = 2: x = lrelu(xs / 3) for the next stage
+    nxt = torch.empty(B, T, cout, device=DEV, dtype=torch.float16)
+    ops.conv1d(pc, x.to(DEV), res16=r16.to(DEV), res2=mrf.to(DEV), out16=nxt, post_lrelu=0.1, scale=scale)
+    torch.cuda.synchronize()
+    assert max_abs(ref.half().float(), acc.float().cpu()) < 6e-3
+    assert max_abs(F.leaky_relu(ref, 0.1).half().float(), nxt.float().cpu()) < 6e-3
