@@ -153,6 +153,32 @@ def test_batch_invariance_and_sharding_equivalence():
         assert torch.equal(part, full[idx])
 
 
+def test_full_size_bench_batch_properties():
+    """BASELINE config 3 (the bench workload: 64 utterances x 30 s, T = 2584 frames, beyond the reference's own
+    2000-frame position table) at full size through size-independent properties: the output is finite and inside
+    tanh's range, every utterance of the batch equals the same utterance synthesised in a 2-way shard and alone
+    (bit for bit: Generator chunks of 12 utterances, 256-row tiles and the split-precision paths are all
+    batch-invariant)."""
+    B, P, T = 64, 258, 2584
+    net, sd = build_model("ae")
+    net.load_state_dict(synthetic.apply_recipe({k: v.clone() for k, v in sd.items()}, positions=T))   # enlarged table
+    net = net.to(DEV)
+    inp = synthetic.make_inputs(B, P, seed=1234)
+    ph_dur = synthetic.make_ph_dur(inp["x_lengths"], P, T, seed=1234)
+    assert int(ph_dur.sum(1).max()) == T
+    noise = synthetic.make_noise(B, 192, T, seed=1234).to(DEV)
+    res = _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise)
+    full = res[0]
+    assert full.shape == (B, 1, T * 256) and bool(torch.isfinite(full).all()) and float(full.abs().max()) <= 1.0
+    assert int(res[1].sum()) == int(ph_dur.sum())
+    from music_generation_b200 import sharding
+    for idx in sharding.partition(ph_dur.sum(1).tolist(), 2):
+        part = _infer(net, sharding.shard_batch(inp, idx), ph_dur=ph_dur[idx].to(DEV), noise=noise[idx])[0]
+        assert torch.equal(part, full[idx])
+    one = _infer(net, sharding.shard_batch(inp, [37]), ph_dur=ph_dur[[37]].to(DEV), noise=noise[[37]])[0]
+    assert torch.equal(one[0], full[37])
+
+
 def test_config1_shape_10s_utterance():
     """BASELINE config 1 shape: B=1, P=86, T=861 (10 s)."""
     net, sd = build_model("ae", device=DEV)
