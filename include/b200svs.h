@@ -90,6 +90,11 @@ typedef struct b200svs_epilogue {
   /* conv1d_tc only: res2 points to a 16-bit tensor of the operand type instead of fp32 (the Generator's MRF sum
    * `xs += resblock_j(x)`, models_ae.py:335-341, kept as a 16-bit stream; same restrictions as res16). */
   int32_t res2_is16;
+  /* conv1d_tc only: res16 holds leaky_relu(x, 1 / res16_unlrelu) instead of x (the 16-bit copy the previous conv
+   * wrote for the NEXT conv's operand); the epilogue adds x = min(r, r * res16_unlrelu).  <= 1: res16 is x itself.
+   * Lets a ResBlock pair `x + c2(lrelu(c1(lrelu(x))))` (modules.py:210-223) take its residual from the tensor c1
+   * consumed, so no un-activated 16-bit stream is written: 10 instead of 12 bytes per element and pair. */
+  float res16_unlrelu;
 } b200svs_epilogue;
 
 /* 1-D convolution over time as an implicit GEMM (replaces nn.Conv1d / ConvTranspose1d + the pointwise

@@ -28,6 +28,7 @@ class Epilogue(C.Structure):
         ("res16", C.c_void_p), ("res16_ld", C.c_int32),
         ("out16r", C.c_void_p), ("out16r_ld", C.c_int32),
         ("res2_is16", C.c_int32),
+        ("res16_unlrelu", C.c_float),
     ]
 
 

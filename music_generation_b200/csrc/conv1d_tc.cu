@@ -190,6 +190,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
   const bool has_res16 = R16 && ep.res16 != nullptr, has_out16r = R16 && ep.out16r != nullptr;
   const bool has_r2h = R16 && ep.res2 != nullptr && ep.res2_is16;      // 16-bit res2 (MRF stream), own slot area
   const uint32_t r2h_delta = static_cast<uint32_t>(p.slot_r2_off - p.slot16_off);
+  const float rinv = (R16 && ep.res16_unlrelu > 1.0f) ? ep.res16_unlrelu : 1.0f;   // min(r, r * 1) == r: no branch
 
   auto process = [&](const uint32_t* a0, const uint32_t* a1, uint32_t slot_u, int pcol, int b, float s, int h) {
     float v[16];
@@ -243,19 +244,20 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
           }
         }
       }
-      if (has_res16) {
+      if (has_res16) {      // rinv > 1: the residual tensor holds lrelu(x, 1 / rinv); x = min(r, r * rinv)
 #pragma unroll
         for (int jj = 0; jj < 2; ++jj) {
           const float4 q = lds128(slot_u + raw_delta + off16[h][jj]);
           const uint32_t u[4] = {__float_as_uint(q.x), __float_as_uint(q.y), __float_as_uint(q.z), __float_as_uint(q.w)};
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
+            float2 f;
             if (BF) {
-              r16v[8 * jj + 2 * e] += __uint_as_float(u[e] << 16); r16v[8 * jj + 2 * e + 1] += __uint_as_float(u[e] & 0xFFFF0000u);
+              f.x = __uint_as_float(u[e] << 16); f.y = __uint_as_float(u[e] & 0xFFFF0000u);
             } else {
-              const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&u[e]));
-              r16v[8 * jj + 2 * e] += f.x; r16v[8 * jj + 2 * e + 1] += f.y;
+              f = __half22float2(*reinterpret_cast<const __half2*>(&u[e]));
             }
+            r16v[8 * jj + 2 * e] += fminf(f.x, f.x * rinv); r16v[8 * jj + 2 * e + 1] += fminf(f.y, f.y * rinv);
           }
         }
       }

@@ -79,7 +79,7 @@ class PackedConv:
 
 def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, res2=None, lens=None,
            out32=None, out16=None, post_lrelu=None, w_rows=None, n_valid=None, split16=False, res16=None,
-           out16r=None):
+           out16r=None, res16_unlrelu=None):
     """out = epilogue(conv(x, pc)).  See b200svs_epilogue in include/b200svs.h for the formula.
     `w_rows=(row0, nrows)` restricts the conv to a block of packed output channels (WN res/skip split)."""
     B, T, cin = x.shape
@@ -127,6 +127,8 @@ def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, 
         e.post_lrelu, e.post_slope = 1, float(post_lrelu)
     if res16 is not None:      # 16-bit residual input (same dtype as the operands), added like res1
         e.res16, e.res16_ld = res16.data_ptr(), _btc(res16, "res16")
+        if res16_unlrelu is not None:      # res16 holds leaky_relu(x, 1 / res16_unlrelu): the epilogue inverts it
+            e.res16_unlrelu = float(res16_unlrelu)
     if out16r is not None:     # 16-bit copy of the result WITHOUT the post-activation (may alias res16)
         e.out16r, e.out16r_ld = out16r.data_ptr(), _btc(out16r, "out16r")
     e.n_valid = n_out if n_valid is None else n_valid

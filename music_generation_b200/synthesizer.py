@@ -39,7 +39,7 @@ class SynthesizerTrn(nn.Module):
                  resblock_dilation_sizes, upsample_rates, upsample_initial_channel, upsample_kernel_sizes,
                  n_speakers=0, gin_channels=0, use_sdp=True, n_vocab_note=100, *, operand_dtype="fp16",
                  max_position_embeddings=2000, generator_chunk_frames=32768, f0_precision="split",
-                 text_precision="split", generator_residual="fp16", generator_mrf="fp16", cuda_graphs=False,
+                 text_precision="split", generator_residual="act16", generator_mrf="fp16", cuda_graphs=False,
                  fuse_spec_proj=False,
                  seed=1234, **kwargs):
         super().__init__()
@@ -62,8 +62,10 @@ class SynthesizerTrn(nn.Module):
         if text_precision not in ("split", "fp32"):
             raise ValueError("text_precision must be 'split' or 'fp32'")
         self.text_precision = text_precision
-        if generator_residual not in ("fp16", "fp32"):
-            raise ValueError("generator_residual must be 'fp16' (16-bit residual stream; fp16 operand mode only) or 'fp32'")
+        if generator_residual not in ("act16", "fp16", "fp32"):
+            raise ValueError("generator_residual must be 'act16' (the residual of a ResBlock pair is recovered from the "
+                             "leaky-ReLU'd 16-bit tensor its first conv consumed; fp16 operand mode only), 'fp16' "
+                             "(separate un-activated 16-bit residual stream) or 'fp32'")
         self.generator_residual = generator_residual
         if generator_mrf not in ("fp16", "fp32"):
             raise ValueError("generator_mrf must be 'fp16' (the MRF sum xs += resblock_j(x) as a 16-bit stream; only "
@@ -349,24 +351,29 @@ class SynthesizerTrn(nn.Module):
         ops.conv1d(P["g_pre"], x16, gbias=gbias, out16=cur16, post_lrelu=LRELU_SLOPE)
         L = T
         n_st = len(self.upsample_rates)
-        r16 = self.generator_residual == "fp16" and dt == torch.float16
+        r16 = self.generator_residual in ("fp16", "act16") and dt == torch.float16
+        # act16: no un-activated stream at all - the pair's second conv reads its residual from the activated tensor
+        # the first conv consumed and inverts the leaky-ReLU (x = min(r, r / slope)): 10 B per element and pair
+        ract = r16 and self.generator_residual == "act16"
         for i, u in enumerate(self.upsample_rates):
             ch = up0 // (2 ** (i + 1))
             Lo = L * u
             # stage residual stream: fp32 (x32) or, by default in fp16 mode, 16-bit (xr16: HBM traffic of a
             # ResBlock pair drops from 16 to 12 bytes per element); xl16 = leaky-ReLU'd copy the convs consume
             x32 = None if r16 else torch.empty(B, Lo, ch, device=dev, dtype=torch.float32)
-            xr16 = torch.empty(B, Lo, ch, device=dev, dtype=dt) if r16 else None
+            xr16 = torch.empty(B, Lo, ch, device=dev, dtype=dt) if r16 and not ract else None
             xl16 = torch.empty(B, Lo, ch, device=dev, dtype=dt)
             # ConvTranspose1d as a 3-tap conv writing the [B, L, u*ch] view of [B, L*u, ch]
-            if r16:
+            if ract:
+                ops.conv1d(P["g_ups"][i], cur16, out16=xl16.view(B, L, u * ch), post_lrelu=LRELU_SLOPE)
+            elif r16:
                 ops.conv1d(P["g_ups"][i], cur16, out16r=xr16.view(B, L, u * ch), out16=xl16.view(B, L, u * ch),
                            post_lrelu=LRELU_SLOPE)
             else:
                 ops.conv1d(P["g_ups"][i], cur16, out32=x32.view(B, L, u * ch), out16=xl16.view(B, L, u * ch),
                            post_lrelu=LRELU_SLOPE)
             c32 = None if r16 else torch.empty_like(x32)
-            cr16 = torch.empty_like(xl16) if r16 else None
+            cr16 = torch.empty_like(xl16) if r16 and not ract else None
             cl16 = torch.empty_like(xl16)
             t16 = torch.empty_like(xl16)
             # MRF accumulator xs (models_ae.py:335-341): 16-bit in the 16-bit-residual mode (16 -> 8 B per element
@@ -389,11 +396,15 @@ class SynthesizerTrn(nn.Module):
                             kw.update(out16r=mrf) if mrf16 else kw.update(out32=mrf)
                         else:
                             kw.update(scale=1.0 / nk, out16=nxt16, post_lrelu=next_slope)
+                    elif ract:
+                        kw.update(out16=cl16, post_lrelu=LRELU_SLOPE)
                     elif r16:
                         kw.update(out16r=cr16, out16=cl16, post_lrelu=LRELU_SLOPE)
                     else:
                         kw.update(out32=c32, out16=cl16, post_lrelu=LRELU_SLOPE)
-                    if r16:
+                    if ract:
+                        kw.update(res16=src16, res16_unlrelu=1.0 / LRELU_SLOPE)
+                    elif r16:
                         kw["res16"] = srcr
                     else:
                         kw["res1"] = src32

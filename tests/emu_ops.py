@@ -32,7 +32,7 @@ def _store(dst, val, split16=False):
 
 def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, res2=None, lens=None,
            out32=None, out16=None, post_lrelu=None, w_rows=None, n_valid=None, split16=False, res16=None,
-           out16r=None):
+           out16r=None, res16_unlrelu=None):
     B, T, cin = x.shape
     assert cin == pc.cin
     xf = x.float()
@@ -75,7 +75,10 @@ def conv1d(pc, x, *, act=ACT_NONE, gbias=None, alpha=1.0, scale=1.0, res1=None, 
     if res2 is not None:
         y = y + res2.float()[:, :, :nv]
     if res16 is not None:
-        y = y + res16.float()[:, :, :nv]
+        r = res16.float()[:, :, :nv]
+        if res16_unlrelu is not None and res16_unlrelu > 1:
+            r = torch.minimum(r, r * res16_unlrelu)
+        y = y + r
     y = y * scale
     m = _mask(lens, B, T)
     if m is not None:

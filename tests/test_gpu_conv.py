@@ -258,6 +258,31 @@ def test_conv1d_tc_16bit_residual_stream(cout, k, dil, with_res2, scale):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("cout,k,with_mrf", [(32, 3, False), (64, 11, True), (128, 7, False)])
+def test_conv1d_tc_residual_from_activated_stream(cout, k, with_mrf):
+    """res16_unlrelu: res16 holds leaky_relu(x, 0.1) (the tensor the pair's first conv consumed) and the epilogue
+    recovers x = min(r, 10 r); the activated result is written in place over it (generator_residual='act16')."""
+    import torch.nn.functional as F
+    B, T, cin = 2, 700, cout
+    w, b = _rand(cout, cin, k, seed=60, scale=(cin * k) ** -0.5), _rand(cout, seed=61, scale=0.1)
+    x = _rand(B, T, cin, seed=62).half()
+    xres = _rand(B, T, cout, seed=63)
+    act_in = F.leaky_relu(xres, 0.1).half()                       # what the previous conv stored
+    xrec = torch.minimum(act_in.float(), act_in.float() * 10.0)    # what the epilogue must recover
+    assert max_abs(xrec, xres) < 4e-3
+    mrf = _rand(B, T, cout, seed=64).half() if with_mrf else None
+    ref = F.conv1d(x.float().transpose(1, 2), w.half().float(), b, padding=k // 2).transpose(1, 2) + xrec
+    if with_mrf:
+        ref = ref + mrf.float()
+    pc = packer.pack_conv(w, b).to(DEV)
+    buf = act_in.clone().to(DEV)
+    ops.conv1d(pc, x.to(DEV), res16=buf, res16_unlrelu=10.0, out16=buf, post_lrelu=0.1,
+               res2=None if mrf is None else mrf.to(DEV))
+    torch.cuda.synchronize()
+    assert max_abs(F.leaky_relu(ref, 0.1).half().float(), buf.float().cpu()) < 4e-3
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("cout,k,dil,scale", [(32, 3, 1, 1.0), (64, 7, 1, 1.0 / 3.0), (128, 11, 1, 1.0 / 3.0), (256, 3, 1, 1.0)])
 def test_conv1d_tc_16bit_mrf_stream(cout, k, dil, scale):
     """res2 as a 16-bit tensor (b200svs_epilogue.res2_is16): the MRF sum xs += resblock_j(x) kept as a 16-bit

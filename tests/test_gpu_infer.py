@@ -96,11 +96,12 @@ def test_predicted_durations_are_bit_exact():
 
 @pytest.mark.parametrize("kw,snr_min", [
     ({"generator_residual": "fp32"}, SNR_DB_TOL),                           # fp32 residual stream in the Generator
+    ({"generator_residual": "fp16"}, SNR_DB_TOL),                           # separate un-activated 16-bit residual stream
     ({"f0_precision": "fp32", "text_precision": "fp32"}, SNR_DB_TOL),       # fp32 SIMT encoders
     ({"operand_dtype": "bf16"}, 34.0),                                      # bf16 operands (8-bit mantissa): reported, looser
     ({"generator_mrf": "fp32"}, SNR_DB_TOL),                                # fp32 MRF accumulator
     ({"fuse_spec_proj": True}, SNR_DB_TOL),                                 # SpecDecoder.proj -> spec_proj as one conv
-], ids=["residual_fp32", "encoders_fp32", "bf16", "mrf_fp32", "fused_spec_proj"])
+], ids=["residual_fp32", "residual_fp16", "encoders_fp32", "bf16", "mrf_fp32", "fused_spec_proj"])
 def test_infer_option_paths_against_golden(kw, snr_min):
     """The non-default constructor paths stay within tolerance of the reference's golden output."""
     name = "ae_phdur_b2"
