@@ -58,7 +58,7 @@ def _btc(t, name):
 class PackedConv:
     """Device-resident packed weights of one convolution (see packer.py)."""
     __slots__ = ("w", "bias", "ntaps", "dil", "pad_left", "cin", "cin_pad", "cout", "cout_pad", "block_n",
-                 "gate", "f32", "n_out", "alg_macs_per_row", "tag", "out_scale")
+                 "gate", "f32", "n_out", "alg_macs_per_row", "tag", "out_scale", "fold")
 
     def __init__(self, w, bias, ntaps, dil, pad_left, cin, cin_pad, cout, cout_pad, block_n, gate, f32):
         self.w, self.bias, self.ntaps, self.dil, self.pad_left = w, bias, ntaps, dil, pad_left
@@ -69,6 +69,7 @@ class PackedConv:
         # form executes 1.5x of that, packer.pack_conv_transpose overrides it) - used by bench.py only
         self.alg_macs_per_row = cin * cout * ntaps
         self.tag = ""
+        self.fold = 1               # 2: time-pair folded (packer.fold_time_pairs); tensors are passed as [B, T/2, 2C] views
         self.out_scale = 1.0        # split-precision convs: power-of-two factor folded into the epilogue's alpha
 
     def to(self, device):

@@ -117,6 +117,40 @@ def pack_conv(weight, bias, *, dil=1, pad_left=None, dtype=torch.float16, f32=Fa
     return pc
 
 
+def fold_time_pairs(weight, bias, pad_left=None):
+    """Time-pair folding of a dilation-1 conv: a channels-last [B, T, C] tensor with even T IS a [B, T/2, 2C] tensor
+    whose row u holds time steps (2u, 2u+1), so
+        y[2u+e, co] = sum_j sum_ci x[2u+e+j-p, ci] w[co, ci, j]
+    is a conv over u with 2*Cin input and 2*Cout output channels and ceil((k+1)/2) taps (block-Toeplitz weights):
+        W'[e*Cout+co, f*Cin+ci, v-vmin] = w[co, ci, 2v+f-e+p]   (0 elsewhere),  pad_left' = -vmin.
+    For the 32- and 64-channel Generator stages (modules.py:210-223) this doubles the MMA's N (32 -> 64, 64 -> 128: an
+    M=128 MMA costs >= 64 cycles whatever its N), trims the K steps of a k-tap conv from 2k to k+1(+1) per time pair
+    and fills the 128-byte TMA rows a 32-channel tensor leaves half empty.  Returns (weight', bias', pad_left')."""
+    weight = weight.detach().float()
+    cout, cin, k = weight.shape
+    p = (k - 1) // 2 if pad_left is None else pad_left
+    vmin, vmax = (0 - p) // 2, (1 + k - 1 - p) // 2
+    w2 = torch.zeros(2 * cout, 2 * cin, vmax - vmin + 1)
+    for e in range(2):
+        for v in range(vmin, vmax + 1):
+            for f in range(2):
+                j = 2 * v + f - e + p
+                if 0 <= j < k:
+                    w2[e * cout:(e + 1) * cout, f * cin:(f + 1) * cin, v - vmin] = weight[:, :, j]
+    b2 = None if bias is None else bias.detach().float().repeat(2)
+    return w2, b2, -vmin
+
+
+def pack_conv_folded(weight, bias, *, dtype=torch.float16, block_n=None):
+    """pack_conv of the time-pair-folded form of a dilation-1 conv; the caller passes [B, T/2, 2C] views (PackedConv.fold == 2)."""
+    cout, cin, k = weight.shape
+    w2, b2, pl = fold_time_pairs(weight, bias)
+    pc = pack_conv(w2, b2, dil=1, pad_left=pl, dtype=dtype, block_n=block_n)
+    pc.alg_macs_per_row = 2 * cin * cout * k      # the unfolded conv's own MACs for the two time steps of a row
+    pc.fold = 2
+    return pc
+
+
 def gate_block_n(hidden):
     """N tile of a gated conv: 192 (two tiles for hidden 192, N=192 MMAs) when hidden splits into 96-wide halves, else 128."""
     return 192 if hidden % 96 == 0 else 128

@@ -39,7 +39,7 @@ class SynthesizerTrn(nn.Module):
                  resblock_dilation_sizes, upsample_rates, upsample_initial_channel, upsample_kernel_sizes,
                  n_speakers=0, gin_channels=0, use_sdp=True, n_vocab_note=100, *, operand_dtype="fp16",
                  max_position_embeddings=2000, generator_chunk_frames=32768, f0_precision="split",
-                 text_precision="split", generator_residual="act16", generator_mrf="fp16", cuda_graphs=False,
+                 text_precision="split", generator_residual="act16", generator_mrf="fp16", generator_fold=32, cuda_graphs=False,
                  fuse_spec_proj=False,
                  seed=1234, **kwargs):
         super().__init__()
@@ -71,6 +71,10 @@ class SynthesizerTrn(nn.Module):
             raise ValueError("generator_mrf must be 'fp16' (the MRF sum xs += resblock_j(x) as a 16-bit stream; only "
                              "with generator_residual='fp16') or 'fp32'")
         self.generator_mrf = generator_mrf
+        # ResBlock convs with dilation 1 and <= generator_fold channels run on [B, T/2, 2C] views (0: never)
+        # or {channels: largest kernel size to fold}, e.g. {32: 11, 64: 3}
+        self.generator_fold = ({int(c): int(k) for c, k in generator_fold.items()} if isinstance(generator_fold, dict)
+                               else int(generator_fold))
         # every call site of the reference discards spec_predict; with fuse_spec_proj=True the two
         # 513-wide 1x1 convs SpecDecoder.proj -> spec_proj collapse into one 192x192 conv (see _pack) and infer
         # returns None in spec_predict's place.  Off by default: the result tuple then matches the reference's.
@@ -234,10 +238,19 @@ class SynthesizerTrn(nn.Module):
             stage = []
             for j, (k, dils) in enumerate(zip(self.resblock_kernel_sizes, self.resblock_dilation_sizes)):
                 p = f"{d}.resblocks.{i * nk + j}"
+                ch_i = self.upsample_initial_channel // (2 ** (i + 1))
+
+                def rconv(name, dl, ch_i=ch_i, k=k):
+                    # dilation-1 convs of the narrow stages run time-pair folded (packer.fold_time_pairs)
+                    gf = self.generator_fold
+                    on = gf.get(ch_i, 0) >= k if isinstance(gf, dict) else ch_i <= gf
+                    if dl == 1 and on and math.prod(self.upsample_rates[:i + 1]) % 2 == 0:
+                        return packer.pack_conv_folded(W(name), Bv(name), dtype=dt).to(dev)
+                    return conv(name, dil=dl)
                 if self.resblock == "1":
-                    pairs = [(conv(f"{p}.convs1.{m}", dil=dl), conv(f"{p}.convs2.{m}", dil=1)) for m, dl in enumerate(dils)]
+                    pairs = [(rconv(f"{p}.convs1.{m}", dl), rconv(f"{p}.convs2.{m}", 1)) for m, dl in enumerate(dils)]
                 else:
-                    pairs = [(conv(f"{p}.convs.{m}", dil=dl), None) for m, dl in enumerate(dils)]
+                    pairs = [(rconv(f"{p}.convs.{m}", dl), None) for m, dl in enumerate(dils)]
                 stage.append(pairs)
             P["g_rb"].append(stage)
         wpost = W(d + ".conv_post")                     # [1, C, 7] -> [7][C] fp32
@@ -343,6 +356,19 @@ class SynthesizerTrn(nn.Module):
             self._generator_chunk(P, x16[b0:b1], None if gbias is None else gbias[b0:b1], out[b0:b1])
         return out
 
+    @staticmethod
+    def _rconv(pc, x, **kw):
+        """ops.conv1d for a ResBlock conv; a time-pair-folded conv (PackedConv.fold == 2) gets [B, T/2, 2C] views of
+        every [B, T, C] tensor (the stage tensors are dense and T = hop-multiple is even)."""
+        if pc.fold == 1:
+            return ops.conv1d(pc, x, **kw)
+        f = pc.fold
+        B, T, C = x.shape
+
+        def v(t):
+            return t.view(B, T // f, f * t.shape[2]) if torch.is_tensor(t) and t.dim() == 3 else t
+        return ops.conv1d(pc, v(x), **{k: v(a) for k, a in kw.items()})
+
     def _generator_chunk(self, P, x16, gbias, out):
         B, T, _ = x16.shape
         dev, dt = x16.device, self.operand_dtype
@@ -409,14 +435,14 @@ class SynthesizerTrn(nn.Module):
                     else:
                         kw["res1"] = src32
                     if c2 is not None:      # ResBlock1 (modules.py:210-223)
-                        ops.conv1d(c1, src16, out16=t16, post_lrelu=LRELU_SLOPE)
-                        ops.conv1d(c2, t16, **kw)
+                        self._rconv(c1, src16, out16=t16, post_lrelu=LRELU_SLOPE)
+                        self._rconv(c2, t16, **kw)
                         src32, srcr, src16 = c32, cr16, cl16
                     else:                   # ResBlock2 (modules.py:243-252): ping-pong the 16-bit stream,
                         dst16 = t16 if src16 is cl16 else cl16      # the conv reads halo rows of its input
                         if "out16" in kw and not last:
                             kw["out16"] = dst16
-                        ops.conv1d(c1, src16, **kw)
+                        self._rconv(c1, src16, **kw)
                         src32, srcr, src16 = c32, cr16, dst16
             cur16, L = nxt16, Lo
         ops.conv_post_tanh(cur16, P["g_post"], out.view(B, L))
