@@ -38,7 +38,8 @@ class SynthesizerTrn(nn.Module):
                  n_heads, n_layers, kernel_size, p_dropout, resblock, resblock_kernel_sizes,
                  resblock_dilation_sizes, upsample_rates, upsample_initial_channel, upsample_kernel_sizes,
                  n_speakers=0, gin_channels=0, use_sdp=True, n_vocab_note=100, *, operand_dtype="fp16",
-                 max_position_embeddings=2000, generator_chunk_frames=32768, f0_precision="split",
+                 max_position_embeddings=2000, generator_chunk_frames=32768, generator_wide_chunk_frames=196608,
+                 generator_wide_stages=1, f0_precision="split",
                  text_precision="split", generator_residual="act16", generator_mrf="fp16", generator_fold=32, cuda_graphs=False,
                  fuse_spec_proj=False,
                  seed=1234, **kwargs):
@@ -56,6 +57,7 @@ class SynthesizerTrn(nn.Module):
         self.n_speakers, self.gin_channels, self.use_sdp = n_speakers, gin_channels, use_sdp
         self.operand_dtype = {"fp16": torch.float16, "bf16": torch.bfloat16}[operand_dtype]
         self.generator_chunk_frames = generator_chunk_frames
+        self.generator_wide_chunk_frames, self.generator_wide_stages = generator_wide_chunk_frames, generator_wide_stages
         if f0_precision not in ("split", "fp32"):
             raise ValueError("f0_precision must be 'split' (tensor cores, fp16 hi/lo operands) or 'fp32' (SIMT)")
         self.f0_precision = f0_precision
@@ -344,16 +346,31 @@ class SynthesizerTrn(nn.Module):
                 ops.conv1d(rs, acts, res1=skip if i > 0 else None, lens=lens, out16=out16)
 
     def _generator(self, x16, gbias=None):
-        """Generator.forward (VISinger/models_ae.py:327-346).  x16: [B,T,C] masked input; returns [B,1,T*hop]."""
+        """Generator.forward (VISinger/models_ae.py:327-346).  x16: [B,T,C] masked input; returns [B,1,T*hop].
+
+        Utterance chunks bound the activation working set (stage tensors are hop*C*T elements).  Two chunk sizes:
+        conv_pre and the first `generator_wide_stages` upsampling stages (few, tensor-bound launches whose fixed
+        costs want long launches) run over `generator_wide_chunk_frames`, the later HBM-bound stages over
+        `generator_chunk_frames` (measured: stage 0 19.0 -> 16.5 ms on the whole 64 x 30 s batch, while stages 2-3
+        lose 10 % beyond ~32 k frames per chunk)."""
         P = self._packed
         B, T, _ = x16.shape
-        dev, dt = x16.device, self.operand_dtype
-        out = torch.empty(B, 1, T * self.hop, device=dev, dtype=torch.float32)
-        # utterance chunks bound the activation working set (stage tensors are hop*C*T elements)
+        out = torch.empty(B, 1, T * self.hop, device=x16.device, dtype=torch.float32)
+        n_st = len(self.upsample_rates)
+        n_wide = min(max(int(self.generator_wide_stages), 0), n_st)
+        wide = max(self.generator_wide_chunk_frames, self.generator_chunk_frames) if n_wide else self.generator_chunk_frames
+        per_w = max(1, wide // max(T, 1))
         per = max(1, self.generator_chunk_frames // max(T, 1))
-        for b0 in range(0, B, per):
-            b1 = min(B, b0 + per)
-            self._generator_chunk(P, x16[b0:b1], None if gbias is None else gbias[b0:b1], out[b0:b1])
+        for w0 in range(0, B, per_w):
+            w1 = min(B, w0 + per_w)
+            cur16 = torch.empty(w1 - w0, T, self.upsample_initial_channel, device=x16.device, dtype=self.operand_dtype)
+            ops.conv1d(P["g_pre"], x16[w0:w1], gbias=None if gbias is None else gbias[w0:w1], out16=cur16,
+                       post_lrelu=LRELU_SLOPE)
+            cur16, L = self._generator_stages(P, cur16, T, 0, n_wide)
+            for b0 in range(w0, w1, per):
+                b1 = min(w1, b0 + per)
+                c16, Lc = self._generator_stages(P, cur16[b0 - w0:b1 - w0], L, n_wide, n_st)
+                ops.conv_post_tanh(c16, P["g_post"], out[b0:b1].view(b1 - b0, Lc))
         return out
 
     @staticmethod
@@ -369,19 +386,19 @@ class SynthesizerTrn(nn.Module):
             return t.view(B, T // f, f * t.shape[2]) if torch.is_tensor(t) and t.dim() == 3 else t
         return ops.conv1d(pc, v(x), **{k: v(a) for k, a in kw.items()})
 
-    def _generator_chunk(self, P, x16, gbias, out):
-        B, T, _ = x16.shape
-        dev, dt = x16.device, self.operand_dtype
+    def _generator_stages(self, P, cur16, L, st0, st1):
+        """Upsampling stages st0 .. st1-1 (ups[i] + MRF of ResBlocks) on the activated 16-bit tensor cur16 [B, L, C_in];
+        returns (activated 16-bit stage output, its length)."""
+        B = cur16.shape[0]
+        dev, dt = cur16.device, self.operand_dtype
         up0 = self.upsample_initial_channel
-        cur16 = torch.empty(B, T, up0, device=dev, dtype=dt)
-        ops.conv1d(P["g_pre"], x16, gbias=gbias, out16=cur16, post_lrelu=LRELU_SLOPE)
-        L = T
         n_st = len(self.upsample_rates)
         r16 = self.generator_residual in ("fp16", "act16") and dt == torch.float16
         # act16: no un-activated stream at all - the pair's second conv reads its residual from the activated tensor
         # the first conv consumed and inverts the leaky-ReLU (x = min(r, r / slope)): 10 B per element and pair
         ract = r16 and self.generator_residual == "act16"
-        for i, u in enumerate(self.upsample_rates):
+        for i in range(st0, st1):
+            u = self.upsample_rates[i]
             ch = up0 // (2 ** (i + 1))
             Lo = L * u
             # stage residual stream: fp32 (x32) or, by default in fp16 mode, 16-bit (xr16: HBM traffic of a
@@ -445,7 +462,7 @@ class SynthesizerTrn(nn.Module):
                         self._rconv(c1, src16, **kw)
                         src32, srcr, src16 = c32, cr16, dst16
             cur16, L = nxt16, Lo
-        ops.conv_post_tanh(cur16, P["g_post"], out.view(B, L))
+        return cur16, L
 
     def _graphed(self, fn, args, shape_key):
         """Run fn(*args) through a cached CUDA graph.  args: tensors or None; the graph owns static copies of them and

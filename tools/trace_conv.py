@@ -18,16 +18,21 @@ CAP = 64
 B, ROWS = 4, 524288            # rows at C=128 (Generator stage 1 of 4 x 2048 frames); scaled so bytes stay equal
 
 
-def run(C, k, dil, res, block_n=None):
+def run(C, k, dil, res, block_n=None, fold=False):
     T = ROWS * 128 // C // B
     g = torch.Generator().manual_seed(0)
     w = torch.randn(C, C, k, generator=g) * (C * k) ** -0.5
     b = torch.randn(C, generator=g) * 0.1
-    pc = packer.pack_conv(w, b, dil=dil, block_n=block_n).to(DEV)
+    pc = (packer.pack_conv_folded(w, b) if fold else packer.pack_conv(w, b, dil=dil, block_n=block_n)).to(DEV)
+    if fold:
+        T, C = T // 2, C * 2
     x = (torch.randn(B, T, C, generator=g)).half().to(DEV)
     o16 = torch.empty(B, T, C, device=DEV, dtype=torch.float16)
     kw = dict(out16=o16, post_lrelu=0.1)
-    if res == 2:       # the Generator's 16-bit residual stream: res16 in, raw out16r in place, activated out16
+    if res == 3:       # act16: residual recovered from the activated tensor, activated result in place
+        r = torch.randn(B, T, C, device=DEV).half()
+        kw.update(res16=r, res16_unlrelu=10.0, out16=r)
+    elif res == 2:       # the Generator's 16-bit residual stream: res16 in, raw out16r in place, activated out16
         r = torch.randn(B, T, C, device=DEV).half()
         kw.update(res16=r, out16r=r)
     elif res:
@@ -79,6 +84,8 @@ if len(_s.argv) > 1 and _s.argv[1] == 'hbm':
     cfgs = [(32, 3, 1, False), (32, 3, 1, 2), (64, 3, 1, False), (64, 3, 1, 2)]
 if len(_s.argv) > 1 and _s.argv[1] == 'gap':
     cfgs = [(32, 11, 1, False), (64, 7, 1, False), (128, 11, 1, False), (32, 3, 1, False)]
+if len(_s.argv) > 1 and _s.argv[1] == 'act':
+    cfgs = [(128, 3, 1, False), (128, 3, 1, 3), (64, 3, 1, False), (64, 3, 1, 3), (32, 3, 1, False, None, True), (32, 3, 1, 3, None, True)]
 if COMPACT:
     cfgs = [(C, k, 1, r) for C in (128, 64, 32) for k in (3, 7, 11) for r in (False, 2)]
 for cfg in cfgs or [(128, 3, 1, False), (128, 3, 1, True), (128, 11, 5, False), (64, 3, 1, False), (64, 7, 3, True), (32, 3, 1, False), (32, 11, 5, False), (32, 7, 1, True), (256, 3, 1, False)]:
