@@ -283,6 +283,33 @@ def test_conv1d_tc_residual_from_activated_stream(cout, k, with_mrf):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("c,k,T", [(32, 3, 700), (32, 7, 1026), (32, 11, 258), (64, 11, 700), (32, 11, 2)])
+def test_conv1d_tc_time_pair_folded(c, k, T):
+    """packer.pack_conv_folded: the dilation-1 conv run on [B, T/2, 2C] views (block-Toeplitz weights) is the same conv
+    - checked against torch and against the unfolded kernel path, including the zero padding at both ends of every
+    utterance (row -1 / row T/2 of the folded view) and the act16 residual epilogue on folded views."""
+    import torch.nn.functional as F
+    B = 3
+    w, b = _rand(c, c, k, seed=70, scale=(c * k) ** -0.5), _rand(c, seed=71, scale=0.1)
+    x = _rand(B, T, c, seed=72).half()
+    res = F.leaky_relu(_rand(B, T, c, seed=73), 0.1).half()
+    xrec = torch.minimum(res.float(), res.float() * 10.0)
+    ref = F.conv1d(x.float().transpose(1, 2), w.half().float(), b, padding=k // 2).transpose(1, 2) + xrec
+    ref16 = F.leaky_relu(ref, 0.1).half().float()
+    pcf, pcu = packer.pack_conv_folded(w, b).to(DEV), packer.pack_conv(w, b).to(DEV)
+    assert pcf.fold == 2 and pcf.cin == 2 * c
+    outs = []
+    for pc, f in ((pcf, 2), (pcu, 1)):
+        buf = res.clone().to(DEV)
+        v = lambda t: t.view(B, T // f, f * c)
+        ops.conv1d(pc, v(x.to(DEV)), res16=v(buf), res16_unlrelu=10.0, out16=v(buf), post_lrelu=0.1)
+        torch.cuda.synchronize()
+        outs.append(buf.float().cpu())
+        assert max_abs(ref16, outs[-1]) < 4e-3
+    assert max_abs(outs[0], outs[1]) < 2e-3          # same products, different accumulation order + fp16 rounding
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("cout,k,dil,scale", [(32, 3, 1, 1.0), (64, 7, 1, 1.0 / 3.0), (128, 11, 1, 1.0 / 3.0), (256, 3, 1, 1.0)])
 def test_conv1d_tc_16bit_mrf_stream(cout, k, dil, scale):
     """res2 as a 16-bit tensor (b200svs_epilogue.res2_is16): the MRF sum xs += resblock_j(x) kept as a 16-bit
