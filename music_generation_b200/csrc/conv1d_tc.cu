@@ -55,6 +55,7 @@ struct ConvTcParams {
   int acc_shift;                           // log2 of the accumulator ring depth (1 or 2)
   int w_resident;                          // all weight tiles stay in shared memory (w_stages = taps x K chunks)
   int epi_alt;                             // epilogue warp pairs take alternate chunks (32 columns each)
+  int lean16;                              // only output: activated 16-bit tensor; only residual: res16 (process_o16)
   int xpre;                                // epilogue prefetches the next tile's first TMEM chunk
   int peek;                                // MMA thread peeks the next tile's barriers before the last tap
   int chunks_per_sub, n_out_tile;          // output chunks per 128-row sub-tile; output columns per N tile
@@ -114,6 +115,18 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
+// packed fp32x2 arithmetic (sm_100: FADD2 / FMUL2, one issue slot for two lanes' worth of fp32 work)
+__device__ __forceinline__ float2 add2(float2 a, float2 b) {
+  unsigned long long r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)));
+  return *reinterpret_cast<float2*>(&r);
+}
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+  unsigned long long r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)));
+  return *reinterpret_cast<float2*>(&r);
+}
+
 static_assert(sizeof(TcBarriers) <= 512, "barrier block must fit its 512-byte reservation");
 
 __device__ __forceinline__ void trace_stamp(const ConvTcParams& p, int it, int slot, long long v) {
@@ -153,7 +166,10 @@ struct TileIter {
 //   speaker bias (the Generator's case).  BF: 16-bit output is bf16.  SPLIT: fp16 [hi | lo | hi] output.
 //   ALT: warp w and w + 4 take alternate 32-column chunks (even / odd) and do all 32 columns of theirs, instead of
 //   splitting every chunk 16 / 16: half as many slot waits, fences, barrier arrivals and loop trips per byte.
-template <int ACT, int RES, bool PLAIN, bool BF, bool SPLIT, bool R16 = false, bool ALT = false>
+//   OUTS == 1 (with PLAIN, act NONE, RES == 0): the launch's only output is the activated 16-bit tensor and its only
+//   residual (R16) is res16 - the Generator's conv1 and act16 conv2 launches.  Every output / residual flag is then
+//   a compile-time constant and the arithmetic runs on packed fp32x2 instructions (process_o16).
+template <int ACT, int RES, bool PLAIN, bool BF, bool SPLIT, bool R16 = false, bool ALT = false, int OUTS = 0>
 __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
                                               uint32_t smE_u, uint32_t bias_u) {
   constexpr bool GATE = ACT == B200SVS_ACT_GATE;
@@ -318,6 +334,46 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
     }
   };
 
+  // OUTS == 1: v = acc + bias [+ unlrelu(res16)]; out16 = cvt16(lrelu(v)).  16 columns of one row.
+  auto process_o16 = [&](const uint32_t* a0, uint32_t slot_u, int pcol, int h) {
+    const uint32_t ba = bias_u + pcol * 4;
+    float2 v2[8];
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) {
+      const float4 bq = lds128(ba + 16 * jj);
+      v2[2 * jj] = add2(make_float2(__uint_as_float(a0[4 * jj]), __uint_as_float(a0[4 * jj + 1])), make_float2(bq.x, bq.y));
+      v2[2 * jj + 1] = add2(make_float2(__uint_as_float(a0[4 * jj + 2]), __uint_as_float(a0[4 * jj + 3])), make_float2(bq.z, bq.w));
+    }
+    if constexpr (R16) {
+      const float2 rinv2 = make_float2(rinv, rinv);
+#pragma unroll
+      for (int jj = 0; jj < 2; ++jj) {
+        const float4 q = lds128(slot_u + raw_delta + off16[h][jj]);
+        const uint32_t u[4] = {__float_as_uint(q.x), __float_as_uint(q.y), __float_as_uint(q.z), __float_as_uint(q.w)};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          float2 f;
+          if (BF) {
+            f.x = __uint_as_float(u[e] << 16); f.y = __uint_as_float(u[e] & 0xFFFF0000u);
+          } else {
+            f = __half22float2(*reinterpret_cast<const __half2*>(&u[e]));
+          }
+          const float2 m = mul2(f, rinv2);
+          v2[4 * jj + e] = add2(v2[4 * jj + e], make_float2(fminf(f.x, m.x), fminf(f.y, m.y)));
+        }
+      }
+    }
+    const float2 slope2 = make_float2(slope, slope);
+    uint32_t p16[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float2 m = mul2(v2[i], slope2);
+      p16[i] = pack2<BF>(fmaxf(v2[i].x, m.x), fmaxf(v2[i].y, m.y));
+    }
+    sts128u(slot_u + off16[h][0], p16[0], p16[1], p16[2], p16[3]);
+    sts128u(slot_u + off16[h][1], p16[4], p16[5], p16[6], p16[7]);
+  };
+
   if constexpr (ALT) {                 // n_chunks is even (host): this warp's chunks are grp, grp + 2, ...
     const int grp = half;
     int it = 0, sl = grp;
@@ -349,8 +405,13 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
         tmem_ld_wait16(ra + 16);
         if (tsub < p.T) {
           const uint32_t slot_u = smE_u + sl * slot_bytes;
-          process(ra, ra, slot_u, pcol0 + ch * kEpiCols, tile_b, s, 0);
-          process(ra + 16, ra, slot_u, pcol0 + ch * kEpiCols + 16, tile_b, s, 1);
+          if constexpr (OUTS == 1) {
+            process_o16(ra, slot_u, pcol0 + ch * kEpiCols, 0);
+            process_o16(ra + 16, slot_u, pcol0 + ch * kEpiCols + 16, 1);
+          } else {
+            process(ra, ra, slot_u, pcol0 + ch * kEpiCols, tile_b, s, 0);
+            process(ra + 16, ra, slot_u, pcol0 + ch * kEpiCols + 16, tile_b, s, 1);
+          }
         }
         // the accumulators of this warp's next chunk are fetched under the fence / barrier traffic below
         if (ci + 2 < n_chunks) {
@@ -401,7 +462,10 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
       const int tsub = tile_t0 + ms * 128;
       const float s = tsub + row < len_b ? ep.scale : 0.0f;
       mbar_wait(&bars->e_full[sl], eph);
-      if (tsub < p.T) process(r0, r1, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, tile_b, s, 0);
+      if (tsub < p.T) {
+        if constexpr (OUTS == 1) process_o16(r0, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, 0);
+        else process(r0, r1, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, tile_b, s, 0);
+      }
       fence_proxy_async();             // generic-proxy smem writes -> visible to the TMA store
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars->s_ready[sl]);
@@ -459,6 +523,10 @@ __device__ __forceinline__ void epilogue_dispatch2(const ConvTcParams& p, TcBarr
       else epilogue_loop<B200SVS_ACT_NONE, 0, false, BF, false, true, true>(p, bars, tmem_base, smE_u, bias_s);
       return;
     }
+    if (R == 0 && plain && p.lean16) {   // act16 conv2: res16 in, activated 16-bit out, nothing else
+      epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, true, false, 1>(p, bars, tmem_base, smE_u, bias_s);
+      return;
+    }
     if (plain) epilogue_loop<B200SVS_ACT_NONE, R, true, BF, false, true>(p, bars, tmem_base, smE_u, bias_s);
     else epilogue_loop<B200SVS_ACT_NONE, R, false, BF, false, true>(p, bars, tmem_base, smE_u, bias_s);
     return;
@@ -475,7 +543,8 @@ __device__ __forceinline__ void epilogue_dispatch2(const ConvTcParams& p, TcBarr
     case B200SVS_ACT_SIGMOID: epilogue_loop<B200SVS_ACT_SIGMOID, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s); break;
     case B200SVS_ACT_TANH: epilogue_loop<B200SVS_ACT_TANH, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s); break;
     default:
-      if (RES == 0 && plain && p.epi_alt) epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, false, true>(p, bars, tmem_base, smE_u, bias_s);
+      if (RES == 0 && plain && p.epi_alt && p.lean16) epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, false, true, 1>(p, bars, tmem_base, smE_u, bias_s);
+      else if (RES == 0 && plain && p.epi_alt) epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, false, true>(p, bars, tmem_base, smE_u, bias_s);
       else if (plain) epilogue_loop<B200SVS_ACT_NONE, RES, true, BF, false>(p, bars, tmem_base, smE_u, bias_s);
       else epilogue_loop<B200SVS_ACT_NONE, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s);
       break;
@@ -930,6 +999,12 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     const int res = ep.res2 ? 2 : (ep.res1 ? 1 : 0);
     p.epi_alt = alt_on && ep.act == B200SVS_ACT_NONE && !split16 && (p.msub * p.chunks_per_sub) % 2 == 0 &&
                 !has_res && (raw16 || plain);
+  }
+  {   // the Generator's two dominant launch types get the compile-time-specialised, packed-fp32x2 epilogue
+    static const int lean_on = [] { const char* e = getenv("B200SVS_TC_LEAN"); return e ? atoi(e) : 1; }();
+    const bool plain = ep.alpha == 1.0f && ep.scale == 1.0f && ep.lens == nullptr && ep.gbias == nullptr;
+    p.lean16 = lean_on && plain && ep.act == B200SVS_ACT_NONE && !split16 && ep.out16 && !ep.out32 && !ep.out16r &&
+               !ep.res1 && !ep.res2 && (ep.res16 ? 1 : p.epi_alt);
   }
   p.idesc = make_idesc_f16(128, a->block_n, a->x_dtype == B200SVS_DT_BF16);
   p.ep = ep;
