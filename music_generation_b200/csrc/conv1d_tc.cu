@@ -55,6 +55,7 @@ struct ConvTcParams {
   int acc_shift;                           // log2 of the accumulator ring depth (1 or 2)
   int w_resident;                          // all weight tiles stay in shared memory (w_stages = taps x K chunks)
   int epi_alt;                             // epilogue warp pairs take alternate chunks (32 columns each)
+  int reverse;                             // walk the tiles from the last one down (L2 reuse across back-to-back launches)
   int lean16;                              // only output: activated 16-bit tensor; only residual: res16 (process_o16)
   int xpre;                                // epilogue prefetches the next tile's first TMEM chunk
   int peek;                                // MMA thread peeks the next tile's barriers before the last tap
@@ -136,9 +137,10 @@ __device__ __forceinline__ void trace_stamp(const ConvTcParams& p, int it, int s
 // Walks this CTA's tiles (tile = blockIdx.x + i * gridDim.x, ordered [n_idx][b][time tile]) without the two
 // integer divisions per tile a direct decode costs every role.
 struct TileIter {
-  int tile, n_idx, b, tt, d_b, d_t;
+  int rank, tile, n_idx, b, tt, d_b, d_t;     // rank: position in this CTA's walk (validity); tile: the tile it maps to
   __device__ __forceinline__ explicit TileIter(const ConvTcParams& p) {
-    tile = blockIdx.x;
+    rank = blockIdx.x;
+    tile = p.reverse ? p.total_tiles - 1 - rank : rank;
     n_idx = tile / p.m_tiles;
     const int m = tile - n_idx * p.m_tiles;
     b = m / p.tiles_t;
@@ -146,14 +148,25 @@ struct TileIter {
     d_b = gridDim.x / p.tiles_t;
     d_t = gridDim.x - d_b * p.tiles_t;
   }
-  __device__ __forceinline__ bool valid(const ConvTcParams& p) const { return tile < p.total_tiles; }
+  __device__ __forceinline__ bool valid(const ConvTcParams& p) const { return rank < p.total_tiles; }
+  // true when this CTA has another tile after the current one
+  __device__ __forceinline__ bool has_next(const ConvTcParams& p) const { return rank + static_cast<int>(gridDim.x) < p.total_tiles; }
   __device__ __forceinline__ int t0(const ConvTcParams& p) const { return tt * (128 * p.msub); }
   __device__ __forceinline__ void next(const ConvTcParams& p) {
-    tile += gridDim.x;
-    tt += d_t;
-    b += d_b;
-    if (tt >= p.tiles_t) { tt -= p.tiles_t; ++b; }
-    while (b >= p.batch) { b -= p.batch; ++n_idx; }
+    rank += gridDim.x;
+    if (!p.reverse) {
+      tile += gridDim.x;
+      tt += d_t;
+      b += d_b;
+      if (tt >= p.tiles_t) { tt -= p.tiles_t; ++b; }
+      while (b >= p.batch) { b -= p.batch; ++n_idx; }
+    } else {               // same walk from the last tile down (ranks past the end are never decoded: valid() is false)
+      tile -= gridDim.x;
+      tt -= d_t;
+      b -= d_b;
+      if (tt < 0) { tt += p.tiles_t; --b; }
+      while (b < 0 && n_idx > 0) { b += p.batch; --n_idx; }
+    }
   }
 };
 
@@ -417,7 +430,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
         if (ci + 2 < n_chunks) {
           tmem_ld16_nowait(taddr + (ci + 2) * kEpiCols, ra);
           tmem_ld16_nowait(taddr + (ci + 2) * kEpiCols + 16, ra + 16);
-        } else if (p.xpre && ti.tile + static_cast<int>(gridDim.x) < p.total_tiles &&
+        } else if (p.xpre && ti.has_next(p) &&
                    mbar_test(&bars->tmem_full[(it + 1) & acc_mask], ((it + 1) >> acc_shift) & 1)) {
           tc_fence_after();
           const uint32_t tn = taddr0 + ((it + 1) & acc_mask) * acc_cols + grp * kEpiCols;
@@ -492,7 +505,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
           tmem_ld_wait16(rb0);
           if (ci + 2 < n_chunks) {
             tmem_ld16_nowait(taddr + (ci + 2) * kEpiCols, ra0);
-          } else if (p.xpre && ti.tile + static_cast<int>(gridDim.x) < p.total_tiles &&
+          } else if (p.xpre && ti.has_next(p) &&
                      mbar_test(&bars->tmem_full[(it + 1) & acc_mask], ((it + 1) >> acc_shift) & 1)) {
             // the next tile's accumulator is already complete (the usual case when the epilogue is the slower
             // side): start fetching its first chunk under the last chunk of this tile
@@ -1005,6 +1018,13 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     const bool plain = ep.alpha == 1.0f && ep.scale == 1.0f && ep.lens == nullptr && ep.gbias == nullptr;
     p.lean16 = lean_on && plain && ep.act == B200SVS_ACT_NONE && !split16 && ep.out16 && !ep.out32 && !ep.out16r &&
                !ep.res1 && !ep.res2 && (ep.res16 ? 1 : p.epi_alt);
+  }
+  {   // Zigzag: consecutive launches walk their tiles in opposite directions, so a launch starts on the rows its
+      // predecessor touched last - still in the 126 MB L2 - instead of on rows evicted long ago (the Generator's
+      // launches are chains conv1 -> conv2 -> conv1 over the same rows).  Tile order never changes a result.
+    static const int zig_on = [] { const char* e = getenv("B200SVS_TC_ZIGZAG"); return e ? atoi(e) : 1; }();
+    static unsigned launch_parity = 0;
+    p.reverse = zig_on ? static_cast<int>(__atomic_fetch_add(&launch_parity, 1u, __ATOMIC_RELAXED) & 1u) : 0;
   }
   p.idesc = make_idesc_f16(128, a->block_n, a->x_dtype == B200SVS_DT_BF16);
   p.ep = ep;
