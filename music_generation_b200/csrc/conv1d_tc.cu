@@ -56,7 +56,8 @@ struct ConvTcParams {
   int w_resident;                          // all weight tiles stay in shared memory (w_stages = taps x K chunks)
   int epi_alt;                             // epilogue warp pairs take alternate chunks (32 columns each)
   int reverse;                             // walk the tiles from the last one down (L2 reuse across back-to-back launches)
-  int lean16;                              // only output: activated 16-bit tensor; only residual: res16 (process_o16)
+  int lean16;                              // process_o16 variant: 1 res16 -> out16 (or conv1: no residual), 2 res16 -> out16r,
+                                           // 3 res16 + 16-bit res2 -> out16r, 4 res16 + 16-bit res2 -> scaled out16; 0: generic
   int xpre;                                // epilogue prefetches the next tile's first TMEM chunk
   int peek;                                // MMA thread peeks the next tile's barriers before the last tap
   int chunks_per_sub, n_out_tile;          // output chunks per 128-row sub-tile; output columns per N tile
@@ -179,10 +180,11 @@ struct TileIter {
 //   speaker bias (the Generator's case).  BF: 16-bit output is bf16.  SPLIT: fp16 [hi | lo | hi] output.
 //   ALT: warp w and w + 4 take alternate 32-column chunks (even / odd) and do all 32 columns of theirs, instead of
 //   splitting every chunk 16 / 16: half as many slot waits, fences, barrier arrivals and loop trips per byte.
-//   OUTS == 1 (with PLAIN, act NONE, RES == 0): the launch's only output is the activated 16-bit tensor and its only
-//   residual (R16) is res16 - the Generator's conv1 and act16 conv2 launches.  Every output / residual flag is then
-//   a compile-time constant and the arithmetic runs on packed fp32x2 instructions (process_o16).
-template <int ACT, int RES, bool PLAIN, bool BF, bool SPLIT, bool R16 = false, bool ALT = false, int OUTS = 0>
+//   OUTS != 0 (act NONE, RES == 0, no alpha / mask / speaker bias): the Generator's launches.  The only output is
+//   the activated 16-bit tensor (OUTS == 1) or the un-activated one (OUTS == 2, the MRF stream), the residuals are
+//   res16 (R16) and optionally the 16-bit MRF sum (R2H), `scale` applies when !PLAIN.  Every output / residual flag
+//   is a compile-time constant and the arithmetic runs on packed fp32x2 instructions (process_o16).
+template <int ACT, int RES, bool PLAIN, bool BF, bool SPLIT, bool R16 = false, bool ALT = false, int OUTS = 0, bool R2H = false>
 __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
                                               uint32_t smE_u, uint32_t bias_u) {
   constexpr bool GATE = ACT == B200SVS_ACT_GATE;
@@ -376,15 +378,44 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
         }
       }
     }
-    const float2 slope2 = make_float2(slope, slope);
-    uint32_t p16[8];
+    if constexpr (R2H) {       // + the 16-bit MRF sum so far
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float2 m = mul2(v2[i], slope2);
-      p16[i] = pack2<BF>(fmaxf(v2[i].x, m.x), fmaxf(v2[i].y, m.y));
+      for (int jj = 0; jj < 2; ++jj) {
+        const float4 q = lds128(slot_u + r2h_delta + off16[h][jj]);
+        const uint32_t u[4] = {__float_as_uint(q.x), __float_as_uint(q.y), __float_as_uint(q.z), __float_as_uint(q.w)};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          float2 f;
+          if (BF) {
+            f.x = __uint_as_float(u[e] << 16); f.y = __uint_as_float(u[e] & 0xFFFF0000u);
+          } else {
+            f = __half22float2(*reinterpret_cast<const __half2*>(&u[e]));
+          }
+          v2[4 * jj + e] = add2(v2[4 * jj + e], f);
+        }
+      }
     }
-    sts128u(slot_u + off16[h][0], p16[0], p16[1], p16[2], p16[3]);
-    sts128u(slot_u + off16[h][1], p16[4], p16[5], p16[6], p16[7]);
+    if constexpr (!PLAIN) {
+      const float2 scale2 = make_float2(ep.scale, ep.scale);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v2[i] = mul2(v2[i], scale2);
+    }
+    uint32_t p16[8];
+    if constexpr (OUTS == 2) {   // un-activated 16-bit result (out16r area of the slot)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) p16[i] = pack2<BF>(v2[i].x, v2[i].y);
+      sts128u(slot_u + raw_delta + off16[h][0], p16[0], p16[1], p16[2], p16[3]);
+      sts128u(slot_u + raw_delta + off16[h][1], p16[4], p16[5], p16[6], p16[7]);
+    } else {
+      const float2 slope2 = make_float2(slope, slope);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float2 m = mul2(v2[i], slope2);
+        p16[i] = pack2<BF>(fmaxf(v2[i].x, m.x), fmaxf(v2[i].y, m.y));
+      }
+      sts128u(slot_u + off16[h][0], p16[0], p16[1], p16[2], p16[3]);
+      sts128u(slot_u + off16[h][1], p16[4], p16[5], p16[6], p16[7]);
+    }
   };
 
   if constexpr (ALT) {                 // n_chunks is even (host): this warp's chunks are grp, grp + 2, ...
@@ -418,7 +449,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
         tmem_ld_wait16(ra + 16);
         if (tsub < p.T) {
           const uint32_t slot_u = smE_u + sl * slot_bytes;
-          if constexpr (OUTS == 1) {
+          if constexpr (OUTS != 0) {
             process_o16(ra, slot_u, pcol0 + ch * kEpiCols, 0);
             process_o16(ra + 16, slot_u, pcol0 + ch * kEpiCols + 16, 1);
           } else {
@@ -476,7 +507,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
       const float s = tsub + row < len_b ? ep.scale : 0.0f;
       mbar_wait(&bars->e_full[sl], eph);
       if (tsub < p.T) {
-        if constexpr (OUTS == 1) process_o16(r0, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, 0);
+        if constexpr (OUTS != 0) process_o16(r0, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, 0);
         else process(r0, r1, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, tile_b, s, 0);
       }
       fence_proxy_async();             // generic-proxy smem writes -> visible to the TMA store
@@ -536,9 +567,14 @@ __device__ __forceinline__ void epilogue_dispatch2(const ConvTcParams& p, TcBarr
       else epilogue_loop<B200SVS_ACT_NONE, 0, false, BF, false, true, true>(p, bars, tmem_base, smE_u, bias_s);
       return;
     }
-    if (R == 0 && plain && p.lean16) {   // act16 conv2: res16 in, activated 16-bit out, nothing else
-      epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, true, false, 1>(p, bars, tmem_base, smE_u, bias_s);
-      return;
+    if (R == 0 && p.lean16) {   // the Generator's conv2 launches: res16 (+ 16-bit MRF sum) in, one 16-bit tensor out
+      switch (p.lean16) {
+        case 1: epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, true, false, 1, false>(p, bars, tmem_base, smE_u, bias_s); return;
+        case 2: epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, true, false, 2, false>(p, bars, tmem_base, smE_u, bias_s); return;
+        case 3: epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, true, false, 2, true>(p, bars, tmem_base, smE_u, bias_s); return;
+        case 4: epilogue_loop<B200SVS_ACT_NONE, 0, false, BF, false, true, false, 1, true>(p, bars, tmem_base, smE_u, bias_s); return;
+        default: break;
+      }
     }
     if (plain) epilogue_loop<B200SVS_ACT_NONE, R, true, BF, false, true>(p, bars, tmem_base, smE_u, bias_s);
     else epilogue_loop<B200SVS_ACT_NONE, R, false, BF, false, true>(p, bars, tmem_base, smE_u, bias_s);
@@ -1016,8 +1052,12 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   {   // the Generator's two dominant launch types get the compile-time-specialised, packed-fp32x2 epilogue
     static const int lean_on = [] { const char* e = getenv("B200SVS_TC_LEAN"); return e ? atoi(e) : 1; }();
     const bool plain = ep.alpha == 1.0f && ep.scale == 1.0f && ep.lens == nullptr && ep.gbias == nullptr;
-    p.lean16 = lean_on && plain && ep.act == B200SVS_ACT_NONE && !split16 && ep.out16 && !ep.out32 && !ep.out16r &&
-               !ep.res1 && !ep.res2 && (ep.res16 ? 1 : p.epi_alt);
+    const bool base = lean_on && ep.alpha == 1.0f && ep.lens == nullptr && ep.gbias == nullptr && ep.act == B200SVS_ACT_NONE &&
+                      !split16 && !ep.out32 && !ep.res1 && !(ep.res2 && !ep.res2_is16);
+    p.lean16 = 0;
+    if (base && plain && ep.out16 && !ep.out16r && !ep.res2) p.lean16 = (ep.res16 || p.epi_alt) ? 1 : 0;
+    else if (base && plain && ep.res16 && ep.out16r && !ep.out16) p.lean16 = ep.res2 ? 3 : 2;
+    else if (base && ep.res16 && ep.res2 && ep.out16 && !ep.out16r) p.lean16 = 4;
   }
   {   // Zigzag: consecutive launches walk their tiles in opposite directions, so a launch starts on the rows its
       // predecessor touched last - still in the 126 MB L2 - instead of on rows evicted long ago (the Generator's

@@ -234,3 +234,39 @@ def test_cuda_graph_replay_equals_eager():
             assert torch.equal(ta, tb)
         assert torch.equal(eager.last_aux["f0_coarse"], graphed.last_aux["f0_coarse"])
     assert 1 <= len(graphed._graphs) <= 2
+
+
+@pytest.mark.parametrize("residual", ["act16", "fp16", "fp32"])
+def test_resblock2_variant_on_gpu(residual):
+    """ResBlock2 (VISinger/modules.py:243-252, selected by resblock != '1', models_ae.py:307): one conv per residual
+    step - the act16 residual and the ping-pong of the 16-bit stream run on the real kernels."""
+    from conftest import HP
+    from music_generation_b200 import models_ae
+    hp = dict(HP, resblock="2", resblock_dilation_sizes=[[1, 3], [1, 3], [1, 3]])
+    net = models_ae.SynthesizerTrn(100, 513, 48, **hp, generator_residual=residual).eval()
+    sd = synthetic.apply_recipe({k: v.clone() for k, v in net.state_dict().items()})
+    net.load_state_dict(sd)
+    net = net.to(DEV)
+    inp = synthetic.make_inputs(2, 12, seed=11, ragged=True)
+    ph_dur = synthetic.make_ph_dur(inp["x_lengths"], 12, 90, seed=11)
+    noise = synthetic.make_noise(2, 192, int(ph_dur.sum(1).max()), seed=11)
+    ref = vo.infer(sd, noise=noise, ph_dur=ph_dur, hp=hp, **inp)
+    res = _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise.to(DEV))
+    o = res[0].cpu()
+    assert torch.equal(res[1].cpu(), ref[1])
+    assert snr_db(ref[0], o) >= SNR_DB_TOL and max_abs(ref[0], o) <= MAX_ABS_TOL
+
+
+def test_max_len_truncates_generator_input_on_gpu():
+    """max_len (models_ae.py:649-650): the Generator sees the first max_len frames only; every frame-level tensor keeps T."""
+    net, sd = build_model("ae", device=DEV)
+    inp = synthetic.make_inputs(2, 10, seed=12, ragged=True)
+    ph_dur = synthetic.make_ph_dur(inp["x_lengths"], 10, 64, seed=12)
+    T = int(ph_dur.sum(1).max())
+    noise = synthetic.make_noise(2, 192, T, seed=12)
+    ref = vo.infer(sd, noise=noise, ph_dur=ph_dur, max_len=40, **inp)
+    res = _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise.to(DEV), max_len=40)
+    o = res[0].cpu()
+    assert o.shape == (2, 1, 40 * 256) == tuple(ref[0].shape)
+    assert res[1].shape[-1] == T
+    assert snr_db(ref[0], o) >= SNR_DB_TOL and max_abs(ref[0], o) <= MAX_ABS_TOL
