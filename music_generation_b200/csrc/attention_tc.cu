@@ -486,43 +486,61 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
 }
 
 // qkv fp32 [B,T,3C] -> (q|k) 16-bit [B,T,2C] (hi [+ lo]) and V^T 16-bit [B,C,Tp] (hi [+ lo]).
-__global__ void __launch_bounds__(256) attn_prep_kernel(const float* qkv, int qkv_ld, void* qk_hi, void* qk_lo, void* vt_hi,
-                                                        void* vt_lo, int dt, int B, int T, int Tp, int C) {
-  __shared__ float tile[32][33];
-  const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;   // c0 over 3C columns
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const bool is_v = c0 >= 2 * C;
-  for (int j = ty; j < 32; j += 8) {
-    const int t = t0 + j, c = c0 + tx;
-    if (t >= T) continue;
-    const float v = qkv[(static_cast<size_t>(b) * T + t) * qkv_ld + c];
-    if (is_v) {
-      tile[j][tx] = v;
-    } else {
-      const size_t o = (static_cast<size_t>(b) * T + t) * (2 * C) + c;
-      if (dt == B200SVS_DT_BF16) {
-        reinterpret_cast<__nv_bfloat16*>(qk_hi)[o] = __float2bfloat16_rn(v);
-      } else {
-        const __half hi = __float2half_rn(v);
-        reinterpret_cast<__half*>(qk_hi)[o] = hi;
-        if (qk_lo) reinterpret_cast<__half*>(qk_lo)[o] = __float2half_rn(v - __half2float(hi));
-      }
-    }
+// One block = 64 time rows x (128 q|k columns, or 32 V channels).  q|k: a thread converts 4 consecutive columns (16-byte
+// load, 8-byte stores, a warp covers 512 contiguous bytes of a row).  V: 64 x 32 tile transposed through shared memory,
+// a warp writes 64 time steps of one channel as half2 (128 contiguous bytes).
+constexpr int kPrepRows = 64;
+template <bool BF>
+__device__ __forceinline__ void prep_cvt2(float a, float b, uint32_t& hi, uint32_t& lo) {
+  if (BF) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    hi = *reinterpret_cast<uint32_t*>(&h);
+    lo = 0;
+  } else {
+    const __half2 h = __floats2half2_rn(a, b);
+    const float2 hf = __half22float2(h);
+    const __half2 l = __floats2half2_rn(a - hf.x, b - hf.y);
+    hi = *reinterpret_cast<const uint32_t*>(&h);
+    lo = *reinterpret_cast<const uint32_t*>(&l);
   }
-  if (!is_v) return;
-  __syncthreads();
-  for (int j = ty; j < 32; j += 8) {
-    const int c = c0 - 2 * C + j, t = t0 + tx;
-    if (t >= T) continue;
-    const float v = tile[tx][j];
-    const size_t o = (static_cast<size_t>(b) * C + c) * Tp + t;
-    if (dt == B200SVS_DT_BF16) {
-      reinterpret_cast<__nv_bfloat16*>(vt_hi)[o] = __float2bfloat16_rn(v);
-    } else {
-      const __half hi = __float2half_rn(v);
-      reinterpret_cast<__half*>(vt_hi)[o] = hi;
-      if (vt_lo) reinterpret_cast<__half*>(vt_lo)[o] = __float2half_rn(v - __half2float(hi));
+}
+template <bool BF>
+__global__ void __launch_bounds__(256) attn_prep_kernel(const float* qkv, int qkv_ld, void* qk_hi, void* qk_lo, void* vt_hi,
+                                                        void* vt_lo, int n_qk_blocks, int B, int T, int Tp, int C) {
+  __shared__ float tile[kPrepRows][33];
+  const int b = blockIdx.z, t0 = blockIdx.x * kPrepRows;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  if (static_cast<int>(blockIdx.y) < n_qk_blocks) {
+    const int c = blockIdx.y * 128 + tx * 4;
+    if (c >= 2 * C) return;
+    for (int j = ty; j < kPrepRows; j += 8) {
+      const int t = t0 + j;
+      if (t >= T) break;
+      const size_t row = static_cast<size_t>(b) * T + t;
+      const float4 v = __ldg(reinterpret_cast<const float4*>(qkv + row * qkv_ld + c));
+      uint32_t h0, l0, h1, l1;
+      prep_cvt2<BF>(v.x, v.y, h0, l0);
+      prep_cvt2<BF>(v.z, v.w, h1, l1);
+      const size_t o = row * (2 * C) + c;
+      *reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(qk_hi) + o) = make_uint2(h0, h1);
+      if (!BF && qk_lo) *reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(qk_lo) + o) = make_uint2(l0, l1);
     }
+    return;
+  }
+  const int c0 = (blockIdx.y - n_qk_blocks) * 32;
+  for (int j = ty; j < kPrepRows; j += 8) {
+    const int t = t0 + j;
+    tile[j][tx] = t < T ? __ldg(qkv + (static_cast<size_t>(b) * T + t) * qkv_ld + 2 * C + c0 + tx) : 0.f;
+  }
+  __syncthreads();
+  const int t = t0 + 2 * tx;                 // this lane's two time steps (t0 and Tp are even)
+  if (t >= Tp) return;
+  for (int j = ty; j < 32; j += 8) {
+    uint32_t h, l;
+    prep_cvt2<BF>(tile[2 * tx][j], tile[2 * tx + 1][j], h, l);      // rows >= T hold zeros: the pad [T, Tp) is written as 0
+    const size_t o = (static_cast<size_t>(b) * C + c0 + j) * Tp + t;
+    *reinterpret_cast<uint32_t*>(reinterpret_cast<uint16_t*>(vt_hi) + o) = h;
+    if (!BF && vt_lo) *reinterpret_cast<uint32_t*>(reinterpret_cast<uint16_t*>(vt_lo) + o) = l;
   }
 }
 
@@ -535,8 +553,14 @@ extern "C" int b200svs_attn_prep(const float* qkv, int32_t qkv_ld, void* qk_hi, 
   B200SVS_REQUIRE(qkv && qk_hi && vt_hi && B > 0 && T > 0 && C > 0, "attn_prep: bad argument");
   B200SVS_REQUIRE(C % 32 == 0 && Tp >= T && Tp % 8 == 0, "attn_prep: C=%d must be a multiple of 32, Tp=%d a multiple of 8 >= T", C, Tp);
   B200SVS_REQUIRE((!qk_lo && !vt_lo) || (qk_lo && vt_lo && dtype == B200SVS_DT_F16), "attn_prep: split mode is fp16 (hi, lo)");
-  dim3 grid((T + 31) / 32, 3 * C / 32, B);
-  attn_prep_kernel<<<grid, 256, 0, as_stream(stream)>>>(qkv, qkv_ld, qk_hi, qk_lo, vt_hi, vt_lo, dtype, B, T, Tp, C);
+  B200SVS_REQUIRE(qkv_ld % 4 == 0 && (reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && C % 2 == 0,
+                  "attn_prep: qkv must be 16-byte aligned with ld %% 4 == 0 (ld=%d)", qkv_ld);
+  const int n_qk = (2 * C + 127) / 128;
+  dim3 grid((T + kPrepRows - 1) / kPrepRows, n_qk + C / 32, B);
+  if (dtype == B200SVS_DT_BF16)
+    attn_prep_kernel<true><<<grid, 256, 0, as_stream(stream)>>>(qkv, qkv_ld, qk_hi, qk_lo, vt_hi, vt_lo, n_qk, B, T, Tp, C);
+  else
+    attn_prep_kernel<false><<<grid, 256, 0, as_stream(stream)>>>(qkv, qkv_ld, qk_hi, qk_lo, vt_hi, vt_lo, n_qk, B, T, Tp, C);
   return check_launch("attn_prep_kernel");
 }
 

@@ -284,5 +284,35 @@ __device__ __forceinline__ void griddep_launch_dependents() { asm volatile("grid
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + __expf(-x)); }
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
 __device__ __forceinline__ float lrelu(float x, float s) { return x > 0.f ? x : x * s; }
+__device__ __forceinline__ float ex2_approx(float x) {        // 2^x, 2 ulp; ex2(-inf) = 0, ex2(+inf) = +inf
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {        // 1/x, 1 ulp; rcp(+inf) = 0
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// tanh(a) * sigmoid(b) (commons.fused_add_tanh_sigmoid_multiply, VISinger/commons.py:100-107) in 10 instructions:
+// tanh(a) = 1 - 2 / (e^{2a} + 1), sigmoid(b) = 1 / (1 + e^{-b}); saturates correctly (e^x = inf -> rcp = 0), absolute
+// error ~2e-7 (the result feeds a 16-bit operand tensor).  tanhf + expf + a division cost ~65.
+__device__ __forceinline__ float gate_fast(float a, float b) {
+  const float r1 = rcp_approx(ex2_approx(a * 2.8853900817779268f) + 1.0f);
+  const float r2 = rcp_approx(ex2_approx(b * -1.4426950408889634f) + 1.0f);
+  return fmaf(-2.0f, r1, 1.0f) * r2;
+}
+// exact-erf GELU (F.gelu default, ext_modules/frame_prior_network.py:38) with erf from Abramowitz-Stegun 7.1.26
+// (|error| <= 1.5e-7): erf(|z|) = 1 - (a1 t + ... + a5 t^5) e^{-z^2}, t = 1 / (1 + p |z|).
+__device__ __forceinline__ float gelu_erf_fast(float x) {
+  const float z = fabsf(x) * 0.70710678118654752f;
+  const float t = rcp_approx(fmaf(0.3275911f, z, 1.0f));
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  const float e = 1.0f - poly * t * ex2_approx(z * z * -1.4426950408889634f);     // erf(|z|)
+  return 0.5f * x * (1.0f + copysignf(e, x));
+}
 
 }  // namespace b200svs

@@ -81,7 +81,7 @@ struct __align__(8) TcBarriers {
 template <int ACT>
 __device__ __forceinline__ float act_fn(float v) {
   if (ACT == B200SVS_ACT_RELU) return fmaxf(v, 0.f);
-  if (ACT == B200SVS_ACT_GELU) return gelu_erf(v);
+  if (ACT == B200SVS_ACT_GELU) return gelu_erf_fast(v);
   if (ACT == B200SVS_ACT_SIGMOID) return 1.0f / (1.0f + expf(-v));
   if (ACT == B200SVS_ACT_TANH) return tanhf(v);
   return v;
@@ -248,7 +248,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           if (gbias) y[i] += __ldg(gbias + static_cast<size_t>(b) * ep.gbias_ld + pcol + half_n + 4 * jj + i);
-          v[4 * jj + i] = tanhf(v[4 * jj + i]) * (1.0f / (1.0f + expf(-y[i])));
+          v[4 * jj + i] = gate_fast(v[4 * jj + i], y[i]);
         }
       }
     } else {
@@ -1045,7 +1045,6 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
       // launches; with a staged residual it is slower (two slots held at once halve the residual prefetch lead)
     static const int alt_on = [] { const char* e = getenv("B200SVS_TC_ALT"); return e ? atoi(e) : 1; }();
     const bool plain = ep.alpha == 1.0f && ep.scale == 1.0f && ep.lens == nullptr && ep.gbias == nullptr;
-    const int res = ep.res2 ? 2 : (ep.res1 ? 1 : 0);
     p.epi_alt = alt_on && ep.act == B200SVS_ACT_NONE && !split16 && (p.msub * p.chunks_per_sub) % 2 == 0 &&
                 !has_res && (raw16 || plain);
   }
