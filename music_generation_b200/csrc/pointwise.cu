@@ -249,20 +249,27 @@ __global__ void __launch_bounds__(kPostTile) conv_post_tanh_kernel(const void* x
   constexpr int kStride = kPostTile + kPostMaxTaps;
   for (int i = threadIdx.x; i < ktaps * C; i += blockDim.x) ws[i] = w[i];
   __syncthreads();
+  // one input row per thread: a block of 256 threads covers 256 input rows = 256 - (ktaps - 1) outputs (with 256
+  // outputs per block the ktaps - 1 halo rows were a second pass that one warp ran while seven waited)
   const int pad = ktaps / 2;
+  const int outs = kPostTile - (ktaps - 1);
   const int b = blockIdx.x / tiles_per_row;
-  const int t0 = (blockIdx.x - b * tiles_per_row) * kPostTile;
-  const int rows = kPostTile + ktaps - 1;
+  const int t0 = (blockIdx.x - b * tiles_per_row) * outs;
   const uint16_t* xb = reinterpret_cast<const uint16_t*>(x) + static_cast<size_t>(b) * L * x_ld;
-  for (int r = threadIdx.x; r < rows; r += kPostTile) {
+  {
+    const int r = threadIdx.x;
     const int t = t0 - pad + r;
     float acc[kPostMaxTaps];
 #pragma unroll
     for (int k = 0; k < kPostMaxTaps; ++k) acc[k] = 0.f;
     if (t >= 0 && t < L) {
       const uint4* src = reinterpret_cast<const uint4*>(xb + static_cast<size_t>(t) * x_ld);
-      for (int c8 = 0; c8 < C / 8; ++c8) {
-        const uint4 q = __ldg(src + c8);
+      const int n8 = C / 8;
+      uint4 qa = __ldg(src), qb = n8 > 1 ? __ldg(src + 1) : qa;      // two 16-byte loads in flight ahead of the FMAs
+      for (int c8 = 0; c8 < n8; ++c8) {
+        const uint4 q = qa;
+        qa = qb;
+        if (c8 + 2 < n8) qb = __ldg(src + c8 + 2);
         const uint32_t u[4] = {q.x, q.y, q.z, q.w};
         float xv[8];
 #pragma unroll
@@ -293,7 +300,7 @@ __global__ void __launch_bounds__(kPostTile) conv_post_tanh_kernel(const void* x
   }
   __syncthreads();
   const int t = t0 + threadIdx.x;
-  if (t < L) {
+  if (static_cast<int>(threadIdx.x) < outs && t < L) {
     float v = 0.f;
     for (int k = 0; k < ktaps; ++k) v += part[k * kStride + threadIdx.x + k];     // same tap order as a direct conv
     out[static_cast<size_t>(b) * L + t] = tanhf(v);
@@ -434,7 +441,8 @@ int b200svs_conv_post_tanh(const void* x, int32_t x_dtype, int32_t x_ld, const f
                   "conv_post_tanh: C=%d ld=%d must be multiples of 8, x 16-B aligned", C, x_ld);
   B200SVS_REQUIRE(ktaps >= 1 && ktaps <= kPostMaxTaps && C <= kPostMaxC, "conv_post_tanh: ktaps=%d (<= %d), C=%d (<= %d)",
                   ktaps, kPostMaxTaps, C, kPostMaxC);
-  const int tiles_per_row = (L + kPostTile - 1) / kPostTile;
+  const int outs = kPostTile - (ktaps - 1);
+  const int tiles_per_row = (L + outs - 1) / outs;
   const size_t smem = (static_cast<size_t>(ktaps) * C + static_cast<size_t>(ktaps) * (kPostTile + kPostMaxTaps)) * sizeof(float);
   const unsigned grid = static_cast<unsigned>(B) * tiles_per_row;
   if (x_dtype == B200SVS_DT_BF16)
