@@ -40,7 +40,7 @@ class SynthesizerTrn(nn.Module):
                  n_speakers=0, gin_channels=0, use_sdp=True, n_vocab_note=100, *, operand_dtype="fp16",
                  max_position_embeddings=2000, generator_chunk_frames=32768, generator_wide_chunk_frames=196608,
                  generator_wide_stages=1, f0_precision="split",
-                 text_precision="split", generator_residual="act16", generator_mrf="fp16", generator_fold=32, cuda_graphs=False,
+                 text_precision="split", generator_residual="act16", generator_mrf="fp16", generator_fold=32, wn_skip="gemm", cuda_graphs=False,
                  fuse_spec_proj=False,
                  seed=1234, **kwargs):
         super().__init__()
@@ -73,6 +73,9 @@ class SynthesizerTrn(nn.Module):
             raise ValueError("generator_mrf must be 'fp16' (the MRF sum xs += resblock_j(x) as a 16-bit stream; only "
                              "with generator_residual='fp16') or 'fp32'")
         self.generator_mrf = generator_mrf
+        if wn_skip not in ("gemm", "accumulate"):
+            raise ValueError("wn_skip must be 'gemm' (WN skip sum as one 1x1 conv over all layers' gate outputs) or 'accumulate'")
+        self.wn_skip = wn_skip
         # ResBlock convs with dilation 1 and <= generator_fold channels run on [B, T/2, 2C] views (0: never)
         # or {channels: largest kernel size to fold}, e.g. {32: 11, 64: 3}
         self.generator_fold = ({int(c): int(k) for c, k in generator_fold.items()} if isinstance(generator_fold, dict)
@@ -161,6 +164,16 @@ class SynthesizerTrn(nn.Module):
                                                  dtype=dt, gate=True).to(dev))
                 st["rs"].append(packer.pack_conv(W(f"{prefix}.res_skip_layers.{i}"), Bv(f"{prefix}.res_skip_layers.{i}"),
                                                  dtype=dt, block_n=192).to(dev))
+            # skip path as ONE GEMM: output = sum_i W_skip_i . acts_i + sum_i b_skip_i (modules.py:165-176 accumulates it
+            # layer by layer) = a 1x1 conv over the K-concatenation of all layers' gate outputs
+            H = self.hidden_channels
+            ws, bs = [], 0.0
+            for i in range(n):
+                w_i, b_i = W(f"{prefix}.res_skip_layers.{i}"), Bv(f"{prefix}.res_skip_layers.{i}")
+                lo = H if i < n - 1 else 0          # the last layer's 192 outputs are all skip
+                ws.append(w_i[lo:lo + H])
+                bs = bs + b_i[lo:lo + H].double()
+            st["skip_cat"] = packer.pack_conv(torch.cat(ws, 1), bs.float(), dtype=dt).to(dev)
             if self.gin_channels:
                 wc, bc = W(prefix + ".cond_layer"), Bv(prefix + ".cond_layer")
                 h2 = 2 * self.hidden_channels
@@ -332,9 +345,21 @@ class SynthesizerTrn(nn.Module):
         place; the masked skip sum is written to out16 (16-bit, consumer is always a 1x1 conv)."""
         B, T, H = x32.shape
         dev = x32.device
+        n = st["n"]
+        if self.wn_skip == "gemm":
+            # every layer's gate output is kept ([B, T, n*H], layer i in columns i*H..) and the skip sum is one 1x1
+            # conv over all of it: no fp32 skip accumulator read and written per layer, one launch less per layer
+            acts_all = torch.empty(B, T, n * H, device=dev, dtype=self.operand_dtype)
+            for i in range(n):
+                gb = None if gcond is None else gcond[:, i * 2 * H:(i + 1) * 2 * H]
+                a_i = acts_all[:, :, i * H:(i + 1) * H]
+                ops.conv1d(st["in"][i], x16, gbias=gb, out16=a_i)
+                if i < n - 1:
+                    ops.conv1d(st["rs"][i], a_i, w_rows=(0, H), res1=x32, lens=lens, out32=x32, out16=x16)
+            ops.conv1d(st["skip_cat"], acts_all, lens=lens, out16=out16)
+            return
         acts = torch.empty(B, T, H, device=dev, dtype=self.operand_dtype)
         skip = torch.empty(B, T, H, device=dev, dtype=torch.float32)
-        n = st["n"]
         for i in range(n):
             gb = None if gcond is None else gcond[:, i * 2 * H:(i + 1) * 2 * H]
             ops.conv1d(st["in"][i], x16, gbias=gb, out16=acts)

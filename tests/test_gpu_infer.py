@@ -101,7 +101,9 @@ def test_predicted_durations_are_bit_exact():
     ({"operand_dtype": "bf16"}, 34.0),                                      # bf16 operands (8-bit mantissa): reported, looser
     ({"generator_mrf": "fp32"}, SNR_DB_TOL),                                # fp32 MRF accumulator
     ({"fuse_spec_proj": True}, SNR_DB_TOL),                                 # SpecDecoder.proj -> spec_proj as one conv
-], ids=["residual_fp32", "residual_fp16", "encoders_fp32", "bf16", "mrf_fp32", "fused_spec_proj"])
+    ({"wn_skip": "accumulate"}, SNR_DB_TOL),                                # WN skip sum accumulated layer by layer in fp32
+    ({"generator_fold": 0, "generator_wide_stages": 0}, SNR_DB_TOL),        # no time-pair folding, one chunk size
+], ids=["residual_fp32", "residual_fp16", "encoders_fp32", "bf16", "mrf_fp32", "fused_spec_proj", "wn_accumulate", "unfolded"])
 def test_infer_option_paths_against_golden(kw, snr_min):
     """The non-default constructor paths stay within tolerance of the reference's golden output."""
     name = "ae_phdur_b2"
