@@ -55,6 +55,7 @@ struct ConvTcParams {
   int acc_shift;                           // log2 of the accumulator ring depth (1 or 2)
   int w_resident;                          // all weight tiles stay in shared memory (w_stages = taps x K chunks)
   int epi_alt;                             // epilogue warp pairs take alternate chunks (32 columns each)
+  int pair;                                // CTA pairs (cluster of 2, tcgen05 cta_group::2): M = 256 MMAs, each CTA holds half of B
   int reverse;                             // walk the tiles from the last one down (L2 reuse across back-to-back launches)
   int lean16;                              // process_o16 variant: 1 res16 -> out16 (or conv1: no residual), 2 res16 -> out16r,
                                            // 3 res16 + 16-bit res2 -> out16r, 4 res16 + 16-bit res2 -> scaled out16; 0: generic
@@ -148,10 +149,14 @@ struct TileIter {
     tt = m - b * p.tiles_t;
     d_b = gridDim.x / p.tiles_t;
     d_t = gridDim.x - d_b * p.tiles_t;
+    if (p.pair && n_idx >= p.n_tiles) { n_idx = 0; b = p.batch; }
   }
-  __device__ __forceinline__ bool valid(const ConvTcParams& p) const { return rank < p.total_tiles; }
+  // CTA pairs walk in lock step: the peer (odd CTA) runs exactly the leader's iterations; if the tile count is odd its
+  // last tile is a phantom (b == batch: every load is zero fill, every store clipped)
+  __device__ __forceinline__ int lead_rank(const ConvTcParams& p) const { return p.pair ? rank - static_cast<int>(blockIdx.x & 1) : rank; }
+  __device__ __forceinline__ bool valid(const ConvTcParams& p) const { return lead_rank(p) < p.total_tiles; }
   // true when this CTA has another tile after the current one
-  __device__ __forceinline__ bool has_next(const ConvTcParams& p) const { return rank + static_cast<int>(gridDim.x) < p.total_tiles; }
+  __device__ __forceinline__ bool has_next(const ConvTcParams& p) const { return lead_rank(p) + static_cast<int>(gridDim.x) < p.total_tiles; }
   __device__ __forceinline__ int t0(const ConvTcParams& p) const { return tt * (128 * p.msub); }
   __device__ __forceinline__ void next(const ConvTcParams& p) {
     rank += gridDim.x;
@@ -161,6 +166,7 @@ struct TileIter {
       b += d_b;
       if (tt >= p.tiles_t) { tt -= p.tiles_t; ++b; }
       while (b >= p.batch) { b -= p.batch; ++n_idx; }
+      if (p.pair && n_idx >= p.n_tiles) { n_idx = 0; b = p.batch; }
     } else {               // same walk from the last tile down (ranks past the end are never decoded: valid() is false)
       tile -= gridDim.x;
       tt -= d_t;
@@ -186,7 +192,7 @@ struct TileIter {
 //   is a compile-time constant and the arithmetic runs on packed fp32x2 instructions (process_o16).
 template <int ACT, int RES, bool PLAIN, bool BF, bool SPLIT, bool R16 = false, bool ALT = false, int OUTS = 0, bool R2H = false>
 __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
-                                              uint32_t smE_u, uint32_t bias_u) {
+                                              uint32_t smE_u, uint32_t bias_u, bool remote_te) {
   constexpr bool GATE = ACT == B200SVS_ACT_GATE;
   const b200svs_epilogue& ep = p.ep;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -477,7 +483,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+      if (lane == 0) { if (remote_te) mbar_arrive_remote(&bars->tmem_empty[acc], 0); else mbar_arrive(&bars->tmem_empty[acc]); }
       if (threadIdx.x == 128) trace_stamp(p, it, 6, clock64());
     }
     return;
@@ -550,78 +556,79 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
     }
     tc_fence_before();
     __syncwarp();
-    if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+    if (lane == 0) { if (remote_te) mbar_arrive_remote(&bars->tmem_empty[acc], 0); else mbar_arrive(&bars->tmem_empty[acc]); }
     if (threadIdx.x == 128) trace_stamp(p, it, 6, clock64());
   }
 }
 
 template <int RES, bool BF>
 __device__ __forceinline__ void epilogue_dispatch2(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
-                                                   uint32_t smE_u, uint32_t bias_s, bool plain, bool split) {
+                                                   uint32_t smE_u, uint32_t bias_s, bool plain, bool split, bool remote_te) {
   const int act = p.ep.act;
   if (p.ep.res16 || p.ep.out16r || (p.ep.res2 && p.ep.res2_is16)) {   // 16-bit residual stream: host restricts it to act NONE, non-split, RES in {0, 2}
     if (RES == 1) return;
     constexpr int R = RES == 1 ? 0 : RES;
     if (R == 0 && p.epi_alt) {       // no residual to stage (the upsampling convs): alternate-chunk epilogue
-      if (plain) epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, true, true>(p, bars, tmem_base, smE_u, bias_s);
-      else epilogue_loop<B200SVS_ACT_NONE, 0, false, BF, false, true, true>(p, bars, tmem_base, smE_u, bias_s);
+      if (plain) epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, true, true>(p, bars, tmem_base, smE_u, bias_s, remote_te);
+      else epilogue_loop<B200SVS_ACT_NONE, 0, false, BF, false, true, true>(p, bars, tmem_base, smE_u, bias_s, remote_te);
       return;
     }
     if (R == 0 && p.lean16) {   // the Generator's conv2 launches: res16 (+ 16-bit MRF sum) in, one 16-bit tensor out
       switch (p.lean16) {
-        case 1: epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, true, false, 1, false>(p, bars, tmem_base, smE_u, bias_s); return;
-        case 2: epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, true, false, 2, false>(p, bars, tmem_base, smE_u, bias_s); return;
-        case 3: epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, true, false, 2, true>(p, bars, tmem_base, smE_u, bias_s); return;
-        case 4: epilogue_loop<B200SVS_ACT_NONE, 0, false, BF, false, true, false, 1, true>(p, bars, tmem_base, smE_u, bias_s); return;
+        case 1: epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, true, false, 1, false>(p, bars, tmem_base, smE_u, bias_s, remote_te); return;
+        case 2: epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, true, false, 2, false>(p, bars, tmem_base, smE_u, bias_s, remote_te); return;
+        case 3: epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, true, false, 2, true>(p, bars, tmem_base, smE_u, bias_s, remote_te); return;
+        case 4: epilogue_loop<B200SVS_ACT_NONE, 0, false, BF, false, true, false, 1, true>(p, bars, tmem_base, smE_u, bias_s, remote_te); return;
         default: break;
       }
     }
-    if (plain) epilogue_loop<B200SVS_ACT_NONE, R, true, BF, false, true>(p, bars, tmem_base, smE_u, bias_s);
-    else epilogue_loop<B200SVS_ACT_NONE, R, false, BF, false, true>(p, bars, tmem_base, smE_u, bias_s);
+    if (plain) epilogue_loop<B200SVS_ACT_NONE, R, true, BF, false, true>(p, bars, tmem_base, smE_u, bias_s, remote_te);
+    else epilogue_loop<B200SVS_ACT_NONE, R, false, BF, false, true>(p, bars, tmem_base, smE_u, bias_s, remote_te);
     return;
   }
   if (split) {   // host restricts split outputs to NONE / RELU, fp16
-    if (act == B200SVS_ACT_RELU) epilogue_loop<B200SVS_ACT_RELU, RES, false, false, true>(p, bars, tmem_base, smE_u, bias_s);
-    else epilogue_loop<B200SVS_ACT_NONE, RES, false, false, true>(p, bars, tmem_base, smE_u, bias_s);
+    if (act == B200SVS_ACT_RELU) epilogue_loop<B200SVS_ACT_RELU, RES, false, false, true>(p, bars, tmem_base, smE_u, bias_s, remote_te);
+    else epilogue_loop<B200SVS_ACT_NONE, RES, false, false, true>(p, bars, tmem_base, smE_u, bias_s, remote_te);
     return;
   }
   switch (act) {
-    case B200SVS_ACT_GATE: epilogue_loop<B200SVS_ACT_GATE, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s); break;
-    case B200SVS_ACT_RELU: epilogue_loop<B200SVS_ACT_RELU, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s); break;
-    case B200SVS_ACT_GELU: epilogue_loop<B200SVS_ACT_GELU, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s); break;
-    case B200SVS_ACT_SIGMOID: epilogue_loop<B200SVS_ACT_SIGMOID, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s); break;
-    case B200SVS_ACT_TANH: epilogue_loop<B200SVS_ACT_TANH, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s); break;
+    case B200SVS_ACT_GATE: epilogue_loop<B200SVS_ACT_GATE, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s, remote_te); break;
+    case B200SVS_ACT_RELU: epilogue_loop<B200SVS_ACT_RELU, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s, remote_te); break;
+    case B200SVS_ACT_GELU: epilogue_loop<B200SVS_ACT_GELU, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s, remote_te); break;
+    case B200SVS_ACT_SIGMOID: epilogue_loop<B200SVS_ACT_SIGMOID, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s, remote_te); break;
+    case B200SVS_ACT_TANH: epilogue_loop<B200SVS_ACT_TANH, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s, remote_te); break;
     default:
-      if (RES == 0 && plain && p.epi_alt && p.lean16) epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, false, true, 1>(p, bars, tmem_base, smE_u, bias_s);
-      else if (RES == 0 && plain && p.epi_alt) epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, false, true>(p, bars, tmem_base, smE_u, bias_s);
-      else if (plain) epilogue_loop<B200SVS_ACT_NONE, RES, true, BF, false>(p, bars, tmem_base, smE_u, bias_s);
-      else epilogue_loop<B200SVS_ACT_NONE, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s);
+      if (RES == 0 && plain && p.epi_alt && p.lean16) epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, false, true, 1>(p, bars, tmem_base, smE_u, bias_s, remote_te);
+      else if (RES == 0 && plain && p.epi_alt) epilogue_loop<B200SVS_ACT_NONE, 0, true, BF, false, false, true>(p, bars, tmem_base, smE_u, bias_s, remote_te);
+      else if (plain) epilogue_loop<B200SVS_ACT_NONE, RES, true, BF, false>(p, bars, tmem_base, smE_u, bias_s, remote_te);
+      else epilogue_loop<B200SVS_ACT_NONE, RES, false, BF, false>(p, bars, tmem_base, smE_u, bias_s, remote_te);
       break;
   }
 }
+// remote_te: this CTA is the peer of a CTA pair - its epilogue frees the accumulator on the LEADER's tmem_empty barrier
 __device__ __forceinline__ void epilogue_dispatch(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
-                                                  uint32_t smE_u, uint32_t bias_s) {
+                                                  uint32_t smE_u, uint32_t bias_s, bool remote_te) {
   const b200svs_epilogue& ep = p.ep;
   const int res = (ep.res2 != nullptr && !ep.res2_is16) ? 2 : (ep.res1 != nullptr ? 1 : 0);   // a 16-bit res2 rides the R16 path
   const bool plain = ep.alpha == 1.0f && ep.scale == 1.0f && ep.lens == nullptr && ep.gbias == nullptr;
   const bool split = ep.out16 && ep.out16_dtype == B200SVS_DT_F16_SPLIT;
   const bool bf = ep.out16 && ep.out16_dtype == B200SVS_DT_BF16;
   if (res == 2) {
-    if (bf) epilogue_dispatch2<2, true>(p, bars, tmem_base, smE_u, bias_s, plain, split);
-    else epilogue_dispatch2<2, false>(p, bars, tmem_base, smE_u, bias_s, plain, split);
+    if (bf) epilogue_dispatch2<2, true>(p, bars, tmem_base, smE_u, bias_s, plain, split, remote_te);
+    else epilogue_dispatch2<2, false>(p, bars, tmem_base, smE_u, bias_s, plain, split, remote_te);
   } else if (res == 1) {
-    if (bf) epilogue_dispatch2<1, true>(p, bars, tmem_base, smE_u, bias_s, plain, split);
-    else epilogue_dispatch2<1, false>(p, bars, tmem_base, smE_u, bias_s, plain, split);
+    if (bf) epilogue_dispatch2<1, true>(p, bars, tmem_base, smE_u, bias_s, plain, split, remote_te);
+    else epilogue_dispatch2<1, false>(p, bars, tmem_base, smE_u, bias_s, plain, split, remote_te);
   } else {
-    if (bf) epilogue_dispatch2<0, true>(p, bars, tmem_base, smE_u, bias_s, plain, split);
-    else epilogue_dispatch2<0, false>(p, bars, tmem_base, smE_u, bias_s, plain, split);
+    if (bf) epilogue_dispatch2<0, true>(p, bars, tmem_base, smE_u, bias_s, plain, split, remote_te);
+    else epilogue_dispatch2<0, false>(p, bars, tmem_base, smE_u, bias_s, plain, split, remote_te);
   }
 }
 
 // The tcgen05.mma issue loop of one CTA, run by a single thread.  KSUB = K=16 steps per 64-channel chunk
 // (0: runtime p.ksub); MSUB = 128-row sub-tiles per tile.  Descriptor arithmetic is done on the 14-bit
 // (address >> 4) field directly: every operand tile lies below 256 KB, so the adds never carry out of it.
-template <int MSUB, int KSUB, bool WRES>
+template <int MSUB, int KSUB, bool WRES, bool PAIR = false>
 __device__ __forceinline__ void mma_issue_loop(const ConvTcParams& p, TcBarriers* bars, uint32_t tmem_base,
                                                uint32_t smA_u, uint32_t smW_u) {
   const uint64_t descA0 = make_desc_k128(smA_u), descW0 = make_desc_k128(smW_u);
@@ -670,29 +677,36 @@ __device__ __forceinline__ void mma_issue_loop(const ConvTcParams& p, TcBarriers
         const uint64_t db = descW0 + (WRES ? static_cast<uint32_t>(ch * p.ntaps + tap) : static_cast<uint32_t>(ws)) * w_stage_d;
 #pragma unroll
         for (int ms = 0; ms < MSUB; ++ms) {
-          umma_f16(d_tmem + ms * p.block_n, da + ms * kSubD, db, idesc, accum);
-          if (KSUB) {
+          if (PAIR) {
+            umma_f16_pair(d_tmem + ms * p.block_n, da + ms * kSubD, db, idesc, accum);
 #pragma unroll
-            for (int k = 1; k < KSUB; ++k) umma_f16(d_tmem + ms * p.block_n, da + ms * kSubD + 2 * k, db + 2 * k, idesc, 1u);
+            for (int k = 1; k < KSUB; ++k) umma_f16_pair(d_tmem + ms * p.block_n, da + ms * kSubD + 2 * k, db + 2 * k, idesc, 1u);
           } else {
-            for (int k = 1; k < ksub; ++k) umma_f16(d_tmem + ms * p.block_n, da + ms * kSubD + 2 * k, db + 2 * k, idesc, 1u);
+            umma_f16(d_tmem + ms * p.block_n, da + ms * kSubD, db, idesc, accum);
+            if (KSUB) {
+#pragma unroll
+              for (int k = 1; k < KSUB; ++k) umma_f16(d_tmem + ms * p.block_n, da + ms * kSubD + 2 * k, db + 2 * k, idesc, 1u);
+            } else {
+              for (int k = 1; k < ksub; ++k) umma_f16(d_tmem + ms * p.block_n, da + ms * kSubD + 2 * k, db + 2 * k, idesc, 1u);
+            }
           }
         }
         accum = 1;
         da += tap_d;
         if (!WRES) {
-          umma_commit(&bars->w_empty[ws]);
+          if (PAIR) umma_commit_pair(&bars->w_empty[ws]); else umma_commit(&bars->w_empty[ws]);
           if (++ws == p.w_stages) { ws = 0; wph ^= 1; }
         }
       }
-      umma_commit(&bars->a_empty[as]);
+      if (PAIR) umma_commit_pair(&bars->a_empty[as]); else umma_commit(&bars->a_empty[as]);
       if (++as == p.a_stages) { as = 0; aph ^= 1; }
     }
-    umma_commit(&bars->tmem_full[acc]);
+    if (PAIR) umma_commit_pair(&bars->tmem_full[acc]); else umma_commit(&bars->tmem_full[acc]);
     trace_stamp(p, it, 4, clock64());
   }
 }
 
+template <bool PAIR>
 __global__ void __launch_bounds__(kTcThreads, 1)
 conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                  const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmR2,
@@ -712,6 +726,11 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const b200svs_epilogue& ep = p.ep;
   const bool has_res1 = ep.res1 != nullptr;
   const bool has_res2 = ep.res2 != nullptr;
+  // PAIR is a separate kernel instantiation: a kernel that contains cta_group::2 instructions can only be launched
+  // as a cluster of two
+  constexpr bool pair = PAIR;
+  uint32_t crank = 0;                                       // 0: leader (issues the MMAs of the pair)
+  if constexpr (PAIR) crank = cluster_ctarank();
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
@@ -726,7 +745,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < p.a_stages; ++s) { mbar_init(&bars->a_full[s], 1); mbar_init(&bars->a_empty[s], 1); }
     for (int s = 0; s < (p.w_resident ? 1 : p.w_stages); ++s) { mbar_init(&bars->w_full[s], 1); mbar_init(&bars->w_empty[s], 1); }
-    for (int s = 0; s < kMaxAcc; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], kEpiThreads / 32); }
+    for (int s = 0; s < kMaxAcc; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], (pair ? 2 : 1) * (kEpiThreads / 32)); }
     for (int s = 0; s < p.n_slots; ++s) {
       mbar_init(&bars->e_full[s], 1); mbar_init(&bars->e_empty[s], 1);
       mbar_init(&bars->s_ready[s], p.epi_alt ? kEpiThreads / 64 : kEpiThreads / 32);
@@ -734,12 +753,13 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     fence_barrier_init();
   }
   if (warp == 2) {
-    tmem_alloc(&bars->tmem_base, p.tmem_cols);
-    tmem_relinquish();
+    if constexpr (PAIR) { tmem_alloc_pair(&bars->tmem_base, p.tmem_cols); tmem_relinquish_pair(); }
+    else { tmem_alloc(&bars->tmem_base, p.tmem_cols); tmem_relinquish(); }
   }
   for (int i = threadIdx.x; i < p.cout_pad; i += kTcThreads) bias_s[i] = p.ep.bias ? __ldg(p.ep.bias + i) : 0.0f;
   tc_fence_before();
-  __syncthreads();
+  if constexpr (PAIR) cluster_sync_all();      // the peer's barriers exist before anything of this CTA signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
   // Programmatic dependent launch: this CTA's setup (barriers, TMEM, bias, tensor-map prefetch, and below the
@@ -762,10 +782,17 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           mbar_wait(&bars->a_empty[as], aph ^ 1);
           if (ch == 0) trace_stamp(p, it, 0, clock64());
           uint8_t* sa = smA + as * p.a_stage_bytes;
-          mbar_arrive_expect_tx(&bars->a_full[as], a_tx);
-          for (int bx = 0; bx < p.a_boxes; ++bx)
-            tma_load_3d(sa + bx * p.a_box_rows * kRowBytes, &tmA, &bars->a_full[as], ch * kBlockK,
-                        tile_t0 - p.pad_left + bx * p.a_box_rows, ti.b);
+          if constexpr (PAIR) {          // both CTAs' bytes land on the leader's barrier
+            if (crank == 0) mbar_arrive_expect_tx(&bars->a_full[as], 2 * a_tx);
+            for (int bx = 0; bx < p.a_boxes; ++bx)
+              tma_load_3d_pair(sa + bx * p.a_box_rows * kRowBytes, &tmA, &bars->a_full[as], ch * kBlockK,
+                               tile_t0 - p.pad_left + bx * p.a_box_rows, ti.b);
+          } else {
+            mbar_arrive_expect_tx(&bars->a_full[as], a_tx);
+            for (int bx = 0; bx < p.a_boxes; ++bx)
+              tma_load_3d(sa + bx * p.a_box_rows * kRowBytes, &tmA, &bars->a_full[as], ch * kBlockK,
+                          tile_t0 - p.pad_left + bx * p.a_box_rows, ti.b);
+          }
           if (++as == p.a_stages) { as = 0; aph ^= 1; }
         }
       }
@@ -775,21 +802,30 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       // ------------------------------------------------------------ weight-ring TMA producer
       int ws = 0, it = 0;
       uint32_t wph = 0;
+      const int wrow0 = pair ? static_cast<int>(crank) * (p.block_n / 2) : 0;      // a pair's CTA holds half of every B tile
       if (p.w_resident) {        // the whole conv's weights (one N tile) fit: loaded once, never recycled
         const int ksteps = p.nchunks * p.ntaps;
-        mbar_arrive_expect_tx(&bars->w_full[0], static_cast<uint32_t>(ksteps) * p.w_stage_bytes);
+        if (!pair || crank == 0) mbar_arrive_expect_tx(&bars->w_full[0], static_cast<uint32_t>(ksteps) * p.w_stage_bytes * (pair ? 2 : 1));
         for (int ch = 0; ch < p.nchunks; ++ch)
-          for (int tap = 0; tap < p.ntaps; ++tap)
-            tma_load_2d(smW + (ch * p.ntaps + tap) * p.w_stage_bytes, &tmW, &bars->w_full[0], ch * kBlockK, tap * p.cout_pad);
+          for (int tap = 0; tap < p.ntaps; ++tap) {
+            if constexpr (PAIR) tma_load_2d_pair(smW + (ch * p.ntaps + tap) * p.w_stage_bytes, &tmW, &bars->w_full[0], ch * kBlockK, tap * p.cout_pad + wrow0);
+            else tma_load_2d(smW + (ch * p.ntaps + tap) * p.w_stage_bytes, &tmW, &bars->w_full[0], ch * kBlockK, tap * p.cout_pad);
+          }
       }
       for (TileIter ti(p); !p.w_resident && ti.valid(p); ti.next(p), ++it) {
         const int n_idx = ti.n_idx;
         for (int ch = 0; ch < p.nchunks; ++ch) {
           for (int tap = 0; tap < p.ntaps; ++tap) {
             mbar_wait(&bars->w_empty[ws], wph ^ 1);
-            mbar_arrive_expect_tx(&bars->w_full[ws], p.w_stage_bytes);
-            tma_load_2d(smW + ws * p.w_stage_bytes, &tmW, &bars->w_full[ws], ch * kBlockK,
-                        tap * p.cout_pad + n_idx * p.block_n);
+            if constexpr (PAIR) {
+              if (crank == 0) mbar_arrive_expect_tx(&bars->w_full[ws], 2 * p.w_stage_bytes);
+              tma_load_2d_pair(smW + ws * p.w_stage_bytes, &tmW, &bars->w_full[ws], ch * kBlockK,
+                               tap * p.cout_pad + n_idx * p.block_n + wrow0);
+            } else {
+              mbar_arrive_expect_tx(&bars->w_full[ws], p.w_stage_bytes);
+              tma_load_2d(smW + ws * p.w_stage_bytes, &tmW, &bars->w_full[ws], ch * kBlockK,
+                          tap * p.cout_pad + n_idx * p.block_n);
+            }
             if (++ws == p.w_stages) { ws = 0; wph ^= 1; }
           }
         }
@@ -800,7 +836,13 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // -------------------------------------------------------------- MMA issuer: one elected thread runs the
     // whole loop (descriptors stay in uniform registers; MSUB / KSUB are compile-time so a tap is a straight
     // run of UTCHMMAs with immediate descriptor offsets)
-    if (elect_one()) {
+    if constexpr (PAIR) {          // host: msub == 2, ksub == 4; only the leader issues
+      if (crank == 0 && elect_one()) {
+        const uint32_t smA_u = smem_u32(smA), smW_u = smem_u32(smW);
+        if (p.w_resident) mma_issue_loop<2, 4, true, true>(p, bars, tmem_base, smA_u, smW_u);
+        else mma_issue_loop<2, 4, false, true>(p, bars, tmem_base, smA_u, smW_u);
+      }
+    } else if (elect_one()) {
       const uint32_t smA_u = smem_u32(smA), smW_u = smem_u32(smW);
       if (p.w_resident) {
         if (p.msub == 2) {
@@ -901,14 +943,15 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp >= 4 && warp < 12) {
     griddep_wait();
-    epilogue_dispatch(p, bars, tmem_base, smem_u32(smE), smem_u32(bias_s));
+    epilogue_dispatch(p, bars, tmem_base, smem_u32(smE), smem_u32(bias_s), PAIR && crank != 0);
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (PAIR) cluster_sync_all();      // neither CTA may exit (or free TMEM) while the pair's MMAs can still touch it
+  else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, p.tmem_cols);
+    if constexpr (PAIR) tmem_dealloc_pair(tmem_base, p.tmem_cols); else tmem_dealloc(tmem_base, p.tmem_cols);
   }
 }
 
@@ -972,7 +1015,17 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   p.a_boxes = ra > 256 ? 2 : 1;
   p.a_box_rows = round_up_i((ra + p.a_boxes - 1) / p.a_boxes, 8);
   p.a_stage_bytes = p.a_boxes * p.a_box_rows * kRowBytes;
-  p.w_stage_bytes = a->block_n * kRowBytes;
+  {   // CTA pairs (cta_group::2) for single-N-tile N = 128 convs (the Generator's 128-channel stage): an N = 128 MMA
+      // reads 4 KB of A and 4 KB of B per 64 cycles - all of an SM's shared-memory bandwidth, 79 cycles measured with
+      // the weight ring's TMA writes next to it; a pair reads 4 KB + 2 KB per SM and halves the weight footprint
+    // Only for tensor-bound launches (>= pair_min K steps of 64 per tile: k >= 7 at 128 channels): measured -9..-15 %
+    // there, while the HBM-bound k = 3 launches lose 6-17 % to the lock step of the two CTAs.
+    static const int pair_on = [] { const char* e = getenv("B200SVS_TC_PAIR"); return e ? atoi(e) : 1; }();
+    static const int pair_min = [] { const char* e = getenv("B200SVS_TC_PAIR_MIN"); return e ? atoi(e) : 10; }();
+    p.pair = pair_on && n_tiles == 1 && a->block_n == 128 && p.msub == 2 && a->Cin >= kBlockK && !gate && !ep.lens && !ep.gbias &&
+             a->ntaps * ((a->Cin + kBlockK - 1) / kBlockK) >= pair_min && p.total_tiles >= 2 * num_sms() && num_sms() % 2 == 0;
+  }
+  p.w_stage_bytes = (p.pair ? a->block_n / 2 : a->block_n) * kRowBytes;
   const bool area32 = ep.res1 || ep.out32;
   const bool res2_f32 = ep.res2 && !ep.res2_is16, res2_h = ep.res2 && ep.res2_is16;
   p.slot_r2_off = res2_f32 ? (area32 ? kSlot32Bytes : 0) : 0;
@@ -1065,7 +1118,8 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     static unsigned launch_parity = 0;
     p.reverse = zig_on ? static_cast<int>(__atomic_fetch_add(&launch_parity, 1u, __ATOMIC_RELAXED) & 1u) : 0;
   }
-  p.idesc = make_idesc_f16(128, a->block_n, a->x_dtype == B200SVS_DT_BF16);
+  if (p.pair) p.reverse = 0;      // the phantom tile of an odd tile count is defined for the forward walk only
+  p.idesc = make_idesc_f16(p.pair ? 256 : 128, a->block_n, a->x_dtype == B200SVS_DT_BF16);
   p.ep = ep;
   p.trace = g_trace; p.trace_cap = g_trace_cap;
 
@@ -1081,7 +1135,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   {
     uint64_t dims[2] = {(uint64_t)a->Cin_pad, (uint64_t)a->ntaps * a->Cout_pad};
     uint64_t strides[1] = {(uint64_t)a->Cin_pad * 2};
-    uint32_t box[2] = {(uint32_t)kBlockK, (uint32_t)a->block_n};
+    uint32_t box[2] = {(uint32_t)kBlockK, (uint32_t)(p.pair ? a->block_n / 2 : a->block_n)};
     int r = make_tmap(&tmW, el16, a->w, 2, dims, strides, box, 128);
     if (r) return r;
   }
@@ -1127,12 +1181,13 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
 
   const size_t smem = (size_t)p.a_stages * p.a_stage_bytes + (size_t)p.w_stages * p.w_stage_bytes +
                       (size_t)p.n_slots * p.slot_bytes + 512 + bias_bytes + 1024;
-  static size_t configured = 0;
-  if (smem > configured) {
-    int r = check_cuda(cudaFuncSetAttribute(conv1d_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+  static size_t configured[2] = {0, 0};
+  if (smem > configured[p.pair ? 1 : 0]) {
+    int r = check_cuda(p.pair ? cudaFuncSetAttribute(conv1d_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                              : cudaFuncSetAttribute(conv1d_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                        "cudaFuncSetAttribute(conv1d_tc)");
     if (r) return r;
-    configured = smem;
+    configured[p.pair ? 1 : 0] = smem;
   }
   int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
   // launched with programmatic stream serialization (PDL): the kernel may start while its predecessor in the
@@ -1140,10 +1195,22 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   static const int pdl_on = [] { const char* e = getenv("B200SVS_PDL"); return e ? atoi(e) : 1; }();
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kTcThreads); cfg.dynamicSmemBytes = smem; cfg.stream = as_stream(stream);
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = attr; cfg.numAttrs = pdl_on ? 1 : 0;
-  return check_cuda(cudaLaunchKernelEx(&cfg, conv1d_tc_kernel, tmA, tmW, tmR, tmR2, tmO32, tmO16, tmR16, tmO16r, p),
+  cudaLaunchAttribute attr[2];
+  int n_attr = 0;
+  if (pdl_on) {
+    attr[n_attr].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n_attr].val.programmaticStreamSerializationAllowed = 1;
+    ++n_attr;
+  }
+  if (p.pair) {                   // grid == num_sms (even): clusters of two CTAs on the SM pair of one TPC
+    attr[n_attr].id = cudaLaunchAttributeClusterDimension;
+    attr[n_attr].val.clusterDim.x = 2; attr[n_attr].val.clusterDim.y = 1; attr[n_attr].val.clusterDim.z = 1;
+    ++n_attr;
+  }
+  cfg.attrs = attr; cfg.numAttrs = n_attr;
+  if (p.pair)
+    return check_cuda(cudaLaunchKernelEx(&cfg, conv1d_tc_kernel<true>, tmA, tmW, tmR, tmR2, tmO32, tmO16, tmR16, tmO16r, p),
+                      "conv1d_tc_kernel<pair> launch");
+  return check_cuda(cudaLaunchKernelEx(&cfg, conv1d_tc_kernel<false>, tmA, tmW, tmR, tmR2, tmO32, tmO16, tmR16, tmO16r, p),
                     "conv1d_tc_kernel launch");
 }
