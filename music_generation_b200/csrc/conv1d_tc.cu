@@ -836,11 +836,16 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // -------------------------------------------------------------- MMA issuer: one elected thread runs the
     // whole loop (descriptors stay in uniform registers; MSUB / KSUB are compile-time so a tap is a straight
     // run of UTCHMMAs with immediate descriptor offsets)
-    if constexpr (PAIR) {          // host: msub == 2, ksub == 4; only the leader issues
+    if constexpr (PAIR) {          // host: ksub == 4, msub == 2 (N = 128) or 1 (N = 256); only the leader issues
       if (crank == 0 && elect_one()) {
         const uint32_t smA_u = smem_u32(smA), smW_u = smem_u32(smW);
-        if (p.w_resident) mma_issue_loop<2, 4, true, true>(p, bars, tmem_base, smA_u, smW_u);
-        else mma_issue_loop<2, 4, false, true>(p, bars, tmem_base, smA_u, smW_u);
+        if (p.msub == 2) {
+          if (p.w_resident) mma_issue_loop<2, 4, true, true>(p, bars, tmem_base, smA_u, smW_u);
+          else mma_issue_loop<2, 4, false, true>(p, bars, tmem_base, smA_u, smW_u);
+        } else {
+          if (p.w_resident) mma_issue_loop<1, 4, true, true>(p, bars, tmem_base, smA_u, smW_u);
+          else mma_issue_loop<1, 4, false, true>(p, bars, tmem_base, smA_u, smW_u);
+        }
       }
     } else if (elect_one()) {
       const uint32_t smA_u = smem_u32(smA), smW_u = smem_u32(smW);
@@ -1022,7 +1027,9 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     // there, while the HBM-bound k = 3 launches lose 6-17 % to the lock step of the two CTAs.
     static const int pair_on = [] { const char* e = getenv("B200SVS_TC_PAIR"); return e ? atoi(e) : 1; }();
     static const int pair_min = [] { const char* e = getenv("B200SVS_TC_PAIR_MIN"); return e ? atoi(e) : 10; }();
-    p.pair = pair_on && n_tiles == 1 && a->block_n == 128 && p.msub == 2 && a->Cin >= kBlockK && !gate && !ep.lens && !ep.gbias &&
+    static const int pair256 = [] { const char* e = getenv("B200SVS_TC_PAIR256"); return e ? atoi(e) : 1; }();
+    const bool shape_ok = (a->block_n == 128 && p.msub == 2) || (pair256 && a->block_n == 256 && p.msub == 1);
+    p.pair = pair_on && n_tiles == 1 && shape_ok && a->Cin >= kBlockK && !gate && !ep.lens && !ep.gbias &&
              a->ntaps * ((a->Cin + kBlockK - 1) / kBlockK) >= pair_min && p.total_tiles >= 2 * num_sms() && num_sms() % 2 == 0;
   }
   p.w_stage_bytes = (p.pair ? a->block_n / 2 : a->block_n) * kRowBytes;

@@ -15,7 +15,8 @@ if sys.argv[1] == "cmp":
 
 from music_generation_b200 import ops, packer
 DEV = "cuda"
-B, T, C = 5, 104000 + 77, 128       # odd tile count, ragged tail
+C = int(os.environ.get("PC_C", "128"))
+B, T = 5, (104000 + 77) * 128 // C       # odd tile count, ragged tail
 res = {}
 for k, dil, mode in ((3, 1, "c"), (7, 3, "c"), (11, 5, "c"), (3, 1, "a"), (7, 1, "a"), (11, 1, "a")):
     g = torch.Generator().manual_seed(k)
