@@ -23,6 +23,10 @@
 //   warps 4..11   : epilogue; warp w and w+4 share a TMEM lane quadrant and split each 32-column chunk 16/16
 //   warp 12 lane 0: TMA producer of the weight ring
 //
+// CTA pairs (conv1d_tc_kernel<true>): for tensor-bound single-N-tile convs two CTAs of a cluster run the same roles on
+// adjacent tiles while the leader's MMA thread issues tcgen05.mma.cta_group::2 (M = 256) over both CTAs' activation
+// rows and weight-tile halves; see the PAIR branches and DESIGN.md 4.1.
+//
 // Replaces: nn.Conv1d/ConvTranspose1d + surrounding pointwise ops of the reference
 // (VISinger/models_ae.py:327-346, modules.py:148-176,210-223,329-349, attentions.py:138-146,277-285).
 #include <cstdlib>
