@@ -29,8 +29,14 @@ for name, v in sorted(per.items(), key=lambda x: -x[1]["gpu__time_duration.sum"]
 open(out_md, "w").write(f"# ncu launch summary - {workload}\n\nSource: `{src}` (ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,"
                         f"dram__bytes_write.sum --clock-control none; per-launch times are serialised and cold-cache, compare shares).\n\n"
                         + "\n".join(lines) + f"\n\nTotal kernel time {tot_t / 1e3:.2f} ms.\n")
-c = per["conv1d_tc_kernel"]
-n = len(ids["conv1d_tc_kernel"])
+# both instantiations of the conv kernel (<0> single CTA, <1> CTA pairs)
+c = defaultdict(float)
+n = 0
+for name in per:
+    if name.startswith("conv1d_tc_kernel"):
+        n += len(ids[name])
+        for m_, v_ in per[name].items():
+            c[m_] += v_
 json.dump({"workload": workload, "launches": n,
            "dram_bytes_per_launch": (c["dram__bytes_read.sum"] + c["dram__bytes_write.sum"]) / max(n, 1),
            "dram_read_bytes": c["dram__bytes_read.sum"], "dram_write_bytes": c["dram__bytes_write.sum"],
