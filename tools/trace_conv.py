@@ -86,6 +86,8 @@ if len(_s.argv) > 1 and _s.argv[1] == 'gap':
     cfgs = [(32, 11, 1, False), (64, 7, 1, False), (128, 11, 1, False), (32, 3, 1, False)]
 if len(_s.argv) > 1 and _s.argv[1] == 'act':
     cfgs = [(128, 3, 1, False), (128, 3, 1, 3), (64, 3, 1, False), (64, 3, 1, 3), (32, 3, 1, False, None, True), (32, 3, 1, 3, None, True)]
+if len(_s.argv) > 1 and _s.argv[1] == 'pair':
+    cfgs = [(128, 11, 1, False), (128, 7, 1, False), (128, 11, 1, 3)]
 if COMPACT:
     cfgs = [(C, k, 1, r) for C in (128, 64, 32) for k in (3, 7, 11) for r in (False, 2)]
 for cfg in cfgs or [(128, 3, 1, False), (128, 3, 1, True), (128, 11, 5, False), (64, 3, 1, False), (64, 7, 3, True), (32, 3, 1, False), (32, 11, 5, False), (32, 7, 1, True), (256, 3, 1, False)]:
