@@ -1032,9 +1032,19 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     static const int pair_on = [] { const char* e = getenv("B200SVS_TC_PAIR"); return e ? atoi(e) : 1; }();
     static const int pair_min = [] { const char* e = getenv("B200SVS_TC_PAIR_MIN"); return e ? atoi(e) : 10; }();
     static const int pair256 = [] { const char* e = getenv("B200SVS_TC_PAIR256"); return e ? atoi(e) : 1; }();
-    const bool shape_ok = (a->block_n == 128 && p.msub == 2) || (pair256 && a->block_n == 256 && p.msub == 1);
-    p.pair = pair_on && n_tiles == 1 && shape_ok && a->Cin >= kBlockK && !gate && !ep.lens && !ep.gbias &&
-             a->ntaps * ((a->Cin + kBlockK - 1) / kBlockK) >= pair_min && p.total_tiles >= 2 * num_sms() && num_sms() % 2 == 0;
+    static const int pair_any = [] { const char* e = getenv("B200SVS_TC_PAIR_ANY"); return e ? atoi(e) : 1; }();
+    static const int pair_tiles = [] { const char* e = getenv("B200SVS_TC_PAIR_TILES"); return e ? atoi(e) : 0; }();   // tests: pair small launches too
+    // generator shapes: one N tile of 128 (256-row tiles) or 256; pair_any: every other wide shape whose pairs never
+    // straddle two N tiles (m_tiles even) - the WN gate convs (N = 192 x 2: the weight ring re-streamed per 128-row tile
+    // is what bounds them, a pair loads half of it per SM), the encoders' FFN / projection convs
+    const bool gen_shape = n_tiles == 1 && ((a->block_n == 128 && p.msub == 2) || (pair256 && a->block_n == 256 && p.msub == 1));
+    const bool any_shape = pair_any && a->block_n >= 128 && a->block_n % 32 == 0 && (n_tiles == 1 || p.m_tiles % 2 == 0);
+    // a phantom tile (odd tile count) must not index lens / gbias
+    const bool phantom_ok = p.total_tiles % 2 == 0 || (!ep.lens && !ep.gbias);
+    const int min_tiles = pair_tiles > 0 ? pair_tiles : 2 * num_sms();
+    p.pair = pair_on && (gen_shape || any_shape) && phantom_ok && a->Cin >= kBlockK && a->Cin % kBlockK == 0 &&
+             a->ntaps * ((a->Cin + kBlockK - 1) / kBlockK) >= pair_min && p.total_tiles >= min_tiles && p.total_tiles >= 2 &&
+             num_sms() % 2 == 0;
   }
   p.w_stage_bytes = (p.pair ? a->block_n / 2 : a->block_n) * kRowBytes;
   const bool area32 = ep.res1 || ep.out32;
@@ -1201,6 +1211,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     configured[p.pair ? 1 : 0] = smem;
   }
   int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
+  if (p.pair) grid = (grid + 1) & ~1;      // whole clusters; a CTA without a tile of its own runs the phantom
   // launched with programmatic stream serialization (PDL): the kernel may start while its predecessor in the
   // stream drains; it orders itself with griddepcontrol.wait (B200SVS_PDL=0 restores full serialization)
   static const int pdl_on = [] { const char* e = getenv("B200SVS_PDL"); return e ? atoi(e) : 1; }();
