@@ -61,6 +61,8 @@ struct ConvTcParams {
   int epi_alt;                             // epilogue warp pairs take alternate chunks (32 columns each)
   int pair;                                // CTA pairs (cluster of 2, tcgen05 cta_group::2): M = 256 MMAs, each CTA holds half of B
   int reverse;                             // walk the tiles from the last one down (L2 reuse across back-to-back launches)
+  int cw;                                  // 32-column units per epilogue chunk: 2 = [128 x 64] 16-bit chunks (128-byte rows, one
+                                           // slot wait / fence / arrive / TMA store per 64 columns); residual-free lean launches only
   int lean16;                              // process_o16 variant: 1 res16 -> out16 (or conv1: no residual), 2 res16 -> out16r,
                                            // 3 res16 + 16-bit res2 -> out16r, 4 res16 + 16-bit res2 -> scaled out16; 0: generic
   int xpre;                                // epilogue prefetches the next tile's first TMEM chunk
@@ -360,7 +362,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
   };
 
   // OUTS == 1: v = acc + bias [+ unlrelu(res16)]; out16 = cvt16(lrelu(v)).  16 columns of one row.
-  auto process_o16 = [&](const uint32_t* a0, uint32_t slot_u, int pcol, int h) {
+  auto process_o16 = [&](const uint32_t* a0, uint32_t slot_u, int pcol, int h, const uint32_t* o16) {
     const uint32_t ba = bias_u + pcol * 4;
     float2 v2[8];
 #pragma unroll
@@ -423,13 +425,23 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
         const float2 m = mul2(v2[i], slope2);
         p16[i] = pack2<BF>(fmaxf(v2[i].x, m.x), fmaxf(v2[i].y, m.y));
       }
-      sts128u(slot_u + off16[h][0], p16[0], p16[1], p16[2], p16[3]);
-      sts128u(slot_u + off16[h][1], p16[4], p16[5], p16[6], p16[7]);
+      sts128u(slot_u + o16[0], p16[0], p16[1], p16[2], p16[3]);
+      sts128u(slot_u + o16[1], p16[4], p16[5], p16[6], p16[7]);
     }
   };
 
   if constexpr (ALT) {                 // n_chunks is even (host): this warp's chunks are grp, grp + 2, ...
     const int grp = half;
+    const int cw = p.cw, ccols = kEpiCols * cw;
+    // wide chunks (cw == 2): the slot is [128 rows][64 x 16-bit] = 128-byte rows, SWIZZLE_128B; 32-column unit j of the
+    // chunk fills cells 4j .. 4j+3 of a row
+    uint32_t offw[2][NH][2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+      for (int h = 0; h < NH; ++h)
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) offw[j][h][jj] = p.slot16_off + row * 128 + (((j * 4 + h * 2 + jj) ^ (row & 7)) << 4);
     int it = 0, sl = grp;
     uint32_t eph = 0;
     const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
@@ -444,8 +456,8 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
       if (!pre) {
         mbar_wait(&bars->tmem_full[acc], (it >> acc_shift) & 1);
         tc_fence_after();
-        tmem_ld16_nowait(taddr + grp * kEpiCols, ra);
-        tmem_ld16_nowait(taddr + grp * kEpiCols + 16, ra + 16);
+        tmem_ld16_nowait(taddr + grp * ccols, ra);
+        tmem_ld16_nowait(taddr + grp * ccols + 16, ra + 16);
       }
       pre = false;
       if (threadIdx.x == 128) trace_stamp(p, it, 5, clock64());
@@ -455,29 +467,35 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
         const int tsub = tile_t0 + ms * 128;
         const float s = tsub + row < len_b ? ep.scale : 0.0f;
         mbar_wait(&bars->e_full[sl], eph);
-        tmem_ld_wait16(ra);
-        tmem_ld_wait16(ra + 16);
-        if (tsub < p.T) {
-          const uint32_t slot_u = smE_u + sl * slot_bytes;
-          if constexpr (OUTS != 0) {
-            process_o16(ra, slot_u, pcol0 + ch * kEpiCols, 0);
-            process_o16(ra + 16, slot_u, pcol0 + ch * kEpiCols + 16, 1);
-          } else {
-            process(ra, ra, slot_u, pcol0 + ch * kEpiCols, tile_b, s, 0);
-            process(ra + 16, ra, slot_u, pcol0 + ch * kEpiCols + 16, tile_b, s, 1);
+        const uint32_t slot_u = smE_u + sl * slot_bytes;
+        for (int j = 0; j < cw; ++j) {
+          tmem_ld_wait16(ra);
+          tmem_ld_wait16(ra + 16);
+          if (tsub < p.T) {
+            const int pc = pcol0 + ch * ccols + j * kEpiCols;
+            if constexpr (OUTS != 0) {
+              process_o16(ra, slot_u, pc, 0, cw == 2 ? offw[j][0] : off16[0]);
+              process_o16(ra + 16, slot_u, pc + 16, 1, cw == 2 ? offw[j][NH - 1] : off16[NH - 1]);
+            } else {
+              process(ra, ra, slot_u, pc, tile_b, s, 0);
+              process(ra + 16, ra, slot_u, pc + 16, tile_b, s, 1);
+            }
           }
-        }
-        // the accumulators of this warp's next chunk are fetched under the fence / barrier traffic below
-        if (ci + 2 < n_chunks) {
-          tmem_ld16_nowait(taddr + (ci + 2) * kEpiCols, ra);
-          tmem_ld16_nowait(taddr + (ci + 2) * kEpiCols + 16, ra + 16);
-        } else if (p.xpre && ti.has_next(p) &&
-                   mbar_test(&bars->tmem_full[(it + 1) & acc_mask], ((it + 1) >> acc_shift) & 1)) {
-          tc_fence_after();
-          const uint32_t tn = taddr0 + ((it + 1) & acc_mask) * acc_cols + grp * kEpiCols;
-          tmem_ld16_nowait(tn, ra);
-          tmem_ld16_nowait(tn + 16, ra + 16);
-          pre = true;
+          // the accumulators of this warp's next 32 columns are fetched under the arithmetic / fence / barrier traffic
+          if (j + 1 < cw) {
+            tmem_ld16_nowait(taddr + ci * ccols + (j + 1) * kEpiCols, ra);
+            tmem_ld16_nowait(taddr + ci * ccols + (j + 1) * kEpiCols + 16, ra + 16);
+          } else if (ci + 2 < n_chunks) {
+            tmem_ld16_nowait(taddr + (ci + 2) * ccols, ra);
+            tmem_ld16_nowait(taddr + (ci + 2) * ccols + 16, ra + 16);
+          } else if (p.xpre && ti.has_next(p) &&
+                     mbar_test(&bars->tmem_full[(it + 1) & acc_mask], ((it + 1) >> acc_shift) & 1)) {
+            tc_fence_after();
+            const uint32_t tn = taddr0 + ((it + 1) & acc_mask) * acc_cols + grp * ccols;
+            tmem_ld16_nowait(tn, ra);
+            tmem_ld16_nowait(tn + 16, ra + 16);
+            pre = true;
+          }
         }
         fence_proxy_async();             // generic-proxy smem writes -> visible to the TMA store
         __syncwarp();
@@ -517,7 +535,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
       const float s = tsub + row < len_b ? ep.scale : 0.0f;
       mbar_wait(&bars->e_full[sl], eph);
       if (tsub < p.T) {
-        if constexpr (OUTS != 0) process_o16(r0, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, 0);
+        if constexpr (OUTS != 0) process_o16(r0, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, 0, off16[0]);
         else process(r0, r1, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, tile_b, s, 0);
       }
       fence_proxy_async();             // generic-proxy smem writes -> visible to the TMA store
@@ -890,7 +908,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_wait(&bars->s_ready[sl], sph);
             if (ms == 0 && ch == 0) trace_stamp(p, it, 8, clock64());
             if (tsub < p.T) {
-              const int ocol = tc.n_idx * p.n_out_tile + ch * kEpiCols;
+              const int ocol = tc.n_idx * p.n_out_tile + ch * kEpiCols * p.cw;
               uint8_t* slot = smE + sl * p.slot_bytes;
               if (ep.out32) tma_store_3d(&tmO32, slot, ocol, tsub, tc.b);
               if (ep.out16) tma_store_3d(&tmO16, slot + p.slot16_off, ocol, tsub, tc.b);
@@ -936,7 +954,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           for (int c = 0; c < p.chunks_per_sub; ++c) {
             mbar_wait(&bars->e_empty[sl], eph ^ 1);
             if ((has_res1 || has_res2 || ep.res16) && t < p.T) {
-              const int col = tc.n_idx * p.n_out_tile + c * kEpiCols;
+              const int col = tc.n_idx * p.n_out_tile + c * kEpiCols * p.cw;
               mbar_arrive_expect_tx(&bars->e_full[sl], (has_res1 ? kSlot32Bytes : 0) + (has_res2 ? (ep.res2_is16 ? kSlot16Bytes : kSlot32Bytes) : 0) +
                                                            (ep.res16 ? kSlot16Bytes : 0));
               if (ep.res16) tma_load_3d(smE + sl * p.slot_bytes + p.slot_raw_off, &tmR16, &bars->e_full[sl], col, t, tc.b);
@@ -1046,6 +1064,20 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
              a->ntaps * ((a->Cin + kBlockK - 1) / kBlockK) >= pair_min && p.total_tiles >= min_tiles && p.total_tiles >= 2 &&
              num_sms() % 2 == 0;
   }
+  {   // 64-column epilogue chunks for the residual-free launches whose only output is the activated 16-bit tensor (the
+      // Generator's conv1 / ConvTranspose launches): a chunk is a latency chain (slot wait, TMEM load, proxy fence,
+      // barrier arrive, store hand-off) of ~600-680 cycles whatever its width; [128 x 64] 16-bit chunks are one
+      // 128-byte-row TMA box and halve the number of chains per byte (k=3 conv1 at 64 channels: 52.6 -> 42.4 us = 6.3 TB/s).
+      // Needs the alternate-chunk lean epilogue; not for CTA pairs (tensor-bound, measured +10 % there).
+    static const int wide_on = [] { const char* e = getenv("B200SVS_TC_WIDE16"); return e ? atoi(e) : 1; }();
+    static const int alt_on0 = [] { const char* e = getenv("B200SVS_TC_ALT"); return e ? atoi(e) : 1; }();
+    static const int lean_on0 = [] { const char* e = getenv("B200SVS_TC_LEAN"); return e ? atoi(e) : 1; }();
+    const bool plain0 = ep.alpha == 1.0f && ep.scale == 1.0f && ep.lens == nullptr && ep.gbias == nullptr;
+    p.cw = (wide_on && alt_on0 && lean_on0 && plain0 && !gate && ep.act == B200SVS_ACT_NONE && ep.out16 &&
+            ep.out16_dtype != B200SVS_DT_F16_SPLIT && !ep.out32 && !ep.out16r && !ep.res1 && !ep.res2 && !ep.res16 &&
+            n_out_tile % 64 == 0 && (p.msub * (n_out_tile / 64)) % 2 == 0 && !p.pair) ? 2 : 1;
+    p.chunks_per_sub = n_out_tile / (kEpiCols * p.cw);
+  }
   p.w_stage_bytes = (p.pair ? a->block_n / 2 : a->block_n) * kRowBytes;
   const bool area32 = ep.res1 || ep.out32;
   const bool res2_f32 = ep.res2 && !ep.res2_is16, res2_h = ep.res2 && ep.res2_is16;
@@ -1059,7 +1091,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
                   "conv1d_tc: res16 / out16r / 16-bit res2 need act NONE, a non-split output and no fp32 res1");
   B200SVS_REQUIRE(!ep.res16 || (ep.res16_ld % 8 == 0 && (reinterpret_cast<uintptr_t>(ep.res16) & 15) == 0), "conv1d_tc: res16 alignment");
   B200SVS_REQUIRE(!ep.out16r || (ep.out16r_ld % 8 == 0 && (reinterpret_cast<uintptr_t>(ep.out16r) & 15) == 0), "conv1d_tc: out16r alignment");
-  p.slot_raw_off = p.slot16_off + (ep.out16 ? kSlot16Bytes : 0) + (split16 ? kSlot16Bytes : 0);
+  p.slot_raw_off = p.slot16_off + (ep.out16 ? kSlot16Bytes * p.cw : 0) + (split16 ? kSlot16Bytes : 0);
   p.slot_bytes = p.slot_raw_off + ((ep.res16 || ep.out16r) ? kSlot16Bytes : 0);
   if (res2_h) { p.slot_r2_off = p.slot_bytes; p.slot_bytes += kSlot16Bytes; }     // 16-bit res2 tile: its own area
   // shared memory: 2 activation stages, >= 3 weight stages (or all k-steps of a tile if fewer), then as many
@@ -1139,6 +1171,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     static unsigned launch_parity = 0;
     p.reverse = zig_on ? static_cast<int>(__atomic_fetch_add(&launch_parity, 1u, __ATOMIC_RELAXED) & 1u) : 0;
   }
+  B200SVS_REQUIRE(p.cw == 1 || (p.epi_alt && p.lean16 == 1), "conv1d_tc: internal: wide chunks without the lean alternate-chunk epilogue");
   if (p.pair) p.reverse = 0;      // the phantom tile of an odd tile count is defined for the forward walk only
   p.idesc = make_idesc_f16(p.pair ? 256 : 128, a->block_n, a->x_dtype == B200SVS_DT_BF16);
   p.ep = ep;
@@ -1185,7 +1218,8 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   if (ep.out16) {
     uint64_t strides[2] = {(uint64_t)ep.out16_ld * 2, (uint64_t)a->T * ep.out16_ld * 2};
     uint64_t odims[3] = {(uint64_t)ep.n_valid * (ep.out16_dtype == B200SVS_DT_F16_SPLIT ? 3 : 1), (uint64_t)a->T, (uint64_t)a->B};
-    int r = make_tmap(&tmO16, ep.out16_dtype == B200SVS_DT_BF16 ? 1 : 0, ep.out16, 3, odims, strides, ebox, 64);
+    const uint32_t obox[3] = {(uint32_t)(kEpiCols * p.cw), 128, 1};
+    int r = make_tmap(&tmO16, ep.out16_dtype == B200SVS_DT_BF16 ? 1 : 0, ep.out16, 3, odims, strides, obox, p.cw == 2 ? 128 : 64);
     if (r) return r;
   }
 
