@@ -375,7 +375,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
       const float2 rinv2 = make_float2(rinv, rinv);
 #pragma unroll
       for (int jj = 0; jj < 2; ++jj) {
-        const float4 q = lds128(slot_u + raw_delta + off16[h][jj]);
+        const float4 q = lds128(slot_u + raw_delta + o16[jj]);
         const uint32_t u[4] = {__float_as_uint(q.x), __float_as_uint(q.y), __float_as_uint(q.z), __float_as_uint(q.w)};
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -393,7 +393,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
     if constexpr (R2H) {       // + the 16-bit MRF sum so far
 #pragma unroll
       for (int jj = 0; jj < 2; ++jj) {
-        const float4 q = lds128(slot_u + r2h_delta + off16[h][jj]);
+        const float4 q = lds128(slot_u + r2h_delta + o16[jj]);
         const uint32_t u[4] = {__float_as_uint(q.x), __float_as_uint(q.y), __float_as_uint(q.z), __float_as_uint(q.w)};
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -416,8 +416,8 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
     if constexpr (OUTS == 2) {   // un-activated 16-bit result (out16r area of the slot)
 #pragma unroll
       for (int i = 0; i < 8; ++i) p16[i] = pack2<BF>(v2[i].x, v2[i].y);
-      sts128u(slot_u + raw_delta + off16[h][0], p16[0], p16[1], p16[2], p16[3]);
-      sts128u(slot_u + raw_delta + off16[h][1], p16[4], p16[5], p16[6], p16[7]);
+      sts128u(slot_u + raw_delta + o16[0], p16[0], p16[1], p16[2], p16[3]);
+      sts128u(slot_u + raw_delta + o16[1], p16[4], p16[5], p16[6], p16[7]);
     } else {
       const float2 slope2 = make_float2(slope, slope);
 #pragma unroll
@@ -511,6 +511,14 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
     return;
   }
 
+  // non-ALT: both warps of a pair work on every 32-column unit (16 columns each); with wide chunks (cw == 2, lean
+  // launches only) two units share one staging slot of 128-byte rows and one wait / fence / arrive / store
+  const int cwn = p.cw, cps32 = cps * cwn, n_units = p.msub * cps32;
+  uint32_t offn[2][2];                 // [unit j of the wide chunk][jj]: this thread's 16-byte cells, 128-byte rows
+#pragma unroll
+  for (int j = 0; j < 2; ++j)
+#pragma unroll
+    for (int jj = 0; jj < 2; ++jj) offn[j][jj] = p.slot16_off + row * 128 + (((j * 4 + half * 2 + jj) ^ (row & 7)) << 4);
   int it = 0, sl = 0;
   uint32_t eph = 0;
   const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + half * 16;
@@ -528,20 +536,23 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
     if (threadIdx.x == 128) trace_stamp(p, it, 5, clock64());
     const uint32_t taddr = taddr0 + acc * acc_cols;
     // chunk ci: sub-tile ms = ci / cps, column chunk ch = ci % cps (msub <= 2)
-    auto finish = [&](int ci, const uint32_t* r0, const uint32_t* r1) {
-      const int ms = ci >= cps ? 1 : 0;
-      const int ch = ci - (ms ? cps : 0);
+    auto finish = [&](int ci, const uint32_t* r0, const uint32_t* r1) {      // ci: 32-column unit of the tile
+      const int ms = ci >= cps32 ? 1 : 0;
+      const int ch = ci - (ms ? cps32 : 0);
+      const int j = cwn == 2 ? (ch & 1) : 0;
       const int tsub = tile_t0 + ms * 128;
       const float s = tsub + row < len_b ? ep.scale : 0.0f;
-      mbar_wait(&bars->e_full[sl], eph);
+      if (j == 0) mbar_wait(&bars->e_full[sl], eph);
       if (tsub < p.T) {
-        if constexpr (OUTS != 0) process_o16(r0, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, 0, off16[0]);
+        if constexpr (OUTS != 0) process_o16(r0, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, 0, cwn == 2 ? offn[j] : off16[0]);
         else process(r0, r1, smE_u + sl * slot_bytes, pcol0 + ch * kEpiCols, tile_b, s, 0);
       }
-      fence_proxy_async();             // generic-proxy smem writes -> visible to the TMA store
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bars->s_ready[sl]);
-      if (++sl == n_slots) { sl = 0; eph ^= 1; }
+      if (j == cwn - 1) {
+        fence_proxy_async();             // generic-proxy smem writes -> visible to the TMA store
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->s_ready[sl]);
+        if (++sl == n_slots) { sl = 0; eph ^= 1; }
+      }
     };
     if constexpr (GATE) {              // two accumulator halves per chunk: no register room for a prefetch
       for (int ci = 0; ci < n_chunks; ++ci) {
@@ -556,13 +567,13 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
     } else {                           // block_n == cps * 32: chunk ci sits at TMEM column ci * 32
       if (!pre) tmem_ld16_nowait(taddr, ra0);
       pre = false;
-      for (int ci = 0; ci < n_chunks; ci += 2) {
+      for (int ci = 0; ci < n_units; ci += 2) {
         tmem_ld_wait16(ra0);
-        if (ci + 1 < n_chunks) tmem_ld16_nowait(taddr + (ci + 1) * kEpiCols, rb0);
+        if (ci + 1 < n_units) tmem_ld16_nowait(taddr + (ci + 1) * kEpiCols, rb0);
         finish(ci, ra0, ra1);
-        if (ci + 1 < n_chunks) {
+        if (ci + 1 < n_units) {
           tmem_ld_wait16(rb0);
-          if (ci + 2 < n_chunks) {
+          if (ci + 2 < n_units) {
             tmem_ld16_nowait(taddr + (ci + 2) * kEpiCols, ra0);
           } else if (p.xpre && ti.has_next(p) &&
                      mbar_test(&bars->tmem_full[(it + 1) & acc_mask], ((it + 1) >> acc_shift) & 1)) {
@@ -955,8 +966,8 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_wait(&bars->e_empty[sl], eph ^ 1);
             if ((has_res1 || has_res2 || ep.res16) && t < p.T) {
               const int col = tc.n_idx * p.n_out_tile + c * kEpiCols * p.cw;
-              mbar_arrive_expect_tx(&bars->e_full[sl], (has_res1 ? kSlot32Bytes : 0) + (has_res2 ? (ep.res2_is16 ? kSlot16Bytes : kSlot32Bytes) : 0) +
-                                                           (ep.res16 ? kSlot16Bytes : 0));
+              mbar_arrive_expect_tx(&bars->e_full[sl], (has_res1 ? kSlot32Bytes : 0) + (has_res2 ? (ep.res2_is16 ? kSlot16Bytes * p.cw : kSlot32Bytes) : 0) +
+                                                           (ep.res16 ? kSlot16Bytes * p.cw : 0));
               if (ep.res16) tma_load_3d(smE + sl * p.slot_bytes + p.slot_raw_off, &tmR16, &bars->e_full[sl], col, t, tc.b);
               if (has_res1) tma_load_3d(smE + sl * p.slot_bytes, &tmR, &bars->e_full[sl], col, t, tc.b);
               if (has_res2) tma_load_3d(smE + sl * p.slot_bytes + p.slot_r2_off, &tmR2, &bars->e_full[sl], col, t, tc.b);
@@ -1070,12 +1081,22 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
       // 128-byte-row TMA box and halve the number of chains per byte (k=3 conv1 at 64 channels: 52.6 -> 42.4 us = 6.3 TB/s).
       // Needs the alternate-chunk lean epilogue; not for CTA pairs (tensor-bound, measured +10 % there).
     static const int wide_on = [] { const char* e = getenv("B200SVS_TC_WIDE16"); return e ? atoi(e) : 1; }();
+    static const int wide_res = [] { const char* e = getenv("B200SVS_TC_WIDE16_RES"); return e ? atoi(e) : 0; }();
     static const int alt_on0 = [] { const char* e = getenv("B200SVS_TC_ALT"); return e ? atoi(e) : 1; }();
     static const int lean_on0 = [] { const char* e = getenv("B200SVS_TC_LEAN"); return e ? atoi(e) : 1; }();
-    const bool plain0 = ep.alpha == 1.0f && ep.scale == 1.0f && ep.lens == nullptr && ep.gbias == nullptr;
-    p.cw = (wide_on && alt_on0 && lean_on0 && plain0 && !gate && ep.act == B200SVS_ACT_NONE && ep.out16 &&
-            ep.out16_dtype != B200SVS_DT_F16_SPLIT && !ep.out32 && !ep.out16r && !ep.res1 && !ep.res2 && !ep.res16 &&
-            n_out_tile % 64 == 0 && (p.msub * (n_out_tile / 64)) % 2 == 0 && !p.pair) ? 2 : 1;
+    const bool base0 = wide_on && lean_on0 && !p.pair && !gate && ep.act == B200SVS_ACT_NONE && ep.alpha == 1.0f && !ep.lens &&
+                       !ep.gbias && !(ep.out16 && ep.out16_dtype == B200SVS_DT_F16_SPLIT) && !ep.out32 && !ep.res1 &&
+                       !(ep.res2 && !ep.res2_is16) && n_out_tile % 64 == 0;
+    bool wide = false;
+    if (base0 && !ep.res16) {          // conv1 / ConvTranspose: alternate-chunk lean epilogue
+      wide = alt_on0 && ep.scale == 1.0f && ep.out16 && !ep.out16r && !ep.res2 && (p.msub * (n_out_tile / 64)) % 2 == 0;
+    } else if (base0 && wide_res) {    // conv2: the lean16 variants 1-4 (residual staged by TMA, both warps of a pair per unit).
+      // Off by default: measured slower (C=64 k=7 75.5 -> 92.8 us, k=11 97.2 -> 127.0 us; k=3 unchanged) - the 32 KB
+      // slots cost the resident weights / slot depth that these launches live on.
+      wide = (ep.scale == 1.0f && ep.out16 && !ep.out16r && !ep.res2) || (ep.scale == 1.0f && ep.out16r && !ep.out16) ||
+             (ep.res2 && ep.out16 && !ep.out16r);
+    }
+    p.cw = wide ? 2 : 1;
     p.chunks_per_sub = n_out_tile / (kEpiCols * p.cw);
   }
   p.w_stage_bytes = (p.pair ? a->block_n / 2 : a->block_n) * kRowBytes;
@@ -1092,8 +1113,8 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   B200SVS_REQUIRE(!ep.res16 || (ep.res16_ld % 8 == 0 && (reinterpret_cast<uintptr_t>(ep.res16) & 15) == 0), "conv1d_tc: res16 alignment");
   B200SVS_REQUIRE(!ep.out16r || (ep.out16r_ld % 8 == 0 && (reinterpret_cast<uintptr_t>(ep.out16r) & 15) == 0), "conv1d_tc: out16r alignment");
   p.slot_raw_off = p.slot16_off + (ep.out16 ? kSlot16Bytes * p.cw : 0) + (split16 ? kSlot16Bytes : 0);
-  p.slot_bytes = p.slot_raw_off + ((ep.res16 || ep.out16r) ? kSlot16Bytes : 0);
-  if (res2_h) { p.slot_r2_off = p.slot_bytes; p.slot_bytes += kSlot16Bytes; }     // 16-bit res2 tile: its own area
+  p.slot_bytes = p.slot_raw_off + ((ep.res16 || ep.out16r) ? kSlot16Bytes * p.cw : 0);
+  if (res2_h) { p.slot_r2_off = p.slot_bytes; p.slot_bytes += kSlot16Bytes * p.cw; }     // 16-bit res2 tile: its own area
   // shared memory: 2 activation stages, >= 3 weight stages (or all k-steps of a tile if fewer), then as many
   // staging slots as fit (stores in flight + residual prefetch), the rest to weight stages
   const int bias_bytes = a->Cout_pad * 4;     // staged bias (zeros when there is none)
@@ -1171,7 +1192,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     static unsigned launch_parity = 0;
     p.reverse = zig_on ? static_cast<int>(__atomic_fetch_add(&launch_parity, 1u, __ATOMIC_RELAXED) & 1u) : 0;
   }
-  B200SVS_REQUIRE(p.cw == 1 || (p.epi_alt && p.lean16 == 1), "conv1d_tc: internal: wide chunks without the lean alternate-chunk epilogue");
+  B200SVS_REQUIRE(p.cw == 1 || (p.lean16 != 0 && (p.epi_alt || ep.res16)), "conv1d_tc: internal: wide chunks without a lean epilogue");
   if (p.pair) p.reverse = 0;      // the phantom tile of an odd tile count is defined for the forward walk only
   p.idesc = make_idesc_f16(p.pair ? 256 : 128, a->block_n, a->x_dtype == B200SVS_DT_BF16);
   p.ep = ep;
@@ -1195,6 +1216,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   }
   tmR = tmA; tmR2 = tmA; tmO32 = tmA; tmO16 = tmA; tmR16 = tmA; tmO16r = tmA;
   const uint32_t ebox[3] = {(uint32_t)kEpiCols, 128, 1};
+  const uint32_t hbox[3] = {(uint32_t)(kEpiCols * p.cw), 128, 1};      // 16-bit tiles: 64 columns (128-byte rows) with wide chunks
   const uint64_t edims[3] = {(uint64_t)ep.n_valid, (uint64_t)a->T, (uint64_t)a->B};
   if (ep.res1) {
     uint64_t strides[2] = {(uint64_t)ep.res1_ld * 4, (uint64_t)a->T * ep.res1_ld * 4};
@@ -1203,7 +1225,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   }
   if (ep.res2 && ep.res2_is16) {
     uint64_t strides[2] = {(uint64_t)ep.res2_ld * 2, (uint64_t)a->T * ep.res2_ld * 2};
-    int r = make_tmap(&tmR2, el16, ep.res2, 3, edims, strides, ebox, 64);
+    int r = make_tmap(&tmR2, el16, ep.res2, 3, edims, strides, hbox, p.cw == 2 ? 128 : 64);
     if (r) return r;
   } else if (ep.res2) {
     uint64_t strides[2] = {(uint64_t)ep.res2_ld * 4, (uint64_t)a->T * ep.res2_ld * 4};
@@ -1225,12 +1247,12 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
 
   if (ep.res16) {
     uint64_t strides[2] = {(uint64_t)ep.res16_ld * 2, (uint64_t)a->T * ep.res16_ld * 2};
-    int r = make_tmap(&tmR16, el16, ep.res16, 3, edims, strides, ebox, 64);
+    int r = make_tmap(&tmR16, el16, ep.res16, 3, edims, strides, hbox, p.cw == 2 ? 128 : 64);
     if (r) return r;
   }
   if (ep.out16r) {
     uint64_t strides[2] = {(uint64_t)ep.out16r_ld * 2, (uint64_t)a->T * ep.out16r_ld * 2};
-    int r = make_tmap(&tmO16r, el16, ep.out16r, 3, edims, strides, ebox, 64);
+    int r = make_tmap(&tmO16r, el16, ep.out16r, 3, edims, strides, hbox, p.cw == 2 ? 128 : 64);
     if (r) return r;
   }
 
