@@ -6,13 +6,17 @@
         --master-port P bench.py --gpus N --steps K --warmup W
 
 Metric (BASELINE.json): audio-seconds synthesised per wall-second (x real-time).  One "step" = one
-full `infer` over a batch of 64 synthetic utterances x 30 s (T = 2584 frames each, BASELINE.json
-configs[2], the configuration the >=1000x RT target is quoted on) per GPU; utterances are independent,
-so ranks shard by utterance with no collective inside the forward (weak scaling: 64 utterances per
-rank).  `value` is measured with inputs resident in HBM (CUDA events, max over ranks); `e2e` goes
-through the public API with pinned HOST inputs and a device->host read of the waveforms inside the
-timed region.  `--impl reference` times the reference algorithm's CPU port (oracle/, torch fp32 on
-the host cores) on a bounded sample of the same workload.
+pass of the hot path over BASELINE.json configs[2] - a FIXED global batch of 64 synthetic utterances
+x 30 s (T = 2584 frames each), the configuration the >= 1000x RT target is quoted on.  Utterances are
+independent, so with N GPUs `sharding.partition` gives every rank 64/N of them (strong scaling, no
+collective inside the forward) and the int16 waveforms are gathered on rank 0 over NCCL at the end.
+`value` is the whole job (64 x 30 s of audio / max-over-ranks device time) with inputs resident in
+HBM; `e2e` goes through the public API from pinned HOST id tensors: H2D, `infer` on the shard, device
+peak-normalise + int16 (`b200svs_song_assemble`), all_gather_into_tensor of the int16 rows, reorder,
+D2H to pinned host memory on rank 0 - all inside the timed region.  `weak` (N > 1 only) keeps round
+1's weak-scaling figure (64 utterances per rank).  `--impl reference` times the UNMODIFIED reference
+`SynthesizerTrn.infer` (oracle/_ref, staged by oracle/stage_ref.py; the oracle port only if the stage
+is missing) on the host cores on one utterance of the same workload.
 
 Only this file's `cpu_baseline` / `--impl reference` legs import oracle/ (as the thing being timed
 on the CPU side, never on the product path).
@@ -41,8 +45,10 @@ UNIT = "audio_s/s"
 
 # workload: BASELINE.json configs[2] per GPU
 UTTS, FRAMES, PHONES = 64, 2584, 258
-# bounded CPU sample of the same workload (one utterance; see cpu_baseline.sample)
+# BASELINE.json configs[0] (the reference's CPU-runnable case): reported inside cpu_baseline
 CPU_FRAMES, CPU_PHONES = 861, 86
+# C-ABI entry points whose launches are tensor-core implicit-GEMM convs (the roofline kernel)
+TC_KINDS = ("conv1d_tc", "resblock_pair")
 
 
 def mflop_per_frame(T):
@@ -124,7 +130,8 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------------
-# CPU side (oracle port of the reference algorithm) - baseline only
+# CPU side: the unmodified reference (oracle/_ref staged copy, or /root/reference in the build container); the oracle
+# port only when neither exists - baseline only
 # ---------------------------------------------------------------------------------------------------
 def cpu_state_dict(positions):
     import torch
@@ -134,47 +141,124 @@ def cpu_state_dict(positions):
     return synthetic.apply_recipe(sd, positions=positions)
 
 
-def cpu_run(frames, phones, reps, warmup, threads=None):
-    """Times oracle.visinger_oracle.infer (the reference forward restated in torch fp32) on the host."""
-    import torch
-    from music_generation_b200 import synthetic
-    from oracle import visinger_oracle as vo
-    cores = threads or os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    sd = cpu_state_dict(max(2000, frames))
-    inp = synthetic.make_inputs(1, phones, seed=1234)
-    ph_dur = synthetic.make_ph_dur(inp["x_lengths"], phones, frames, seed=1234)
-    noise = synthetic.make_noise(1, 192, frames, seed=1234)
-    times = []
-    with torch.no_grad():
-        for i in range(warmup + reps):
-            t0 = time.perf_counter()
-            vo.infer(sd, noise=noise, ph_dur=ph_dur, hp=HP, **inp)
-            dt = time.perf_counter() - t0
-            if i >= warmup:
-                times.append(dt)
-    return times, cores
+def cpu_info():
+    model = "unknown"
+    try:
+        for ln in open("/proc/cpuinfo"):
+            if ln.startswith("model name"):
+                model = ln.split(":", 1)[1].strip()
+                break
+    except OSError:
+        pass
+    return {"cpu_model": model, "logical_cpus": os.cpu_count()}
+
+
+class CpuArm:
+    """SynthesizerTrn.infer on the host cores.  kind 'reference': the reference's own modules (ref_harness);
+    kind 'port': oracle.visinger_oracle (only when no reference tree / stage is present)."""
+
+    def __init__(self, positions):
+        import torch
+        from oracle import ref_harness
+        self.torch = torch
+        self.sd = cpu_state_dict(positions)
+        self.net = None
+        if ref_harness.available():
+            self.kind = "reference"
+            self.src = "oracle/_ref (staged copy)" if ref_harness.source_kind() == "staged" else ref_harness.REF_ROOT
+            self.rh = ref_harness
+            self.net = ref_harness.enlarge_positions(ref_harness.build_reference("ae"), positions)
+            self.net.load_state_dict(self.sd, strict=True)
+        else:
+            self.kind, self.src = "port", "oracle/visinger_oracle.py"
+
+    def infer_times(self, frames, phones, reps, warmup, threads):
+        from music_generation_b200 import synthetic
+        torch = self.torch
+        torch.set_num_threads(threads)
+        inp = synthetic.make_inputs(1, phones, seed=1234)
+        ph_dur = synthetic.make_ph_dur(inp["x_lengths"], phones, frames, seed=1234)
+        noise = synthetic.make_noise(1, 192, frames, seed=1234)
+        times = []
+        with torch.no_grad():
+            for i in range(warmup + reps):
+                t0 = time.perf_counter()
+                if self.net is not None:
+                    self.rh.run_reference_infer(self.net, inp, noise, ph_dur)
+                else:
+                    from oracle import visinger_oracle as vo
+                    vo.infer(self.sd, noise=noise, ph_dur=ph_dur, hp=HP, **inp)
+                dt = time.perf_counter() - t0
+                if i >= warmup:
+                    times.append(dt)
+        return times
+
+    def generator_times(self, frames, reps, warmup, threads):
+        """Generator.forward only (models_ae.py:327-346) on z [1,192,frames]."""
+        torch = self.torch
+        torch.set_num_threads(threads)
+        z = torch.randn(1, 192, frames, generator=torch.Generator().manual_seed(3)) * 0.14
+        times = []
+        with torch.no_grad():
+            for i in range(warmup + reps):
+                t0 = time.perf_counter()
+                if self.net is not None:
+                    self.net.decoder(z)
+                else:
+                    from oracle import visinger_oracle as vo
+                    vo.generator(self.sd, z, HP)
+                dt = time.perf_counter() - t0
+                if i >= warmup:
+                    times.append(dt)
+        return times
 
 
 def run_reference_arm(args, rank):
+    """`--impl reference`: the reference's own CPU forward, all host threads, one utterance (T = args.frames) of the
+    arm's workload per step."""
     if rank != 0:
         return 0
-    frames, phones = CPU_FRAMES, CPU_PHONES
-    times, cores = cpu_run(frames, phones, args.steps, args.warmup)
+    frames, phones = args.frames, args.phones
+    cores = os.cpu_count() or 1
+    arm = CpuArm(max(2000, frames))
+    times = arm.infer_times(frames, phones, args.steps, args.warmup, cores)
     ms = 1e3 * sum(times) / len(times)
     val = audio_seconds(frames) / (ms / 1e3)
-    sample = (f"1 utterance x {frames} frames ({audio_seconds(frames):.1f} s) of the 64 x 30 s workload per step, "
-              f"oracle port of SynthesizerTrn.infer (torch fp32, {cores} threads)")
+    sample = (f"1 utterance x {frames} frames ({audio_seconds(frames):.1f} s) = 1/{args.utts} of the {args.utts} x "
+              f"{audio_seconds(frames):.0f} s workload per step; {arm.kind} SynthesizerTrn.infer from {arm.src}, torch fp32, "
+              f"{cores} threads")
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "svs_v5_infer_64x30s (bounded CPU sample)", "model": "VISinger ours_ae.json",
-                       "frames": frames, "phonemes": phones},
-            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"svs_v5_infer_{args.utts}x{audio_seconds(frames):.0f}s (bounded CPU sample: 1 utterance)",
+                       "model": "VISinger ours_ae.json (SVS v5)", "frames": frames, "phonemes": phones, **cpu_info()},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": arm.kind, "sample": sample},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
     return 0
+
+
+def cpu_baseline_block(args):
+    """cpu_baseline of the GPU arm's line (rank 0, N = 1): ~30-60 s of CPU work in total."""
+    frames, phones = args.frames, args.phones
+    cores = os.cpu_count() or 1
+    arm = CpuArm(max(2000, frames))
+    med = statistics.median
+    t_full = arm.infer_times(frames, phones, reps=3, warmup=1, threads=cores)
+    v = audio_seconds(frames) / med(t_full)
+    out = {"value": v, "unit": UNIT, "cores": cores, "kind": arm.kind,
+           "sample": f"1 utterance x {frames} frames ({audio_seconds(frames):.1f} s) of the workload, median of 3 after 1 "
+                     f"warm-up; {arm.kind} SynthesizerTrn.infer from {arm.src}, torch fp32, {cores} threads",
+           **cpu_info()}
+    # SURVEY 8d: config 1 (B=1, T=861) on all cores and on one core; Generator only z[1,192,2048]
+    t1 = arm.infer_times(CPU_FRAMES, CPU_PHONES, reps=3, warmup=1, threads=cores)
+    out["config1_T861_all_cores"] = {"value": audio_seconds(CPU_FRAMES) / med(t1), "cores": cores}
+    t1c = arm.infer_times(CPU_FRAMES, CPU_PHONES, reps=1, warmup=0, threads=1)
+    out["config1_T861_one_core"] = {"value": audio_seconds(CPU_FRAMES) / med(t1c), "cores": 1}
+    tg = arm.generator_times(2048, reps=2, warmup=1, threads=cores)
+    out["generator_only_1x192x2048"] = {"value": audio_seconds(2048) / med(tg), "cores": cores}
+    return out
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -183,7 +267,7 @@ def run_reference_arm(args, rank):
 def run_gpu_arm(args, rank, local_rank, world):
     import torch
     import torch.distributed as dist
-    from music_generation_b200 import _lib, models_ae, synthetic
+    from music_generation_b200 import _lib, models_ae, ops, sharding, synthetic
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -198,41 +282,57 @@ def run_gpu_arm(args, rank, local_rank, world):
     sd = synthetic.apply_recipe({k: v.clone() for k, v in net.state_dict().items()}, positions=positions)
     net.load_state_dict(sd)
     net = net.to(dev)
+    hop = net.hop
 
-    # every rank synthesises its own `utts` utterances (weak scaling): seed by rank
-    inp = synthetic.make_inputs(utts, phones, seed=1234 + rank)
-    ph_dur = synthetic.make_ph_dur(inp["x_lengths"], phones, frames, seed=1234 + rank)
-    host = {k: v.pin_memory() for k, v in inp.items()}
-    host["ph_dur"] = ph_dur.pin_memory()
-    devin = {k: v.to(dev) for k, v in host.items()}
-    n_samples = frames * HOP
-    host_wave = torch.empty(utts, 1, n_samples, dtype=torch.float32).pin_memory()
-    h2d_bytes = sum(v.numel() * v.element_size() for v in host.values())
-    d2h_bytes = host_wave.numel() * host_wave.element_size()
+    class Job:
+        """One global batch (identical on every rank: same seed), partitioned by sharding.partition; this rank's shard
+        as pinned host tensors + device-resident copies."""
 
-    def step_device():
-        return net.infer(devin["x"], devin["x_lengths"], devin["note_pitch_id"], devin["note_duration"],
-                         phone_shengdiao=devin["phone_shengdiao"], ph_dur=devin["ph_dur"], noise_scale=1.0)
+        def __init__(self, n_utts, seed, ragged_frames=None):
+            inp = synthetic.make_inputs(n_utts, phones, seed=seed)
+            if ragged_frames is None:
+                ph_dur = synthetic.make_ph_dur(inp["x_lengths"], phones, frames, seed=seed)
+            else:       # utterance b gets ragged_frames[b] frames over all of its phonemes
+                ph_dur = torch.cat([synthetic.make_ph_dur(inp["x_lengths"][b:b + 1], phones, int(f), seed=seed + b)
+                                    for b, f in enumerate(ragged_frames)], 0)
+            self.frames = ph_dur.sum(1)
+            self.bins = sharding.partition(self.frames.tolist(), world)
+            self.mine = self.bins[rank]
+            self.per = max(1, max(len(b) for b in self.bins))
+            self.audio_s = audio_seconds(int(self.frames.sum()))
+            sh = sharding.shard_batch(dict(inp, ph_dur=ph_dur), self.mine)
+            self.host = {k: v.pin_memory() for k, v in sh.items()}
+            self.dev = {k: v.to(dev) for k, v in self.host.items()}
+            self.n = len(self.mine)
+            self.smax = int(self.frames.max()) * hop
+            # int16 path: per-rank rows [per, smax] (rows >= n stay zero), receive buffer, pinned host result on rank 0
+            self.rows = torch.zeros(self.per, self.smax, device=dev, dtype=torch.int16)
+            self.offsets = (torch.arange(max(self.n, 1), device=dev, dtype=torch.int64) * self.smax)[:max(self.n, 1)]
+            self.recv = torch.empty(world * self.per, self.smax, device=dev, dtype=torch.int16) if world > 1 else None
+            self.host_wave16 = torch.empty(n_utts, self.smax, dtype=torch.int16).pin_memory() if rank == 0 else None
+            self.h2d_bytes = sum(v.numel() * v.element_size() for v in self.host.values())
+            self.d2h_bytes = n_utts * self.smax * 2 if rank == 0 else 0
 
-    def step_e2e():
-        d = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
-        res = net.infer(d["x"], d["x_lengths"], d["note_pitch_id"], d["note_duration"],
-                        phone_shengdiao=d["phone_shengdiao"], ph_dur=d["ph_dur"], noise_scale=1.0)
-        host_wave.copy_(res[0], non_blocking=True)
-        return res
+        def infer(self, d):
+            return net.infer(d["x"], d["x_lengths"], d["note_pitch_id"], d["note_duration"],
+                             phone_shengdiao=d["phone_shengdiao"], ph_dur=d["ph_dur"], noise_scale=1.0)
 
-    # song driver: the same utterances as the lines of one song - one ragged batch, peak-normalised,
-    # int16, concatenated on the device; only the int16 song crosses PCIe
-    from music_generation_b200 import pipeline
-    syn = pipeline.Synthesiser(net)
-    host_lines = [(host["x"][b], host["note_pitch_id"][b], host["note_duration"][b], host["phone_shengdiao"][b])
-                  for b in range(utts)]
-    host_song = torch.empty(pipeline.LEAD_IN + utts * n_samples, dtype=torch.int16).pin_memory()
+        def step_device(self):
+            return self.infer(self.dev) if self.n else None
 
-    def step_song():
-        song = syn.syn_song(host_lines, ph_dur=host["ph_dur"].to(dev, non_blocking=True))
-        host_song.copy_(song, non_blocking=True)
-        return song
+        def step_e2e(self):
+            """host ids -> H2D -> infer -> device peak-normalise + int16 -> NCCL all-gather -> reorder -> D2H (rank 0)."""
+            if self.n:
+                d = {k: v.to(dev, non_blocking=True) for k, v in self.host.items()}
+                res = self.infer(d)
+                mel_len = d["ph_dur"].sum(1)
+                ops.song_assemble(res[0], mel_len, self.offsets, self.rows.view(-1), hop=hop, lead_in=0)
+            if world > 1:
+                full = sharding.gather_rows(self.rows[:self.n], self.bins, dst=0, out=self.recv)
+            else:
+                full = self.rows[:self.n]
+            if rank == 0:
+                self.host_wave16.copy_(full, non_blocking=True)
 
     def barrier():
         if world > 1:
@@ -256,56 +356,103 @@ def run_gpu_arm(args, rank, local_rank, world):
             ms = float(t.item())
         return ms, launches
 
-    for _ in range(max(args.warmup, 3)):
-        step_device()
+    job = Job(utts, 1234)
+    warm = max(args.warmup, 3)
+    for _ in range(warm):
+        job.step_device()
     sampler = ClockSampler(local_rank)
     sampler.start()
-    ms_total, launches = timed(step_device, args.steps)
+    ms_total, launches = timed(job.step_device, args.steps)
     clocks = sampler.stop()
     if args.ncu_range:        # one extra step inside a cudaProfiler range (ncu --profile-from-start off); not timed
         torch.cuda.synchronize()
         torch.cuda.profiler.start()
-        step_device()
+        job.step_device()
         torch.cuda.synchronize()
         torch.cuda.profiler.stop()
     for _ in range(2):
-        step_e2e()
-    ms_e2e, _ = timed(step_e2e, args.steps)
-    step_song()
-    ms_song, _ = timed(step_song, args.steps)
+        job.step_e2e()
+    ms_e2e, _ = timed(job.step_e2e, args.steps)
 
     ms_step = ms_total / args.steps
-    audio_per_step = audio_seconds(utts * frames) * world
-    value = audio_per_step / (ms_step / 1e3)
-    e2e_value = audio_per_step / (ms_e2e / args.steps / 1e3)
+    value = job.audio_s / (ms_step / 1e3)
+    e2e_value = job.audio_s / (ms_e2e / args.steps / 1e3)
+    extra = {}
+
+    # the same global batch with ragged lengths (20-30 s): sharding.partition has something to balance
+    if not args.no_extras:
+        g = torch.Generator().manual_seed(4321)
+        rag = torch.randint(int(frames * 2 / 3), frames + 1, (utts,), generator=g)
+        rag[0] = frames
+        rjob = Job(utts, 1234, ragged_frames=rag.tolist())
+        for _ in range(2):
+            rjob.step_e2e()
+        ms_r, _ = timed(rjob.step_device, 3)
+        ms_re, _ = timed(rjob.step_e2e, 3)
+        loads = [sum(sharding.utterance_cost(int(rjob.frames[i])) for i in b) for b in rjob.bins]
+        extra["ragged_20_30s"] = {"value": rjob.audio_s / (ms_r / 3 / 1e3), "e2e": rjob.audio_s / (ms_re / 3 / 1e3),
+                                  "unit": UNIT, "ms_per_step": ms_r / 3, "audio_s": rjob.audio_s,
+                                  "partition_imbalance": max(loads) / (sum(loads) / world),
+                                  "what": "64 utterances of 20-30 s (uniform random frames), LPT partition, same e2e path"}
+        del rjob
+    # weak scaling (round 1's SCALE figure): every rank synthesises its own `utts` utterances
+    if world > 1 and not args.no_extras:
+        inp = synthetic.make_inputs(utts, phones, seed=1234 + rank)
+        ph = synthetic.make_ph_dur(inp["x_lengths"], phones, frames, seed=1234 + rank)
+        wd = {k: v.to(dev) for k, v in dict(inp, ph_dur=ph).items()}
+        wstep = lambda: job.infer(wd)
+        wstep()
+        ms_w, _ = timed(wstep, min(args.steps, 5))
+        extra["weak"] = {"value": audio_seconds(utts * frames) * world / (ms_w / min(args.steps, 5) / 1e3), "unit": UNIT,
+                         "utterances_per_gpu": utts, "ms_per_step": ms_w / min(args.steps, 5), "scaling": "weak"}
+        del wd
+
+    # song driver on this rank's shard: one ragged batch -> int16 song with lead-in -> pinned host
+    if rank == 0 and world == 1 and not args.no_extras:
+        from music_generation_b200 import pipeline
+        syn = pipeline.Synthesiser(net)
+        host_lines = [(job.host["x"][b], job.host["note_pitch_id"][b], job.host["note_duration"][b],
+                       job.host["phone_shengdiao"][b]) for b in range(job.n)]
+        host_song = torch.empty(pipeline.LEAD_IN + job.n * job.smax, dtype=torch.int16).pin_memory()
+
+        def step_song():
+            song = syn.syn_song(host_lines, ph_dur=job.host["ph_dur"].to(dev, non_blocking=True))
+            host_song.copy_(song, non_blocking=True)
+        step_song()
+        ms_song, _ = timed(step_song, args.steps)
+        extra["e2e_song"] = {"value": job.audio_s / (ms_song / args.steps / 1e3), "unit": UNIT,
+                             "d2h_bytes_per_step": host_song.numel() * 2, "ms_per_step": ms_song / args.steps,
+                             "what": "pipeline.Synthesiser.syn_song: host id tensors -> one ragged batch -> infer -> "
+                                     "device peak-normalise / int16 / concatenate -> int16 song to pinned host memory"}
 
     # instrumented pass (outside the timed region): per-launch CUDA events around every conv launch
-    roofline, extra = None, {}
+    roofline = None
     if rank == 0:
         _lib.PROFILE = []
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
         ev0.record()
-        step_device()
+        job.step_device()
         ev1.record()
         torch.cuda.synchronize()
         prof, _lib.PROFILE = _lib.PROFILE, None
         step_ms = ev0.elapsed_time(ev1)
         agg = {}
-        hbm_t = hbm_b = 0.0       # launches that are HBM-bound by their algorithmic intensity
         for kind, tag, flops, a, b, nbytes in prof:
             t = a.elapsed_time(b)
             key = (kind, tag)
             f, tt, n, by = agg.get(key, (0.0, 0.0, 0, 0.0))
             agg[key] = (f + flops, tt + t, n + 1, by + nbytes)
-        tc_f = sum(v[0] for k, v in agg.items() if k[0] == "conv1d_tc")
-        tc_t = sum(v[1] for k, v in agg.items() if k[0] == "conv1d_tc")
-        tc_n = sum(v[2] for k, v in agg.items() if k[0] == "conv1d_tc")
+        is_tc = lambda k: k[0] in TC_KINDS
+        tc_f = sum(v[0] for k, v in agg.items() if is_tc(k))
+        tc_t = sum(v[1] for k, v in agg.items() if is_tc(k))
+        tc_n = sum(v[2] for k, v in agg.items() if is_tc(k))
         peaks = load_peaks()
         ach = tc_f / (tc_t * 1e-3) / 1e12 if tc_t > 0 else 0.0
-        tc_b = sum(v[3] for k, v in agg.items() if k[0] == "conv1d_tc")
-        traffic = load_traffic(f"svs_v5_infer_{utts}x{audio_seconds(frames):.0f}s")
-        roofline = {"bound": "tensor", "kernel": "conv1d_tc_kernel", "achieved": ach, "peak": peaks["tf_sustained"],
+        tc_b = sum(v[3] for k, v in agg.items() if is_tc(k))
+        traffic = load_traffic(f"svs_v5_infer_{job.n}x{audio_seconds(frames):.0f}s")
+        roofline = {"bound": "tensor", "kernel": "conv1d_tc_kernel (+ resblock_pair_kernel, the same implicit-GEMM conv fused pairwise)",
+                    "achieved": ach, "peak": peaks["tf_sustained"],
                     "unit": "TFLOP/s", "frac": ach / peaks["tf_sustained"],
                     "traffic": None if traffic is None else traffic["dram_bytes_per_launch"],
                     "traffic_source": None if traffic is None else traffic["source"],
@@ -322,32 +469,28 @@ def run_gpu_arm(args, rank, local_rank, world):
                                                               "alg_gbs": round(v[3] / max(v[1], 1e-9) / 1e6, 1)}
                               for k, v in sorted(agg.items())}
         extra["instrumented_step_ms"] = step_ms
-        extra["step_tflops"] = mflop_per_frame(frames) * 1e6 * utts * frames / (ms_step * 1e-3) / 1e12
+        extra["step_tflops"] = mflop_per_frame(frames) * 1e6 * int(job.frames.sum()) / (ms_step * 1e-3) / 1e12
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        times, cores = cpu_run(CPU_FRAMES, CPU_PHONES, reps=3, warmup=1)
-        v = audio_seconds(CPU_FRAMES) / statistics.median(times)
-        cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                        "sample": f"1 utterance x {CPU_FRAMES} frames ({audio_seconds(CPU_FRAMES):.1f} s), median of 3 "
-                                  f"after 1 warm-up, oracle port of SynthesizerTrn.infer (torch fp32, {cores} threads)"}
+        cpu_baseline = cpu_baseline_block(args)
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-                "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "warmup": warm, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
                 "config": {"workload": f"svs_v5_infer_{utts}x{audio_seconds(frames):.0f}s", "model": "VISinger ours_ae.json (SVS v5)",
-                           "utterances_per_gpu": utts, "frames_per_utterance": frames, "phonemes": phones,
-                           "global_batch": utts * world, "parallelism": f"dp{world} (utterance-sharded, no collective)",
+                           "global_batch": utts, "utterances_per_gpu": [len(b) for b in job.bins],
+                           "frames_per_utterance": frames, "phonemes": phones,
+                           "parallelism": f"dp{world} (sharding.partition by utterance, no collective inside the forward; "
+                                          f"final int16 all_gather_into_tensor over NCCL in e2e)",
                            "weights": "random init + synthetic.apply_recipe", "noise": "device randn",
                            "l2": "activations per step >> 126 MB L2 (no flush needed)"},
                 "per_gpu": value / world,
-                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                        "ms_per_step": ms_e2e / args.steps},
-                "e2e_song": {"value": audio_per_step / (ms_song / args.steps / 1e3), "unit": UNIT,
-                             "d2h_bytes_per_step": host_song.numel() * 2, "ms_per_step": ms_song / args.steps,
-                             "what": "pipeline.Synthesiser.syn_song: host id tensors -> one ragged batch -> infer -> "
-                                     "device peak-normalise / int16 / concatenate -> int16 song to pinned host memory"},
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": job.h2d_bytes, "d2h_bytes_per_step": job.d2h_bytes,
+                        "ms_per_step": ms_e2e / args.steps,
+                        "what": "pinned host ids -> H2D -> SynthesizerTrn.infer -> device peak-normalise + int16 "
+                                "(b200svs_song_assemble) -> all_gather_into_tensor (N > 1) -> int16 waveforms D2H on rank 0"},
                 "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline}
         line.update(extra)
         print(json.dumps(line), flush=True)
@@ -368,6 +511,7 @@ def main():
     ap.add_argument("--frames", type=int, default=FRAMES)
     ap.add_argument("--phones", type=int, default=PHONES)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the ragged / weak / song extra measurements")
     ap.add_argument("--model-kw", default="{}", help='JSON of extra SynthesizerTrn keyword arguments for A/B runs, '
                     'e.g. \'{"generator_mrf": "fp32"}\' (the default line uses none)')
     ap.add_argument("--ncu-range", action="store_true",

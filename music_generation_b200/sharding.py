@@ -68,3 +68,35 @@ def gather_waveforms(local_wave: torch.Tensor, local_len: torch.Tensor, indices:
         wave[m[ok, 0]] = b[ok]
         lens[m[ok, 0]] = m[ok, 1]
     return wave, lens
+
+
+def gather_rows(local: torch.Tensor, bins: Sequence[Sequence[int]], dst: int = 0, out: torch.Tensor = None):
+    """Final gather of config 3: every rank holds the rows (e.g. int16 waveforms [n_local, S]) of the
+    utterances `bins[rank]` (the deterministic `partition` every rank computes for itself, so no metadata travels);
+    ONE `all_gather_into_tensor` of equally padded blocks moves the payload (NCCL over NVLink on GPUs, gloo in the
+    CPU tests) and `dst` returns the rows in the original utterance order [n_total, S]; other ranks return None.
+    `out` (optional, [world * per, S]) is a reusable receive buffer."""
+    world, rank = dist.get_world_size(), dist.get_rank()
+    if local.dtype == torch.int16:        # neither NCCL nor gloo moves int16: the payload travels as bytes
+        res = gather_rows(local.view(torch.uint8), bins, dst, None if out is None else out.view(torch.uint8))
+        return None if res is None else res.view(torch.int16)
+    per = max(1, max(len(b) for b in bins))
+    n = local.shape[0]
+    if n != len(bins[rank]):
+        raise ValueError(f"rank {rank} holds {n} rows but its bin has {len(bins[rank])} utterances")
+    if n == per:
+        send = local.contiguous()
+    else:
+        send = local.new_zeros((per,) + tuple(local.shape[1:]))
+        send[:n] = local
+    if out is None:
+        out = local.new_empty((world * per,) + tuple(local.shape[1:]))
+    dist.all_gather_into_tensor(out, send)
+    if rank != dst:
+        return None
+    n_total = sum(len(b) for b in bins)
+    perm = torch.empty(n_total, dtype=torch.long)
+    for r, b in enumerate(bins):
+        for slot, i in enumerate(b):
+            perm[i] = r * per + slot
+    return out.index_select(0, perm.to(out.device))

@@ -69,3 +69,41 @@ def test_gather_world_size_2_gloo():
         p.join(120)
         assert p.exitcode == 0
     assert ret.get(timeout=5) is True
+
+
+def _rows_worker(rank, world, port, frames, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        bins = sharding.partition(frames, world)
+        mine = bins[rank]
+        S = 16
+        # int16 stand-in for song_assemble's rows: utterance i is the constant i + 1 on its valid samples
+        rows = torch.zeros(len(mine), S, dtype=torch.int16)
+        for n, i in enumerate(mine):
+            rows[n, : frames[i]] = i + 1
+        full = sharding.gather_rows(rows, bins, dst=0)
+        if rank == 0:
+            ok = full.shape == (len(frames), S) and full.dtype == torch.int16
+            for i, f in enumerate(frames):
+                ok &= bool((full[i, :f] == i + 1).all()) and bool((full[i, f:] == 0).all())
+            ret.put(bool(ok))
+        else:
+            assert full is None
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gather_rows_world_size_2_gloo():
+    """bench.py's config-3 gather: uneven bins (5 utterances on 2 ranks), int16 payload, original order on rank 0."""
+    frames = [7, 3, 11, 5, 2]
+    ctx = mp.get_context("spawn")
+    ret = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_rows_worker, args=(r, 2, port, frames, ret)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert ret.get(timeout=5) is True
