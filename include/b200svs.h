@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200SVS_ABI_VERSION 1
+#define B200SVS_ABI_VERSION 2
 
 enum {
   B200SVS_OK = 0,
@@ -118,6 +118,12 @@ int b200svs_abi_version(void);
 /* 0 if an sm_100 device is current and the driver exports cuTensorMapEncodeTiled */
 int b200svs_check_device(void);
 
+/* Numeric-range canary: every fp32 -> 16-bit conversion in the library saturates (+-65504 for fp16)
+ * instead of overflowing to inf; conv1d_tc additionally counts, in a library-owned device word of the current device,
+ * the epilogue threads that stored a saturated or NaN fp16 value.  Copies the count to *host_out (nullable;
+ * synchronises `stream`) and optionally resets it.  0 after a forward = no 16-bit tensor clipped. */
+int b200svs_saturation_events(uint32_t* host_out, int32_t reset, void* stream);
+
 /* tcgen05/TMEM/TMA implicit-GEMM conv, fp16|bf16 operands, fp32 accumulate */
 int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream);
 /* Diagnostic (tuning aid, not part of the data path): when dev_buf != NULL every following conv1d_tc launch
@@ -156,11 +162,15 @@ int b200svs_layernorm(const float* x, int32_t x_ld, const float* res, int32_t re
                       void* out16, int32_t out16_ld, int32_t out16_dtype, int32_t B, int32_t T, int32_t C,
                       void* stream);
 
-/* TextEncoder input (models_ae.py:204-215): (E_ph[x] + W_dur*dur + b_dur + E_pitch[p] + E_tone[s])*sqrt(C)*mask */
+/* TextEncoder input (models_ae.py:204-215): (E_ph[x] + W_dur*dur + b_dur + E_pitch[p] + E_tone[s])*sqrt(C)*mask.
+ * n_ph / n_pitch / n_tone: rows of the three tables.  nn.Embedding raises on an id outside its table; here a live
+ * out-of-range id is clamped and sets bit 0 of status[1] (status: nullable int32[2], zeroed by the caller, shared with
+ * b200svs_lr_scan) so that the host can raise at its next synchronisation instead of reading out of bounds. */
 int b200svs_text_embed(const int64_t* phon, const int64_t* pitch, const int64_t* tone, const float* dur,
                        const float* e_ph, const float* e_pitch, const float* e_tone, const float* w_dur,
                        const float* b_dur, const int64_t* x_lengths, int32_t* lens32_out, float* out,
-                       int32_t B, int32_t P, int32_t C, void* stream);
+                       int32_t B, int32_t P, int32_t C, int32_t n_ph, int32_t n_pitch, int32_t n_tone,
+                       int32_t* status, void* stream);
 
 /* floor(pred * note_dur / 0.0116) -> int64 (models_ae.py:624-625), bit-exact fp32 op order */
 int b200svs_duration_quantize(const float* pred, const float* note_dur, int64_t* dur_out, int32_t n,
@@ -169,8 +179,10 @@ int b200svs_duration_quantize(const float* pred, const float* note_dur, int64_t*
 /* Length regulator (models_ae.py:689-721 + utils/utils.py:344-361) as a gather.
  * pass 1: mel_len[b] = sum_i max(dur[b,i],0), ends = inclusive cumsum (int32 workspace [B,P]).
  * pass 2: out[b,t,:] = h[b, idx(b,t), :] for t < mel_len[b] else 0; index[b,t] = idx or -1. */
+/* status (nullable int32[2], zeroed by the caller): status[0] = max_b mel_len[b] (atomicMax) - the one number the
+ * host has to read back (the padded frame count T). */
 int b200svs_lr_scan(const int64_t* dur, int32_t B, int32_t P, int32_t* ends, int64_t* mel_len64,
-                    int32_t* mel_len32, void* stream);
+                    int32_t* mel_len32, int32_t* status, void* stream);
 int b200svs_lr_gather(const float* h, int32_t h_ld, const int32_t* ends, const int32_t* mel_len32,
                       int32_t B, int32_t P, int32_t T, int32_t C, float* out, int32_t out_ld,
                       int32_t* index_out, void* stream);
@@ -181,10 +193,12 @@ int b200svs_add_pos_mask(const float* x, int32_t x_ld, const float* pos, const i
                          int32_t T, int32_t C, void* stream);
 
 /* f0_to_coarse(exp(log_f0)-1) (utils/pitch_utils.py:22-31) + f0_emb gather * mask
- * (text_post_net.py:80-85).  coarse_in != NULL overrides the prediction (f0_score argument). */
+ * (text_post_net.py:80-85).  coarse_in != NULL overrides the prediction (f0_score argument); n_rows = rows of the
+ * f0_emb table (indices are clamped to it). */
 int b200svs_f0_embed(const float* log_f0, const int64_t* coarse_in, const float* f0_emb,
                      const int32_t* lens, int64_t* coarse_out, float* out32, int32_t out32_ld, void* out16,
-                     int32_t out16_ld, int32_t out16_dtype, int32_t B, int32_t T, int32_t C, void* stream);
+                     int32_t out16_ld, int32_t out16_dtype, int32_t B, int32_t T, int32_t C, int32_t n_rows,
+                     void* stream);
 
 /* z_p = m_p + noise * exp(logs_p) * noise_scale (models_ae.py:643); stats: [B,T,2C] (m|logs);
  * noise is the reference layout [B,C,T]; writes z_p fp32 [B,T,C] (+16-bit copy) */
@@ -202,11 +216,6 @@ int b200svs_bct_to_btc(const float* in_bct, int32_t B, int32_t C, int32_t T, flo
                        void* out16, int32_t out16_ld, int32_t out16_dtype, const int32_t* lens, void* stream);
 int b200svs_btc_to_bct(const float* in_btc, int32_t in_ld, int32_t B, int32_t C, int32_t T, float* out_bct,
                        void* stream);
-
-/* Debug probe: GEMM of a row-shifted smem operand view, used once to pin the UMMA descriptor
- * base-offset semantics on hardware (DESIGN.md "A-tile reuse"). */
-int b200svs_probe_rowshift(const void* a_f16, const void* b_f16, float* out, int32_t rows_a, int32_t shift,
-                           int32_t base_offset_mode, void* stream);
 
 /* Song assembly: what the reference does on the host after every per-line infer()
  * (pipline_inference_svs_v5.py:134-139,225-243,241-258; pipline_inference_svs_v6_multispeaker.py:240-258), on a

@@ -49,6 +49,7 @@ _i32, _f32, _vp = C.c_int32, C.c_float, C.c_void_p
 PROTOTYPES = {
     "b200svs_abi_version": [],
     "b200svs_check_device": [],
+    "b200svs_saturation_events": [C.POINTER(C.c_uint32), _i32, _vp],
     "b200svs_conv1d_tc": [C.POINTER(ConvArgs), _vp],
     "b200svs_conv1d_tc_set_trace": [_vp, _i32],
     "b200svs_song_assemble": [_vp, C.c_int64, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp],
@@ -58,12 +59,12 @@ PROTOTYPES = {
     "b200svs_attention_tc": [_vp, _vp, _vp, _vp, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _i32, _i32,
                              _i32, _i32, _i32, _vp],
     "b200svs_layernorm": [_vp, _i32, _vp, _i32, _vp, _vp, _f32, _vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
-    "b200svs_text_embed": [_vp] * 12 + [_i32, _i32, _i32, _vp],
+    "b200svs_text_embed": [_vp] * 12 + [_i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp],
     "b200svs_duration_quantize": [_vp, _vp, _vp, _i32, _vp],
-    "b200svs_lr_scan": [_vp, _i32, _i32, _vp, _vp, _vp, _vp],
+    "b200svs_lr_scan": [_vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp],
     "b200svs_lr_gather": [_vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _vp],
     "b200svs_add_pos_mask": [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
-    "b200svs_f0_embed": [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
+    "b200svs_f0_embed": [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp],
     "b200svs_sample_prior": [_vp, _i32, _vp, _f32, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
     "b200svs_conv_post_tanh": [_vp, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _vp, _vp],
     "b200svs_bct_to_btc": [_vp, _i32, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _vp, _vp],

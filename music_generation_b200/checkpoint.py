@@ -26,15 +26,23 @@ from .synthesizer import _Enc
 
 logger = logging.getLogger(__name__)
 
-PACK_FORMAT = 3            # bump when packer.py / SynthesizerTrn._pack change what they produce
+PACK_FORMAT = 4            # bump when packer.py / SynthesizerTrn._pack change what they produce
 CACHE_SUFFIX = ".b200pack"
 
 
 # ---------------------------------------------------------------------------------------------- reference format
-def load_checkpoint(checkpoint_path, model, optimizer=None, *, packed_cache=False):
-    """Reference signature and return value: (model, optimizer, learning_rate, iteration)."""
+def load_checkpoint(checkpoint_path, model, optimizer=None, *, packed_cache=False, allow_pickle=False):
+    """Reference signature and return value: (model, optimizer, learning_rate, iteration).
+    The reference format is plain tensors / dicts / numbers, so the file is read with `weights_only=True` (no arbitrary
+    pickle execution); `allow_pickle=True` is the explicit opt-in for a checkpoint that carries other objects (the
+    reference's own `torch.load(path, map_location='cpu')` on an old torch, VISinger/utils/utils.py:35)."""
     assert os.path.isfile(checkpoint_path), checkpoint_path
-    ckpt = torch.load(checkpoint_path, map_location="cpu", weights_only=False)
+    try:
+        ckpt = torch.load(checkpoint_path, map_location="cpu", weights_only=True)
+    except Exception:
+        if not allow_pickle:
+            raise
+        ckpt = torch.load(checkpoint_path, map_location="cpu", weights_only=False)
     iteration = ckpt["iteration"]
     learning_rate = ckpt["learning_rate"]
     if optimizer is not None:
@@ -67,8 +75,13 @@ def save_checkpoint(model, optimizer, learning_rate, iteration, checkpoint_path)
 def fingerprint(model):
     """Digest of everything `_pack` depends on."""
     h = hashlib.blake2b(digest_size=20)
+    gf = model.generator_fold
     knobs = (PACK_FORMAT, model.variant, str(model.operand_dtype), model.f0_precision, model.text_precision,
-             model.gin_channels, model.resblock, tuple(model.upsample_rates), model.hidden_channels)
+             model.gin_channels, model.resblock, tuple(model.upsample_rates), model.hidden_channels,
+             tuple(sorted(gf.items())) if isinstance(gf, dict) else gf, tuple(model.resblock_kernel_sizes),
+             tuple(tuple(d) for d in model.resblock_dilation_sizes), tuple(model.upsample_kernel_sizes),
+             model.upsample_initial_channel, model.n_layers, model.n_heads, model.filter_channels, model.kernel_size,
+             getattr(model, "generator_pair", None))
     h.update(repr(knobs).encode())
     for k, v in model.state_dict().items():
         t = v.detach().cpu().contiguous()

@@ -69,20 +69,42 @@ int make_tmap(CUtensorMap* out, int elem, const void* base, int rank, const uint
   return B200SVS_OK;
 }
 
-static int g_sms = 0, g_smem = 0, g_cc = 0;
-static void query_device() {
-  if (g_sms) return;
+struct DevInfo { int sms, smem, cc; };
+static DevInfo g_dev[kMaxDevices] = {};
+int device_ordinal() {
   int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess) { (void)cudaGetLastError(); return; }
-  cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev);
-  cudaDeviceGetAttribute(&g_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-  int major = 0, minor = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) { (void)cudaGetLastError(); return 0; }
+  return dev < 0 ? 0 : (dev >= kMaxDevices ? kMaxDevices - 1 : dev);
+}
+static const DevInfo& query_device() {
+  const int dev = device_ordinal();
+  DevInfo& d = g_dev[dev];
+  if (d.sms) return d;
+  int sms = 0, smem = 0, major = 0, minor = 0;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) { (void)cudaGetLastError(); return d; }
+  cudaDeviceGetAttribute(&smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
   cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev);
-  g_cc = major * 10 + minor;
+  d.smem = smem; d.cc = major * 10 + minor; d.sms = sms;
+  return d;
 }
-int num_sms() { query_device(); return g_sms > 0 ? g_sms : 148; }
-int max_smem_optin() { query_device(); return g_smem > 0 ? g_smem : 227 * 1024; }
+int num_sms() { const int v = query_device().sms; return v > 0 ? v : 148; }
+int max_smem_optin() { const int v = query_device().smem; return v > 0 ? v : 227 * 1024; }
+static int device_cc() { return query_device().cc; }
+
+static unsigned int* g_sat[kMaxDevices] = {};
+unsigned int* sat_counter() {
+  const int dev = device_ordinal();
+  if (!g_sat[dev]) {
+    unsigned int* p = nullptr;
+    if (cudaMalloc(&p, sizeof(unsigned int)) != cudaSuccess || cudaMemset(p, 0, sizeof(unsigned int)) != cudaSuccess) {
+      (void)cudaGetLastError();
+      return nullptr;
+    }
+    g_sat[dev] = p;
+  }
+  return g_sat[dev];
+}
 
 }  // namespace b200svs
 
@@ -91,15 +113,28 @@ extern "C" {
 const char* b200svs_last_error(void) { return b200svs::g_err; }
 int b200svs_abi_version(void) { return B200SVS_ABI_VERSION; }
 
+int b200svs_saturation_events(uint32_t* host_out, int32_t reset, void* stream) {
+  unsigned int* c = b200svs::sat_counter();
+  if (!c) return b200svs::set_error(B200SVS_ECUDA, "saturation_events: counter allocation failed");
+  cudaStream_t s = b200svs::as_stream(stream);
+  if (host_out) {
+    int r = b200svs::check_cuda(cudaMemcpyAsync(host_out, c, sizeof(uint32_t), cudaMemcpyDeviceToHost, s), "cudaMemcpyAsync(sat)");
+    if (r) return r;
+    r = b200svs::check_cuda(cudaStreamSynchronize(s), "cudaStreamSynchronize(sat)");
+    if (r) return r;
+  }
+  if (reset) return b200svs::check_cuda(cudaMemsetAsync(c, 0, sizeof(uint32_t), s), "cudaMemsetAsync(sat)");
+  return B200SVS_OK;
+}
+
 int b200svs_check_device(void) {
   int n = 0;
   if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
     (void)cudaGetLastError();
     return b200svs::set_error(B200SVS_ENODEV, "no CUDA device visible");
   }
-  b200svs::query_device();
-  if (b200svs::g_cc / 10 != 10)
-    return b200svs::set_error(B200SVS_ENODEV, "device is sm_%d, this library is sm_100a only", b200svs::g_cc);
+  if (b200svs::device_cc() / 10 != 10)
+    return b200svs::set_error(B200SVS_ENODEV, "device is sm_%d, this library is sm_100a only", b200svs::device_cc());
   if (!b200svs::get_encode_tiled())
     return b200svs::set_error(B200SVS_ENODEV, "driver lacks cuTensorMapEncodeTiled");
   return B200SVS_OK;

@@ -26,12 +26,31 @@ int make_tmap_16bit(CUtensorMap* out, int dtype, const void* base, int rank, con
 int make_tmap(CUtensorMap* out, int elem, const void* base, int rank, const uint64_t* dims,
               const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes);
 
+// Per-DEVICE cached attributes of the current device (a process may drive several GPUs: SingerBank(device=...)).
+constexpr int kMaxDevices = 64;
+int device_ordinal();            // cudaGetDevice(), clamped to [0, kMaxDevices)
 int num_sms();
 int max_smem_optin();
+// Overflow canary of the current device: one library-owned uint32 in device memory (allocated on first use - the only
+// allocation this library makes; NULL if that fails, the kernels then skip the count).
+unsigned int* sat_counter();
 
 inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
 }  // namespace b200svs
+
+// One-time (per device and kernel) opt-in to the device's full dynamic shared memory; returns from the caller on error.
+#define B200SVS_SMEM_OPTIN(kernel, what)                                                                    \
+  do {                                                                                                      \
+    static bool done_[::b200svs::kMaxDevices] = {};                                                         \
+    const int d_ = ::b200svs::device_ordinal();                                                             \
+    if (!done_[d_]) {                                                                                       \
+      int r_ = ::b200svs::check_cuda(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                                          ::b200svs::max_smem_optin()), what);              \
+      if (r_) return r_;                                                                                    \
+      done_[d_] = true;                                                                                     \
+    }                                                                                                       \
+  } while (0)
 
 #define B200SVS_REQUIRE(cond, ...)                                  \
   do {                                                              \

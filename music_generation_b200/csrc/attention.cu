@@ -62,8 +62,8 @@ __global__ void __launch_bounds__(256) attention_f32_kernel(const AttnParams p) 
         const size_t row = static_cast<size_t>(b) * p.T + t;
         p.out[row * p.out_ld + qc + c] = 0.f;
         if (p.out16) {
-          if (p.out16_dtype == B200SVS_DT_BF16) reinterpret_cast<__nv_bfloat16*>(p.out16)[row * p.out16_ld + qc + c] = __float2bfloat16_rn(0.f);
-          else reinterpret_cast<__half*>(p.out16)[row * p.out16_ld + qc + c] = __float2half_rn(0.f);
+          if (p.out16_dtype == B200SVS_DT_BF16) reinterpret_cast<__nv_bfloat16*>(p.out16)[row * p.out16_ld + qc + c] = cvt_bf16_sat(0.f);
+          else reinterpret_cast<__half*>(p.out16)[row * p.out16_ld + qc + c] = cvt_f16_sat(0.f);
         }
       }
     }
@@ -204,8 +204,8 @@ __global__ void __launch_bounds__(256) attention_f32_kernel(const AttnParams p) 
       const int c = qc + tx * 6 + j;
       p.out[row * p.out_ld + c] = v;
       if (p.out16) {
-        if (p.out16_dtype == B200SVS_DT_BF16) reinterpret_cast<__nv_bfloat16*>(p.out16)[row * p.out16_ld + c] = __float2bfloat16_rn(v);
-        else reinterpret_cast<__half*>(p.out16)[row * p.out16_ld + c] = __float2half_rn(v);
+        if (p.out16_dtype == B200SVS_DT_BF16) reinterpret_cast<__nv_bfloat16*>(p.out16)[row * p.out16_ld + c] = cvt_bf16_sat(v);
+        else reinterpret_cast<__half*>(p.out16)[row * p.out16_ld + c] = cvt_f16_sat(v);
       }
     }
   }
@@ -226,13 +226,7 @@ extern "C" int b200svs_attention_f32(const float* qkv, int32_t qkv_ld, float* ou
   p.qkv = qkv; p.qkv_ld = qkv_ld; p.out = out; p.out_ld = out_ld; p.out16 = out16; p.out16_ld = out16_ld;
   p.out16_dtype = out16_dtype; p.rel_k = rel_k; p.rel_v = rel_v; p.lens = lens; p.B = B; p.T = T; p.C = C; p.H = H;
   const size_t smem = sizeof(AttnSmem);
-  static bool configured = false;
-  if (!configured) {
-    int r = check_cuda(cudaFuncSetAttribute(attention_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
-                       "cudaFuncSetAttribute(attention_f32)");
-    if (r) return r;
-    configured = true;
-  }
+  B200SVS_SMEM_OPTIN(attention_f32_kernel, "cudaFuncSetAttribute(attention_f32)");
   dim3 grid((T + kAQ - 1) / kAQ, H, B);
   attention_f32_kernel<<<grid, 256, smem, as_stream(stream)>>>(p);
   return check_launch("attention_f32_kernel");

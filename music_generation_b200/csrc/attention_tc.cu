@@ -60,16 +60,11 @@ __device__ __forceinline__ float ld16f(const void* base, size_t idx, int dtype) 
   return __half2float(reinterpret_cast<const __half*>(base)[idx]);
 }
 __device__ __forceinline__ uint32_t pk16(float a, float b, int dtype) {
-  if (dtype == B200SVS_DT_BF16) {
-    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<uint32_t*>(&h);
-  }
-  __half2 h = __floats2half2_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&h);
+  return dtype == B200SVS_DT_BF16 ? cvt_bf16x2_sat(a, b) : cvt_f16x2_sat(a, b);      // saturating (common.cuh)
 }
 __device__ __forceinline__ float rt16(float a, int dtype) {   // round trip through the 16-bit type
-  if (dtype == B200SVS_DT_BF16) return __bfloat162float(__float2bfloat16_rn(a));
-  return __half2float(__float2half_rn(a));
+  if (dtype == B200SVS_DT_BF16) return __bfloat162float(cvt_bf16_sat(a));
+  return __half2float(cvt_f16_sat(a));
 }
 __device__ __forceinline__ float ex2f(float x) {              // 2^x, 2 ulp; ex2(-inf) = 0
   float y;
@@ -493,15 +488,12 @@ constexpr int kPrepRows = 64;
 template <bool BF>
 __device__ __forceinline__ void prep_cvt2(float a, float b, uint32_t& hi, uint32_t& lo) {
   if (BF) {
-    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-    hi = *reinterpret_cast<uint32_t*>(&h);
+    hi = cvt_bf16x2_sat(a, b);
     lo = 0;
   } else {
-    const __half2 h = __floats2half2_rn(a, b);
-    const float2 hf = __half22float2(h);
-    const __half2 l = __floats2half2_rn(a - hf.x, b - hf.y);
-    hi = *reinterpret_cast<const uint32_t*>(&h);
-    lo = *reinterpret_cast<const uint32_t*>(&l);
+    hi = cvt_f16x2_sat(a, b);
+    const float2 hf = __half22float2(*reinterpret_cast<const __half2*>(&hi));
+    lo = cvt_f16x2_sat(a - hf.x, b - hf.y);
   }
 }
 template <bool BF>
@@ -610,20 +602,10 @@ extern "C" int b200svs_attention_tc(const void* qk_hi, const void* qk_lo, const 
                       sizeof(AttnBars) + 1024;
   dim3 grid((T + kTQ - 1) / kTQ, H, B);
   if (split) {
-    static bool cfg = false;
-    if (!cfg) {
-      int r = check_cuda(cudaFuncSetAttribute(attention_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "cudaFuncSetAttribute(attention_tc<split>)");
-      if (r) return r;
-      cfg = true;
-    }
+    B200SVS_SMEM_OPTIN(attention_tc_kernel<true>, "cudaFuncSetAttribute(attention_tc<split>)");
     attention_tc_kernel<true><<<grid, kAttnThreads, smem, as_stream(stream)>>>(tmQ[0], tmK[0], tmV[0], tmQ[1], tmK[1], tmV[1], p);
   } else {
-    static bool cfg = false;
-    if (!cfg) {
-      int r = check_cuda(cudaFuncSetAttribute(attention_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "cudaFuncSetAttribute(attention_tc)");
-      if (r) return r;
-      cfg = true;
-    }
+    B200SVS_SMEM_OPTIN(attention_tc_kernel<false>, "cudaFuncSetAttribute(attention_tc)");
     attention_tc_kernel<false><<<grid, kAttnThreads, smem, as_stream(stream)>>>(tmQ[0], tmK[0], tmV[0], tmQ[1], tmK[1], tmV[1], p);
   }
   return check_launch("attention_tc_kernel");

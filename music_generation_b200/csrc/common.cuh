@@ -346,6 +346,34 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n, bool bf16) {
 __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// ---------------------------------------------------------------- 16-bit conversions
+// fp32 -> fp16 with saturation to +-65504 instead of overflow to inf (one F2FP.SATFINITE; NaN stays NaN): a trained
+// checkpoint with one |x| > 65504 must give a clipped sample, not a NaN waveform.  bf16 has fp32's
+// exponent range; its conversion saturates the same way for symmetry.
+__device__ __forceinline__ uint32_t cvt_f16x2_sat(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ uint32_t cvt_bf16x2_sat(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ __half cvt_f16_sat(float v) {
+  unsigned short h;
+  asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(h) : "f"(v));
+  return __ushort_as_half(h);
+}
+__device__ __forceinline__ __nv_bfloat16 cvt_bf16_sat(float v) {
+  unsigned short h;
+  asm("cvt.rn.satfinite.bf16.f32 %0, %1;" : "=h"(h) : "f"(v));
+  return __ushort_as_bfloat16(h);
+}
+// Overflow canary on packed fp16 pairs: bit 15 of a half of ((p & 0x7FFF7FFF) + 0x04010401) is set iff that half is
+// >= 0x7BFF in magnitude bits, i.e. saturated (65504) or NaN.  OR the results, test `& 0x80008000` once per launch.
+__device__ __forceinline__ uint32_t sat_probe_f16x2(uint32_t p) { return (p & 0x7FFF7FFFu) + 0x04010401u; }
+
 // ---------------------------------------------------------------- math
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + __expf(-x)); }
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }

@@ -112,9 +112,9 @@ __global__ void __launch_bounds__(256) conv1d_f32_kernel(const ConvF32Params p) 
       if (ep.out16) {
         const float o = ep.post_lrelu ? lrelu(v, ep.post_slope) : v;
         if (ep.out16_dtype == B200SVS_DT_BF16)
-          reinterpret_cast<__nv_bfloat16*>(ep.out16)[row * ep.out16_ld + c] = __float2bfloat16_rn(o);
+          reinterpret_cast<__nv_bfloat16*>(ep.out16)[row * ep.out16_ld + c] = cvt_bf16_sat(o);
         else
-          reinterpret_cast<__half*>(ep.out16)[row * ep.out16_ld + c] = __float2half_rn(o);
+          reinterpret_cast<__half*>(ep.out16)[row * ep.out16_ld + c] = cvt_f16_sat(o);
       }
     }
   }

@@ -71,6 +71,7 @@ struct ConvTcParams {
   int tmem_cols;
   int ksub;                                // K=16 MMA steps per K chunk (4, or fewer when Cin < 64)
   uint32_t idesc;
+  unsigned int* sat_events;                // overflow canary: += 1 per epilogue thread that stored a saturated / NaN fp16 value
   long long* trace;                        // diagnostic: [grid][trace_cap][16] clock64 stamps (NULL: off)
   int trace_cap;
   b200svs_epilogue ep;
@@ -94,15 +95,6 @@ __device__ __forceinline__ float act_fn(float v) {
   return v;
 }
 
-__device__ __forceinline__ uint32_t pack16(float a, float b, int dtype) {
-  if (dtype == B200SVS_DT_BF16) {
-    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<uint32_t*>(&h);
-  }
-  __half2 h = __floats2half2_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&h);
-}
-
 __device__ __forceinline__ float4 lds128(uint32_t a) {
   float4 v;
   asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
@@ -114,14 +106,10 @@ __device__ __forceinline__ void sts128(uint32_t a, float x, float y, float z, fl
 __device__ __forceinline__ void sts128u(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
 }
+// saturating conversions (common.cuh): an fp16 overflow clips to +-65504 instead of becoming inf
 template <bool BF>
 __device__ __forceinline__ uint32_t pack2(float a, float b) {
-  if (BF) {
-    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<uint32_t*>(&h);
-  }
-  __half2 h = __floats2half2_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&h);
+  return BF ? cvt_bf16x2_sat(a, b) : cvt_f16x2_sat(a, b);
 }
 
 // packed fp32x2 arithmetic (sm_100: FADD2 / FMUL2, one issue slot for two lanes' worth of fp32 work)
@@ -235,6 +223,8 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
   const uint32_t r2h_delta = static_cast<uint32_t>(p.slot_r2_off - p.slot16_off);
   const float rinv = (R16 && ep.res16_unlrelu > 1.0f) ? ep.res16_unlrelu : 1.0f;   // min(r, r * 1) == r: no branch
 
+  uint32_t sat = 0;          // fp16 overflow canary (sat_probe_f16x2 of every packed pair this thread stores)
+
   auto process = [&](const uint32_t* a0, const uint32_t* a1, uint32_t slot_u, int pcol, int b, float s, int h) {
     float v[16];
     const uint32_t ba = bias_u + pcol * 4;
@@ -337,7 +327,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
       if (has_out16r) {
         uint32_t p16[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) p16[i] = pack2<BF>(v[2 * i], v[2 * i + 1]);
+        for (int i = 0; i < 8; ++i) { p16[i] = pack2<BF>(v[2 * i], v[2 * i + 1]); if (!BF) sat |= sat_probe_f16x2(p16[i]); }
         sts128u(slot_u + raw_delta + off16[h][0], p16[0], p16[1], p16[2], p16[3]);
         sts128u(slot_u + raw_delta + off16[h][1], p16[4], p16[5], p16[6], p16[7]);
       }
@@ -347,12 +337,12 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
 #pragma unroll
       for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], v[i] * slope);     // leaky-ReLU, 0 < slope <= 1
 #pragma unroll
-      for (int i = 0; i < 8; ++i) p16[i] = pack2<BF>(v[2 * i], v[2 * i + 1]);
+      for (int i = 0; i < 8; ++i) { p16[i] = pack2<BF>(v[2 * i], v[2 * i + 1]); if (!BF) sat |= sat_probe_f16x2(p16[i]); }
       sts128u(slot_u + off16[h][0], p16[0], p16[1], p16[2], p16[3]);
       sts128u(slot_u + off16[h][1], p16[4], p16[5], p16[6], p16[7]);
       if constexpr (SPLIT) {   // lo = v - hi, so that hi + lo == v to ~2^-22
 #pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] -= __half2float(__float2half_rn(v[i]));
+        for (int i = 0; i < 16; ++i) v[i] -= __half2float(cvt_f16_sat(v[i]));
 #pragma unroll
         for (int i = 0; i < 8; ++i) p16[i] = pack2<false>(v[2 * i], v[2 * i + 1]);
         sts128u(slot_u + kSlot16Bytes + off16[h][0], p16[0], p16[1], p16[2], p16[3]);
@@ -415,7 +405,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
     uint32_t p16[8];
     if constexpr (OUTS == 2) {   // un-activated 16-bit result (out16r area of the slot)
 #pragma unroll
-      for (int i = 0; i < 8; ++i) p16[i] = pack2<BF>(v2[i].x, v2[i].y);
+      for (int i = 0; i < 8; ++i) { p16[i] = pack2<BF>(v2[i].x, v2[i].y); if (!BF) sat |= sat_probe_f16x2(p16[i]); }
       sts128u(slot_u + raw_delta + o16[0], p16[0], p16[1], p16[2], p16[3]);
       sts128u(slot_u + raw_delta + o16[1], p16[4], p16[5], p16[6], p16[7]);
     } else {
@@ -424,6 +414,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
       for (int i = 0; i < 8; ++i) {
         const float2 m = mul2(v2[i], slope2);
         p16[i] = pack2<BF>(fmaxf(v2[i].x, m.x), fmaxf(v2[i].y, m.y));
+        if (!BF) sat |= sat_probe_f16x2(p16[i]);
       }
       sts128u(slot_u + o16[0], p16[0], p16[1], p16[2], p16[3]);
       sts128u(slot_u + o16[1], p16[4], p16[5], p16[6], p16[7]);
@@ -508,6 +499,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
       if (lane == 0) { if (remote_te) mbar_arrive_remote(&bars->tmem_empty[acc], 0); else mbar_arrive(&bars->tmem_empty[acc]); }
       if (threadIdx.x == 128) trace_stamp(p, it, 6, clock64());
     }
+    if ((sat & 0x80008000u) && p.sat_events) atomicAdd(p.sat_events, 1u);
     return;
   }
 
@@ -592,6 +584,7 @@ __device__ __forceinline__ void epilogue_loop(const ConvTcParams& p, TcBarriers*
     if (lane == 0) { if (remote_te) mbar_arrive_remote(&bars->tmem_empty[acc], 0); else mbar_arrive(&bars->tmem_empty[acc]); }
     if (threadIdx.x == 128) trace_stamp(p, it, 6, clock64());
   }
+  if ((sat & 0x80008000u) && p.sat_events) atomicAdd(p.sat_events, 1u);
 }
 
 template <int RES, bool BF>
@@ -1197,6 +1190,7 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
   p.idesc = make_idesc_f16(p.pair ? 256 : 128, a->block_n, a->x_dtype == B200SVS_DT_BF16);
   p.ep = ep;
   p.trace = g_trace; p.trace_cap = g_trace_cap;
+  p.sat_events = sat_counter();
 
   const int el16 = a->x_dtype == B200SVS_DT_BF16 ? 1 : 0;
   CUtensorMap tmA, tmW, tmR, tmR2, tmO32, tmO16, tmR16, tmO16r;
@@ -1258,14 +1252,8 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
 
   const size_t smem = (size_t)p.a_stages * p.a_stage_bytes + (size_t)p.w_stages * p.w_stage_bytes +
                       (size_t)p.n_slots * p.slot_bytes + 512 + bias_bytes + 1024;
-  static size_t configured[2] = {0, 0};
-  if (smem > configured[p.pair ? 1 : 0]) {
-    int r = check_cuda(p.pair ? cudaFuncSetAttribute(conv1d_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
-                              : cudaFuncSetAttribute(conv1d_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
-                       "cudaFuncSetAttribute(conv1d_tc)");
-    if (r) return r;
-    configured[p.pair ? 1 : 0] = smem;
-  }
+  if (p.pair) B200SVS_SMEM_OPTIN(conv1d_tc_kernel<true>, "cudaFuncSetAttribute(conv1d_tc<pair>)");
+  else B200SVS_SMEM_OPTIN(conv1d_tc_kernel<false>, "cudaFuncSetAttribute(conv1d_tc)");
   int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
   if (p.pair) grid = (grid + 1) & ~1;      // whole clusters; a CTA without a tile of its own runs the phantom
   // launched with programmatic stream serialization (PDL): the kernel may start while its predecessor in the

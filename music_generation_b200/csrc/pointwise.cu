@@ -7,16 +7,16 @@
 namespace b200svs {
 
 __device__ __forceinline__ void store16(void* base, size_t idx, float v, int dtype) {
-  if (dtype == B200SVS_DT_BF16) reinterpret_cast<__nv_bfloat16*>(base)[idx] = __float2bfloat16_rn(v);
-  else reinterpret_cast<__half*>(base)[idx] = __float2half_rn(v);
+  if (dtype == B200SVS_DT_BF16) reinterpret_cast<__nv_bfloat16*>(base)[idx] = cvt_bf16_sat(v);
+  else reinterpret_cast<__half*>(base)[idx] = cvt_f16_sat(v);
 }
 // 16-bit store of column c of a C-column row at `row_off`; B200SVS_DT_F16_SPLIT writes [hi | lo | hi]
 __device__ __forceinline__ void store16c(void* base, size_t row_off, int c, int C, float v, int dtype) {
   if (dtype != B200SVS_DT_F16_SPLIT) { store16(base, row_off + c, v, dtype); return; }
   __half* o = reinterpret_cast<__half*>(base) + row_off;
-  const __half hi = __float2half_rn(v);
+  const __half hi = cvt_f16_sat(v);
   o[c] = hi;
-  o[C + c] = __float2half_rn(v - __half2float(hi));
+  o[C + c] = cvt_f16_sat(v - __half2float(hi));
   o[2 * C + c] = hi;
 }
 __device__ __forceinline__ float load16(const void* base, size_t idx, int dtype) {
@@ -78,13 +78,20 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LnParams p) {
 __global__ void text_embed_kernel(const int64_t* phon, const int64_t* pitch, const int64_t* tone, const float* dur,
                                   const float* e_ph, const float* e_pitch, const float* e_tone, const float* w_dur,
                                   const float* b_dur, const int64_t* x_lengths, int32_t* lens32, float* out, int B,
-                                  int P, int C, float scale) {
+                                  int P, int C, float scale, int n_ph, int n_pitch, int n_tone, int32_t* status) {
   const int bp = blockIdx.x;
   const int b = bp / P, i = bp - b * P;
   const int len = static_cast<int>(x_lengths[b]);
   if (i == 0 && threadIdx.x == 0 && lens32) lens32[b] = len;
   const bool live = i < len;
-  const long long ip = phon[bp], it = pitch[bp], is = tone[bp];
+  long long ip = phon[bp], it = pitch[bp], is = tone[bp];
+  // nn.Embedding raises on an id outside its table; here a live out-of-range id sets status[1] bit 0 (the host raises
+  // at its next sync) and is clamped so that the read stays inside the table
+  const bool bad = live && (ip < 0 || ip >= n_ph || it < 0 || it >= n_pitch || is < 0 || is >= n_tone);
+  if (bad && threadIdx.x == 0 && status) atomicOr(status + 1, 1);
+  ip = ip < 0 ? 0 : (ip >= n_ph ? n_ph - 1 : ip);
+  it = it < 0 ? 0 : (it >= n_pitch ? n_pitch - 1 : it);
+  is = is < 0 ? 0 : (is >= n_tone ? n_tone - 1 : is);
   const float d = dur[bp];
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     // (emb_phoneme + emb_note_duration + emb_note_pitch + emb_phone_shengdiao) * sqrt(C), same add order
@@ -109,7 +116,8 @@ __global__ void duration_quantize_kernel(const float* pred, const float* note_du
 
 // ------------------------------------------------------------------ length regulator
 // scan: one warp per utterance, inclusive prefix sum of clamped durations.
-__global__ void lr_scan_kernel(const int64_t* dur, int B, int P, int32_t* ends, int64_t* mel64, int32_t* mel32) {
+__global__ void lr_scan_kernel(const int64_t* dur, int B, int P, int32_t* ends, int64_t* mel64, int32_t* mel32,
+                               int32_t* status) {
   const int b = blockIdx.x;
   const int lane = threadIdx.x;
   int carry = 0;
@@ -129,6 +137,7 @@ __global__ void lr_scan_kernel(const int64_t* dur, int B, int P, int32_t* ends, 
   if (lane == 0) {
     if (mel64) mel64[b] = carry;
     if (mel32) mel32[b] = carry;
+    if (status) atomicMax(status, carry);      // status[0] = max_b mel_len[b]: the padded frame count T
   }
 }
 // gather: one warp per output frame; binary search of t in ends[b,:], then a 128-bit row copy.
@@ -190,7 +199,7 @@ __device__ __forceinline__ long long f0_coarse_of(float lf0) {
 __global__ void __launch_bounds__(256) f0_embed_kernel(const float* log_f0, const int64_t* coarse_in, const float* f0_emb,
                                                        const int32_t* lens, int64_t* coarse_out, float* out32,
                                                        int out32_ld, void* out16, int out16_ld, int dt, int B, int T,
-                                                       int C) {
+                                                       int C, int n_rows) {
   const long long row = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= static_cast<long long>(B) * T) return;
@@ -198,6 +207,7 @@ __global__ void __launch_bounds__(256) f0_embed_kernel(const float* log_f0, cons
   const bool live = lens ? t < lens[b] : true;
   long long k = coarse_in ? coarse_in[row] : f0_coarse_of(log_f0[row]);
   if (lane == 0 && coarse_out) coarse_out[row] = k;
+  k = k < 0 ? 0 : (k >= n_rows ? n_rows - 1 : k);      // a user f0_score outside the table (validated on the host) never reads out of bounds
   const float* src = f0_emb + static_cast<size_t>(k) * C;
   for (int c = lane; c < C; c += 32) {
     const float v = live ? src[c] : 0.f;
@@ -371,12 +381,14 @@ int b200svs_layernorm(const float* x, int32_t x_ld, const float* res, int32_t re
 int b200svs_text_embed(const int64_t* phon, const int64_t* pitch, const int64_t* tone, const float* dur,
                        const float* e_ph, const float* e_pitch, const float* e_tone, const float* w_dur,
                        const float* b_dur, const int64_t* x_lengths, int32_t* lens32_out, float* out, int32_t B,
-                       int32_t P, int32_t C, void* stream) {
+                       int32_t P, int32_t C, int32_t n_ph, int32_t n_pitch, int32_t n_tone, int32_t* status, void* stream) {
   B200SVS_REQUIRE(phon && pitch && tone && dur && e_ph && e_pitch && e_tone && w_dur && b_dur && x_lengths && out,
                   "text_embed: null argument");
   B200SVS_REQUIRE(B > 0 && P > 0 && C > 0, "text_embed: B=%d P=%d C=%d", B, P, C);
+  B200SVS_REQUIRE(n_ph > 0 && n_pitch > 0 && n_tone > 0, "text_embed: table sizes %d %d %d", n_ph, n_pitch, n_tone);
   text_embed_kernel<<<B * P, 64, 0, as_stream(stream)>>>(phon, pitch, tone, dur, e_ph, e_pitch, e_tone, w_dur, b_dur,
-                                                        x_lengths, lens32_out, out, B, P, C, sqrtf((float)C));
+                                                        x_lengths, lens32_out, out, B, P, C, sqrtf((float)C), n_ph, n_pitch,
+                                                        n_tone, status);
   return check_launch("text_embed_kernel");
 }
 
@@ -387,9 +399,9 @@ int b200svs_duration_quantize(const float* pred, const float* note_dur, int64_t*
 }
 
 int b200svs_lr_scan(const int64_t* dur, int32_t B, int32_t P, int32_t* ends, int64_t* mel_len64, int32_t* mel_len32,
-                    void* stream) {
+                    int32_t* status, void* stream) {
   B200SVS_REQUIRE(dur && ends && B > 0 && P > 0, "lr_scan: bad argument");
-  lr_scan_kernel<<<B, 32, 0, as_stream(stream)>>>(dur, B, P, ends, mel_len64, mel_len32);
+  lr_scan_kernel<<<B, 32, 0, as_stream(stream)>>>(dur, B, P, ends, mel_len64, mel_len32, status);
   return check_launch("lr_scan_kernel");
 }
 
@@ -416,11 +428,11 @@ int b200svs_add_pos_mask(const float* x, int32_t x_ld, const float* pos, const i
 
 int b200svs_f0_embed(const float* log_f0, const int64_t* coarse_in, const float* f0_emb, const int32_t* lens,
                      int64_t* coarse_out, float* out32, int32_t out32_ld, void* out16, int32_t out16_ld,
-                     int32_t out16_dtype, int32_t B, int32_t T, int32_t C, void* stream) {
-  B200SVS_REQUIRE((log_f0 || coarse_in) && f0_emb && (out32 || out16) && B > 0 && T > 0, "f0_embed: bad argument");
+                     int32_t out16_dtype, int32_t B, int32_t T, int32_t C, int32_t n_rows, void* stream) {
+  B200SVS_REQUIRE((log_f0 || coarse_in) && f0_emb && (out32 || out16) && B > 0 && T > 0 && n_rows > 0, "f0_embed: bad argument");
   const long long rows = static_cast<long long>(B) * T;
   f0_embed_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, as_stream(stream)>>>(
-      log_f0, coarse_in, f0_emb, lens, coarse_out, out32, out32_ld, out16, out16_ld, out16_dtype, B, T, C);
+      log_f0, coarse_in, f0_emb, lens, coarse_out, out32, out32_ld, out16, out16_ld, out16_dtype, B, T, C, n_rows);
   return check_launch("f0_embed_kernel");
 }
 

@@ -7,6 +7,7 @@
 // out[128][64] = A[shift : shift+128, 0:64] . B[0:64, 0:64]^T   (fp16 operands, fp32 accumulate)
 #include "common.cuh"
 #include "api_internal.h"
+#include "../../include/b200svs_debug.h"
 
 namespace b200svs {
 

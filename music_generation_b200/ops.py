@@ -192,20 +192,20 @@ def layernorm(x, gamma, beta, lens, out32=None, out16=None, res=None, eps=1e-5, 
               out16_code(out16, split16), B, T, c, _stream())
 
 
-def text_embed(phon, pitch, tone, dur, e_ph, e_pitch, e_tone, w_dur, b_dur, x_lengths, lens32, out):
+def text_embed(phon, pitch, tone, dur, e_ph, e_pitch, e_tone, w_dur, b_dur, x_lengths, lens32, out, status=None):
     B, P = phon.shape
     _lib.call("b200svs_text_embed", _ptr(phon), _ptr(pitch), _ptr(tone), _ptr(dur), _ptr(e_ph), _ptr(e_pitch),
               _ptr(e_tone), _ptr(w_dur), _ptr(b_dur), _ptr(x_lengths), _ptr(lens32), _ptr(out), B, P,
-              out.shape[-1], _stream())
+              out.shape[-1], e_ph.shape[0], e_pitch.shape[0], e_tone.shape[0], _ptr(status), _stream())
 
 
 def duration_quantize(pred, note_dur, out):
     _lib.call("b200svs_duration_quantize", _ptr(pred), _ptr(note_dur), _ptr(out), pred.numel(), _stream())
 
 
-def lr_scan(dur, ends, mel64, mel32):
+def lr_scan(dur, ends, mel64, mel32, status=None):
     B, P = dur.shape
-    _lib.call("b200svs_lr_scan", _ptr(dur), B, P, _ptr(ends), _ptr(mel64), _ptr(mel32), _stream())
+    _lib.call("b200svs_lr_scan", _ptr(dur), B, P, _ptr(ends), _ptr(mel64), _ptr(mel32), _ptr(status), _stream())
 
 
 def lr_gather(h, ends, mel32, out, index_out=None):
@@ -227,7 +227,7 @@ def f0_embed(log_f0, coarse_in, table, lens, coarse_out, out32=None, out16=None)
     B, T, c = o.shape
     _lib.call("b200svs_f0_embed", _ptr(log_f0), _ptr(coarse_in), _ptr(table), _ptr(lens), _ptr(coarse_out),
               _ptr(out32), _btc(out32, "out32"), _ptr(out16), _btc(out16, "out16"),
-              0 if out16 is None else dt_code(out16.dtype), B, T, c, _stream())
+              0 if out16 is None else dt_code(out16.dtype), B, T, c, table.shape[0], _stream())
 
 
 def sample_prior(stats, noise_bct, noise_scale, zp32=None, zp16=None):

@@ -55,7 +55,8 @@ class Synthesiser:
         total = int(samples.sum().item())
         song = torch.empty(LEAD_IN + total, device=dev, dtype=torch.int16)
         scales = torch.empty(len(lines), 2, device=dev, dtype=torch.float32)
-        ops.song_assemble(o, mel_len, offsets.contiguous(), song, hop=self.net_g.hop, lead_in=LEAD_IN,
-                          legacy_scalar=self.legacy_scalar, scales_out=scales)
+        with torch.cuda.device(dev):          # the library launches on the current device's stream
+            ops.song_assemble(o, mel_len, offsets.contiguous(), song, hop=self.net_g.hop, lead_in=LEAD_IN,
+                              legacy_scalar=self.legacy_scalar, scales_out=scales)
         self.last = {"o": o, "mel_len": mel_len, "offsets": offsets, "scales": scales}
         return song

@@ -26,6 +26,14 @@ def _require_cuda(t):
         raise RuntimeError("SynthesizerTrn.infer: inputs must be CUDA tensors - this build has no CPU path")
 
 
+def _device_guard(dev):
+    """Makes `dev` the current CUDA device for the duration of a call: the kernels of libb200svs launch on the current
+    device's stream (ops._stream) and must match the device of the tensors they are handed."""
+    if dev.type != "cuda":
+        raise RuntimeError("SynthesizerTrn.infer: the model is not on a CUDA device (call .cuda() / .to(device))")
+    return torch.cuda.device(dev)
+
+
 class _Enc:
     """Packed weights of one attentions.Encoder layer."""
     __slots__ = ("qkv", "o", "ffn1", "ffn2", "rel_k", "rel_v", "ln1", "ln2")
@@ -196,6 +204,7 @@ class SynthesizerTrn(nn.Module):
         P["dp_proj"] = conv(dp + ".proj", f32=True)
         tp = "text_post_net"
         P["pos"] = sd[tp + ".position_embeddings.weight"].contiguous().to(dev)
+        P["zero_pos"] = torch.zeros(512, self.hidden_channels, device=dev)      # "no position table" operand of add_pos_mask
         f0_split = self.f0_precision == "split"
         P["f0_enc"] = enc(tp + ".f0_predictor.encoder", 6, not f0_split, split=f0_split)
         P["f0_mode"] = "split" if f0_split else "f32"
@@ -514,29 +523,66 @@ class SynthesizerTrn(nn.Module):
     # ------------------------------------------------------------------ the public entry point
     @torch.no_grad()
     def infer(self, x, x_lengths, note_pitch_id, note_duration, phone_shengdiao, ph_dur=None, lf0=None, sid=None,
-              noise_scale=1, length_scale=1, noise_scale_w=1., max_len=None, *, noise=None, g=None, f0_score=None):
+              noise_scale=1, length_scale=1, noise_scale_w=1., max_len=None, *, noise=None, g=None, f0_score=None,
+              check_range=False):
         """Same signature and result tuple as the reference (models_ae.py:608-651 / models.py:622-673).
         Extensions (keyword-only, not in the reference): `noise` [B,C,T] replaces torch.randn_like for
         parity runs; `g` [B,gin,1] speaker conditioning (the reference hard-codes g=None, :634);
-        `f0_score` [B,T] int64 overrides the predicted coarse f0 (TextPostNet.forward's own argument)."""
+        `f0_score` [B,T] int64 overrides the predicted coarse f0 (TextPostNet.forward's own argument);
+        `check_range`: read the library's fp16 overflow canary after the call (one extra sync) into
+        last_aux["saturation_events"] (0 = no 16-bit tensor of this forward clipped).
+
+        The kernels launch on the device of the model's parameters (SURVEY 8b "device conventions"), whatever the
+        current device is; inputs on another device are an error, id / length tensors are normalised to int64 like
+        nn.Embedding / sequence_mask accept them."""
         _require_cuda(x)
+        dev = self.device
+        for name, t in (("x", x), ("x_lengths", x_lengths), ("note_pitch_id", note_pitch_id),
+                        ("note_duration", note_duration), ("phone_shengdiao", phone_shengdiao)):
+            if t.device != dev:
+                raise RuntimeError(f"SynthesizerTrn.infer: {name} is on {t.device}, the model on {dev}")
+        with _device_guard(dev):
+            if check_range:
+                _lib.check(_lib.lib().b200svs_saturation_events(None, 1, ops._stream()), "saturation_events")
+            res = self._infer(x, x_lengths, note_pitch_id, note_duration, phone_shengdiao, ph_dur, lf0, noise_scale, max_len,
+                              noise, g, f0_score)
+            if check_range:
+                import ctypes
+                n = ctypes.c_uint32(0)
+                _lib.check(_lib.lib().b200svs_saturation_events(ctypes.byref(n), 0, ops._stream()), "saturation_events")
+                self.last_aux["saturation_events"] = int(n.value)
+        return res
+
+    def _infer(self, x, x_lengths, note_pitch_id, note_duration, phone_shengdiao, ph_dur, lf0, noise_scale, max_len,
+               noise, g, f0_score):
         P = self._packed or self._pack()
-        dev, dt = x.device, self.operand_dtype
+        dev, dt = self.device, self.operand_dtype
         f32 = torch.float32
         B, Pn = x.shape
         H = self.hidden_channels
-        x = x.contiguous(); note_pitch_id = note_pitch_id.contiguous(); phone_shengdiao = phone_shengdiao.contiguous()
-        note_duration = note_duration.contiguous().float(); x_lengths = x_lengths.contiguous()
+        i64 = lambda t: t.to(device=dev, dtype=torch.int64).contiguous()
+        y_dtype = x.dtype                     # y_mask takes x's dtype (commons.sequence_mask(...).to(x.dtype), models_ae.py:632)
+        x, note_pitch_id, phone_shengdiao, x_lengths = i64(x), i64(note_pitch_id), i64(phone_shengdiao), i64(x_lengths)
+        note_duration = note_duration.contiguous().float()
+        if f0_score is not None:              # user-supplied buckets: validated here (nn.Embedding would raise)
+            f0_score = i64(f0_score)
+            lo, hi = int(f0_score.min()), int(f0_score.max())
+            if lo < 0 or hi >= P["f0_emb"].shape[0]:
+                raise IndexError(f"f0_score out of range [0, {P['f0_emb'].shape[0]}): min {lo} max {hi}")
         aux = self.last_aux = {}
+        status = torch.zeros(2, device=dev, dtype=torch.int32)     # [0] max frames T (lr_scan), [1] bad-id flag (text_embed)
 
         # 1. TextEncoder (models_ae.py:203-220), fp32
         plen = torch.empty(B, device=dev, dtype=torch.int32)
         h = torch.empty(B, Pn, H, device=dev, dtype=f32)
-        ops.text_embed(x, note_pitch_id, phone_shengdiao, note_duration, *P["emb"], *P["emb_dur"], x_lengths, plen, h)
+        ops.text_embed(x, note_pitch_id, phone_shengdiao, note_duration, *P["emb"], *P["emb_dur"], x_lengths, plen, h,
+                       status=status)
         hs = None
         if P["text_mode"] == "split":     # fp16 (hi, lo) split copy for the tensor-core path: (h + 0) * mask == h
             hs = torch.empty(B, Pn, 3 * H, device=dev, dtype=torch.float16)
-            ops.add_pos_mask(h, torch.zeros(Pn, H, device=dev, dtype=f32), plen, out16=hs, split16=True)
+            if P["zero_pos"].shape[0] < Pn:
+                P["zero_pos"] = torch.zeros(Pn, H, device=dev, dtype=f32)
+            ops.add_pos_mask(h, P["zero_pos"], plen, out16=hs, split16=True)
         self._encoder(P["text_enc"], h, hs, plen, P["text_mode"])
 
         # 2. durations (models_ae.py:622-627)
@@ -561,8 +607,11 @@ class SynthesizerTrn(nn.Module):
         ends = torch.empty(B, Pn, device=dev, dtype=torch.int32)
         mel_len = torch.empty(B, device=dev, dtype=torch.int64)
         mlen = torch.empty(B, device=dev, dtype=torch.int32)
-        ops.lr_scan(durations, ends, mel_len, mlen)
-        T = int(mel_len.max().item())
+        ops.lr_scan(durations, ends, mel_len, mlen, status=status)
+        T, bad_ids = status.tolist()           # the one host sync of infer (the reference does B*P .item() calls)
+        if bad_ids:
+            raise IndexError("SynthesizerTrn.infer: a phoneme / note-pitch / tone id is outside its embedding table "
+                             "(index out of range in self)")
         if T <= 0:
             raise RuntimeError("SynthesizerTrn.infer: every utterance has zero frames")
         n_pos = P["pos"].shape[0]
@@ -570,7 +619,7 @@ class SynthesizerTrn(nn.Module):
             # the reference fails here too: position table has 2000 rows (text_post_net.py:26,69-72)
             raise RuntimeError(f"The size of tensor a ({T}) must match the size of tensor b ({n_pos}) at "
                                f"non-singleton dimension 1 (frames exceed the position table)")
-        y_mask = (torch.arange(T, device=dev).unsqueeze(0) < mel_len.unsqueeze(1)).unsqueeze(1).to(x.dtype)
+        y_mask = (torch.arange(T, device=dev).unsqueeze(0) < mel_len.unsqueeze(1)).unsqueeze(1).to(y_dtype)
         Ci = self.inter_channels
 
         def frame_level(h, ends, mlen, noise, g, f0_score):

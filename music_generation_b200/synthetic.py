@@ -58,13 +58,15 @@ def make_noise(batch, channels, frames, seed=1234, device="cpu"):
     return torch.randn(batch, channels, frames, generator=g).to(device)
 
 
-def apply_recipe(sd, seed=1234, generator_gain=0.7, f0_bias=math.log(250.0), positions=None, pre_gain=None):
+def apply_recipe(sd, seed=1234, generator_gain=0.7, f0_bias=math.log(250.0), positions=None, pre_gain=None, post_gain=1.0):
     """Seeded, in-place edit of a state-dict (SURVEY.md 7.3-A / 8c "weight recipe").
 
     * spec_flow.*.post.{weight,bias} ~ N(0, 0.05)   (zero-init in the reference => flow vacuous)
     * decoder weight_v / weight_g rescaled so activations stay O(1) (He-style gain on g)
     * f0_predictor.output_layer.bias = log(250)      (spread f0 buckets)
     * optional: enlarge the 2000-row position table for T > 2000
+    * pre_gain / post_gain scale conv_pre / conv_post: pre_gain * s with post_gain / s keeps the waveform O(1) while the
+      Generator's activations grow by s (numeric-range tests: fp16 tops out at 65504)
     """
     g = torch.Generator().manual_seed(seed + 7)
     for k in list(sd.keys()):
@@ -85,7 +87,7 @@ def apply_recipe(sd, seed=1234, generator_gain=0.7, f0_bias=math.log(250.0), pos
                 fan = w[0].numel()
                 # generator input std at random init: spec_hidden ~0.14 (ae), z ~1.0 (v4, no spec_proj)
                 default_pre = 4.0 if "spec_proj.weight" in sd else 0.6
-                gain = (pre_gain or default_pre) if "pre" in k else 1.0
+                gain = (pre_gain or default_pre) if "pre" in k else post_gain
                 sd[k] = torch.randn(w.shape, generator=g) * gain * math.sqrt(1.0 / fan)
             elif k.endswith(".bias"):
                 sd[k] = torch.randn(sd[k].shape, generator=g) * 0.05

@@ -31,9 +31,23 @@ CASES = {
 }
 
 
-def state_dict_for(variant, seed=1234):
+# speaker-conditioned stages (the reference's infer hard-codes g=None, models_ae.py:634, so the g path of
+# ResidualCouplingBlock / SpecDecoder / Generator is pinned stage by stage): name -> (batch, frames, gin, seed)
+G_CASES = {"ae_gin256_stages": (2, 40, 256, 777)}
+
+
+def g_case_inputs(name):
+    b, t, gin, seed = G_CASES[name]
+    g_ = torch.Generator().manual_seed(seed)
+    z_p = torch.randn(b, 192, t, generator=g_)
+    mel_len = torch.tensor([t] + [max(1, t - 13 * i) for i in range(1, b)], dtype=torch.int64)
+    g = torch.randn(b, gin, 1, generator=g_)
+    return z_p, mel_len, g, gin
+
+
+def state_dict_for(variant, seed=1234, gin=0):
     mod = models_ae if variant == "ae" else models
-    net = mod.SynthesizerTrn(100, 513, 48, **HP, seed=seed)
+    net = mod.SynthesizerTrn(100, 513, 48, **HP, seed=seed, gin_channels=gin)
     sd = {k: v.clone() for k, v in net.state_dict().items()}
     return synthetic.apply_recipe(sd, seed=seed)
 
@@ -74,7 +88,23 @@ def main():
             rec["spec"] = res[4][:, ::16].numpy()
         np.savez_compressed(os.path.join(out_dir, name + ".npz"), **rec)
         print(name, "T =", T, "o", tuple(o.shape), "|o|max %.3f" % o.abs().max())
-    json.dump({"cases": {k: list(v) for k, v in CASES.items()}, "torch": torch.__version__,
+    for name in G_CASES:
+        z_p, mel_len, g, gin = g_case_inputs(name)
+        sd = state_dict_for("ae", gin=gin)
+        net = ref_harness.build_reference("ae", gin_channels=gin)
+        missing = net.load_state_dict(sd, strict=True)
+        assert not missing.missing_keys and not missing.unexpected_keys
+        with torch.no_grad():
+            y_mask = (torch.arange(z_p.shape[2])[None] < mel_len[:, None]).unsqueeze(1).float()
+            z = net.spec_flow(z_p * y_mask, y_mask, g=g, reverse=True)          # models_ae.py:246-253, modules.py:152-159
+            spec = net.spec_decoder(z, mel_len, g=g)                            # ext_modules/spec_decoder.py:41-46
+            hid = net.spec_proj(spec) * y_mask
+            o = net.decoder(hid, g=g)                                           # models_ae.py:327-346 with cond (:329-330)
+        np.savez_compressed(os.path.join(out_dir, name + ".npz"), z=z.numpy(), spec=spec[:, ::8].numpy(), hid=hid.numpy(),
+                            o=o.numpy())
+        print(name, "o", tuple(o.shape), "|o|max %.3f" % o.abs().max())
+    json.dump({"cases": {k: list(v) for k, v in CASES.items()}, "g_cases": {k: list(v) for k, v in G_CASES.items()},
+               "torch": torch.__version__,
                "reference": "GuluOfficial/music_generation VISinger/models_ae.py + models.py (unmodified, CPU fp32)"},
               open(os.path.join(out_dir, "MANIFEST.json"), "w"), indent=1)
 

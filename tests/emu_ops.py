@@ -148,8 +148,14 @@ def layernorm(x, gamma, beta, lens, out32=None, out16=None, res=None, eps=1e-5, 
     _store(out16, y, split16)
 
 
-def text_embed(phon, pitch, tone, dur, e_ph, e_pitch, e_tone, w_dur, b_dur, x_lengths, lens32, out):
+def text_embed(phon, pitch, tone, dur, e_ph, e_pitch, e_tone, w_dur, b_dur, x_lengths, lens32, out, status=None):
     B, P = phon.shape
+    live = _mask(x_lengths, B, P).squeeze(-1) > 0
+    bad = live & ((phon < 0) | (phon >= e_ph.shape[0]) | (pitch < 0) | (pitch >= e_pitch.shape[0]) | (tone < 0) |
+                  (tone >= e_tone.shape[0]))
+    if status is not None and bool(bad.any()):
+        status[1] |= 1
+    phon, pitch, tone = (t.clamp(0, n - 1) for t, n in ((phon, e_ph.shape[0]), (pitch, e_pitch.shape[0]), (tone, e_tone.shape[0])))
     v = (e_ph[phon] + (dur.unsqueeze(-1) * w_dur + b_dur) + e_pitch[pitch] + e_tone[tone]) * math.sqrt(out.shape[-1])
     lens32.copy_(x_lengths.to(torch.int32))
     out.copy_(v * _mask(x_lengths, B, P))
@@ -159,8 +165,10 @@ def duration_quantize(pred, note_dur, out):
     out.copy_(torch.floor(pred.reshape(note_dur.shape) * note_dur / 0.0116).long())
 
 
-def lr_scan(dur, ends, mel64, mel32):
+def lr_scan(dur, ends, mel64, mel32, status=None):
     e = dur.clamp_min(0).cumsum(1)
+    if status is not None:
+        status[0] = torch.maximum(status[0], e[:, -1].max().to(torch.int32))
     ends.copy_(e.to(torch.int32))
     mel64.copy_(e[:, -1])
     mel32.copy_(e[:, -1].to(torch.int32))
@@ -223,3 +231,5 @@ def install(monkeypatch):
                  "add_pos_mask", "f0_embed", "sample_prior", "conv_post_tanh"):
         monkeypatch.setattr(real_ops, name, globals()[name])
     monkeypatch.setattr(syn, "_require_cuda", lambda t: None)
+    import contextlib
+    monkeypatch.setattr(syn, "_device_guard", lambda dev: contextlib.nullcontext())

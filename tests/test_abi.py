@@ -9,11 +9,13 @@ import torch
 
 from music_generation_b200 import _lib, ops
 
-HEADER = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "b200svs.h")
+_INC = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include")
+HEADER = os.path.join(_INC, "b200svs.h")
+DEBUG_HEADER = os.path.join(_INC, "b200svs_debug.h")       # bring-up probes: exported, not part of the product ABI
 
 
 def declared_functions():
-    src = open(HEADER).read()
+    src = open(HEADER).read() + open(DEBUG_HEADER).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     out = {}
     for m in re.finditer(r"\b(?:int|const char\*)\s+(b200svs_\w+)\s*\(([^;{]*?)\)\s*;", src, flags=re.S):
@@ -53,7 +55,7 @@ def test_struct_layout_matches_header():
 
 
 def test_abi_version(built_lib):
-    assert built_lib.b200svs_abi_version() == 1
+    assert built_lib.b200svs_abi_version() == 2
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="CPU-only check")

@@ -5,7 +5,8 @@ max-abs <= 2e-3 and SNR >= 40 dB against the fp32 reference."""
 import pytest
 import torch
 
-from common import MAX_ABS_TOL, SNR_DB_TOL, build_model, flat, load_golden, max_abs, snr_db
+from common import (MAX_ABS_TOL, SNR_DB_TOL, build_model, coarse_edge_distance, flat, load_golden, max_abs, report,
+                    snr_db)
 from music_generation_b200 import synthetic
 from oracle import visinger_oracle as vo
 from oracle.make_golden import CASES, case_inputs
@@ -45,6 +46,23 @@ def test_infer_matches_reference_golden(name):
         assert snr_db(g["spec"], res[4].cpu()[:, ::16]) > 50
 
 
+def _f0_flips_reported(tag, net, taps, ref_log_f0, res, rerun):
+    """f0_coarse is an fp32 -> int64 boundary - mismatches against the oracle are REPORTED (count in the test
+    output and gpurun_out/parity_report.json), must sit on a rounding edge of f0_to_coarse (two fp32 evaluations of the
+    same value), and only then is the waveform compared with the reference's buckets injected (announced, not silent:
+    one flipped bucket swaps one f0 embedding row, which is a different input, not a kernel error)."""
+    diff = net.last_aux["f0_coarse"].cpu() != taps["f0_coarse"]
+    mism = int(diff.sum())
+    report(f"f0_coarse_mismatches/{tag}", mism)
+    if not mism:
+        return res
+    edge = coarse_edge_distance(ref_log_f0)[diff]
+    report(f"f0_coarse_edge_distance_max/{tag}", float(edge.max()))
+    assert float(edge.max()) < 2e-3 and mism <= max(2, diff.numel() // 2000), (mism, float(edge.max()))
+    print(f"[parity] {tag}: waveform compared with the reference's f0 buckets injected for {mism} edge frame(s)")
+    return rerun(f0_score=taps["f0_coarse"].to(DEV))
+
+
 @pytest.mark.parametrize("variant,gin", [("ae", 0), ("ae", 256), ("v4", 0)])
 def test_infer_matches_oracle_ragged_batch(variant, gin):
     net, sd = build_model(variant, gin=gin, device=DEV)
@@ -61,13 +79,9 @@ def test_infer_matches_oracle_ragged_batch(variant, gin):
     torch.cuda.synchronize()
     assert torch.equal(net.last_aux["lr_index"].long().cpu(), taps["lr_index"])    # alignment indices bit-exact
     assert torch.equal(res[1].cpu(), ref[1])
-    mism = int((net.last_aux["f0_coarse"].cpu() != taps["f0_coarse"]).sum())
-    if mism:
-        # a coarse-f0 bucket may flip only when the reference value sits on a bucket edge; re-run with the
-        # reference's buckets injected so the waveform comparison stays meaningful
-        assert mism <= 2, mism
-        res = _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise.to(DEV), g=None if gsp is None else gsp.to(DEV),
-                     f0_score=taps["f0_coarse"].to(DEV))
+    res = _f0_flips_reported(f"ragged_b3_t300_{variant}_gin{gin}", net, taps, ref[3], res,
+                             lambda **kw: _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise.to(DEV),
+                                                 g=None if gsp is None else gsp.to(DEV), **kw))
     o = res[0].cpu()
     mel_len = taps["mel_len"]
     for b in range(B):                                                            # valid samples, per utterance
@@ -77,8 +91,12 @@ def test_infer_matches_oracle_ragged_batch(variant, gin):
     assert snr_db(ref[2][0], res[2][0].cpu()) > 55
 
 
-def test_predicted_durations_are_bit_exact():
-    net, sd = build_model("ae", device=DEV)
+@pytest.mark.parametrize("prec", ["fp32", "split"])
+def test_predicted_durations_vs_oracle(prec):
+    """Durations are floor(pred * note_duration / 0.0116) (models_ae.py:624-625).  text_precision="fp32" (SIMT fp32
+    phoneme encoder): STRICTLY bit-exact.  The default "split" path (tensor cores, fp16 hi/lo operands): flips are
+    reported, never absorbed, and may only occur where the reference's own value sits on a floor edge."""
+    net, sd = build_model("ae", device=DEV, text_precision=prec)
     inp = synthetic.make_inputs(4, 40, seed=33, ragged=True)
     h, m = vo.text_encoder(sd, inp["x"], inp["note_pitch_id"], inp["note_duration"], inp["x_lengths"], inp["phone_shengdiao"])
     pred = vo.duration_predictor(sd, h, m)
@@ -87,11 +105,12 @@ def test_predicted_durations_are_bit_exact():
     _infer(net, inp, noise=torch.zeros(4, 192, T, device=DEV))
     got = net.last_aux["durations"].cpu()
     diff = got != want
-    if diff.any():   # only allowed where the reference value is within 1e-4 of an integer (floor edge)
+    report(f"duration_mismatches/text_precision_{prec}", int(diff.sum()))
+    if prec == "fp32":
+        assert torch.equal(got, want)
+    elif diff.any():
         q = pred * inp["note_duration"] / 0.0116
         assert ((q - q.round()).abs()[diff] < 1e-4).all() and int(diff.sum()) <= 1
-    else:
-        assert torch.equal(got, want)
 
 
 @pytest.mark.parametrize("kw,snr_min", [
@@ -136,7 +155,10 @@ def test_f0_split_precision_matches_fp32_path():
         res = _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise)
         got[prec] = (res[3].cpu(), net.last_aux["f0_coarse"].cpu())
     assert max_abs(got["split"][0], got["fp32"][0]) < 4e-5
-    assert int((got["split"][1] != got["fp32"][1]).sum()) <= 1
+    diff = got["split"][1] != got["fp32"][1]
+    report("f0_coarse_mismatches/split_vs_fp32_b2_t800", int(diff.sum()))
+    if diff.any():
+        assert float(coarse_edge_distance(got["fp32"][0])[diff].max()) < 2e-3 and int(diff.sum()) <= 1
 
 
 def test_batch_invariance_and_sharding_equivalence():
@@ -156,30 +178,122 @@ def test_batch_invariance_and_sharding_equivalence():
         assert torch.equal(part, full[idx])
 
 
-def test_full_size_bench_batch_properties():
-    """BASELINE config 3 (the bench workload: 64 utterances x 30 s, T = 2584 frames, beyond the reference's own
-    2000-frame position table) at full size through size-independent properties: the output is finite and inside
-    tanh's range, every utterance of the batch equals the same utterance synthesised in a 2-way shard and alone
-    (bit for bit: Generator chunks of 12 utterances, 256-row tiles and the split-precision paths are all
-    batch-invariant)."""
+@pytest.fixture(scope="module")
+def bench_batch():
+    """BASELINE config 3, the bench workload at full size: 64 utterances x 30 s, T = 2584 frames (beyond the reference's own
+    2000-frame position table: enlarged in the state-dict both sides load), same seeds as bench.py."""
     B, P, T = 64, 258, 2584
     net, sd = build_model("ae")
-    net.load_state_dict(synthetic.apply_recipe({k: v.clone() for k, v in sd.items()}, positions=T))   # enlarged table
+    sd = synthetic.apply_recipe({k: v.clone() for k, v in sd.items()}, positions=T)      # enlarged table
+    net.load_state_dict(sd)
     net = net.to(DEV)
     inp = synthetic.make_inputs(B, P, seed=1234)
     ph_dur = synthetic.make_ph_dur(inp["x_lengths"], P, T, seed=1234)
     assert int(ph_dur.sum(1).max()) == T
-    noise = synthetic.make_noise(B, 192, T, seed=1234).to(DEV)
-    res = _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise)
-    full = res[0]
+    noise = synthetic.make_noise(B, 192, T, seed=1234)
+    res = _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise.to(DEV))
+    torch.cuda.synchronize()
+    aux = {k: v.cpu() for k, v in net.last_aux.items() if torch.is_tensor(v)}
+    return dict(net=net, sd=sd, inp=inp, ph_dur=ph_dur, noise=noise, res=res, aux=aux, B=B, P=P, T=T)
+
+
+def test_full_size_bench_batch_properties(bench_batch):
+    """Size-independent properties at full size: the output is finite and inside tanh's range, every utterance of the
+    batch equals the same utterance synthesised in a 2-way shard and alone (bit for bit: Generator chunks of 12 utterances,
+    256-row tiles, CTA pairs and the split-precision paths are all batch-invariant)."""
+    bb = bench_batch
+    net, inp, ph_dur, noise, B, T = bb["net"], bb["inp"], bb["ph_dur"], bb["noise"].to(DEV), bb["B"], bb["T"]
+    full = bb["res"][0]
     assert full.shape == (B, 1, T * 256) and bool(torch.isfinite(full).all()) and float(full.abs().max()) <= 1.0
-    assert int(res[1].sum()) == int(ph_dur.sum())
+    assert int(bb["res"][1].sum()) == int(ph_dur.sum())
     from music_generation_b200 import sharding
     for idx in sharding.partition(ph_dur.sum(1).tolist(), 2):
         part = _infer(net, sharding.shard_batch(inp, idx), ph_dur=ph_dur[idx].to(DEV), noise=noise[idx])[0]
         assert torch.equal(part, full[idx])
     one = _infer(net, sharding.shard_batch(inp, [37]), ph_dur=ph_dur[[37]].to(DEV), noise=noise[[37]])[0]
     assert torch.equal(one[0], full[37])
+
+
+@pytest.mark.parametrize("b", [37])
+def test_bench_batch_row_matches_oracle_at_full_length(bench_batch, b):
+    """Chains the benchmark's own batch to the oracle: utterance b of the 64 x 2584 batch (21 key tiles, enlarged position
+    table, wide Generator chunks, CTA pairs) against oracle.visinger_oracle.infer on the same inputs at T = 2584 -
+    lr_index / y_mask bit-exact, f0_coarse mismatches reported, waveform within the north_star tolerance."""
+    from music_generation_b200 import sharding
+    bb = bench_batch
+    sub = sharding.shard_batch(bb["inp"], [b])
+    taps = {}
+    ref = vo.infer(bb["sd"], noise=bb["noise"][[b]], ph_dur=bb["ph_dur"][[b]], taps=taps, **sub)
+    assert torch.equal(bb["aux"]["lr_index"][[b]].long(), taps["lr_index"])
+    assert torch.equal(bb["res"][1][[b]].cpu(), ref[1])
+    diff = bb["aux"]["f0_coarse"][[b]] != taps["f0_coarse"]
+    report(f"f0_coarse_mismatches/bench_batch_row{b}_t2584", int(diff.sum()))
+    o = bb["res"][0][[b]].cpu()
+    if diff.any():      # edge flips only; compare the waveform with the reference's buckets injected (announced)
+        assert float(coarse_edge_distance(ref[3])[diff].max()) < 2e-3 and int(diff.sum()) <= 2
+        print(f"[parity] bench row {b}: waveform compared with the reference's f0 buckets injected")
+        o = _infer(bb["net"], sub, ph_dur=bb["ph_dur"][[b]].to(DEV), noise=bb["noise"][[b]].to(DEV),
+                   f0_score=taps["f0_coarse"].to(DEV))[0].cpu()
+    s, m = snr_db(ref[0], o), max_abs(ref[0], o)
+    report(f"waveform_snr_db/bench_batch_row{b}_t2584", round(s, 2))
+    report(f"waveform_max_abs/bench_batch_row{b}_t2584", m)
+    assert s >= SNR_DB_TOL and m <= MAX_ABS_TOL, (s, m)
+    assert max_abs(ref[3], bb["res"][3][[b]].cpu()) < 1e-3                         # log_f0
+    assert snr_db(ref[2][0], bb["res"][2][0][[b]].cpu()) > 55                      # z after the reverse flow
+    assert snr_db(ref[4], bb["res"][4][[b]].cpu()) > 50                            # spec_predict
+    assert snr_db(ref[5], bb["res"][5][[b]].cpu()) > 50                            # mel_predict
+
+
+def test_ragged_batch_at_bench_length_matches_oracle(bench_batch):
+    """Ragged B = 3 with the longest utterance at T = 2584 (the bench length) against the oracle."""
+    net, sd = bench_batch["net"], bench_batch["sd"]
+    B, P, T = 3, 258, 2584
+    inp = synthetic.make_inputs(B, P, seed=61, ragged=True)
+    ph_dur = synthetic.make_ph_dur(inp["x_lengths"], P, T, seed=61)
+    assert int(ph_dur.sum(1).max()) == T
+    noise = synthetic.make_noise(B, 192, T, seed=61)
+    taps = {}
+    ref = vo.infer(sd, noise=noise, ph_dur=ph_dur, taps=taps, **inp)
+    res = _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise.to(DEV))
+    torch.cuda.synchronize()
+    assert torch.equal(net.last_aux["lr_index"].long().cpu(), taps["lr_index"])
+    assert torch.equal(res[1].cpu(), ref[1])
+    res = _f0_flips_reported("ragged_b3_t2584", net, taps, ref[3], res,
+                             lambda **kw: _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise.to(DEV), **kw))
+    o = res[0].cpu()
+    for b in range(B):
+        n = int(taps["mel_len"][b]) * 256
+        assert snr_db(ref[0][b, :, :n], o[b, :, :n]) >= SNR_DB_TOL
+    s, m = snr_db(ref[0], o), max_abs(ref[0], o)
+    report("waveform_snr_db/ragged_b3_t2584", round(s, 2))
+    assert s >= SNR_DB_TOL and m <= MAX_ABS_TOL, (s, m)
+
+
+def test_config4_multispeaker_segments_match_oracle():
+    """BASELINE config 4 shape: gin_channels = 256 speaker conditioning, segments of T = 2000 frames (the reference's native
+    maximum), B = 2, against the oracle (whose g path is pinned by tests/golden/ae_gin256_stages.npz)."""
+    gin, B, P, T = 256, 2, 200, 2000
+    net, sd = build_model("ae", gin=gin, device=DEV)
+    inp = synthetic.make_inputs(B, P, seed=4, ragged=True)
+    ph_dur = synthetic.make_ph_dur(inp["x_lengths"], P, T, seed=4)
+    assert int(ph_dur.sum(1).max()) == T
+    noise = synthetic.make_noise(B, 192, T, seed=4)
+    g = torch.randn(B, gin, 1, generator=torch.Generator().manual_seed(4))
+    taps = {}
+    ref = vo.infer(sd, noise=noise, ph_dur=ph_dur, g=g, taps=taps, **inp)
+    res = _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise.to(DEV), g=g.to(DEV))
+    torch.cuda.synchronize()
+    assert torch.equal(net.last_aux["lr_index"].long().cpu(), taps["lr_index"])
+    assert torch.equal(res[1].cpu(), ref[1])
+    res = _f0_flips_reported("config4_gin256_b2_t2000", net, taps, ref[3], res,
+                             lambda **kw: _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise.to(DEV), g=g.to(DEV), **kw))
+    o = res[0].cpu()
+    s, m = snr_db(ref[0], o), max_abs(ref[0], o)
+    report("waveform_snr_db/config4_gin256_b2_t2000", round(s, 2))
+    assert s >= SNR_DB_TOL and m <= MAX_ABS_TOL, (s, m)
+    # the conditioning is live: without g the waveform differs by far more than the tolerance
+    o0 = _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise.to(DEV))[0].cpu()
+    assert max_abs(o, o0) > 10 * MAX_ABS_TOL
 
 
 def test_config1_shape_10s_utterance():
@@ -216,6 +330,12 @@ def test_generator_only_config2_properties():
     ref = vo.generator(sd, z[:1, :200].float().cpu().transpose(1, 2), vo.DEFAULT_HP)
     got = net._generator(z[:1, :200].contiguous()).cpu()
     assert snr_db(ref, got) >= SNR_DB_TOL and max_abs(ref, got) <= MAX_ABS_TOL
+    # full-length rows of the [16,192,2048] batch itself against the oracle's Generator
+    for b in (0, 11):
+        ref = vo.generator(sd, z[b:b + 1].float().cpu().transpose(1, 2), vo.DEFAULT_HP)
+        s_, m_ = snr_db(ref, o[b:b + 1].cpu()), max_abs(ref, o[b:b + 1].cpu())
+        report(f"waveform_snr_db/config2_row{b}_t2048", round(s_, 2))
+        assert s_ >= SNR_DB_TOL and m_ <= MAX_ABS_TOL, (b, s_, m_)
 
 
 def test_cuda_graph_replay_equals_eager():

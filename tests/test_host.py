@@ -183,3 +183,32 @@ def test_enlarged_position_table_loads():
     sd2 = synthetic.apply_recipe({k: v.clone() for k, v in sd.items()}, positions=4096)
     net.load_state_dict(sd2)
     assert net.text_post_net.position_embeddings.weight.shape[0] == 4096
+
+
+def test_infer_normalises_id_dtypes_and_rejects_out_of_range_ids(monkeypatch):
+    """nn.Embedding / sequence_mask accept int32 ids and lengths and raise IndexError on an id outside the table
+    (ADVICE r1): int32 inputs give the same result as int64 ones, a live out-of-range id raises, one in the padded
+    tail of a shorter utterance does not."""
+    _emu(monkeypatch)
+    net, _ = build_model("ae")
+    inp = synthetic.make_inputs(2, 8, seed=5, ragged=True)
+    ph_dur = synthetic.make_ph_dur(inp["x_lengths"], 8, 30, seed=5)
+    noise = synthetic.make_noise(2, 192, int(ph_dur.sum(1).max()), seed=5)
+    call = lambda i: net.infer(i["x"], i["x_lengths"], i["note_pitch_id"], i["note_duration"],
+                               phone_shengdiao=i["phone_shengdiao"], ph_dur=ph_dur, noise=noise)
+    a = call(inp)
+    b = call({k: (v.to(torch.int32) if v.dtype == torch.int64 else v) for k, v in inp.items()})
+    assert torch.equal(a[0], b[0]) and b[1].dtype == torch.int32          # y_mask follows x.dtype like the reference
+    bad = {k: v.clone() for k, v in inp.items()}
+    bad["x"][0, 0] = 100                                                    # table has 100 rows
+    with pytest.raises(IndexError):
+        call(bad)
+    short = int(inp["x_lengths"].argmin())
+    if int(inp["x_lengths"][short]) < 8:
+        pad = {k: v.clone() for k, v in inp.items()}
+        pad["phone_shengdiao"][short, -1] = 9999                            # padded slot: never read by the reference either
+        assert torch.equal(call(pad)[0], a[0])
+    with pytest.raises(IndexError):
+        net.infer(inp["x"], inp["x_lengths"], inp["note_pitch_id"], inp["note_duration"],
+                  phone_shengdiao=inp["phone_shengdiao"], ph_dur=ph_dur, noise=noise,
+                  f0_score=torch.full((2, int(ph_dur.sum(1).max())), 300))

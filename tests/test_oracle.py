@@ -8,7 +8,7 @@ import torch
 
 from common import GOLDEN, flat, load_golden, max_abs, state_dict_for
 from oracle import ref_harness, visinger_oracle as vo
-from oracle.make_golden import CASES, case_inputs
+from oracle.make_golden import CASES, G_CASES, case_inputs, g_case_inputs
 from music_generation_b200 import synthetic
 
 TOL = 2e-5     # fp32 reduction-order noise between thread counts / machines
@@ -52,6 +52,44 @@ def test_oracle_matches_live_reference(variant):
         assert max_abs(a, b) < TOL
 
 
+@pytest.mark.parametrize("name", sorted(G_CASES))
+def test_oracle_speaker_conditioning_matches_reference_golden(name):
+    """The `g` path (WN.cond_layer modules.py:152-159, Generator.cond models_ae.py:329-330) of the oracle against
+    outputs of the reference's own ResidualCouplingBlock / SpecDecoder / Generator called with g."""
+    gold = load_golden(name)
+    z_p, mel_len, g, gin = g_case_inputs(name)
+    sd = state_dict_for("ae", gin=gin)
+    y_mask = (torch.arange(z_p.shape[2])[None] < mel_len[:, None]).unsqueeze(1).float()
+    z = vo.flow_reverse(sd, z_p * y_mask, y_mask, g=g)
+    assert max_abs(gold["z"], z) < TOL
+    spec = vo.spec_decoder(sd, z, mel_len, g=g)
+    assert max_abs(gold["spec"], spec[:, ::8]) < 1e-4
+    hid = vo.conv(sd, "spec_proj", spec) * y_mask
+    assert max_abs(gold["hid"], hid) < 1e-4
+    o = vo.generator(sd, gold["hid"], vo.DEFAULT_HP, g=g)
+    assert o.shape == gold["o"].shape and max_abs(gold["o"], o) < TOL
+    # g must matter: the unconditioned path gives a different waveform
+    assert max_abs(gold["o"], vo.generator(sd, gold["hid"], vo.DEFAULT_HP)) > 1e-3
+
+
+@pytest.mark.skipif(not ref_harness.available(), reason="reference tree only exists in the build container")
+def test_oracle_speaker_conditioning_matches_live_reference():
+    gin = 256
+    sd = state_dict_for("ae", gin=gin)
+    net = ref_harness.build_reference("ae", gin_channels=gin)
+    net.load_state_dict(sd, strict=True)
+    gen = torch.Generator().manual_seed(5)
+    z_p, mel_len, g = torch.randn(2, 192, 33, generator=gen), torch.tensor([33, 20]), torch.randn(2, gin, 1, generator=gen)
+    y_mask = (torch.arange(33)[None] < mel_len[:, None]).unsqueeze(1).float()
+    with torch.no_grad():
+        z = net.spec_flow(z_p * y_mask, y_mask, g=g, reverse=True)
+        spec = net.spec_decoder(z, mel_len, g=g)
+        o = net.decoder(net.spec_proj(spec) * y_mask, g=g)
+    assert max_abs(z, vo.flow_reverse(sd, z_p * y_mask, y_mask, g=g)) < TOL
+    assert max_abs(spec, vo.spec_decoder(sd, z, mel_len, g=g)) < 1e-4
+    assert max_abs(o, vo.generator(sd, net.spec_proj(spec) * y_mask, vo.DEFAULT_HP, g=g)) < TOL
+
+
 def test_length_regulator_edge_cases():
     h = torch.arange(2 * 3 * 4, dtype=torch.float32).reshape(2, 3, 4)     # [B,C,P]
     dur = torch.tensor([[2, 0, 1, 3], [0, 0, 0, 0]])
@@ -82,5 +120,5 @@ def test_position_table_limit_raises_like_reference():
 
 def test_manifest_lists_every_fixture():
     m = json.load(open(os.path.join(GOLDEN, "MANIFEST.json")))
-    for name in m["cases"]:
+    for name in list(m["cases"]) + list(m["g_cases"]):
         assert os.path.exists(os.path.join(GOLDEN, name + ".npz"))
