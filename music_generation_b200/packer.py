@@ -110,6 +110,10 @@ def pack_conv(weight, bias, *, dil=1, pad_left=None, dtype=torch.float16, f32=Fa
     if b is not None:
         bp = torch.zeros(cout_pad)
         bp[:cout] = b
+    if dtype == torch.float16 and float(w.abs().max()) > 65504.0:
+        # an fp16 weight would become inf and every zero-padded input row NaN (0 * inf): refuse instead
+        raise ValueError(f"conv weight magnitude {float(w.abs().max()):.3g} exceeds the fp16 range (65504): "
+                         "build the model with operand_dtype='bf16'")
     pc = PackedConv(w.to(dtype).contiguous(), bp, k, dil, pad_left, cin, cin_pad, cout, cout_pad, bn, gate, False)
     if split:
         pc.alg_macs_per_row = (cin // 3) * cout * k      # algorithmic (fp32-equivalent) MACs, not the 3x executed

@@ -58,7 +58,9 @@ def _f0_flips_reported(tag, net, taps, ref_log_f0, res, rerun):
         return res
     edge = coarse_edge_distance(ref_log_f0)[diff]
     report(f"f0_coarse_edge_distance_max/{tag}", float(edge.max()))
-    assert float(edge.max()) < 2e-3 and mism <= max(2, diff.numel() // 2000), (mism, float(edge.max()))
+    # every flipped frame must sit within 2e-3 bucket widths of a rounding edge (= 2.6e-5 in log_f0, the fp32 evaluation
+    # noise of a 6-layer encoder); frames that close to an edge are 2 * 2e-3 = 0.4 % of all frames, which bounds the count
+    assert float(edge.max()) < 2e-3 and mism <= max(2, diff.numel() // 250), (mism, float(edge.max()))
     print(f"[parity] {tag}: waveform compared with the reference's f0 buckets injected for {mism} edge frame(s)")
     return rerun(f0_score=taps["f0_coarse"].to(DEV))
 

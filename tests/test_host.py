@@ -212,3 +212,10 @@ def test_infer_normalises_id_dtypes_and_rejects_out_of_range_ids(monkeypatch):
         net.infer(inp["x"], inp["x_lengths"], inp["note_pitch_id"], inp["note_duration"],
                   phone_shengdiao=inp["phone_shengdiao"], ph_dur=ph_dur, noise=noise,
                   f0_score=torch.full((2, int(ph_dur.sum(1).max())), 300))
+
+
+def test_packer_refuses_weights_beyond_fp16_range():
+    w = torch.zeros(4, 4, 3); w[1, 2, 0] = 7.0e4
+    with pytest.raises(ValueError, match="fp16 range"):
+        packer.pack_conv(w, None, dtype=torch.float16)
+    assert torch.isfinite(packer.pack_conv(w, None, dtype=torch.bfloat16).w.float()).all()
