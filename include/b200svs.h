@@ -228,6 +228,19 @@ int b200svs_song_assemble(const float* o, int64_t o_ld, const int64_t* mel_len, 
                           const int64_t* offsets, int32_t n_lines, int32_t hop, int32_t lead_in, int32_t legacy_scalar,
                           uint32_t* peak_ws, int16_t* song, float* scales_out, void* stream);
 
+/* Allocation-free variant of b200svs_song_assemble.  It has no counterpart in the reference and was added
+ * for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc): same arguments minus `peak_ws` - the per-line peak scratch is a file-scope
+ * `static __device__ __align__(256)` array of B200SVS_SONG_NOALLOC_MAX_LINES uint32 (16 KB, resident in every GPU that
+ * loads the library until exit), resolved with cudaGetSymbolAddress once per device.  n_lines beyond the maximum is
+ * B200SVS_EINVAL.  The call makes no cudaMalloc / cudaFree / allocating library call; it clears the n_lines words it uses
+ * (the array keeps the previous call's contents).  Every call on a GPU shares the array: calls that overlap on the GPU
+ * (different streams) race - serialise them, or use b200svs_song_assemble with one workspace per stream. */
+#define B200SVS_SONG_NOALLOC_MAX_LINES 4096
+int b200svs_song_assemble_noalloc(const float* o, int64_t o_ld, const int64_t* mel_len, const int32_t* order,
+                                  const int64_t* offsets, int32_t n_lines, int32_t hop, int32_t lead_in,
+                                  int32_t legacy_scalar, int16_t* song, float* scales_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

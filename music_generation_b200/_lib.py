@@ -53,6 +53,7 @@ PROTOTYPES = {
     "b200svs_conv1d_tc": [C.POINTER(ConvArgs), _vp],
     "b200svs_conv1d_tc_set_trace": [_vp, _i32],
     "b200svs_song_assemble": [_vp, C.c_int64, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp],
+    "b200svs_song_assemble_noalloc": [_vp, C.c_int64, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp],
     "b200svs_conv1d_f32": [C.POINTER(ConvArgs), _vp],
     "b200svs_attention_f32": [_vp, _i32, _vp, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
     "b200svs_attn_prep": [_vp, _i32, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp],

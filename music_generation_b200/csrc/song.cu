@@ -91,3 +91,55 @@ extern "C" int b200svs_song_assemble(const float* o, int64_t o_ld, const int64_t
                                                         legacy_scalar, song, scales_out);
   return check_launch("song_write_kernel");
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// b200svs_song_assemble_noalloc: the same two kernels with the per-line peak scratch in a file-scope device array instead
+// of a caller workspace, for callers that cannot allocate (CUDA graph capture, tight serving loops).  No counterpart in
+// the reference.  The array lives in every GPU that loads the library
+// until exit (16 KB); all calls share it, so two calls that overlap on one GPU (different streams) race.
+namespace b200svs {
+constexpr int kSongNoallocMaxLines = 4096;
+static __device__ __align__(256) unsigned int g_song_peak_scratch[kSongNoallocMaxLines];
+
+// In host code `g_song_peak_scratch` is a host-side stand-in, not a device address: resolve it once per device, with
+// that device current, and hand the kernels the resolved pointer.
+static int song_scratch_ptr(unsigned int** out) {
+  static unsigned int* ptrs[kMaxDevices] = {};
+  const int dev = device_ordinal();
+  if (!ptrs[dev]) {
+    unsigned int* p = nullptr;
+    int r = check_cuda(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_song_peak_scratch),
+                       "cudaGetSymbolAddress(g_song_peak_scratch)");
+    if (r) return r;
+    if (!p) return set_error(B200SVS_ECUDA, "song_assemble_noalloc: cudaGetSymbolAddress returned NULL");
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return B200SVS_OK;
+}
+}  // namespace b200svs
+
+extern "C" int b200svs_song_assemble_noalloc(const float* o, int64_t o_ld, const int64_t* mel_len, const int32_t* order,
+                                             const int64_t* offsets, int32_t n_lines, int32_t hop, int32_t lead_in,
+                                             int32_t legacy_scalar, int16_t* song, float* scales_out, void* stream) {
+  B200SVS_REQUIRE(o && mel_len && offsets && song, "song_assemble_noalloc: null argument");
+  B200SVS_REQUIRE(n_lines > 0 && hop > 0 && lead_in >= 0 && o_ld > 0, "song_assemble_noalloc: n_lines=%d hop=%d lead_in=%d",
+                  n_lines, hop, lead_in);
+  B200SVS_REQUIRE(n_lines <= kSongNoallocMaxLines,
+                  "song_assemble_noalloc: n_lines=%d exceeds the static scratch of %d lines (use b200svs_song_assemble with a "
+                  "caller workspace)", n_lines, kSongNoallocMaxLines);
+  unsigned int* peak_ws = nullptr;
+  int r = song_scratch_ptr(&peak_ws);
+  if (r) return r;
+  // the array keeps the previous call's peaks: the atomicMax reduction must start from zero
+  r = check_cuda(cudaMemsetAsync(peak_ws, 0, sizeof(unsigned int) * n_lines, as_stream(stream)), "cudaMemsetAsync(song scratch)");
+  if (r) return r;
+  const int bx = (num_sms() * 4 + n_lines - 1) / n_lines;
+  dim3 grid(bx > 0 ? bx : 1, n_lines);
+  song_peak_kernel<<<grid, 256, 0, as_stream(stream)>>>(o, o_ld, mel_len, order, hop, peak_ws);
+  r = check_launch("song_peak_kernel (noalloc)");
+  if (r) return r;
+  song_write_kernel<<<grid, 256, 0, as_stream(stream)>>>(o, o_ld, mel_len, order, offsets, hop, lead_in, peak_ws,
+                                                        legacy_scalar, song, scales_out);
+  return check_launch("song_write_kernel (noalloc)");
+}
