@@ -201,10 +201,11 @@ int b200svs_f0_embed(const float* log_f0, const int64_t* coarse_in, const float*
                      void* stream);
 
 /* z_p = m_p + noise * exp(logs_p) * noise_scale (models_ae.py:643); stats: [B,T,2C] (m|logs);
- * noise is the reference layout [B,C,T]; writes z_p fp32 [B,T,C] (+16-bit copy) */
+ * noise is the reference layout [B,C,T]; writes z_p fp32 [B,T,C] (+16-bit copy).  lens (nullable): rows t >= lens[b]
+ * are written as 0 - PosteriorEncoder's z = (m + randn * exp(logs)) * x_mask (models_ae.py:290). */
 int b200svs_sample_prior(const float* stats, int32_t stats_ld, const float* noise_bct, float noise_scale,
                          float* zp32, int32_t zp_ld, void* zp16, int32_t zp16_ld, int32_t out16_dtype,
-                         int32_t B, int32_t T, int32_t C, void* stream);
+                         int32_t B, int32_t T, int32_t C, const int32_t* lens, void* stream);
 
 /* Generator tail (models_ae.py:342-344): tanh(conv_post_k7(x)) with x = leaky_relu(.,0.01) already
  * applied by the producer; x: 16-bit [B,L,C], w: fp32 [7][C]; out: fp32 [B,L] */

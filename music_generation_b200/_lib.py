@@ -66,7 +66,7 @@ PROTOTYPES = {
     "b200svs_lr_gather": [_vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _vp],
     "b200svs_add_pos_mask": [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
     "b200svs_f0_embed": [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp],
-    "b200svs_sample_prior": [_vp, _i32, _vp, _f32, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
+    "b200svs_sample_prior": [_vp, _i32, _vp, _f32, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp],
     "b200svs_conv_post_tanh": [_vp, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _vp, _vp],
     "b200svs_bct_to_btc": [_vp, _i32, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _vp, _vp],
     "b200svs_btc_to_bct": [_vp, _i32, _i32, _i32, _i32, _vp, _vp],

@@ -220,7 +220,8 @@ __global__ void __launch_bounds__(256) f0_embed_kernel(const float* log_f0, cons
 // stats is channels-last [B,T,2C]; noise is the reference layout [B,C,T] (tile transpose via smem).
 __global__ void __launch_bounds__(256) sample_prior_kernel(const float* stats, int stats_ld, const float* noise,
                                                            float noise_scale, float* zp32, int zp_ld, void* zp16,
-                                                           int zp16_ld, int dt, int B, int T, int C) {
+                                                           int zp16_ld, int dt, int B, int T, int C,
+                                                           const int32_t* lens) {
   __shared__ float tile[32][33];
   const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
@@ -235,7 +236,8 @@ __global__ void __launch_bounds__(256) sample_prior_kernel(const float* stats, i
       const size_t row = static_cast<size_t>(b) * T + t;
       const float m = stats[row * stats_ld + c], logs = stats[row * stats_ld + C + c];
       // torch: m_p + randn * exp(logs_p) * noise_scale  (left to right)
-      const float v = m + (tile[tx][j] * expf(logs)) * noise_scale;
+      float v = m + (tile[tx][j] * expf(logs)) * noise_scale;
+      if (lens && t >= lens[b]) v = 0.f;      // PosteriorEncoder: (m + randn * exp(logs)) * x_mask (models_ae.py:290)
       if (zp32) zp32[row * zp_ld + c] = v;
       if (zp16) store16(zp16, row * zp16_ld + c, v, dt);
     }
@@ -438,11 +440,11 @@ int b200svs_f0_embed(const float* log_f0, const int64_t* coarse_in, const float*
 
 int b200svs_sample_prior(const float* stats, int32_t stats_ld, const float* noise_bct, float noise_scale, float* zp32,
                          int32_t zp_ld, void* zp16, int32_t zp16_ld, int32_t out16_dtype, int32_t B, int32_t T,
-                         int32_t C, void* stream) {
+                         int32_t C, const int32_t* lens, void* stream) {
   B200SVS_REQUIRE(stats && noise_bct && (zp32 || zp16) && B > 0 && T > 0 && C > 0, "sample_prior: bad argument");
   dim3 grid((T + 31) / 32, (C + 31) / 32, B);
   sample_prior_kernel<<<grid, 256, 0, as_stream(stream)>>>(stats, stats_ld, noise_bct, noise_scale, zp32, zp_ld, zp16,
-                                                          zp16_ld, out16_dtype, B, T, C);
+                                                          zp16_ld, out16_dtype, B, T, C, lens);
   return check_launch("sample_prior_kernel");
 }
 

@@ -230,11 +230,11 @@ def f0_embed(log_f0, coarse_in, table, lens, coarse_out, out32=None, out16=None)
               0 if out16 is None else dt_code(out16.dtype), B, T, c, table.shape[0], _stream())
 
 
-def sample_prior(stats, noise_bct, noise_scale, zp32=None, zp16=None):
+def sample_prior(stats, noise_bct, noise_scale, zp32=None, zp16=None, lens=None):
     B, T, c2 = stats.shape
     _lib.call("b200svs_sample_prior", _ptr(stats), _btc(stats, "stats"), _ptr(noise_bct), float(noise_scale),
               _ptr(zp32), _btc(zp32, "zp32"), _ptr(zp16), _btc(zp16, "zp16"),
-              0 if zp16 is None else dt_code(zp16.dtype), B, T, c2 // 2, _stream())
+              0 if zp16 is None else dt_code(zp16.dtype), B, T, c2 // 2, _ptr(lens), _stream())
 
 
 def conv_post_tanh(x16, w, out):

@@ -133,6 +133,38 @@ class SynthesizerTrn(nn.Module):
     def device(self):
         return self.text_post_net.f0_emb.weight.device
 
+    def _pack_wn_stack(self, sd, prefix, dev, dt):
+        """Packed weights of one modules.WN stack (modules.py:110-176): gate-interleaved in_layers, res/skip 1x1 convs, the
+        skip sum as one K-concatenated 1x1 conv, the speaker cond_layer in gate order."""
+        W = lambda p: packer.fold_weight_norm(sd, p)
+        Bv = lambda p: sd.get(p + ".bias")
+        n = 0
+        while f"{prefix}.in_layers.{n}.bias" in sd:
+            n += 1
+        st = {"in": [], "rs": [], "n": n, "cond": None}
+        for i in range(n):
+            st["in"].append(packer.pack_conv(W(f"{prefix}.in_layers.{i}"), Bv(f"{prefix}.in_layers.{i}"),
+                                             dtype=dt, gate=True).to(dev))
+            st["rs"].append(packer.pack_conv(W(f"{prefix}.res_skip_layers.{i}"), Bv(f"{prefix}.res_skip_layers.{i}"),
+                                             dtype=dt, block_n=192).to(dev))
+        # skip path as ONE GEMM: output = sum_i W_skip_i . acts_i + sum_i b_skip_i (modules.py:165-176 accumulates it
+        # layer by layer) = a 1x1 conv over the K-concatenation of all layers' gate outputs
+        H = self.hidden_channels
+        ws, bs = [], 0.0
+        for i in range(n):
+            w_i, b_i = W(f"{prefix}.res_skip_layers.{i}"), Bv(f"{prefix}.res_skip_layers.{i}")
+            lo = H if i < n - 1 else 0          # the last layer's 192 outputs are all skip
+            ws.append(w_i[lo:lo + H])
+            bs = bs + b_i[lo:lo + H].double()
+        st["skip_cat"] = packer.pack_conv(torch.cat(ws, 1), bs.float(), dtype=dt).to(dev)
+        if self.gin_channels:
+            wc, bc = W(prefix + ".cond_layer"), Bv(prefix + ".cond_layer")
+            h2 = 2 * self.hidden_channels
+            order = packer.gate_order(self.hidden_channels)
+            idx = torch.cat([order + i * h2 for i in range(n)])
+            st["cond"] = packer.pack_conv(wc[idx], bc[idx], f32=True).to(dev)
+        return st
+
     # ------------------------------------------------------------------ weight packing (once per load)
     def _pack(self):
         sd = {k: v.detach().float().cpu() for k, v in self.state_dict().items()}
@@ -163,32 +195,7 @@ class SynthesizerTrn(nn.Module):
             return packer.pack_conv(W(p), Bv(p), dtype=dt, f32=f32, **kw).to(dev)
 
         def wn_stack(prefix):
-            n = 0
-            while f"{prefix}.in_layers.{n}.bias" in sd:
-                n += 1
-            st = {"in": [], "rs": [], "n": n, "cond": None}
-            for i in range(n):
-                st["in"].append(packer.pack_conv(W(f"{prefix}.in_layers.{i}"), Bv(f"{prefix}.in_layers.{i}"),
-                                                 dtype=dt, gate=True).to(dev))
-                st["rs"].append(packer.pack_conv(W(f"{prefix}.res_skip_layers.{i}"), Bv(f"{prefix}.res_skip_layers.{i}"),
-                                                 dtype=dt, block_n=192).to(dev))
-            # skip path as ONE GEMM: output = sum_i W_skip_i . acts_i + sum_i b_skip_i (modules.py:165-176 accumulates it
-            # layer by layer) = a 1x1 conv over the K-concatenation of all layers' gate outputs
-            H = self.hidden_channels
-            ws, bs = [], 0.0
-            for i in range(n):
-                w_i, b_i = W(f"{prefix}.res_skip_layers.{i}"), Bv(f"{prefix}.res_skip_layers.{i}")
-                lo = H if i < n - 1 else 0          # the last layer's 192 outputs are all skip
-                ws.append(w_i[lo:lo + H])
-                bs = bs + b_i[lo:lo + H].double()
-            st["skip_cat"] = packer.pack_conv(torch.cat(ws, 1), bs.float(), dtype=dt).to(dev)
-            if self.gin_channels:
-                wc, bc = W(prefix + ".cond_layer"), Bv(prefix + ".cond_layer")
-                h2 = 2 * self.hidden_channels
-                order = packer.gate_order(self.hidden_channels)
-                idx = torch.cat([order + i * h2 for i in range(n)])
-                st["cond"] = packer.pack_conv(wc[idx], bc[idx], f32=True).to(dev)
-            return st
+            return self._pack_wn_stack(sd, prefix, dev, dt)
 
         te = "text_encoder"
         P["emb"] = tuple(sd[f"{te}.{n}"].contiguous().to(dev) for n in
@@ -497,6 +504,62 @@ class SynthesizerTrn(nn.Module):
                         src32, srcr, src16 = c32, cr16, dst16
             cur16, L = nxt16, Lo
         return cur16, L
+
+    # ------------------------------------------------------------------ training-side piece that shares the kernels (8f-4)
+    def _pack_posterior(self):
+        """PosteriorEncoder = pre (1x1) + WN x 16 + proj (models_ae.py:256-291), packed on first use only: infer never
+        touches spec_encoder, so its 7.2 M parameters are not packed by `_pack`."""
+        P = self._packed or self._pack()
+        if "pe_pre" in P:
+            return P
+        sd = {k: v.detach().float().cpu() for k, v in self.state_dict().items() if k.startswith("spec_encoder.")}
+        dev, dt = self.device, self.operand_dtype
+        W = lambda p: packer.fold_weight_norm(sd, p)
+        P["pe_pre"] = packer.pack_conv(W("spec_encoder.pre"), sd["spec_encoder.pre.bias"], dtype=dt).to(dev)
+        P["pe_proj"] = packer.pack_conv(W("spec_encoder.proj"), sd["spec_encoder.proj.bias"], dtype=dt).to(dev)
+        P["pe_wn"] = self._pack_wn_stack(sd, "spec_encoder.enc", dev, dt)
+        for pc in [P["pe_pre"], P["pe_proj"], *P["pe_wn"]["in"], *P["pe_wn"]["rs"], P["pe_wn"]["skip_cat"]]:
+            pc.tag = "posterior"
+        return P
+
+    @torch.no_grad()
+    def posterior_encode(self, y, y_lengths, g=None, *, noise=None):
+        """`self.spec_encoder(y, y_lengths, g=g)` of the reference (PosteriorEncoder.forward, models_ae.py:284-291):
+        y [B, spec_channels, T] fp32 linear spectrogram -> (z, m, logs, y_mask, x) in the reference's [B,C,T] layout.
+        `noise` [B, inter, T] replaces torch.randn_like (parity runs).  Inference-only restatement of the training-side
+        encoder on the same kernels as the SpecDecoder."""
+        _require_cuda(y)
+        dev, dt, f32 = self.device, self.operand_dtype, torch.float32
+        with _device_guard(dev):
+            P = self._pack_posterior()
+            B, Cs, T = y.shape
+            H, Ci = self.hidden_channels, self.inter_channels
+            lens = y_lengths.to(device=dev, dtype=torch.int32).contiguous()
+            y_mask = (torch.arange(T, device=dev).unsqueeze(0) < lens.unsqueeze(1)).unsqueeze(1).to(y.dtype)
+            ld = (Cs + 63) // 64 * 64
+            y16 = torch.empty(B, T, ld, device=dev, dtype=dt)
+            ops.bct_to_btc(y.contiguous().float(), out16=y16[:, :, :Cs])
+            hx32 = torch.empty(B, T, H, device=dev, dtype=f32)
+            hx16 = torch.empty(B, T, H, device=dev, dtype=dt)
+            wo16 = torch.empty(B, T, H, device=dev, dtype=dt)
+            ops.conv1d(P["pe_pre"], y16[:, :, :Cs], lens=lens, out32=hx32, out16=hx16)
+            gcond = None
+            if g is not None:
+                if not self.gin_channels:
+                    raise ValueError("model was built with gin_channels=0")
+                g_btc = g.to(device=dev, dtype=f32).reshape(B, 1, self.gin_channels).contiguous()
+                gc = torch.empty(B, 1, P["pe_wn"]["cond"].cout, device=dev, dtype=f32)
+                ops.conv1d(P["pe_wn"]["cond"], g_btc, out32=gc)
+                gcond = gc.view(B, -1)
+            self._wn(P["pe_wn"], hx32, hx16, lens, wo16, gcond)
+            stats = torch.empty(B, T, 2 * Ci, device=dev, dtype=f32)
+            ops.conv1d(P["pe_proj"], wo16, lens=lens, out32=stats)
+            if noise is None:
+                noise = torch.randn(B, Ci, T, device=dev, dtype=f32)
+            z32 = torch.empty(B, T, Ci, device=dev, dtype=f32)
+            ops.sample_prior(stats, noise.to(device=dev, dtype=f32).contiguous(), 1.0, zp32=z32, lens=lens)
+        bct = lambda t: t.transpose(1, 2)
+        return bct(z32), bct(stats[:, :, :Ci]), bct(stats[:, :, Ci:]), y_mask, bct(wo16.float())
 
     def _graphed(self, fn, args, shape_key):
         """Run fn(*args) through a cached CUDA graph.  args: tensors or None; the graph owns static copies of them and

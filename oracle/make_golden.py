@@ -45,6 +45,16 @@ def g_case_inputs(name):
     return z_p, mel_len, g, gin
 
 
+def posterior_spectrogram(name):
+    b, t, gin, seed = G_CASES[name]
+    return torch.rand(b, 513, t, generator=torch.Generator().manual_seed(seed + 1)) * 2.0
+
+
+def posterior_noise(name):
+    b, t, gin, seed = G_CASES[name]
+    return torch.randn(b, 192, t, generator=torch.Generator().manual_seed(seed + 2))
+
+
 def state_dict_for(variant, seed=1234, gin=0):
     mod = models_ae if variant == "ae" else models
     net = mod.SynthesizerTrn(100, 513, 48, **HP, seed=seed, gin_channels=gin)
@@ -100,8 +110,17 @@ def main():
             spec = net.spec_decoder(z, mel_len, g=g)                            # ext_modules/spec_decoder.py:41-46
             hid = net.spec_proj(spec) * y_mask
             o = net.decoder(hid, g=g)                                           # models_ae.py:327-346 with cond (:329-330)
+            # training-side PosteriorEncoder (models_ae.py:256-291) on a synthetic spectrogram, with g
+            y = posterior_spectrogram(name)
+            pn = posterior_noise(name)
+            orig = torch.randn_like
+            torch.randn_like = lambda t, *a, **k: pn.to(t.dtype)
+            try:
+                pz, pm, plogs, pmask, px = net.spec_encoder(y, mel_len, g=g)
+            finally:
+                torch.randn_like = orig
         np.savez_compressed(os.path.join(out_dir, name + ".npz"), z=z.numpy(), spec=spec[:, ::8].numpy(), hid=hid.numpy(),
-                            o=o.numpy())
+                            o=o.numpy(), post_z=pz.numpy(), post_m=pm.numpy(), post_logs=plogs.numpy(), post_x=px.numpy())
         print(name, "o", tuple(o.shape), "|o|max %.3f" % o.abs().max())
     json.dump({"cases": {k: list(v) for k, v in CASES.items()}, "g_cases": {k: list(v) for k, v in G_CASES.items()},
                "torch": torch.__version__,

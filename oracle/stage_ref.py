@@ -31,6 +31,9 @@ FILES = [
     "VISinger/utils/__init__.py", "VISinger/utils/utils.py", "VISinger/utils/pitch_utils.py",
     "VISinger/utils/config_loader.py", "VISinger/utils/audio.py", "VISinger/utils/logger.py",
     "VISinger/configs/ours_ae.json", "VISinger/configs/ours.json",
+    # front-end tensorisation: vocabularies + the reference's encoder and driver (parsed, never imported whole)
+    "VISinger/phone_set.json", "VISinger/phone_shengdiao_set.json", "VISinger/utils/text_encoder.py",
+    "pipline_inference_svs_v5.py",
 ]
 
 

@@ -322,6 +322,18 @@ def spec_decoder(sd, z, mel_len, g=None, p="spec_decoder"):
 # --------------------------------------------------------------------------------------
 # Generator (models_ae.py:327-346; ResBlock1/2 modules.py:210-223, 243-252)
 # --------------------------------------------------------------------------------------
+def posterior_encoder(sd, y, y_lengths, noise, g=None, p="spec_encoder"):
+    """PosteriorEncoder.forward (models_ae.py:284-291); `noise` replaces torch.randn_like(m).
+    Returns (z, m, logs, x_mask, x) like the reference."""
+    x_mask = sequence_mask(y_lengths, y.size(2)).unsqueeze(1).to(y.dtype)
+    x = conv(sd, p + ".pre", y) * x_mask
+    x = wn(sd, p + ".enc", x, x_mask, g=g)
+    stats = conv(sd, p + ".proj", x) * x_mask
+    m, logs = torch.split(stats, stats.size(1) // 2, dim=1)
+    z = (m + noise * torch.exp(logs)) * x_mask
+    return z, m, logs, x_mask, x
+
+
 def resblock1(sd, prefix, x, dilations=(1, 3, 5)):
     for j, d in enumerate(dilations):
         k = wn_weight(sd, f"{prefix}.convs1.{j}").shape[-1]

@@ -210,11 +210,21 @@ def f0_embed(log_f0, coarse_in, table, lens, coarse_out, out32=None, out16=None)
     _store(out16, y)
 
 
-def sample_prior(stats, noise_bct, noise_scale, zp32=None, zp16=None):
+def sample_prior(stats, noise_bct, noise_scale, zp32=None, zp16=None, lens=None):
     c = stats.shape[-1] // 2
     y = stats[:, :, :c] + noise_bct.transpose(1, 2) * torch.exp(stats[:, :, c:]) * noise_scale
+    if lens is not None:
+        y = y * _mask(lens, y.shape[0], y.shape[1])
     _store(zp32, y)
     _store(zp16, y)
+
+
+def bct_to_btc(x_bct, out32=None, out16=None, lens=None):
+    y = x_bct.transpose(1, 2)
+    if lens is not None:
+        y = y * _mask(lens, y.shape[0], y.shape[1])
+    _store(out32, y)
+    _store(out16, y)
 
 
 def conv_post_tanh(x16, w, out):
@@ -228,7 +238,7 @@ def install(monkeypatch):
     """Route music_generation_b200.ops.* to the emulation above (CPU tests only)."""
     import music_generation_b200.synthesizer as syn
     for name in ("conv1d", "attention", "attention_tc", "layernorm", "text_embed", "duration_quantize", "lr_scan", "lr_gather",
-                 "add_pos_mask", "f0_embed", "sample_prior", "conv_post_tanh"):
+                 "add_pos_mask", "f0_embed", "sample_prior", "conv_post_tanh", "bct_to_btc"):
         monkeypatch.setattr(real_ops, name, globals()[name])
     monkeypatch.setattr(syn, "_require_cuda", lambda t: None)
     import contextlib

@@ -112,3 +112,23 @@ def test_fp16_numeric_range_saturates_and_reports(scale, expect_sat):
         s, m = snr_db(ref[0], o), max_abs(ref[0], o)
         report(f"waveform_snr_db/fp16_scale_{scale:g}", round(s, 2))
         assert s >= SNR_DB_TOL and m <= MAX_ABS_TOL, (s, m)
+
+
+def test_posterior_encoder_on_device_matches_reference_golden():
+    """`posterior_encode` (= reference spec_encoder, models_ae.py:256-291, with speaker conditioning) on the
+    B200 against outputs of the reference's own module."""
+    from common import load_golden
+    from oracle.make_golden import g_case_inputs, posterior_noise, posterior_spectrogram
+    name = "ae_gin256_stages"
+    gold = load_golden(name)
+    _, mel_len, g, gin = g_case_inputs(name)
+    net = _net(gin_channels=gin)
+    net.load_state_dict(state_dict_for("ae", gin=gin))
+    net = net.to(DEV)
+    z, m, logs, mask, x = net.posterior_encode(posterior_spectrogram(name).to(DEV), mel_len.to(DEV), g=g.to(DEV),
+                                               noise=posterior_noise(name).to(DEV))
+    torch.cuda.synchronize()
+    s = snr_db(gold["post_z"], z.cpu())
+    report("posterior_z_snr_db/gin256", round(s, 2))
+    assert s > 50 and snr_db(gold["post_m"], m.cpu()) > 50 and snr_db(gold["post_x"], x.cpu()) > 45
+    assert float(z[1, :, int(mel_len[1]):].abs().max()) == 0.0

@@ -219,3 +219,20 @@ def test_packer_refuses_weights_beyond_fp16_range():
     with pytest.raises(ValueError, match="fp16 range"):
         packer.pack_conv(w, None, dtype=torch.float16)
     assert torch.isfinite(packer.pack_conv(w, None, dtype=torch.bfloat16).w.float()).all()
+
+
+def test_posterior_encode_orchestration_against_reference_golden(monkeypatch):
+    """PosteriorEncoder (models_ae.py:256-291) on the SpecDecoder's kernels - host orchestration through the
+    emulated ops against outputs of the reference's own spec_encoder (tests/golden/ae_gin256_stages.npz)."""
+    from oracle.make_golden import g_case_inputs, posterior_noise, posterior_spectrogram
+    _emu(monkeypatch)
+    name = "ae_gin256_stages"
+    gold = load_golden(name)
+    _, mel_len, g, gin = g_case_inputs(name)
+    net, _ = build_model("ae", gin=gin)
+    z, m, logs, mask, x = net.posterior_encode(posterior_spectrogram(name), mel_len, g=g, noise=posterior_noise(name))
+    assert z.shape == gold["post_z"].shape and mask.shape == (2, 1, z.shape[2])
+    assert snr_db(gold["post_m"], m) > 50 and snr_db(gold["post_z"], z) > 50 and snr_db(gold["post_x"], x) > 45
+    assert max_abs(gold["post_logs"], logs) < 2e-2
+    n1 = int(mel_len[1])
+    assert float(z[1, :, n1:].abs().max()) == 0.0            # z is masked (models_ae.py:290)

@@ -8,7 +8,7 @@ import torch
 
 from common import GOLDEN, flat, load_golden, max_abs, state_dict_for
 from oracle import ref_harness, visinger_oracle as vo
-from oracle.make_golden import CASES, G_CASES, case_inputs, g_case_inputs
+from oracle.make_golden import CASES, G_CASES, case_inputs, g_case_inputs, posterior_noise, posterior_spectrogram
 from music_generation_b200 import synthetic
 
 TOL = 2e-5     # fp32 reduction-order noise between thread counts / machines
@@ -70,6 +70,10 @@ def test_oracle_speaker_conditioning_matches_reference_golden(name):
     assert o.shape == gold["o"].shape and max_abs(gold["o"], o) < TOL
     # g must matter: the unconditioned path gives a different waveform
     assert max_abs(gold["o"], vo.generator(sd, gold["hid"], vo.DEFAULT_HP)) > 1e-3
+    # training-side PosteriorEncoder (models_ae.py:256-291), same g
+    pz, pm, plogs, pmask, px = vo.posterior_encoder(sd, posterior_spectrogram(name), mel_len, posterior_noise(name), g=g)
+    for key, t in (("post_z", pz), ("post_m", pm), ("post_logs", plogs), ("post_x", px)):
+        assert max_abs(gold[key], t) < 1e-4, key
 
 
 @pytest.mark.skipif(not ref_harness.available(), reason="reference tree only exists in the build container")
