@@ -60,3 +60,24 @@ class Synthesiser:
                               legacy_scalar=self.legacy_scalar, scales_out=scales)
         self.last = {"o": o, "mel_len": mel_len, "offsets": offsets, "scales": scales}
         return song
+
+    @torch.no_grad()
+    def syn_long(self, line, *, segment_frames=None, overlap=0, noise=None, ph_dur=None, g=None):
+        """One utterance of any length (a multi-minute take; BASELINE config 4) -> peak-normalised int16 audio with the
+        0.2 s lead-in, on the device.  `line`: the (phones, notes, note_lengths, phoneme_shengdiao) tuple `get_text`
+        returns.  Frame-level transformers per segment, everything convolutional over the full length
+        (SynthesizerTrn.infer_long, segments.py): no seam between segments, unlike the reference's per-line concatenation
+        (pipline_inference_svs_v6_multispeaker.py:242)."""
+        dev = self.net_g.device
+        x, lens, notes, durs, tones = (t.to(dev) for t in self.collate([line]))
+        res = self.net_g.infer_long(x, lens, notes, durs, tones, ph_dur=ph_dur, segment_frames=segment_frames, overlap=overlap,
+                                    noise=noise, g=g)
+        o = res[0]
+        mel_len = res[1].sum(dim=(1, 2)).to(torch.int64)
+        total = int(mel_len.sum().item()) * self.net_g.hop
+        song = torch.empty(LEAD_IN + total, device=dev, dtype=torch.int16)
+        with torch.cuda.device(dev):
+            ops.song_assemble(o, mel_len, torch.zeros(1, device=dev, dtype=torch.int64), song, hop=self.net_g.hop,
+                              lead_in=LEAD_IN, legacy_scalar=self.legacy_scalar)
+        self.last = {"o": o, "mel_len": mel_len}
+        return song

@@ -41,6 +41,7 @@ class _Enc:
 
 class SynthesizerTrn(nn.Module):
     variant = "ae"
+    GENERATOR_HALO_FRAMES = 32          # > receptive field of the Generator in frames (conv_pre 3 + stage 0: 7.5 + ...)
 
     def __init__(self, n_vocab, spec_channels, segment_size, inter_channels, hidden_channels, filter_channels,
                  n_heads, n_layers, kernel_size, p_dropout, resblock, resblock_kernel_sizes,
@@ -65,6 +66,7 @@ class SynthesizerTrn(nn.Module):
         self.n_speakers, self.gin_channels, self.use_sdp = n_speakers, gin_channels, use_sdp
         self.operand_dtype = {"fp16": torch.float16, "bf16": torch.bfloat16}[operand_dtype]
         self.generator_chunk_frames = generator_chunk_frames
+        self.generator_time_chunk_frames = 65536       # per utterance; longer inputs are cut in time with exact halos
         self.generator_wide_chunk_frames, self.generator_wide_stages = generator_wide_chunk_frames, generator_wide_stages
         if f0_precision not in ("split", "fp32"):
             raise ValueError("f0_precision must be 'split' (tensor cores, fp16 hi/lo operands) or 'fp32' (SIMT)")
@@ -396,6 +398,18 @@ class SynthesizerTrn(nn.Module):
         lose 10 % beyond ~32 k frames per chunk)."""
         P = self._packed
         B, T, _ = x16.shape
+        tc = self.generator_time_chunk_frames
+        if tc and T > tc + 2 * self.GENERATOR_HALO_FRAMES:
+            # one very long utterance: cut in time with exact halos (the Generator's receptive field is < 16 frames per
+            # side; conv zero padding is only ever seen at the true ends) - bit-identical to the uncut call
+            out = torch.empty(B, 1, T * self.hop, device=x16.device, dtype=torch.float32)
+            hl = self.GENERATOR_HALO_FRAMES
+            for t0 in range(0, T, tc):
+                t1 = min(T, t0 + tc)
+                s0, s1 = max(0, t0 - hl), min(T, t1 + hl)
+                part = self._generator(x16[:, s0:s1].contiguous(), gbias)
+                out[:, :, t0 * self.hop:t1 * self.hop] = part[:, :, (t0 - s0) * self.hop:(t1 - s0) * self.hop]
+            return out
         out = torch.empty(B, 1, T * self.hop, device=x16.device, dtype=torch.float32)
         n_st = len(self.upsample_rates)
         n_wide = min(max(int(self.generator_wide_stages), 0), n_st)
@@ -583,6 +597,186 @@ class SynthesizerTrn(nn.Module):
         gr.replay()
         return tuple(None if o_ is None else o_.clone() for o_ in outs), {k: v.clone() for k, v in faux.items()}
 
+    def _text_post_net(self, h_lr, mlen, f0_score):
+        """TextPostNet (ext_modules/text_post_net.py:64-94) on length-regulated frames h_lr [B,T,H] (fp32, rows >= mlen[b]
+        are ignored).  Returns (stats [B,T,2*inter] = m_p | logs_p, log_f0 [B,T], mel [B,T,80], coarse f0 [B,T]).
+        Pure device work (CUDA-graph capturable).  Row t of every utterance takes position embedding t."""
+        P = self._packed
+        B, T, H = h_lr.shape
+        dev, dt, f32 = h_lr.device, self.operand_dtype, torch.float32
+        faux = {}
+        # 4. TextPostNet (ext_modules/text_post_net.py:64-94)
+        xe32 = torch.empty(B, T, H, device=dev, dtype=f32)
+        xe16 = torch.empty(B, T, H, device=dev, dtype=dt)
+        ops.add_pos_mask(h_lr, P["pos"], mlen, out32=xe32, out16=xe16)
+        # F0 predictor: tensor cores with fp16 (hi, lo) split operands (default), or fp32 SIMT (f0_precision="fp32")
+        f0h = torch.empty_like(xe32)
+        if P["f0_mode"] == "split":
+            f0s = torch.empty(B, T, 3 * H, device=dev, dtype=torch.float16)
+            ops.add_pos_mask(h_lr, P["pos"], mlen, out32=f0h, out16=f0s, split16=True)
+        else:
+            f0s = None
+            ops.add_pos_mask(h_lr, P["pos"], mlen, out32=f0h)
+        self._encoder(P["f0_enc"], f0h, f0s, mlen, P["f0_mode"])
+        log_f0 = torch.empty(B, T, 1, device=dev, dtype=f32)
+        ops.conv1d(P["f0_out"], f0h, lens=mlen, out32=log_f0)
+        log_f0 = log_f0.view(B, T)
+        coarse = torch.empty(B, T, device=dev, dtype=torch.int64)
+        f0e16 = torch.empty(B, T, H, device=dev, dtype=dt)
+        cin = None if f0_score is None else f0_score.to(device=dev, dtype=torch.int64).contiguous()
+        ops.f0_embed(log_f0, cin, P["f0_emb"], mlen, coarse, out16=f0e16)
+        # MelPredictNetwork (mel_predict_network.py:37-45)
+        m32 = torch.empty(B, T, H, device=dev, dtype=f32)
+        m16 = torch.empty(B, T, H, device=dev, dtype=dt)
+        ops.conv1d(P["mel_cond"], f0e16, res1=xe32, lens=mlen, out32=m32, out16=m16)
+        self._encoder(P["mel_enc"], m32, m16, mlen, "tc")
+        mel32 = torch.empty(B, T, 80, device=dev, dtype=f32)
+        ops.conv1d(P["mel_out"], m16, lens=mlen, out32=mel32)
+        # FramePriorNetwork (frame_prior_network.py:31-41)
+        fp_a = torch.empty(B, T, 80, device=dev, dtype=dt)
+        ops.conv1d(P["fp_cond"], f0e16, res1=mel32, lens=mlen, out16=fp_a)
+        src = fp_a
+        for pc in P["fp"]:
+            dst = torch.empty(B, T, H, device=dev, dtype=dt)
+            ops.conv1d(pc, src, act=ACT_GELU, lens=mlen, out16=dst)
+            src = dst
+        stats = torch.empty(B, T, 2 * self.inter_channels, device=dev, dtype=f32)
+        ops.conv1d(P["proj"], src, lens=mlen, out32=stats)
+        Ci = self.inter_channels
+
+        faux["f0_coarse"] = coarse
+        return stats, log_f0, mel32, faux
+
+    def _decode(self, stats, mlen, noise, g, noise_scale, max_len):
+        """Prior sample -> reverse flow -> [SpecDecoder + spec_proj] -> Generator (models_ae.py:643-650) on frame-level
+        statistics stats [B,T,2*inter].  Convolutional only: no limit on T.  Returns (o, z32, zp32, spec32 or None)."""
+        P = self._packed
+        B, T, _ = stats.shape
+        H, Ci = self.hidden_channels, self.inter_channels
+        dev, dt, f32 = stats.device, self.operand_dtype, torch.float32
+        # 5. z_p = m_p + noise * exp(logs_p) * noise_scale (models_ae.py:643)
+        if noise is None:
+            noise = torch.randn(B, Ci, T, device=dev, dtype=f32)
+        noise = noise.to(device=dev, dtype=f32).contiguous()
+        zp32 = torch.empty(B, T, Ci, device=dev, dtype=f32)
+        z16 = torch.empty(B, T, Ci, device=dev, dtype=dt)
+        ops.sample_prior(stats, noise, float(noise_scale), zp32=zp32, zp16=z16)
+        z32 = zp32.clone()
+
+        # speaker conditioning (optional; WN.cond_layer modules.py:152-159, Generator.cond models_ae.py:329-330)
+        g_btc = None
+        if g is not None:
+            if not self.gin_channels:
+                raise ValueError("model was built with gin_channels=0")
+            g_btc = g.to(device=dev, dtype=f32).reshape(B, 1, self.gin_channels).contiguous()
+
+        def cond_of(st):
+            if g_btc is None:
+                return None
+            out = torch.empty(B, 1, st["cond"].cout, device=dev, dtype=f32)
+            ops.conv1d(st["cond"], g_btc, out32=out)
+            return out.view(B, -1)
+
+        # 6. reverse flow (models_ae.py:246-253; modules.py:329-349), Flips folded into the weights
+        half = Ci // 2
+        hx32 = torch.empty(B, T, H, device=dev, dtype=f32)
+        hx16 = torch.empty(B, T, H, device=dev, dtype=dt)
+        wo16 = torch.empty(B, T, H, device=dev, dtype=dt)
+        for fl in P["flow"]:
+            io, oo = fl["in_off"], fl["out_off"]
+            ops.conv1d(fl["pre"], z16[:, :, io:io + half], lens=mlen, out32=hx32, out16=hx16)
+            self._wn(fl["wn"], hx32, hx16, mlen, wo16, cond_of(fl["wn"]))
+            ops.conv1d(fl["post"], wo16, alpha=-1.0, res1=z32[:, :, oo:oo + half], lens=mlen,
+                       out32=z32[:, :, oo:oo + half], out16=z16[:, :, oo:oo + half])
+
+        # 7. SpecDecoder + spec_proj (ae only; spec_decoder.py:41-46, models_ae.py:647-648)
+        gen_g = None
+        if g_btc is not None:
+            gg = torch.empty(B, 1, self.upsample_initial_channel, device=dev, dtype=f32)
+            ops.conv1d(P["g_cond"], g_btc, out32=gg)
+            gen_g = gg.view(B, -1)
+        Tg = T if max_len is None else min(T, int(max_len))
+        if self.variant == "ae":
+            ops.conv1d(P["sd_pre"], z16, lens=mlen, out32=hx32, out16=hx16)
+            self._wn(P["sd_wn"], hx32, hx16, mlen, wo16, cond_of(P["sd_wn"]))
+            gin16 = torch.empty(B, T, Ci, device=dev, dtype=dt)
+            spec32, sc = None, self.spec_channels
+            if self.fuse_spec_proj:
+                ops.conv1d(P["sd_fused"], wo16, lens=mlen, out16=gin16)
+            else:
+                sc_ld = 576
+                spec32 = torch.empty(B, T, sc_ld, device=dev, dtype=f32)
+                spec16 = torch.empty(B, T, sc_ld, device=dev, dtype=dt)
+                ops.conv1d(P["sd_proj"], wo16, lens=mlen, out32=spec32[:, :, :sc], out16=spec16[:, :, :sc])
+                ops.conv1d(P["spec_proj"], spec16[:, :, :sc], lens=mlen, out16=gin16)
+            gen_in = gin16
+        else:
+            gen_in = z16          # z is already masked ((x1 - m) * mask; x0 masked upstream)
+        if Tg != T:
+            gen_in = gen_in[:, :Tg].contiguous()
+
+        # 8. Generator
+        o = self._generator(gen_in, gen_g)
+
+        spec = spec32[:, :, :sc] if self.variant == "ae" and spec32 is not None else None
+        return o, z32, zp32, spec
+
+    # ------------------------------------------------------------------ long utterances (SURVEY 8f-2, config 4)
+    @torch.no_grad()
+    def infer_long(self, x, x_lengths, note_pitch_id, note_duration, phone_shengdiao, ph_dur=None, *, segment_frames=None,
+                   overlap=0, noise_scale=1, max_len=None, noise=None, g=None):
+        """`infer` for utterances longer than the position table (2000 frames = 23.2 s in the reference, which raises
+        there: text_post_net.py:26,69-72).  Same inputs and result tuple as `infer`.
+
+        Phoneme level (text encoder, durations, length regulator) runs over the whole utterance.  The frame-level
+        transformers (TextPostNet) run per segment - `segment_frames` core frames plus `overlap` frames of context on
+        each side (segments.plan_segments), all segments of all utterances as ONE ragged batch - and the core frames'
+        statistics are written into full-length tensors.  Prior sample, reverse flow, SpecDecoder and Generator are
+        convolutional and run over the full length, so there is no seam in the waveform; the Generator is cut in time
+        (`generator_time_chunk_frames`, exact halos) only to bound memory.  With one segment this is `infer` bit for bit."""
+        from . import segments as seg
+        _require_cuda(x)
+        dev = self.device
+        with _device_guard(dev):
+            y_dtype = x.dtype
+            B = x.shape[0]
+            h, ends, mel_len, mlen, T, _ = self._phoneme_level(x, x_lengths, note_pitch_id, note_duration, phone_shengdiao,
+                                                               ph_dur)
+            P = self._packed
+            f32, H, Ci = torch.float32, self.hidden_channels, self.inter_channels
+            n_pos = P["pos"].shape[0]
+            if segment_frames is None:
+                segment_frames = n_pos - 2 * overlap
+            if segment_frames <= 0 or segment_frames + 2 * overlap > n_pos:
+                raise ValueError(f"segment_frames={segment_frames} + 2 * overlap={overlap} exceeds the {n_pos}-row position table")
+            h_lr = torch.empty(B, T, H, device=dev, dtype=f32)
+            lr_index = torch.empty(B, T, device=dev, dtype=torch.int32)
+            ops.lr_gather(h, ends, mlen, h_lr, lr_index)
+            lens = mel_len.tolist()
+            plan = [(b, *s_) for b in range(B) for s_ in seg.plan_segments(int(lens[b]), segment_frames, overlap)]
+            Ts = max(c[4] - c[3] for c in plan)
+            seg_h = torch.zeros(len(plan), Ts, H, device=dev, dtype=f32)
+            for i, (b, c0, c1, x0, x1) in enumerate(plan):
+                seg_h[i, :x1 - x0] = h_lr[b, x0:x1]
+            seg_len = torch.tensor([c[4] - c[3] for c in plan], device=dev, dtype=torch.int32)
+            s_stats, s_lf0, s_mel, faux = self._text_post_net(seg_h, seg_len, None)
+            stats = torch.zeros(B, T, 2 * Ci, device=dev, dtype=f32)
+            log_f0 = torch.zeros(B, T, device=dev, dtype=f32)
+            mel32 = torch.zeros(B, T, 80, device=dev, dtype=f32)
+            coarse = torch.zeros(B, T, device=dev, dtype=torch.int64)
+            for i, (b, c0, c1, x0, x1) in enumerate(plan):
+                a, e = c0 - x0, c1 - x0
+                stats[b, c0:c1], log_f0[b, c0:c1], mel32[b, c0:c1] = s_stats[i, a:e], s_lf0[i, a:e], s_mel[i, a:e]
+                coarse[b, c0:c1] = faux["f0_coarse"][i, a:e]
+            o, z32, zp32, spec = self._decode(stats, mlen, noise, g, noise_scale, max_len)
+            self.last_aux.update(lr_index=lr_index, f0_coarse=coarse, segments=plan)
+        y_mask = (torch.arange(T, device=dev).unsqueeze(0) < mel_len.unsqueeze(1)).unsqueeze(1).to(y_dtype)
+        bct = lambda t: t.transpose(1, 2)
+        m_p, logs_p = bct(stats[:, :, :Ci]), bct(stats[:, :, Ci:])
+        if self.variant == "ae":
+            return o, y_mask, (bct(z32), bct(zp32), m_p, logs_p), log_f0, None if spec is None else bct(spec), bct(mel32)
+        return o, y_mask, (bct(z32), bct(zp32), m_p, logs_p), log_f0, bct(mel32)
+
     # ------------------------------------------------------------------ the public entry point
     @torch.no_grad()
     def infer(self, x, x_lengths, note_pitch_id, note_duration, phone_shengdiao, ph_dur=None, lf0=None, sid=None,
@@ -616,15 +810,15 @@ class SynthesizerTrn(nn.Module):
                 self.last_aux["saturation_events"] = int(n.value)
         return res
 
-    def _infer(self, x, x_lengths, note_pitch_id, note_duration, phone_shengdiao, ph_dur, lf0, noise_scale, max_len,
-               noise, g, f0_score):
+    def _phoneme_level(self, x, x_lengths, note_pitch_id, note_duration, phone_shengdiao, ph_dur, f0_score=None):
+        """TextEncoder -> DurationPredictor -> floor -> LengthRegulator scan (models_ae.py:612-627).  Returns
+        (h [B,P,H] fp32, ends, mel_len int64, mlen int32, T, f0_score) and fills last_aux; ONE host sync (T)."""
         P = self._packed or self._pack()
         dev, dt = self.device, self.operand_dtype
         f32 = torch.float32
         B, Pn = x.shape
         H = self.hidden_channels
         i64 = lambda t: t.to(device=dev, dtype=torch.int64).contiguous()
-        y_dtype = x.dtype                     # y_mask takes x's dtype (commons.sequence_mask(...).to(x.dtype), models_ae.py:632)
         x, note_pitch_id, phone_shengdiao, x_lengths = i64(x), i64(note_pitch_id), i64(phone_shengdiao), i64(x_lengths)
         note_duration = note_duration.contiguous().float()
         if f0_score is not None:              # user-supplied buckets: validated here (nn.Embedding would raise)
@@ -677,6 +871,18 @@ class SynthesizerTrn(nn.Module):
                              "(index out of range in self)")
         if T <= 0:
             raise RuntimeError("SynthesizerTrn.infer: every utterance has zero frames")
+        return h, ends, mel_len, mlen, T, f0_score
+
+    def _infer(self, x, x_lengths, note_pitch_id, note_duration, phone_shengdiao, ph_dur, lf0, noise_scale, max_len,
+               noise, g, f0_score):
+        y_dtype = x.dtype                     # y_mask takes x's dtype (commons.sequence_mask(...).to(x.dtype), models_ae.py:632)
+        B, Pn = x.shape
+        h, ends, mel_len, mlen, T, f0_score = self._phoneme_level(x, x_lengths, note_pitch_id, note_duration,
+                                                                   phone_shengdiao, ph_dur, f0_score)
+        P = self._packed
+        dev, dt, f32 = self.device, self.operand_dtype, torch.float32
+        H = self.hidden_channels
+        aux = self.last_aux
         n_pos = P["pos"].shape[0]
         if T > n_pos:
             # the reference fails here too: position table has 2000 rows (text_post_net.py:26,69-72)
@@ -688,117 +894,13 @@ class SynthesizerTrn(nn.Module):
         def frame_level(h, ends, mlen, noise, g, f0_score):
             """Everything after the host learns T: ~95 % of the launches.  Pure device work on its arguments (no host
             sync), so it can be captured in a CUDA graph."""
-            faux = {}
             h_lr = torch.empty(B, T, H, device=dev, dtype=f32)
             lr_index = torch.empty(B, T, device=dev, dtype=torch.int32)
             ops.lr_gather(h, ends, mlen, h_lr, lr_index)
-            faux["lr_index"] = lr_index
-
-            # 4. TextPostNet (ext_modules/text_post_net.py:64-94)
-            xe32 = torch.empty(B, T, H, device=dev, dtype=f32)
-            xe16 = torch.empty(B, T, H, device=dev, dtype=dt)
-            ops.add_pos_mask(h_lr, P["pos"], mlen, out32=xe32, out16=xe16)
-            # F0 predictor: tensor cores with fp16 (hi, lo) split operands (default), or fp32 SIMT (f0_precision="fp32")
-            f0h = torch.empty_like(xe32)
-            if P["f0_mode"] == "split":
-                f0s = torch.empty(B, T, 3 * H, device=dev, dtype=torch.float16)
-                ops.add_pos_mask(h_lr, P["pos"], mlen, out32=f0h, out16=f0s, split16=True)
-            else:
-                f0s = None
-                ops.add_pos_mask(h_lr, P["pos"], mlen, out32=f0h)
-            self._encoder(P["f0_enc"], f0h, f0s, mlen, P["f0_mode"])
-            log_f0 = torch.empty(B, T, 1, device=dev, dtype=f32)
-            ops.conv1d(P["f0_out"], f0h, lens=mlen, out32=log_f0)
-            log_f0 = log_f0.view(B, T)
-            coarse = torch.empty(B, T, device=dev, dtype=torch.int64)
-            f0e16 = torch.empty(B, T, H, device=dev, dtype=dt)
             cin = None if f0_score is None else f0_score.to(device=dev, dtype=torch.int64).contiguous()
-            ops.f0_embed(log_f0, cin, P["f0_emb"], mlen, coarse, out16=f0e16)
-            faux["f0_coarse"] = coarse
-            # MelPredictNetwork (mel_predict_network.py:37-45)
-            m32 = torch.empty(B, T, H, device=dev, dtype=f32)
-            m16 = torch.empty(B, T, H, device=dev, dtype=dt)
-            ops.conv1d(P["mel_cond"], f0e16, res1=xe32, lens=mlen, out32=m32, out16=m16)
-            self._encoder(P["mel_enc"], m32, m16, mlen, "tc")
-            mel32 = torch.empty(B, T, 80, device=dev, dtype=f32)
-            ops.conv1d(P["mel_out"], m16, lens=mlen, out32=mel32)
-            # FramePriorNetwork (frame_prior_network.py:31-41)
-            fp_a = torch.empty(B, T, 80, device=dev, dtype=dt)
-            ops.conv1d(P["fp_cond"], f0e16, res1=mel32, lens=mlen, out16=fp_a)
-            src = fp_a
-            for pc in P["fp"]:
-                dst = torch.empty(B, T, H, device=dev, dtype=dt)
-                ops.conv1d(pc, src, act=ACT_GELU, lens=mlen, out16=dst)
-                src = dst
-            stats = torch.empty(B, T, 2 * self.inter_channels, device=dev, dtype=f32)
-            ops.conv1d(P["proj"], src, lens=mlen, out32=stats)
-            Ci = self.inter_channels
-
-            # 5. z_p = m_p + noise * exp(logs_p) * noise_scale (models_ae.py:643)
-            if noise is None:
-                noise = torch.randn(B, Ci, T, device=dev, dtype=f32)
-            noise = noise.to(device=dev, dtype=f32).contiguous()
-            zp32 = torch.empty(B, T, Ci, device=dev, dtype=f32)
-            z16 = torch.empty(B, T, Ci, device=dev, dtype=dt)
-            ops.sample_prior(stats, noise, float(noise_scale), zp32=zp32, zp16=z16)
-            z32 = zp32.clone()
-
-            # speaker conditioning (optional; WN.cond_layer modules.py:152-159, Generator.cond models_ae.py:329-330)
-            g_btc = None
-            if g is not None:
-                if not self.gin_channels:
-                    raise ValueError("model was built with gin_channels=0")
-                g_btc = g.to(device=dev, dtype=f32).reshape(B, 1, self.gin_channels).contiguous()
-
-            def cond_of(st):
-                if g_btc is None:
-                    return None
-                out = torch.empty(B, 1, st["cond"].cout, device=dev, dtype=f32)
-                ops.conv1d(st["cond"], g_btc, out32=out)
-                return out.view(B, -1)
-
-            # 6. reverse flow (models_ae.py:246-253; modules.py:329-349), Flips folded into the weights
-            half = Ci // 2
-            hx32 = torch.empty(B, T, H, device=dev, dtype=f32)
-            hx16 = torch.empty(B, T, H, device=dev, dtype=dt)
-            wo16 = torch.empty(B, T, H, device=dev, dtype=dt)
-            for fl in P["flow"]:
-                io, oo = fl["in_off"], fl["out_off"]
-                ops.conv1d(fl["pre"], z16[:, :, io:io + half], lens=mlen, out32=hx32, out16=hx16)
-                self._wn(fl["wn"], hx32, hx16, mlen, wo16, cond_of(fl["wn"]))
-                ops.conv1d(fl["post"], wo16, alpha=-1.0, res1=z32[:, :, oo:oo + half], lens=mlen,
-                           out32=z32[:, :, oo:oo + half], out16=z16[:, :, oo:oo + half])
-
-            # 7. SpecDecoder + spec_proj (ae only; spec_decoder.py:41-46, models_ae.py:647-648)
-            gen_g = None
-            if g_btc is not None:
-                gg = torch.empty(B, 1, self.upsample_initial_channel, device=dev, dtype=f32)
-                ops.conv1d(P["g_cond"], g_btc, out32=gg)
-                gen_g = gg.view(B, -1)
-            Tg = T if max_len is None else min(T, int(max_len))
-            if self.variant == "ae":
-                ops.conv1d(P["sd_pre"], z16, lens=mlen, out32=hx32, out16=hx16)
-                self._wn(P["sd_wn"], hx32, hx16, mlen, wo16, cond_of(P["sd_wn"]))
-                gin16 = torch.empty(B, T, Ci, device=dev, dtype=dt)
-                spec32, sc = None, self.spec_channels
-                if self.fuse_spec_proj:
-                    ops.conv1d(P["sd_fused"], wo16, lens=mlen, out16=gin16)
-                else:
-                    sc_ld = 576
-                    spec32 = torch.empty(B, T, sc_ld, device=dev, dtype=f32)
-                    spec16 = torch.empty(B, T, sc_ld, device=dev, dtype=dt)
-                    ops.conv1d(P["sd_proj"], wo16, lens=mlen, out32=spec32[:, :, :sc], out16=spec16[:, :, :sc])
-                    ops.conv1d(P["spec_proj"], spec16[:, :, :sc], lens=mlen, out16=gin16)
-                gen_in = gin16
-            else:
-                gen_in = z16          # z is already masked ((x1 - m) * mask; x0 masked upstream)
-            if Tg != T:
-                gen_in = gen_in[:, :Tg].contiguous()
-
-            # 8. Generator
-            o = self._generator(gen_in, gen_g)
-
-            spec = spec32[:, :, :sc] if self.variant == "ae" and spec32 is not None else None
+            stats, log_f0, mel32, faux = self._text_post_net(h_lr, mlen, cin)
+            faux["lr_index"] = lr_index
+            o, z32, zp32, spec = self._decode(stats, mlen, noise, g, noise_scale, max_len)
             return (o, z32, zp32, stats, log_f0, spec, mel32), faux
 
         args = (h, ends, mlen, noise, g, f0_score)

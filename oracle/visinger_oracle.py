@@ -418,3 +418,41 @@ def infer(sd, x, x_lengths, note_pitch_id, note_duration, phone_shengdiao, noise
         return o, y_mask, (z, z_p, m_p, logs_p), log_f0, spec, mel
     o = generator(sd, (z * y_mask)[:, :, :max_len], hp, g=g, taps=taps)
     return o, y_mask, (z, z_p, m_p, logs_p), log_f0, mel
+
+
+def infer_long(sd, x, x_lengths, note_pitch_id, note_duration, phone_shengdiao, noise, plan, ph_dur=None, noise_scale=1.0,
+               variant="ae", hp=None, g=None, taps=None):
+    """Composition checked by tests/test_gpu_long.py for utterances beyond the reference's 2000-frame position table:
+    the reference's modules exactly as `infer` calls them, except that TextPostNet (the only module with the limit,
+    text_post_net.py:26,69-72) is evaluated per segment of `plan` = [(b, core0, core1, ctx0, ctx1)] on the
+    length-regulated frames [ctx0, ctx1) - positions restart at ctx0 - and the core frames' m_p / logs_p / log_f0 / mel
+    are concatenated; flow, SpecDecoder and Generator then run over the full length (they are convolutional)."""
+    hp = hp or DEFAULT_HP
+    h_text, x_mask = text_encoder(sd, x, note_pitch_id, note_duration, x_lengths, phone_shengdiao)
+    if ph_dur is None:
+        durations = quantize_durations(duration_predictor(sd, h_text, x_mask), note_duration)
+    else:
+        durations = ph_dur
+    h_lr, mel_len, lr_index = length_regulate(h_text, durations)
+    B, _, T = h_lr.shape
+    y_mask = sequence_mask(mel_len, T).unsqueeze(1).to(x.dtype)
+    m_p, logs_p = torch.zeros(B, 192, T), torch.zeros(B, 192, T)
+    log_f0, mel, f0c = torch.zeros(B, T), torch.zeros(B, 80, T), torch.zeros(B, T, dtype=torch.long)
+    for b, c0, c1, x0, x1 in plan:
+        seg = h_lr[b:b + 1, :, x0:x1].clone()
+        ones = torch.ones(1, 1, x1 - x0, dtype=x.dtype)
+        sm, sl, sf, smel, sc = text_post_net(sd, seg, ones)
+        a, e = c0 - x0, c1 - x0
+        m_p[b, :, c0:c1], logs_p[b, :, c0:c1], log_f0[b, c0:c1] = sm[0, :, a:e], sl[0, :, a:e], sf[0, a:e]
+        mel[b, :, c0:c1], f0c[b, c0:c1] = smel[0, :, a:e], sc[0, a:e]
+    z_p = m_p + noise * torch.exp(logs_p) * noise_scale
+    z = flow_reverse(sd, z_p, y_mask, g=g)
+    if taps is not None:
+        taps.update(durations=durations, mel_len=mel_len, lr_index=lr_index, f0_coarse=f0c)
+    if variant == "ae":
+        spec = spec_decoder(sd, z, mel_len, g=g)
+        hid = conv(sd, "spec_proj", spec)
+        o = generator(sd, hid * y_mask, hp, g=g)
+        return o, y_mask, (z, z_p, m_p, logs_p), log_f0, spec, mel
+    o = generator(sd, z * y_mask, hp, g=g)
+    return o, y_mask, (z, z_p, m_p, logs_p), log_f0, mel

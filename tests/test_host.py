@@ -236,3 +236,33 @@ def test_posterior_encode_orchestration_against_reference_golden(monkeypatch):
     assert max_abs(gold["post_logs"], logs) < 2e-2
     n1 = int(mel_len[1])
     assert float(z[1, :, n1:].abs().max()) == 0.0            # z is masked (models_ae.py:290)
+
+
+def test_infer_long_orchestration_vs_oracle_and_single_segment_identity(monkeypatch):
+    """segment plan + scatter of the per-segment TextPostNet statistics + full-length conv stages, through
+    the emulated ops against oracle.infer_long; one segment covering everything is `infer` itself."""
+    from music_generation_b200 import segments
+    _emu(monkeypatch)
+    assert segments.plan_segments(70, 30, 5) == [(0, 30, 0, 35), (30, 60, 25, 65), (60, 70, 55, 70)]
+    assert segments.plan_segments(30, 30, 5) == [(0, 30, 0, 30)] and segments.plan_segments(0, 30, 5) == []
+    net, sd = build_model("ae")
+    inp = synthetic.make_inputs(2, 9, seed=13, ragged=True)
+    ph_dur = synthetic.make_ph_dur(inp["x_lengths"], 9, 70, seed=13)
+    T = int(ph_dur.sum(1).max())
+    noise = synthetic.make_noise(2, 192, T, seed=13)
+    args = (inp["x"], inp["x_lengths"], inp["note_pitch_id"], inp["note_duration"])
+    res = net.infer_long(*args, phone_shengdiao=inp["phone_shengdiao"], ph_dur=ph_dur, noise=noise, segment_frames=30, overlap=5)
+    plan = net.last_aux["segments"]
+    assert [p[0] for p in plan] == sorted(p[0] for p in plan) and plan[0][1:] == (0, 30, 0, 35)
+    ref = vo.infer_long(sd, noise=noise, ph_dur=ph_dur, plan=plan, **inp)
+    assert torch.equal(res[1], ref[1])
+    assert snr_db(ref[0], res[0]) >= SNR_DB_TOL and max_abs(ref[0], res[0]) <= MAX_ABS_TOL
+    assert snr_db(ref[2][2], res[2][2]) > 50                                  # m_p: per-segment statistics in the right frames
+    one = net.infer_long(*args, phone_shengdiao=inp["phone_shengdiao"], ph_dur=ph_dur, noise=noise, segment_frames=1000)
+    full = net.infer(*args, phone_shengdiao=inp["phone_shengdiao"], ph_dur=ph_dur, noise=noise)
+    for a, b in zip(flat(one), flat(full)):
+        assert torch.equal(a, b)
+    # segmentation changes the frame-level transformer's context, so the segmented result differs from the unsegmented one
+    assert max_abs(res[0], full[0]) > 1e-4
+    with pytest.raises(ValueError):
+        net.infer_long(*args, phone_shengdiao=inp["phone_shengdiao"], ph_dur=ph_dur, noise=noise, segment_frames=1990, overlap=10)
