@@ -342,14 +342,14 @@ def run_gpu_arm(args, rank, local_rank, world):
     def timed(fn, steps):
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
-        l0 = _lib.LAUNCHES
+        l0 = _lib.launches()
         ev0.record()
         for _ in range(steps):
             fn()
         ev1.record()
         barrier()
         ms = ev0.elapsed_time(ev1)
-        launches = _lib.LAUNCHES - l0
+        launches = _lib.launches() - l0
         if world > 1:
             t = torch.tensor([ms], device=dev, dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)

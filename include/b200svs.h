@@ -115,6 +115,11 @@ typedef struct b200svs_conv_args {
 
 const char* b200svs_last_error(void);
 int b200svs_abi_version(void);
+/* Kernels launched through this library by the calling process so far (every entry point counts its own launches). */
+int64_t b200svs_launch_count(void);
+/* sizeof of the ABI structs as the library was compiled (0 epilogue, 1 conv_args, 2 conv_w, 3 generator_w, 4 wn_w,
+ * 5 encoder_layer_w): lets a binding verify its mirror of the layouts. */
+int b200svs_abi_struct_size(int32_t which);
 /* 0 if an sm_100 device is current and the driver exports cuTensorMapEncodeTiled */
 int b200svs_check_device(void);
 
@@ -228,6 +233,85 @@ int b200svs_btc_to_bct(const float* in_btc, int32_t in_ld, int32_t B, int32_t C,
 int b200svs_song_assemble(const float* o, int64_t o_ld, const int64_t* mel_len, const int32_t* order,
                           const int64_t* offsets, int32_t n_lines, int32_t hop, int32_t lead_in, int32_t legacy_scalar,
                           uint32_t* peak_ws, int16_t* song, float* scales_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * Stage-level entry points: one call enqueues every kernel of a stage from a table of packed weights and
+ * ONE caller-owned workspace - no host language in the loop, so a C / C++ / Go / Rust host can drive the path, and a
+ * small (B = 1) call does not pay an interpreter round trip per kernel.  Nothing is allocated; the workspace size comes
+ * from the matching *_workspace_bytes function and must be 256-byte aligned.  All calls enqueue on `stream` and return
+ * without synchronising. */
+
+/* Packed weights of one convolution (music_generation_b200/packer.py produces them; layout as in b200svs_conv_args). */
+typedef struct b200svs_conv_w {
+  const void* w;      /* tc: 16-bit [ntaps][cout_pad][cin_pad]; f32: float [ntaps][cin][cout_pad] */
+  const float* bias;  /* [cout_pad] or NULL */
+  int32_t ntaps, dil, pad_left, cin, cin_pad, cout, cout_pad, block_n;
+  int32_t gate;       /* GATE epilogue (WN in_layers): n_out = cout / 2 */
+  int32_t f32;        /* 1: fp32 SIMT conv */
+  int32_t fold;       /* 2: time-pair folded (dense [B,T,C] tensors are passed as [B,T/2,2C]) */
+  int32_t n_out;      /* columns the epilogue stores */
+  float out_scale;    /* split-precision convs: folded into the epilogue's alpha */
+} b200svs_conv_w;
+
+#define B200SVS_MAX_STAGES 6
+#define B200SVS_MAX_KERNELS 4
+#define B200SVS_MAX_PAIRS 4
+
+/* Generator.forward (VISinger/models_ae.py:327-346) with ResBlock1 (modules.py:210-223), the default 16-bit streams
+ * (residual recovered from the activated tensor, 16-bit MRF sum): conv_pre -> n_stages x { ConvTranspose (polyphase),
+ * n_kernels ResBlocks of n_pairs pairs, MRF average } -> leaky-ReLU(0.01) -> conv_post -> tanh. */
+typedef struct b200svs_generator_w {
+  int32_t n_stages, n_kernels, n_pairs;
+  int32_t dtype;                       /* B200SVS_DT_F16 (the 16-bit residual recovery needs fp16 operands) */
+  int32_t up_rate[B200SVS_MAX_STAGES];
+  int32_t channels[B200SVS_MAX_STAGES]; /* output channels of stage i */
+  int32_t pre_channels;                /* upsample_initial_channel */
+  int32_t chunk_frames, wide_chunk_frames, wide_stages;   /* utterance chunking */
+  float lrelu_slope;                   /* 0.1 (modules.py:17) */
+  b200svs_conv_w pre;
+  b200svs_conv_w ups[B200SVS_MAX_STAGES];
+  b200svs_conv_w rb[B200SVS_MAX_STAGES][B200SVS_MAX_KERNELS][B200SVS_MAX_PAIRS][2];   /* [stage][kernel][pair][conv1, conv2] */
+  const float* post_w;                 /* conv_post [taps][C] fp32 */
+  int32_t post_taps;
+} b200svs_generator_w;
+
+size_t b200svs_generator_workspace_bytes(const b200svs_generator_w* w, int32_t B, int32_t T);
+/* x16: [B,T,inter] 16-bit masked Generator input (row stride x_ld); gbias: nullable [B, pre_channels] speaker term added
+ * to conv_pre (Generator.cond, models_ae.py:329-330); out: [B, T * prod(up_rate)] fp32. */
+int b200svs_generator_fwd(const b200svs_generator_w* w, const void* x16, int32_t x_ld, int32_t B, int32_t T,
+                          const float* gbias, int32_t gbias_ld, float* out, void* workspace, size_t workspace_bytes,
+                          void* stream);
+
+/* modules.WN.forward (VISinger/modules.py:148-176): n_layers x { gate conv (tanh * sigmoid fused), res 1x1 conv,
+ * x = (x + res) * mask }, skip sum as ONE 1x1 conv over the K-concatenation of every layer's gate output. */
+#define B200SVS_MAX_WN_LAYERS 16
+typedef struct b200svs_wn_w {
+  int32_t n_layers, hidden, dtype;
+  b200svs_conv_w in[B200SVS_MAX_WN_LAYERS];
+  b200svs_conv_w rs[B200SVS_MAX_WN_LAYERS];   /* rows [0, hidden) = residual half (unused for the last layer) */
+  b200svs_conv_w skip_cat;                    /* [hidden, n_layers * hidden] */
+} b200svs_wn_w;
+size_t b200svs_wn_workspace_bytes(const b200svs_wn_w* w, int32_t B, int32_t T);
+/* x32 / x16: [B,T,hidden] masked input, fp32 + 16-bit copy, both updated in place; lens: [B] valid rows; gcond: nullable
+ * [B, n_layers * 2 * hidden] speaker term (cond_layer output in gate order); out16: [B,T,hidden] masked skip sum. */
+int b200svs_wn_stack_fwd(const b200svs_wn_w* w, float* x32, void* x16, const int32_t* lens, int32_t B, int32_t T,
+                         const float* gcond, int32_t gcond_ld, void* out16, void* workspace, size_t workspace_bytes,
+                         void* stream);
+
+/* One attentions.Encoder layer (VISinger/attentions.py:35-47,138-179,277-285), post-LN:
+ *   x = LN1(x + conv_o(MHA(x)));  x = LN2(x + FFN(x)).
+ * mode 0: fp32 SIMT convs + fp32 attention (x16 unused); 1: tensor cores, 16-bit operands (x16 = 16-bit copy of x32);
+ * 2: split precision (x16 = fp16 [hi | lo | hi], 3 * hidden columns). */
+typedef struct b200svs_encoder_layer_w {
+  int32_t hidden, filter, heads, window, mode, dtype;
+  b200svs_conv_w qkv, o, ffn1, ffn2;
+  const float *rel_k, *rel_v;          /* [2 * window + 1, hidden / heads] */
+  const float *ln1_g, *ln1_b, *ln2_g, *ln2_b;
+} b200svs_encoder_layer_w;
+size_t b200svs_encoder_workspace_bytes(const b200svs_encoder_layer_w* w, int32_t B, int32_t T);
+/* Runs n_layers consecutive layers (w[0..n_layers)) in place on x32 (and x16); lens: [B] int32. */
+int b200svs_encoder_fwd(const b200svs_encoder_layer_w* w, int32_t n_layers, float* x32, void* x16, const int32_t* lens,
+                        int32_t B, int32_t T, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Allocation-free variant of b200svs_song_assemble.  It has no counterpart in the reference and was added
  * for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses

@@ -45,15 +45,50 @@ class ConvArgs(C.Structure):
 
 _i32, _f32, _vp = C.c_int32, C.c_float, C.c_void_p
 
+# ---- stage-level API (include/b200svs.h "Stage-level entry points")
+MAX_STAGES, MAX_KERNELS, MAX_PAIRS, MAX_WN_LAYERS = 6, 4, 4, 16
+
+
+class ConvW(C.Structure):
+    _fields_ = [("w", _vp), ("bias", _vp),
+                ("ntaps", _i32), ("dil", _i32), ("pad_left", _i32), ("cin", _i32), ("cin_pad", _i32), ("cout", _i32),
+                ("cout_pad", _i32), ("block_n", _i32), ("gate", _i32), ("f32", _i32), ("fold", _i32), ("n_out", _i32),
+                ("out_scale", _f32)]
+
+
+class GeneratorW(C.Structure):
+    _fields_ = [("n_stages", _i32), ("n_kernels", _i32), ("n_pairs", _i32), ("dtype", _i32),
+                ("up_rate", _i32 * MAX_STAGES), ("channels", _i32 * MAX_STAGES), ("pre_channels", _i32),
+                ("chunk_frames", _i32), ("wide_chunk_frames", _i32), ("wide_stages", _i32), ("lrelu_slope", _f32),
+                ("pre", ConvW), ("ups", ConvW * MAX_STAGES),
+                ("rb", ((ConvW * 2) * MAX_PAIRS) * MAX_KERNELS * MAX_STAGES),
+                ("post_w", _vp), ("post_taps", _i32)]
+
+
+class WnW(C.Structure):
+    _fields_ = [("n_layers", _i32), ("hidden", _i32), ("dtype", _i32),
+                ("in_", ConvW * MAX_WN_LAYERS), ("rs", ConvW * MAX_WN_LAYERS), ("skip_cat", ConvW)]
+
+
+class EncoderLayerW(C.Structure):
+    _fields_ = [("hidden", _i32), ("filter", _i32), ("heads", _i32), ("window", _i32), ("mode", _i32), ("dtype", _i32),
+                ("qkv", ConvW), ("o", ConvW), ("ffn1", ConvW), ("ffn2", ConvW),
+                ("rel_k", _vp), ("rel_v", _vp), ("ln1_g", _vp), ("ln1_b", _vp), ("ln2_g", _vp), ("ln2_b", _vp)]
+
+
 # name -> argtypes (all return int); mirrors include/b200svs.h one to one
 PROTOTYPES = {
     "b200svs_abi_version": [],
     "b200svs_check_device": [],
+    "b200svs_abi_struct_size": [_i32],
     "b200svs_saturation_events": [C.POINTER(C.c_uint32), _i32, _vp],
     "b200svs_conv1d_tc": [C.POINTER(ConvArgs), _vp],
     "b200svs_conv1d_tc_set_trace": [_vp, _i32],
     "b200svs_song_assemble": [_vp, C.c_int64, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp],
     "b200svs_song_assemble_noalloc": [_vp, C.c_int64, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp],
+    "b200svs_generator_fwd": [C.POINTER(GeneratorW), _vp, _i32, _i32, _i32, _vp, _i32, _vp, _vp, C.c_size_t, _vp],
+    "b200svs_wn_stack_fwd": [C.POINTER(WnW), _vp, _vp, _vp, _i32, _i32, _vp, _i32, _vp, _vp, C.c_size_t, _vp],
+    "b200svs_encoder_fwd": [C.POINTER(EncoderLayerW), _i32, _vp, _vp, _vp, _i32, _i32, _vp, C.c_size_t, _vp],
     "b200svs_conv1d_f32": [C.POINTER(ConvArgs), _vp],
     "b200svs_attention_f32": [_vp, _i32, _vp, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
     "b200svs_attn_prep": [_vp, _i32, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
@@ -97,6 +132,13 @@ def lib():
         h = C.CDLL(LIB_PATH)
         h.b200svs_last_error.restype = C.c_char_p
         h.b200svs_last_error.argtypes = []
+        h.b200svs_launch_count.restype = C.c_int64
+        h.b200svs_launch_count.argtypes = []
+        for name, wt in (("b200svs_generator_workspace_bytes", GeneratorW), ("b200svs_wn_workspace_bytes", WnW),
+                         ("b200svs_encoder_workspace_bytes", EncoderLayerW)):
+            fn = getattr(h, name)
+            fn.restype = C.c_size_t
+            fn.argtypes = [C.POINTER(wt), _i32, _i32]
         for name, args in PROTOTYPES.items():
             fn = getattr(h, name)          # AttributeError if the .so does not export it
             fn.restype = C.c_int
@@ -111,8 +153,10 @@ def check(rc, what=""):
         raise RuntimeError(f"b200svs {what} failed (code {rc}): {msg}")
 
 
-# number of C-ABI compute calls issued by this process; each one launches exactly one kernel
-LAUNCHES = 0
+def launches():
+    """Kernels launched through the library by this process (b200svs_launch_count)."""
+    return int(lib().b200svs_launch_count())
+
 
 
 # bench.py's instrumented pass: when PROFILE is a list every call appends
@@ -122,8 +166,7 @@ NEXT_META = None
 
 
 def call(name, *args):
-    global LAUNCHES, NEXT_META
-    LAUNCHES += 1
+    global NEXT_META
     if PROFILE is None:
         check(getattr(lib(), name)(*args), name)
         return

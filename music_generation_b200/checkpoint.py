@@ -26,7 +26,7 @@ from .synthesizer import _Enc
 
 logger = logging.getLogger(__name__)
 
-PACK_FORMAT = 4            # bump when packer.py / SynthesizerTrn._pack change what they produce
+PACK_FORMAT = 5            # bump when packer.py / SynthesizerTrn._pack change what they produce
 CACHE_SUFFIX = ".b200pack"
 
 
@@ -78,7 +78,7 @@ def fingerprint(model):
     gf = model.generator_fold
     knobs = (PACK_FORMAT, model.variant, str(model.operand_dtype), model.f0_precision, model.text_precision,
              model.gin_channels, model.resblock, tuple(model.upsample_rates), model.hidden_channels,
-             tuple(sorted(gf.items())) if isinstance(gf, dict) else gf, tuple(model.resblock_kernel_sizes),
+             repr(sorted(gf.items())) if isinstance(gf, dict) else gf, tuple(model.resblock_kernel_sizes),
              tuple(tuple(d) for d in model.resblock_dilation_sizes), tuple(model.upsample_kernel_sizes),
              model.upsample_initial_channel, model.n_layers, model.n_heads, model.filter_channels, model.kernel_size,
              getattr(model, "generator_pair", None))
@@ -98,8 +98,8 @@ def _encode(obj):
         return {"__pc__": {s: _encode(getattr(obj, s)) for s in ops.PackedConv.__slots__}}
     if isinstance(obj, _Enc):
         return {"__enc__": {s: _encode(getattr(obj, s)) for s in _Enc.__slots__}}
-    if isinstance(obj, dict):
-        return {"__dict__": {str(k): _encode(v) for k, v in obj.items()}}
+    if isinstance(obj, dict):      # "c" / "c_gen" / "c_enc": ctypes weight tables of the stage-level API, rebuilt on attach
+        return {"__dict__": {str(k): _encode(v) for k, v in obj.items() if k not in ("c", "c_gen", "c_enc")}}
     if isinstance(obj, tuple):
         return {"__tuple__": [_encode(v) for v in obj]}
     if isinstance(obj, list):
@@ -155,6 +155,7 @@ def load_packed(model, path):
     if blob.get("format") != PACK_FORMAT or blob.get("fingerprint") != fingerprint(model):
         return False
     model._packed = _decode(blob["packed"], model.device)
+    model._build_stage_tables(model._packed)
     return True
 
 

@@ -20,7 +20,13 @@ int check_cuda(cudaError_t e, const char* what) {
   return set_error(B200SVS_ECUDA, "%s: %s", what, cudaGetErrorString(e));
 }
 
-int check_launch(const char* what) { return check_cuda(cudaGetLastError(), what); }
+static long long g_launches = 0;     // kernels launched by this process through the library (bench.py's gpu_launches)
+void count_launch() { __atomic_fetch_add(&g_launches, 1ll, __ATOMIC_RELAXED); }
+int check_launch(const char* what) {
+  const int r = check_cuda(cudaGetLastError(), what);
+  if (r == B200SVS_OK) count_launch();
+  return r;
+}
 
 EncodeTiledFn get_encode_tiled() {
   static EncodeTiledFn fn = nullptr;
@@ -112,6 +118,18 @@ extern "C" {
 
 const char* b200svs_last_error(void) { return b200svs::g_err; }
 int b200svs_abi_version(void) { return B200SVS_ABI_VERSION; }
+int64_t b200svs_launch_count(void) { return __atomic_load_n(&b200svs::g_launches, __ATOMIC_RELAXED); }
+int b200svs_abi_struct_size(int32_t which) {
+  switch (which) {
+    case 0: return (int)sizeof(b200svs_epilogue);
+    case 1: return (int)sizeof(b200svs_conv_args);
+    case 2: return (int)sizeof(b200svs_conv_w);
+    case 3: return (int)sizeof(b200svs_generator_w);
+    case 4: return (int)sizeof(b200svs_wn_w);
+    case 5: return (int)sizeof(b200svs_encoder_layer_w);
+    default: return -1;
+  }
+}
 
 int b200svs_saturation_events(uint32_t* host_out, int32_t reset, void* stream) {
   unsigned int* c = b200svs::sat_counter();

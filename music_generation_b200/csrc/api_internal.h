@@ -12,6 +12,8 @@ int set_error(int code, const char* fmt, ...);
 int check_cuda(cudaError_t e, const char* what);
 // Checks the launch that was just issued (cudaGetLastError; no sync).
 int check_launch(const char* what);
+// Adds one to the process-wide count of kernels launched through the library (check_launch does it for <<<>>> launches).
+void count_launch();
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,

@@ -1274,9 +1274,11 @@ extern "C" int b200svs_conv1d_tc(const b200svs_conv_args* a, void* stream) {
     ++n_attr;
   }
   cfg.attrs = attr; cfg.numAttrs = n_attr;
-  if (p.pair)
-    return check_cuda(cudaLaunchKernelEx(&cfg, conv1d_tc_kernel<true>, tmA, tmW, tmR, tmR2, tmO32, tmO16, tmR16, tmO16r, p),
-                      "conv1d_tc_kernel<pair> launch");
-  return check_cuda(cudaLaunchKernelEx(&cfg, conv1d_tc_kernel<false>, tmA, tmW, tmR, tmR2, tmO32, tmO16, tmR16, tmO16r, p),
-                    "conv1d_tc_kernel launch");
+  const int rl = p.pair
+      ? check_cuda(cudaLaunchKernelEx(&cfg, conv1d_tc_kernel<true>, tmA, tmW, tmR, tmR2, tmO32, tmO16, tmR16, tmO16r, p),
+                   "conv1d_tc_kernel<pair> launch")
+      : check_cuda(cudaLaunchKernelEx(&cfg, conv1d_tc_kernel<false>, tmA, tmW, tmR, tmR2, tmO32, tmO16, tmR16, tmO16r, p),
+                   "conv1d_tc_kernel launch");
+  if (rl == B200SVS_OK) count_launch();
+  return rl;
 }

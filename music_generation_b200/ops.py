@@ -262,3 +262,52 @@ def song_assemble(o, mel_len, offsets, song, *, order=None, hop=256, lead_in=441
     ws = torch.empty(n, device=o.device, dtype=torch.int32)
     _lib.call("b200svs_song_assemble", _ptr(o), o.stride(0), _ptr(mel_len), _ptr(order), _ptr(offsets), n, hop, lead_in,
               1 if legacy_scalar else 0, _ptr(ws), _ptr(song), _ptr(scales_out), _stream())
+
+
+# ---------------------------------------------------------------------------------------------- stage-level API
+def conv_w(pc):
+    """ctypes mirror (b200svs_conv_w) of a PackedConv; the PackedConv must stay alive as long as the table is used."""
+    c = _lib.ConvW()
+    c.w, c.bias = pc.w.data_ptr(), (0 if pc.bias is None else pc.bias.data_ptr())
+    c.ntaps, c.dil, c.pad_left, c.cin, c.cin_pad = pc.ntaps, pc.dil, pc.pad_left, pc.cin, pc.cin_pad
+    c.cout, c.cout_pad, c.block_n = pc.cout, pc.cout_pad, pc.block_n
+    c.gate, c.f32, c.fold, c.n_out, c.out_scale = int(pc.gate), int(pc.f32), pc.fold, pc.n_out, pc.out_scale
+    return c
+
+
+_WS = {}
+
+
+def workspace(nbytes, device):
+    """Caller-owned workspace of the stage-level entry points: one cached uint8 tensor per (device, stream), grown on
+    demand (stream-ordered reuse: consecutive stage calls on a stream may share it)."""
+    key = (device.index if device.index is not None else torch.cuda.current_device(), torch.cuda.current_stream(device).cuda_stream)
+    t = _WS.get(key)
+    if t is None or t.numel() < nbytes:
+        t = _WS[key] = torch.empty(max(int(nbytes), 1 << 20), device=device, dtype=torch.uint8)
+    return t
+
+
+def generator_fwd(table, x16, gbias, out):
+    B, T, _ = x16.shape
+    n = _lib.lib().b200svs_generator_workspace_bytes(C.byref(table), B, T)
+    if n == 0:
+        _lib.check(-1, "generator_workspace_bytes")
+    ws = workspace(n, x16.device)
+    _lib.call("b200svs_generator_fwd", C.byref(table), _ptr(x16), _btc(x16, "x16"), B, T, _ptr(gbias),
+              0 if gbias is None else gbias.stride(0), _ptr(out), _ptr(ws), ws.numel(), _stream())
+
+
+def wn_stack_fwd(table, x32, x16, lens, gcond, out16):
+    B, T, _ = x32.shape
+    n = _lib.lib().b200svs_wn_workspace_bytes(C.byref(table), B, T)
+    ws = workspace(n, x32.device)
+    _lib.call("b200svs_wn_stack_fwd", C.byref(table), _ptr(x32), _ptr(x16), _ptr(lens), B, T, _ptr(gcond),
+              0 if gcond is None else gcond.stride(0), _ptr(out16), _ptr(ws), ws.numel(), _stream())
+
+
+def encoder_fwd(tables, n_layers, x32, x16, lens):
+    B, T, _ = x32.shape
+    n = _lib.lib().b200svs_encoder_workspace_bytes(tables, B, T)
+    ws = workspace(n, x32.device)
+    _lib.call("b200svs_encoder_fwd", tables, n_layers, _ptr(x32), _ptr(x16), _ptr(lens), B, T, _ptr(ws), ws.numel(), _stream())

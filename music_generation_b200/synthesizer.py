@@ -26,6 +26,9 @@ def _require_cuda(t):
         raise RuntimeError("SynthesizerTrn.infer: inputs must be CUDA tensors - this build has no CPU path")
 
 
+_STAGE_API = True       # module switch: the CPU test-suite's emulated ops (tests/emu_ops.py) have no stage-level entry points
+
+
 def _device_guard(dev):
     """Makes `dev` the current CUDA device for the duration of a call: the kernels of libb200svs launch on the current
     device's stream (ops._stream) and must match the device of the tensors they are handed."""
@@ -50,7 +53,7 @@ class SynthesizerTrn(nn.Module):
                  max_position_embeddings=2000, generator_chunk_frames=32768, generator_wide_chunk_frames=196608,
                  generator_wide_stages=1, f0_precision="split",
                  text_precision="split", generator_residual="act16", generator_mrf="fp16", generator_fold=32, wn_skip="gemm", cuda_graphs=False,
-                 fuse_spec_proj=False,
+                 fuse_spec_proj=False, stage_api=True,
                  seed=1234, **kwargs):
         super().__init__()
         if hidden_channels != 192 or n_heads != 2:
@@ -88,12 +91,18 @@ class SynthesizerTrn(nn.Module):
         self.wn_skip = wn_skip
         # ResBlock convs with dilation 1 and <= generator_fold channels run on [B, T/2, 2C] views (0: never)
         # or {channels: largest kernel size to fold}, e.g. {32: 11, 64: 3}
-        self.generator_fold = ({int(c): int(k) for c, k in generator_fold.items()} if isinstance(generator_fold, dict)
+        # dict values: largest kernel size to fold, or an explicit list of kernel sizes (e.g. {32: 11, 64: [7, 11]})
+        self.generator_fold = ({int(c): (sorted(int(v) for v in k) if isinstance(k, (list, tuple)) else int(k))
+                                for c, k in generator_fold.items()} if isinstance(generator_fold, dict)
                                else int(generator_fold))
         # every call site of the reference discards spec_predict; with fuse_spec_proj=True the two
         # 513-wide 1x1 convs SpecDecoder.proj -> spec_proj collapse into one 192x192 conv (see _pack) and infer
         # returns None in spec_predict's place.  Off by default: the result tuple then matches the reference's.
         self.fuse_spec_proj = bool(fuse_spec_proj)
+        # stage-level C entry points (b200svs_generator_fwd / _wn_stack_fwd / _encoder_fwd): one library call per stage
+        # instead of one per kernel; False keeps the per-op Python loops (bit-identical; also used by bench.py's
+        # per-launch instrumentation and by the non-default precision knobs)
+        self.stage_api = bool(stage_api)
         # launch-bound (small) calls: replay the frame-level part of infer from a CUDA graph keyed by its shapes
         self.cuda_graphs = bool(cuda_graphs)
         self.cuda_graph_max_frames = 32768
@@ -276,7 +285,8 @@ class SynthesizerTrn(nn.Module):
                 def rconv(name, dl, ch_i=ch_i, k=k):
                     # dilation-1 convs of the narrow stages run time-pair folded (packer.fold_time_pairs)
                     gf = self.generator_fold
-                    on = gf.get(ch_i, 0) >= k if isinstance(gf, dict) else ch_i <= gf
+                    sel = gf.get(ch_i, 0) if isinstance(gf, dict) else None
+                    on = ((k in sel) if isinstance(sel, list) else sel >= k) if isinstance(gf, dict) else ch_i <= gf
                     if dl == 1 and on and math.prod(self.upsample_rates[:i + 1]) % 2 == 0:
                         return packer.pack_conv_folded(W(name), Bv(name), dtype=dt).to(dev)
                     return conv(name, dil=dl)
@@ -313,8 +323,64 @@ class SynthesizerTrn(nn.Module):
             tag(pc, f"gen_up{i}")
         for i, st in enumerate(P["g_rb"]):
             tag(st, f"gen_rb{i}")
+        self._build_stage_tables(P)
         self._packed = P
         return P
+
+    def _use_stage_api(self):
+        # bench.py's per-launch instrumentation (_lib.PROFILE) needs one library call per kernel
+        return self.stage_api and _STAGE_API and _lib.PROFILE is None
+
+    def _build_stage_tables(self, P):
+        """b200svs_generator_w / _wn_w / _encoder_layer_w tables over the packed weights (include/b200svs.h)."""
+        dtc = ops.dt_code(self.operand_dtype)
+        H = self.hidden_channels
+
+        def wn_table(st):
+            t = _lib.WnW()
+            t.n_layers, t.hidden, t.dtype = st["n"], H, dtc
+            for i in range(st["n"]):
+                t.in_[i], t.rs[i] = ops.conv_w(st["in"][i]), ops.conv_w(st["rs"][i])
+            t.skip_cat = ops.conv_w(st["skip_cat"])
+            st["c"] = t if st["n"] <= _lib.MAX_WN_LAYERS else None
+        for fl in P["flow"]:
+            wn_table(fl["wn"])
+        if "sd_wn" in P:
+            wn_table(P["sd_wn"])
+        if "pe_wn" in P:
+            wn_table(P["pe_wn"])
+
+        def enc_table(layers, mode):
+            arr = (_lib.EncoderLayerW * len(layers))()
+            for t, e in zip(arr, layers):
+                t.hidden, t.filter, t.heads, t.window = H, self.filter_channels, self.n_heads, 4
+                t.mode, t.dtype = {"f32": 0, "tc": 1, "split": 2}[mode], dtc
+                t.qkv, t.o, t.ffn1, t.ffn2 = (ops.conv_w(getattr(e, a)) for a in ("qkv", "o", "ffn1", "ffn2"))
+                t.rel_k, t.rel_v = e.rel_k.data_ptr(), e.rel_v.data_ptr()
+                t.ln1_g, t.ln1_b, t.ln2_g, t.ln2_b = (x.data_ptr() for x in (*e.ln1, *e.ln2))
+            return arr
+        P["c_enc"] = {id(P[k]): enc_table(P[k], m) for k, m in (("text_enc", P["text_mode"]), ("f0_enc", P["f0_mode"]),
+                                                                  ("mel_enc", "tc"))}
+        # Generator: the default 16-bit streams only (act16 residual + fp16 MRF need fp16 operands), ResBlock1
+        P["c_gen"] = None
+        n_st, nk = len(self.upsample_rates), len(self.resblock_kernel_sizes)
+        npairs = len(self.resblock_dilation_sizes[0]) if self.resblock_dilation_sizes else 0
+        if (self.resblock == "1" and self.operand_dtype == torch.float16 and self.generator_residual == "act16"
+                and self.generator_mrf == "fp16" and n_st <= _lib.MAX_STAGES and nk <= _lib.MAX_KERNELS
+                and npairs <= _lib.MAX_PAIRS and all(len(d) == npairs for d in self.resblock_dilation_sizes)):
+            g = _lib.GeneratorW()
+            g.n_stages, g.n_kernels, g.n_pairs, g.dtype = n_st, nk, npairs, dtc
+            g.pre_channels, g.lrelu_slope = self.upsample_initial_channel, LRELU_SLOPE
+            g.pre = ops.conv_w(P["g_pre"])
+            for i in range(n_st):
+                g.up_rate[i] = self.upsample_rates[i]
+                g.channels[i] = self.upsample_initial_channel // (2 ** (i + 1))
+                g.ups[i] = ops.conv_w(P["g_ups"][i])
+                for j in range(nk):
+                    for m in range(npairs):
+                        g.rb[i][j][m][0], g.rb[i][j][m][1] = (ops.conv_w(c) for c in P["g_rb"][i][j][m])
+            g.post_w, g.post_taps = P["g_post"].data_ptr(), P["g_post"].shape[0]
+            P["c_gen"] = g
 
     # ------------------------------------------------------------------ building blocks
     def _encoder(self, layers, x32, x16, lens, mode):
@@ -328,6 +394,10 @@ class SynthesizerTrn(nn.Module):
         dev = x32.device
         dt = self.operand_dtype
         f32, split = mode == "f32", mode == "split"
+        tab = self._packed["c_enc"].get(id(layers)) if self._packed else None
+        if self._use_stage_api() and tab is not None:
+            ops.encoder_fwd(tab, len(layers), x32, x16, lens)
+            return
         qkv = torch.empty(B, T, 3 * Cc, device=dev, dtype=torch.float32)
         tmp = torch.empty(B, T, Cc, device=dev, dtype=torch.float32)
         F_ = self.filter_channels
@@ -364,6 +434,9 @@ class SynthesizerTrn(nn.Module):
         B, T, H = x32.shape
         dev = x32.device
         n = st["n"]
+        if self._use_stage_api() and self.wn_skip == "gemm" and st.get("c") is not None:
+            ops.wn_stack_fwd(st["c"], x32, x16, lens, gcond, out16)
+            return
         if self.wn_skip == "gemm":
             # every layer's gate output is kept ([B, T, n*H], layer i in columns i*H..) and the skip sum is one 1x1
             # conv over all of it: no fp32 skip accumulator read and written per layer, one launch less per layer
@@ -411,6 +484,12 @@ class SynthesizerTrn(nn.Module):
                 out[:, :, t0 * self.hop:t1 * self.hop] = part[:, :, (t0 - s0) * self.hop:(t1 - s0) * self.hop]
             return out
         out = torch.empty(B, 1, T * self.hop, device=x16.device, dtype=torch.float32)
+        if self._use_stage_api() and P.get("c_gen") is not None:
+            g = P["c_gen"]
+            g.chunk_frames, g.wide_chunk_frames = int(self.generator_chunk_frames), int(self.generator_wide_chunk_frames)
+            g.wide_stages = int(self.generator_wide_stages)
+            ops.generator_fwd(g, x16, gbias, out)
+            return out
         n_st = len(self.upsample_rates)
         n_wide = min(max(int(self.generator_wide_stages), 0), n_st)
         wide = max(self.generator_wide_chunk_frames, self.generator_chunk_frames) if n_wide else self.generator_chunk_frames
@@ -534,6 +613,7 @@ class SynthesizerTrn(nn.Module):
         P["pe_wn"] = self._pack_wn_stack(sd, "spec_encoder.enc", dev, dt)
         for pc in [P["pe_pre"], P["pe_proj"], *P["pe_wn"]["in"], *P["pe_wn"]["rs"], P["pe_wn"]["skip_cat"]]:
             pc.tag = "posterior"
+        self._build_stage_tables(P)
         return P
 
     @torch.no_grad()

@@ -241,5 +241,6 @@ def install(monkeypatch):
                  "add_pos_mask", "f0_embed", "sample_prior", "conv_post_tanh", "bct_to_btc"):
         monkeypatch.setattr(real_ops, name, globals()[name])
     monkeypatch.setattr(syn, "_require_cuda", lambda t: None)
+    monkeypatch.setattr(syn, "_STAGE_API", False)          # the emulation covers the per-op entry points
     import contextlib
     monkeypatch.setattr(syn, "_device_guard", lambda dev: contextlib.nullcontext())

@@ -50,7 +50,7 @@ def timed(fn, steps, warm=3):
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
-    l0 = _lib.LAUNCHES
+    l0 = _lib.launches()
     e0.record()
     for _ in range(steps):
         fn()
@@ -63,7 +63,7 @@ def timed(fn, steps, warm=3):
         t = torch.tensor([ms], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t)
-    return ms, (_lib.LAUNCHES - l0) // steps
+    return ms, (_lib.launches() - l0) // steps
 
 
 def emit(**kw):
