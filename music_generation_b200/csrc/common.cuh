@@ -82,8 +82,13 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
-// Blocks until the phase with `parity` completes.  A wait that lasts longer than 4 s of wall clock is a protocol
-// bug: trap instead of hanging the GPU.
+// Blocks until the phase with `parity` completes.  A wait that lasts longer than B200SVS_MBAR_TIMEOUT_NS of wall clock
+// (default 30 s: far beyond any legitimate wait, including a context time-sliced out by another process or slowed by a
+// profiler's replay; -DB200SVS_MBAR_TIMEOUT_NS=0 compiles the watchdog out) is a protocol bug: trap instead of hanging
+// the GPU box.
+#ifndef B200SVS_MBAR_TIMEOUT_NS
+#define B200SVS_MBAR_TIMEOUT_NS 30000000000ull
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   uint32_t spins = 0;
@@ -92,7 +97,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if ((++spins & 0xff) == 0) {
       const unsigned long long now = global_timer_ns();
       if (t0 == 0) t0 = now;
-      else if (now - t0 > 4000000000ull) {
+      else if (B200SVS_MBAR_TIMEOUT_NS != 0 && now - t0 > B200SVS_MBAR_TIMEOUT_NS) {
         printf("b200svs: mbarrier timeout block %d thread %d\n", blockIdx.x, threadIdx.x);
         __trap();
       }

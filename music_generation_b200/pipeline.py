@@ -46,8 +46,13 @@ class Synthesiser:
         `noise`, `ph_dur`, `g` are forwarded to `infer` (parity runs)."""
         dev = self.net_g.device
         x, lens, notes, durs, tones = (t.to(dev) for t in self.collate(lines))
-        res = self.net_g.infer(x, lens, notes, durs, phone_shengdiao=tones, noise_scale=1., length_scale=1,
-                               noise=noise, ph_dur=ph_dur, g=g)
+        # only the valid samples of every line reach the song: let the Generator skip the padded frames of short lines
+        bucket, self.net_g.generator_bucket = self.net_g.generator_bucket, True
+        try:
+            res = self.net_g.infer(x, lens, notes, durs, phone_shengdiao=tones, noise_scale=1., length_scale=1,
+                                   noise=noise, ph_dur=ph_dur, g=g)
+        finally:
+            self.net_g.generator_bucket = bucket
         o = res[0]
         mel_len = res[1].sum(dim=(1, 2)).to(torch.int64)                   # y_mask [B,1,T] -> frames per line
         samples = mel_len * self.net_g.hop

@@ -53,7 +53,7 @@ class SynthesizerTrn(nn.Module):
                  max_position_embeddings=2000, generator_chunk_frames=32768, generator_wide_chunk_frames=196608,
                  generator_wide_stages=1, f0_precision="split",
                  text_precision="split", generator_residual="act16", generator_mrf="fp16", generator_fold=32, wn_skip="gemm", cuda_graphs=False,
-                 fuse_spec_proj=False, stage_api=True,
+                 fuse_spec_proj=False, stage_api=True, generator_bucket=False,
                  seed=1234, **kwargs):
         super().__init__()
         if hidden_channels != 192 or n_heads != 2:
@@ -103,6 +103,11 @@ class SynthesizerTrn(nn.Module):
         # instead of one per kernel; False keeps the per-op Python loops (bit-identical; also used by bench.py's
         # per-launch instrumentation and by the non-default precision knobs)
         self.stage_api = bool(stage_api)
+        # ragged batches: run the Generator on length-sorted utterance groups, each over its own longest length + halo
+        # instead of the batch's padded length.  Valid samples are bit-identical; samples of the PADDED region (which the
+        # reference fills with bias-driven values and every consumer masks) are written as 0.  Off by default so that
+        # `infer` matches the reference over the whole padded tensor; pipeline.Synthesiser turns it on.
+        self.generator_bucket = bool(generator_bucket)
         # launch-bound (small) calls: replay the frame-level part of infer from a CUDA graph keyed by its shapes
         self.cuda_graphs = bool(cuda_graphs)
         self.cuda_graph_max_frames = 32768
@@ -461,7 +466,29 @@ class SynthesizerTrn(nn.Module):
             else:
                 ops.conv1d(rs, acts, res1=skip if i > 0 else None, lens=lens, out16=out16)
 
-    def _generator(self, x16, gbias=None):
+    def _generator_bucketed(self, x16, gbias, frame_lens):
+        """Length-sorted utterance groups, each synthesised over min(T, its longest utterance + halo) frames."""
+        B, T, _ = x16.shape
+        hl = self.GENERATOR_HALO_FRAMES
+        order = sorted(range(B), key=lambda b: -int(frame_lens[b]))
+        groups, i = [], 0
+        while i < B:
+            tc = min(T, int(frame_lens[order[i]]) + hl)
+            tc += tc & 1                                    # even: time-pair folded convs
+            tc = min(tc, T)
+            n = max(1, self.generator_chunk_frames // max(tc, 1))
+            groups.append((order[i:i + n], tc))
+            i += n
+        if sum(len(g) * tc for g, tc in groups) > 0.93 * B * T:
+            return None                                     # not ragged enough to pay for the gathers
+        out = torch.zeros(B, 1, T * self.hop, device=x16.device, dtype=torch.float32)
+        for idx, tc in groups:
+            ix = torch.tensor(idx, device=x16.device)
+            part = self._generator(x16.index_select(0, ix)[:, :tc].contiguous(), None if gbias is None else gbias.index_select(0, ix))
+            out[ix, :, :tc * self.hop] = part
+        return out
+
+    def _generator(self, x16, gbias=None, frame_lens=None):
         """Generator.forward (VISinger/models_ae.py:327-346).  x16: [B,T,C] masked input; returns [B,1,T*hop].
 
         Utterance chunks bound the activation working set (stage tensors are hop*C*T elements).  Two chunk sizes:
@@ -471,6 +498,10 @@ class SynthesizerTrn(nn.Module):
         lose 10 % beyond ~32 k frames per chunk)."""
         P = self._packed
         B, T, _ = x16.shape
+        if frame_lens is not None and self.generator_bucket and B > 1:
+            out = self._generator_bucketed(x16, gbias, frame_lens)
+            if out is not None:
+                return out
         tc = self.generator_time_chunk_frames
         if tc and T > tc + 2 * self.GENERATOR_HALO_FRAMES:
             # one very long utterance: cut in time with exact halos (the Generator's receptive field is < 16 frames per
@@ -796,7 +827,10 @@ class SynthesizerTrn(nn.Module):
             gen_in = gen_in[:, :Tg].contiguous()
 
         # 8. Generator
-        o = self._generator(gen_in, gen_g)
+        lens_host = mlen.tolist() if (self.generator_bucket and B > 1 and not torch.cuda.is_current_stream_capturing()) else None
+        if lens_host is not None and Tg != T:
+            lens_host = [min(n, Tg) for n in lens_host]
+        o = self._generator(gen_in, gen_g, lens_host)
 
         spec = spec32[:, :, :sc] if self.variant == "ae" and spec32 is not None else None
         return o, z32, zp32, spec

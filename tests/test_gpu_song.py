@@ -57,3 +57,31 @@ def test_synthesiser_song_matches_oracle_pipeline():
     ref = vo.infer(sd, noise=noise, ph_dur=ph_dur, **inp)[0]
     want = so.assemble_song([ref[b, 0, :int(mel_len[b]) * 256].numpy() for b in range(B)])
     assert snr_db(torch.from_numpy(want.astype(np.float32)), song.cpu().float()) >= SNR_DB_TOL
+
+
+def test_generator_bucketing_keeps_valid_samples_bit_identical():
+    """generator_bucket=True (what syn_song uses): a ragged batch's Generator runs on length-sorted groups over their own
+    longest length + halo; every VALID sample equals the unbucketed result bit for bit, the padded region is zero."""
+    B, P, T = 6, 60, 700
+    inp = synthetic.make_inputs(B, P, seed=51, ragged=True)
+    ph_dur = synthetic.make_ph_dur(inp["x_lengths"], P, T, seed=51)
+    ph_dur[2, 5:] = 0; ph_dur[4, 20:] = 0                                   # two much shorter utterances
+    mel_len = ph_dur.sum(1)
+    noise = synthetic.make_noise(B, 192, int(mel_len.max()), seed=51).to(DEV)
+    net, _ = build_model("ae", device=DEV)
+    net.generator_chunk_frames = 1500                                        # groups of two utterances
+    i = {k: v.to(DEV) for k, v in inp.items()}
+    call = lambda: net.infer(i["x"], i["x_lengths"], i["note_pitch_id"], i["note_duration"], phone_shengdiao=i["phone_shengdiao"],
+                             ph_dur=ph_dur.to(DEV), noise=noise)[0]
+    plain = call()
+    net.generator_bucket = True
+    bucketed = call()
+    torch.cuda.synchronize()
+    assert not torch.equal(plain, bucketed)                                  # the padded region differs (zeros) ...
+    for b in range(B):
+        n = int(mel_len[b]) * 256
+        assert torch.equal(plain[b, :, :n], bucketed[b, :, :n])              # ... the valid samples do not
+    # the shortest utterances sit in the last group: beyond that group's own length + halo nothing was computed
+    short = int(mel_len.argmin())
+    assert float(bucketed[short, :, (int(mel_len.sort().values[1]) + 40) * 256:].abs().max()) == 0.0
+    assert float(plain[short, :, (int(mel_len.sort().values[1]) + 40) * 256:].abs().max()) > 0.0

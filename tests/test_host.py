@@ -266,3 +266,19 @@ def test_infer_long_orchestration_vs_oracle_and_single_segment_identity(monkeypa
     assert max_abs(res[0], full[0]) > 1e-4
     with pytest.raises(ValueError):
         net.infer_long(*args, phone_shengdiao=inp["phone_shengdiao"], ph_dur=ph_dur, noise=noise, segment_frames=1990, overlap=10)
+
+
+@pytest.mark.parametrize("variant,gin", [("ae", 0), ("ae", 256), ("v4", 0)])
+def test_state_dict_keys_match_reference(variant, gin):
+    """The package's parameter tree has exactly the reference's state-dict keys and shapes (what `utils.load_checkpoint`,
+    VISinger/utils/utils.py:40-55, iterates), for the shipped configs and with speaker conditioning."""
+    from oracle import ref_harness
+    if not ref_harness.available():
+        pytest.skip("reference tree / oracle/_ref stage not present")
+    ref = ref_harness.build_reference(variant, gin_channels=gin).state_dict()
+    net, _ = build_model(variant, gin=gin)
+    mine = net.state_dict()
+    assert set(mine) == set(ref)
+    for k, v in ref.items():
+        assert tuple(mine[k].shape) == tuple(v.shape), k
+        assert mine[k].dtype == v.dtype, k
