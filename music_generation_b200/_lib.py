@@ -8,7 +8,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libb200svs.so")
+LIB_PATH = os.environ.get("B200SVS_LIB") or os.path.join(_HERE, "lib", "libb200svs.so")      # override: A/B builds
 CSRC_DIR = os.path.join(_HERE, "csrc")
 
 ACT_NONE, ACT_RELU, ACT_GELU, ACT_SIGMOID, ACT_TANH, ACT_GATE = range(6)

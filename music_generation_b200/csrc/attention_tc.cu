@@ -294,14 +294,19 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
     for (int c = 0; c < kOC; ++c) o[c] = 0.f;
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
     auto fold = [&](float alpha) {       // O = O * alpha + PV  (this thread's 48 of the 96 PV columns)
+      uint32_t r0[16], r1[16], r2[16];   // all three loads in flight before the first use
+      tmem_ld16_nowait(tmem_o + lane_off + half * kOC, r0);
+      tmem_ld16_nowait(tmem_o + lane_off + half * kOC + 16, r1);
+      tmem_ld16_nowait(tmem_o + lane_off + half * kOC + 32, r2);
+      tmem_ld_wait16(r0);
 #pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        uint32_t r[16];
-        tmem_ld16_nowait(tmem_o + lane_off + half * kOC + c * 16, r);
-        tmem_ld_wait16(r);
+      for (int e = 0; e < 16; ++e) o[e] = fmaf(o[e], alpha, __uint_as_float(r0[e]));
+      tmem_ld_wait16(r1);
 #pragma unroll
-        for (int e = 0; e < 16; ++e) o[c * 16 + e] = fmaf(o[c * 16 + e], alpha, __uint_as_float(r[e]));
-      }
+      for (int e = 0; e < 16; ++e) o[16 + e] = fmaf(o[16 + e], alpha, __uint_as_float(r1[e]));
+      tmem_ld_wait16(r2);
+#pragma unroll
+      for (int e = 0; e < 16; ++e) o[32 + e] = fmaf(o[32 + e], alpha, __uint_as_float(r2[e]));
     };
 
     for (int j = 0; j < n_kt; ++j) {
@@ -324,32 +329,26 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
         if (key >= p.T) x = -INFINITY;                 // beyond the tensor: not a key at all
         return x;
       };
-      // ---- pass 1: row maximum over this thread's 32 keys, then over the pair
+      // ---- S_j: this thread's 32 scores are read from TMEM ONCE and stay in registers for both passes; the S buffer
+      // is handed back to the MMA warp right away (S_{j+2} can be issued while this tile's exponentials run)
+      uint32_t sv[32];
+      tmem_ld32_nowait(ta, sv);
+      tmem_ld_wait32(sv);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars->s_free[sb]);
+      // ---- pass 1: row maximum over this thread's 32 keys, then over the pair.  Slow tiles keep the adjusted score.
       float mx = -INFINITY;
-      {
-        uint32_t ra[8], rb[8];
-        tmem_ld8_nowait(ta, ra);
-#pragma unroll 1
-        for (int g = 0; g < 4; g += 2) {
-          tmem_ld_wait8(ra);
-          tmem_ld8_nowait(ta + (g + 1) * 8, rb);
-          if (slow) {
+      if (slow) {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) mx = fmaxf(mx, adjust(ra[e], g * 8 + e));
-          } else {
-#pragma unroll
-            for (int e = 0; e < 8; ++e) mx = fmaxf(mx, __uint_as_float(ra[e]));
-          }
-          tmem_ld_wait8(rb);
-          if (g + 2 < 4) tmem_ld8_nowait(ta + (g + 2) * 8, ra);
-          if (slow) {
-#pragma unroll
-            for (int e = 0; e < 8; ++e) mx = fmaxf(mx, adjust(rb[e], (g + 1) * 8 + e));
-          } else {
-#pragma unroll
-            for (int e = 0; e < 8; ++e) mx = fmaxf(mx, __uint_as_float(rb[e]));
-          }
+        for (int e = 0; e < 32; ++e) {
+          const float x = adjust(sv[e], e);
+          sv[e] = __float_as_uint(x);
+          mx = fmaxf(mx, x);
         }
+      } else {
+#pragma unroll
+        for (int e = 0; e < 32; ++e) mx = fmaxf(mx, __uint_as_float(sv[e]));
       }
       if (!slow) mx *= scale2;                         // scale2 > 0 commutes with max
       pmax[(sb * 2 + half) * kTQ + row] = mx;
@@ -374,7 +373,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
           float x;
           if constexpr (kSlow) {
             const int ee = g * 8 + e;
-            x = adjust(r[e], ee);
+            x = __uint_as_float(r[e]);                    // adjusted in pass 1
             const int d = kb + ee - t + kWin;
             if (near_diag && d >= 0 && d < kNR && kb + ee < p.T) band[row * kNR + d] = x;
             x -= m_new;
@@ -394,29 +393,20 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
               make_uint4(pk16(pv[0], pv[1], dt), pk16(pv[2], pv[3], dt), pk16(pv[4], pv[5], dt), pk16(pv[6], pv[7], dt));
         }
       };
-      {
-        uint32_t ra[8], rb[8];
-        tmem_ld8_nowait(ta, ra);
-#pragma unroll 1
-        for (int g = 0; g < 4; g += 2) {
-          tmem_ld_wait8(ra);
-          tmem_ld8_nowait(ta + (g + 1) * 8, rb);
-          if (slow) emit(ra, g, std::true_type{}); else emit(ra, g, std::false_type{});
-          tmem_ld_wait8(rb);
-          if (g + 2 < 4) tmem_ld8_nowait(ta + (g + 2) * 8, ra);
-          if (slow) emit(rb, g + 1, std::true_type{}); else emit(rb, g + 1, std::false_type{});
-        }
+      if (slow) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) emit(sv + 8 * g, g, std::true_type{});
+      } else {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) emit(sv + 8 * g, g, std::false_type{});
       }
       l_run = l_run * alpha + sum;
       m_run = m_new;
       alpha_prev = alpha;
       fence_proxy_async();               // P (generic-proxy stores) -> visible to the tensor core
-      tc_fence_before();                 // S_j and PV_{j-1} reads are complete
+      tc_fence_before();                 // PV_{j-1} reads are complete
       __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(&bars->s_free[sb]);
-        mbar_arrive(&bars->p_full);
-      }
+      if (lane == 0) mbar_arrive(&bars->p_full);
     }
     mbar_wait(&bars->o_full, (n_kt - 1) & 1);
     tc_fence_after();
