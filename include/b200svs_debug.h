@@ -16,6 +16,10 @@ extern "C" {
 int b200svs_probe_rowshift(const void* a_f16, const void* b_f16, float* out, int32_t rows_a, int32_t shift,
                            int32_t base_offset_mode, void* stream);
 
+/* Diagnostic: per-tile clock64 stamps of b200svs_resblock_pair's pipeline roles into dev_buf[grid][tiles_per_cta][16]
+ * (int64); NULL switches it off.  Slot meanings: tools/trace_pair.py. */
+int b200svs_resblock_pair_set_trace(void* dev_buf, int32_t tiles_per_cta);
+
 #ifdef __cplusplus
 }
 #endif

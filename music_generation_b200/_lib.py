@@ -59,7 +59,7 @@ class ConvW(C.Structure):
 class GeneratorW(C.Structure):
     _fields_ = [("n_stages", _i32), ("n_kernels", _i32), ("n_pairs", _i32), ("dtype", _i32),
                 ("up_rate", _i32 * MAX_STAGES), ("channels", _i32 * MAX_STAGES), ("pre_channels", _i32),
-                ("chunk_frames", _i32), ("wide_chunk_frames", _i32), ("wide_stages", _i32), ("lrelu_slope", _f32),
+                ("chunk_frames", _i32), ("wide_chunk_frames", _i32), ("wide_stages", _i32), ("fuse_pairs", _i32), ("lrelu_slope", _f32),
                 ("pre", ConvW), ("ups", ConvW * MAX_STAGES),
                 ("rb", ((ConvW * 2) * MAX_PAIRS) * MAX_KERNELS * MAX_STAGES),
                 ("post_w", _vp), ("post_taps", _i32)]
@@ -89,6 +89,7 @@ PROTOTYPES = {
     "b200svs_generator_fwd": [C.POINTER(GeneratorW), _vp, _i32, _i32, _i32, _vp, _i32, _vp, _vp, C.c_size_t, _vp],
     "b200svs_wn_stack_fwd": [C.POINTER(WnW), _vp, _vp, _vp, _i32, _i32, _vp, _i32, _vp, _vp, C.c_size_t, _vp],
     "b200svs_encoder_fwd": [C.POINTER(EncoderLayerW), _i32, _vp, _vp, _vp, _i32, _i32, _vp, C.c_size_t, _vp],
+    "b200svs_resblock_pair": [C.POINTER(ConvW), C.POINTER(ConvW), _vp, _i32, _i32, _vp, _vp, _i32, _f32, _f32, _f32, _vp],
     "b200svs_conv1d_f32": [C.POINTER(ConvArgs), _vp],
     "b200svs_attention_f32": [_vp, _i32, _vp, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
     "b200svs_attn_prep": [_vp, _i32, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp],
@@ -105,6 +106,7 @@ PROTOTYPES = {
     "b200svs_conv_post_tanh": [_vp, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _vp, _vp],
     "b200svs_bct_to_btc": [_vp, _i32, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _vp, _vp],
     "b200svs_btc_to_bct": [_vp, _i32, _i32, _i32, _i32, _vp, _vp],
+    "b200svs_resblock_pair_set_trace": [_vp, _i32],
     "b200svs_probe_rowshift": [_vp, _vp, _vp, _i32, _i32, _i32, _vp],
 }
 

@@ -9,6 +9,9 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#ifndef B200SVS_MBAR_TIMEOUT_NS
+#define B200SVS_MBAR_TIMEOUT_NS 30000000000ull
+#endif
 #ifndef B200SVS_SPIN_LIMIT
 // mbarrier waits trap instead of hanging the GPU box if a pipeline bug dead-locks.
 #define B200SVS_SPIN_LIMIT (1u << 28)
@@ -86,15 +89,38 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
 // (default 30 s: far beyond any legitimate wait, including a context time-sliced out by another process or slowed by a
 // profiler's replay; -DB200SVS_MBAR_TIMEOUT_NS=0 compiles the watchdog out) is a protocol bug: trap instead of hanging
 // the GPU box.
-#ifndef B200SVS_MBAR_TIMEOUT_NS
-#define B200SVS_MBAR_TIMEOUT_NS 30000000000ull
-#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   uint32_t spins = 0;
   unsigned long long t0 = 0;
   while (!mbar_try_wait(bar, parity)) {
     if ((++spins & 0xff) == 0) {
+      const unsigned long long now = global_timer_ns();
+      if (t0 == 0) t0 = now;
+      else if (B200SVS_MBAR_TIMEOUT_NS != 0 && now - t0 > B200SVS_MBAR_TIMEOUT_NS) {
+        printf("b200svs: mbarrier timeout block %d thread %d\n", blockIdx.x, threadIdx.x);
+        __trap();
+      }
+    }
+  }
+}
+
+// Polling wait without the suspend-time hint: for short, latency-critical hand-offs in shallow pipelines (a parked
+// thread wakes up noticeably later than a polling one sees the phase flip).  Same watchdog as mbar_wait.
+__device__ __forceinline__ void mbar_wait_poll(uint64_t* bar, uint32_t parity) {
+  uint32_t spins = 0;
+  unsigned long long t0 = 0;
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (ok) return;
+    if ((++spins & 0xfff) == 0) {
       const unsigned long long now = global_timer_ns();
       if (t0 == 0) t0 = now;
       else if (B200SVS_MBAR_TIMEOUT_NS != 0 && now - t0 > B200SVS_MBAR_TIMEOUT_NS) {

@@ -125,6 +125,20 @@ static int generator_stages(const b200svs_generator_w* w, const void* cur, int c
         const bool last = m == w->n_pairs - 1;
         const b200svs_conv_w& c1 = w->rb[i][j][m][0];
         const b200svs_conv_w& c2 = w->rb[i][j][m][1];
+        if (w->fuse_pairs && ch == 32 && c2.fold == 2 && T2 % 2 == 0) {
+          // one kernel per pair (resblock_pair.cu); the output must not alias the input: cl and t16 ping-pong
+          void* dst = (src == cl) ? t16 : cl;
+          int r;
+          if (!last) r = b200svs_resblock_pair(&c1, &c2, src, nb, T2, nullptr, dst, 1, slope, 1.0f, 1.0f / slope, stream);
+          else if (j < w->n_kernels - 1)
+            r = b200svs_resblock_pair(&c1, &c2, src, nb, T2, j > 0 ? mrf : nullptr, mrf, 0, 0.0f, 1.0f, 1.0f / slope, stream);
+          else
+            r = b200svs_resblock_pair(&c1, &c2, src, nb, T2, j > 0 ? mrf : nullptr, nxt, 1, next_slope, 1.0f / w->n_kernels,
+                                      1.0f / slope, stream);
+          if (r) return r;
+          src = dst;
+          continue;
+        }
         {   // xt = lrelu(conv1(lrelu(x)))
           b200svs_epilogue e; init_ep(&e);
           e.out16 = t16; e.out16_ld = ch; e.out16_dtype = dt; e.post_lrelu = 1; e.post_slope = slope;

@@ -311,3 +311,17 @@ def encoder_fwd(tables, n_layers, x32, x16, lens):
     n = _lib.lib().b200svs_encoder_workspace_bytes(tables, B, T)
     ws = workspace(n, x32.device)
     _lib.call("b200svs_encoder_fwd", tables, n_layers, _ptr(x32), _ptr(x16), _ptr(lens), B, T, _ptr(ws), ws.numel(), _stream())
+
+
+def resblock_pair(c1, c2, x, out, *, mrf=None, out_lrelu=True, post_slope=0.1, scale=1.0, res_unlrelu=10.0):
+    """Fused ResBlock1 pair of the 32-channel Generator stage (b200svs_resblock_pair): out = x + c2(lrelu(c1(lrelu(x))))
+    [+ mrf], x recovered from the activated 16-bit tensor.  x / out / mrf: dense [B, L, 32] fp16."""
+    B, L, ch = x.shape
+    if ch != 32 or not x.is_contiguous() or not out.is_contiguous() or x.dtype != torch.float16:
+        raise ValueError("resblock_pair: dense [B, L, 32] fp16 tensors expected")
+    if _lib.PROFILE is not None:
+        n = float(B) * L * ch
+        _lib.NEXT_META = (c2.tag, 2.0 * B * L * (c1.alg_macs_per_row / c1.fold + c2.alg_macs_per_row / c2.fold),
+                          2.0 * n * (2 + (mrf is not None)) + c1.w.numel() * 2 + c2.w.numel() * 2)
+    _lib.call("b200svs_resblock_pair", C.byref(conv_w(c1)), C.byref(conv_w(c2)), _ptr(x), B, L, _ptr(mrf), _ptr(out),
+              1 if out_lrelu else 0, float(post_slope), float(scale), float(res_unlrelu), _stream())

@@ -53,7 +53,7 @@ class SynthesizerTrn(nn.Module):
                  max_position_embeddings=2000, generator_chunk_frames=32768, generator_wide_chunk_frames=196608,
                  generator_wide_stages=1, f0_precision="split",
                  text_precision="split", generator_residual="act16", generator_mrf="fp16", generator_fold=32, wn_skip="gemm", cuda_graphs=False,
-                 fuse_spec_proj=False, stage_api=True, generator_bucket=False,
+                 fuse_spec_proj=False, stage_api=True, generator_bucket=False, generator_pair_fused=True,
                  seed=1234, **kwargs):
         super().__init__()
         if hidden_channels != 192 or n_heads != 2:
@@ -108,6 +108,9 @@ class SynthesizerTrn(nn.Module):
         # reference fills with bias-driven values and every consumer masks) are written as 0.  Off by default so that
         # `infer` matches the reference over the whole padded tensor; pipeline.Synthesiser turns it on.
         self.generator_bucket = bool(generator_bucket)
+        # 32-channel stage: one fused kernel per ResBlock pair (b200svs_resblock_pair, 4 instead of 10 B of HBM traffic per
+        # element, bit-identical to the two conv launches; -1 % on the whole step).
+        self.generator_pair_fused = bool(generator_pair_fused)
         # launch-bound (small) calls: replay the frame-level part of infer from a CUDA graph keyed by its shapes
         self.cuda_graphs = bool(cuda_graphs)
         self.cuda_graph_max_frames = 32768
@@ -519,6 +522,7 @@ class SynthesizerTrn(nn.Module):
             g = P["c_gen"]
             g.chunk_frames, g.wide_chunk_frames = int(self.generator_chunk_frames), int(self.generator_wide_chunk_frames)
             g.wide_stages = int(self.generator_wide_stages)
+            g.fuse_pairs = int(self.generator_pair_fused)
             ops.generator_fwd(g, x16, gbias, out)
             return out
         n_st = len(self.upsample_rates)
@@ -616,7 +620,18 @@ class SynthesizerTrn(nn.Module):
                         kw["res16"] = srcr
                     else:
                         kw["res1"] = src32
-                    if c2 is not None:      # ResBlock1 (modules.py:210-223)
+                    if c2 is not None and ract and mrf16 and self.generator_pair_fused and ch == 32 and c2.fold == 2:
+                        # one fused kernel per pair (resblock_pair.cu); output must not alias the input: cl16 / t16 ping-pong
+                        dst16 = t16 if src16 is cl16 else cl16
+                        if not last:
+                            ops.resblock_pair(c1, c2, src16, dst16, post_slope=LRELU_SLOPE)
+                        elif j < nk - 1:
+                            ops.resblock_pair(c1, c2, src16, mrf, mrf=mrf if j > 0 else None, out_lrelu=False)
+                        else:
+                            ops.resblock_pair(c1, c2, src16, nxt16, mrf=mrf if j > 0 else None, post_slope=next_slope,
+                                              scale=1.0 / nk)
+                        src32, srcr, src16 = c32, cr16, dst16
+                    elif c2 is not None:      # ResBlock1 (modules.py:210-223)
                         self._rconv(c1, src16, out16=t16, post_lrelu=LRELU_SLOPE)
                         self._rconv(c2, t16, **kw)
                         src32, srcr, src16 = c32, cr16, cl16

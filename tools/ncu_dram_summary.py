@@ -29,11 +29,11 @@ for name, v in sorted(per.items(), key=lambda x: -x[1]["gpu__time_duration.sum"]
 open(out_md, "w").write(f"# ncu launch summary - {workload}\n\nSource: `{src}` (ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,"
                         f"dram__bytes_write.sum --clock-control none; per-launch times are serialised and cold-cache, compare shares).\n\n"
                         + "\n".join(lines) + f"\n\nTotal kernel time {tot_t / 1e3:.2f} ms.\n")
-# both instantiations of the conv kernel (<0> single CTA, <1> CTA pairs)
+# both instantiations of the conv kernel (<0> single CTA, <1> CTA pairs) and the fused pair kernel (the same implicit-GEMM conv)
 c = defaultdict(float)
 n = 0
 for name in per:
-    if name.startswith("conv1d_tc_kernel"):
+    if name.startswith("conv1d_tc_kernel") or name.startswith("resblock_pair_kernel"):
         n += len(ids[name])
         for m_, v_ in per[name].items():
             c[m_] += v_
