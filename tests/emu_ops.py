@@ -227,6 +227,23 @@ def bct_to_btc(x_bct, out32=None, out16=None, lens=None):
     _store(out16, y)
 
 
+def resblock_pair(c1, c2, x, out, *, mrf=None, out_lrelu=True, post_slope=0.1, scale=1.0, res_unlrelu=10.0):
+    """b200svs_resblock_pair = the two conv launches it fuses (documented as bit-identical to them)."""
+    f = lambda pc, t: t.view(t.shape[0], t.shape[1] // pc.fold, t.shape[2] * pc.fold) if pc.fold > 1 else t
+    t16 = torch.empty_like(x)
+    conv1d(c1, f(c1, x), out16=f(c1, t16), post_lrelu=0.1)
+    kw = dict(res16=f(c2, x), res16_unlrelu=res_unlrelu, scale=scale)
+    if mrf is not None:
+        kw["res2"] = f(c2, mrf.clone())
+    tmp = torch.empty_like(x)
+    if out_lrelu:
+        kw.update(out16=f(c2, tmp), post_lrelu=post_slope)
+    else:
+        kw.update(out16r=f(c2, tmp))
+    conv1d(c2, f(c2, t16), **kw)
+    out.copy_(tmp)
+
+
 def conv_post_tanh(x16, w, out):
     B, L, c = x16.shape
     k = w.shape[0]
@@ -238,7 +255,7 @@ def install(monkeypatch):
     """Route music_generation_b200.ops.* to the emulation above (CPU tests only)."""
     import music_generation_b200.synthesizer as syn
     for name in ("conv1d", "attention", "attention_tc", "layernorm", "text_embed", "duration_quantize", "lr_scan", "lr_gather",
-                 "add_pos_mask", "f0_embed", "sample_prior", "conv_post_tanh", "bct_to_btc"):
+                 "add_pos_mask", "f0_embed", "sample_prior", "conv_post_tanh", "bct_to_btc", "resblock_pair"):
         monkeypatch.setattr(real_ops, name, globals()[name])
     monkeypatch.setattr(syn, "_require_cuda", lambda t: None)
     monkeypatch.setattr(syn, "_STAGE_API", False)          # the emulation covers the per-op entry points
