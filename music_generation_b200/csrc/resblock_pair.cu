@@ -15,9 +15,9 @@
 //
 // Warp roles (384 threads, 1 CTA/SM, persistent over tiles); everything meets at mbarriers only:
 //   warp 0 lane 0 : TMA producer of the conv1 input tile (rows with halo; zero padding = TMA out-of-bounds fill)
-//   warp 1 lane 0 : tcgen05.mma issuer, software-pipelined: conv1(i+1) is issued before conv2(i)
+//   warp 1 lane 0 : tcgen05.mma issuer of every conv1
+//   warp 3 lane 0 : loads both weight sets once (resident for the whole kernel), then tcgen05.mma issuer of every conv2
 //   warp 2        : TMEM alloc / dealloc; lane 0 = TMA store thread
-//   warp 3 lane 0 : loads both weight sets once (resident for the whole kernel)
 //   warps 4..11   : both epilogues, in the MMA thread's order (epilogue 1 of tile i+1, then epilogue 2 of tile i); warp w
 //                   and w + 4 share a TMEM lane quadrant and split the 64 folded columns 32 / 32:
 //                   epilogue 1: acc1 (TMEM) + bias -> lrelu -> fp16 -> intermediate tile in shared memory in the UMMA
@@ -37,7 +37,7 @@ namespace b200svs {
 #endif
 #define pwait(bar, parity) do { if (p.poll) mbar_wait_poll(bar, parity); else mbar_wait(bar, parity); } while (0)
 
-constexpr int kPairThreads = 384;
+constexpr int kPairThreads = 640;        // 4 control warps + 2 epilogue groups of 8 warps (alternate tiles)
 constexpr int kMidGuard = 8;                                  // guard rows above and below the 128 intermediate rows
 constexpr int kMidBytes = (128 + 2 * kMidGuard) * 128;        // 18 KB, 1024-byte aligned
 constexpr int kPairSlotBytes = 128 * 128;                     // 16 KB output staging slot
@@ -167,17 +167,20 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
           tma_load_3d(dst + bx * p.a_box_rows * 128, &tmX, &bars->a_full[ab], 0, row0 + bx * p.a_box_rows, b);
       }
     }
-  } else if (warp == 3) {
-    if (lane == 0) {
+  } else if (warp == 1 || warp == 3) {
+    if (warp == 3 && lane == 0) {
       // ------------------------------------------------------------ both weight sets, once
       mbar_arrive_expect_tx(&bars->w_full, static_cast<uint32_t>(p.taps1 * p.w1_tile_bytes + p.taps2 * p.w2_tile_bytes));
       const int n1 = p.c1_folded ? 64 : 32;
       for (int v = 0; v < p.taps1; ++v) tma_load_2d(smW1 + v * p.w1_tile_bytes, &tmW1, &bars->w_full, 0, v * n1);
       for (int v = 0; v < p.taps2; ++v) tma_load_2d(smW2 + v * p.w2_tile_bytes, &tmW2, &bars->w_full, 0, v * 64);
     }
-  } else if (warp == 1) {
+    __syncwarp();
     if (elect_one()) {
-      // ------------------------------------------------------------ MMA issuer
+      // ------------------------------------------------------------ MMA issuers: warp 1 issues every conv1, warp 3 every
+      // conv2.  A barrier round trip costs an issuing thread ~230-450 cycles during which the tensor pipe drains its
+      // queue; with one thread per conv the two sets of waits overlap and the pipe stays fed (tcgen05.commit tracks the
+      // MMAs of the executing thread only, so each thread's commits cover exactly its own conv).
       const uint64_t dA0 = make_desc_k128(smem_u32(smA)), dM0 = make_desc_k128(smem_u32(smM));
       const uint64_t dW1 = make_desc_k128(smem_u32(smW1)), dW2 = make_desc_k128(smem_u32(smW2));
       const uint32_t a_stage_d = static_cast<uint32_t>(p.a_stage_bytes) >> 4, w1_d = static_cast<uint32_t>(p.w1_tile_bytes) >> 4;
@@ -187,6 +190,7 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
         const int ab = p.na == 2 ? (it & 1) : 0;
         const int use = p.na == 2 ? (it >> 1) : it;
         const int buf = it & 1;
+        pstamp(p, it, 15);
         pwait(&bars->a_full[ab], use & 1);
         pwait(&bars->acc1_empty[buf], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
@@ -218,8 +222,10 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
         const int mb = p.nm == 2 ? (it & 1) : 0;
         const int use = p.nm == 2 ? (it >> 1) : it;
         const int buf = it & 1;
+        pstamp(p, it, 13);
         pwait(&bars->mid_full[mb], use & 1);
-        pwait(&bars->acc2_empty[buf], ((it >> 1) & 1) ^ 1);
+        // acc2[buf] is free as well: its last reader, epilogue 2 of tile it-2, precedes epilogue 1 of tile it in the same
+        // warp group, whose arrival on mid_full(it) was just observed.
         tc_fence_after();
         pstamp(p, it, 3);
         const uint32_t d = tmem_base + buf * 128 + 64;
@@ -231,13 +237,14 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
         }
         umma_commit(&bars->mid_empty[mb]);
         umma_commit(&bars->acc2_full[buf]);
+        pstamp(p, it, 14);
       };
       pwait(&bars->w_full, 0);
       tc_fence_after();
-      if (n_my > 0) conv1(0);
-      for (int it = 0; it < n_my; ++it) {
-        if (it + 1 < n_my) conv1(it + 1);
-        conv2(it);
+      if (warp == 1) {
+        for (int it = 0; it < n_my; ++it) conv1(it);
+      } else {
+        for (int it = 0; it < n_my; ++it) conv2(it);
       }
     }
     __syncwarp();
@@ -265,7 +272,9 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
     // lane quadrant w % 4 (row r of the tile) and split the 64 folded columns 32 / 32 (half = time step of the row pair).
     // Both phases run on all eight warps, in the MMA thread's order: epilogue 1 of tile i+1, then epilogue 2 of tile i.
     griddep_wait();
-    const int q = warp & 3, half = (warp - 4) >> 2, r = q * 32 + lane;
+    const int grp = (warp - 4) >> 3;                    // group g owns tiles g, g + 2, ... of this CTA
+    const int q = warp & 3, half = ((warp - 4) >> 2) & 1, r = q * 32 + lane;
+    const bool tracer = ((threadIdx.x - 128) & 255) == 0;
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
     const uint32_t smM_u = smem_u32(smM), smS_u = smem_u32(smS);
     const uint32_t b1_u = smem_u32(bias1_s) + (p.c1_folded ? half * 128 : 0), b2_u = smem_u32(bias2_s) + half * 128;
@@ -283,7 +292,7 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
       const int use = p.nm == 2 ? (it >> 1) : it;
       pwait(&bars->acc1_full[buf], (it >> 1) & 1);
       tc_fence_after();
-      if (threadIdx.x == 128) pstamp(p, it, 4);
+      if (tracer) pstamp(p, it, 4);
       uint32_t a[32];
       tmem_ld32_nowait(tmem_base + buf * 128 + lane_off + half * 32, a);
       tmem_ld_wait32(a);
@@ -291,7 +300,7 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars->acc1_empty[buf]);
       pwait(&bars->mid_empty[mb], (use & 1) ^ 1);          // conv2 of the tile that used this buffer has read it
-      if (threadIdx.x == 128) pstamp(p, it, 5);
+      if (tracer) pstamp(p, it, 5);
       // folded conv1: row r of the tile, columns [32*half, +32) = time step `half` of the pair -> cells 4*half ..
       // plain conv1 : sub-tile `half`, time step half*128 + r, its 32 channels -> row (half*128 + r)/2, cells 4*(r&1) ..
       int R, cell0;
@@ -325,7 +334,7 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars->mid_full[mb]);
-      if (threadIdx.x == 128) pstamp(p, it, 6);
+      if (tracer) pstamp(p, it, 6);
     };
 
     // out = acc2 + bias2 + x [+ mrf] -> [scale] -> [lrelu] -> fp16 for this thread's 32 columns -> 4 cells of the slot
@@ -336,21 +345,17 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
       const int buf = it & 1, s = it & 1;
       const int g = s_mid + r;
       const bool ok = r >= p.p2 && r < 128 - p.p2 && g < p.Lh;
-      if (threadIdx.x == 128) pstamp(p, it, 12);
+      if (tracer) pstamp(p, it, 12);
       // residual (and MRF) half rows first: their latency hides behind the wait for conv2
-      uint4 xr[4] = {}, mr[4] = {};
+      uint4 xr[4] = {};
       const size_t row_off = (static_cast<size_t>(b) * p.Lh + (ok ? g : 0)) * 128 + half * 64;
       if (ok) {
 #pragma unroll
         for (int c = 0; c < 4; ++c) xr[c] = ldg_nc128(static_cast<const uint8_t*>(p.x) + row_off + c * 16);
-        if (p.mrf) {       // plain loads: these rows are overwritten by this tile's own store when out aliases mrf
-#pragma unroll
-          for (int c = 0; c < 4; ++c) mr[c] = *reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(p.mrf) + row_off + c * 16);
-        }
       }
       pwait(&bars->acc2_full[buf], (it >> 1) & 1);
       tc_fence_after();
-      if (threadIdx.x == 128) pstamp(p, it, 7);
+      if (tracer) pstamp(p, it, 7);
       uint32_t a[32];
       tmem_ld32_nowait(tmem_base + buf * 128 + 64 + lane_off + half * 32, a);
       tmem_ld_wait32(a);
@@ -358,7 +363,7 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars->acc2_empty[buf]);
       pwait(&bars->slot_empty[s], ((it >> 1) & 1) ^ 1);
-      if (threadIdx.x == 128) pstamp(p, it, 8);
+      if (tracer) pstamp(p, it, 8);
       if (ok) {
         const int ro = r - p.p2;
         const uint32_t rowa = smS_u + s * kPairSlotBytes + ro * 128;
@@ -367,7 +372,9 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
           const float4 bq0 = lds128(b2_u + c * 32), bq1 = lds128(b2_u + c * 32 + 16);
           const float2 bb[4] = {make_float2(bq0.x, bq0.y), make_float2(bq0.z, bq0.w), make_float2(bq1.x, bq1.y), make_float2(bq1.z, bq1.w)};
           const uint32_t xw[4] = {xr[c].x, xr[c].y, xr[c].z, xr[c].w};
-          const uint32_t mw[4] = {mr[c].x, mr[c].y, mr[c].z, mr[c].w};
+          uint4 mrc = make_uint4(0, 0, 0, 0);      // plain load: these rows are overwritten by this tile's own store when out aliases mrf
+          if (p.mrf) mrc = *reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(p.mrf) + row_off + c * 16);
+          const uint32_t mw[4] = {mrc.x, mrc.y, mrc.z, mrc.w};
           uint32_t pk[4];
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
@@ -389,13 +396,14 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars->slot_full[s]);
-      if (threadIdx.x == 128) pstamp(p, it, 9);
+      if (tracer) pstamp(p, it, 9);
     };
 
-    if (n_my > 0) epi1(0);
-    for (int it = 0; it < n_my; ++it) {
-      if (it + 1 < n_my) epi1(it + 1);
+    // conv2's result of tile i is drained, then conv1's of tile i + 2 (the order in which the tensor pipe produces them)
+    if (grp < n_my) epi1(grp);
+    for (int it = grp; it < n_my; it += 2) {
       epi2(it);
+      if (it + 2 < n_my) epi1(it + 2);
     }
   }
 

@@ -26,7 +26,7 @@ _lib.call("b200svs_resblock_pair_set_trace", None, 0)
 t = buf.cpu()
 cta = 5
 base = int(t[cta, 20, 0])
-names = {0: "Aload", 1: "c1beg", 2: "c1iss", 3: "c2beg", 4: "e1acc", 5: "e1mid", 6: "e1end", 12: "e2top", 13: "ldres", 14: "e1top", 7: "e2acc", 8: "e2slot", 9: "e2end", 10: "stbeg", 11: "stend"}
+names = {0: "Aload", 1: "c1beg", 2: "c1iss", 3: "c2beg", 4: "e1acc", 5: "e1mid", 6: "e1end", 12: "e2top", 13: "c2top", 14: "c2iss", 15: "c1top", 7: "e2acc", 8: "e2slot", 9: "e2end", 10: "stbeg", 11: "stend"}
 for it in range(20, 26):
     print(f"tile {it}: " + " ".join(f"{names[s]}={int(t[cta, it, s]) - base}" for s in (0, 1, 2, 4, 5, 6, 3, 12, 7, 8, 9, 10, 11)))
 ev = sorted((int(t[cta, it, s_]) - base, f"{names[s_]}({it})") for it in range(22, 27) for s_ in names if int(t[cta, it, s_]))
