@@ -267,7 +267,8 @@ typedef struct b200svs_generator_w {
   int32_t channels[B200SVS_MAX_STAGES]; /* output channels of stage i */
   int32_t pre_channels;                /* upsample_initial_channel */
   int32_t chunk_frames, wide_chunk_frames, wide_stages;   /* utterance chunking */
-  int32_t fuse_pairs;                  /* 1: stages with 32 channels run b200svs_resblock_pair (one kernel per pair) */
+  int32_t fuse_pairs;                  /* 1: the 32- and 64-channel stages run b200svs_resblock_pair (one kernel per pair)
+                                          where both weight sets fit in shared memory */
   float lrelu_slope;                   /* 0.1 (modules.py:17) */
   b200svs_conv_w pre;
   b200svs_conv_w ups[B200SVS_MAX_STAGES];
@@ -314,13 +315,14 @@ size_t b200svs_encoder_workspace_bytes(const b200svs_encoder_layer_w* w, int32_t
 int b200svs_encoder_fwd(const b200svs_encoder_layer_w* w, int32_t n_layers, float* x32, void* x16, const int32_t* lens,
                         int32_t B, int32_t T, void* workspace, size_t workspace_bytes, void* stream);
 
-/* One ResBlock1 pair of the Generator's 32-channel stage, fused (VISinger/modules.py:210-223):
+/* One ResBlock1 pair of the Generator's 32- or 64-channel stage, fused (VISinger/modules.py:210-223):
  *   v   = x + conv2(lrelu(conv1(lrelu(x)), 0.1))  [+ mrf]      x = min(r, r * res_unlrelu) recovered from the input tensor,
  *   out = cvt16(out_lrelu ? lrelu(v * scale, post_slope) : v * scale)
  * with the intermediate tile in shared memory (4 B of HBM traffic per element instead of the 10 of two conv1d_tc
- * launches; bit-identical to them).  x / mrf / out: dense [B, L, 32] fp16, L even; x holds lrelu(x, 1 / res_unlrelu).
- * c2 must be the time-pair-folded conv (fold == 2), c1 folded (dilation 1) or plain (any dilation).  out must not alias
- * x; it may alias mrf. */
+ * launches; bit-identical to them).  x / mrf / out: dense [B, L, C] fp16; x holds lrelu(x, 1 / res_unlrelu).
+ * C = 32 (L even): c2 must be the time-pair-folded conv (fold == 2), c1 folded (dilation 1) or plain (any dilation).
+ * C = 64: two plain 64 -> 64 convs whose weights fit in shared memory together (taps1 + taps2 <= 14).
+ * out must not alias x; it may alias mrf. */
 int b200svs_resblock_pair(const b200svs_conv_w* c1, const b200svs_conv_w* c2, const void* x, int32_t B, int32_t L,
                           const void* mrf, void* out, int32_t out_lrelu, float post_slope, float scale,
                           float res_unlrelu, void* stream);

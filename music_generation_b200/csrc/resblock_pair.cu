@@ -201,7 +201,7 @@ resblock_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
           uint32_t accum = 0;
           for (int v = 0; v < p.taps1; ++v) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) { umma_f16(d, da + v * kRowD + 2 * k, dW1 + v * w1_d + 2 * k, p.idesc1, accum); accum = 1; }
+            for (int k = 0; k < 4; ++k) { umma_f16(d, da + static_cast<uint32_t>(v * p.dil1) * kRowD + 2 * k, dW1 + v * w1_d + 2 * k, p.idesc1, accum); accum = 1; }
           }
         } else {
 #pragma unroll
@@ -433,19 +433,27 @@ extern "C" int b200svs_resblock_pair(const b200svs_conv_w* c1, const b200svs_con
                                      const void* mrf, void* out, int32_t out_lrelu, float post_slope, float scale,
                                      float res_unlrelu, void* stream) {
   B200SVS_REQUIRE(c1 && c2 && x && out && B > 0 && L > 0, "resblock_pair: bad argument");
-  B200SVS_REQUIRE(L % 2 == 0, "resblock_pair: L=%d must be even (time-pair folding)", L);
   B200SVS_REQUIRE(out != x, "resblock_pair: out must not alias x");
   B200SVS_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(mrf)) & 15) == 0,
                   "resblock_pair: tensors must be 16-byte aligned");
-  B200SVS_REQUIRE(c2->fold == 2 && c2->cin == 64 && c2->cout_pad == 64 && c2->cin_pad == 64 && c2->dil == 1 && !c2->f32 && !c2->gate,
-                  "resblock_pair: conv2 must be the time-pair-folded 32-channel conv (64 -> 64)");
-  const bool f1 = c1->fold == 2;
-  B200SVS_REQUIRE(!c1->f32 && !c1->gate && c1->cin_pad == 64 &&
-                      (f1 ? (c1->cin == 64 && c1->cout_pad == 64 && c1->dil == 1) : (c1->cin == 32 && c1->cout_pad == 32 && c1->fold <= 1)),
-                  "resblock_pair: conv1 must be the folded (64 -> 64) or plain (32 -> 32) 32-channel conv");
+  B200SVS_REQUIRE(!c1->f32 && !c1->gate && !c2->f32 && !c2->gate && c1->cin_pad == 64 && c2->cin_pad == 64 && c2->dil == 1,
+                  "resblock_pair: 16-bit tensor-core convs with K <= 64 expected, conv2 with dilation 1");
+  // 64-channel stage: rows are time steps (64 channels = 128 bytes), both convs plain 64 -> 64.
+  // 32-channel stage: rows are time-step PAIRS; conv2 folded (64 -> 64), conv1 folded or plain 32 -> 32.
+  const bool wide = c2->fold <= 1;
+  if (wide) {
+    B200SVS_REQUIRE(c2->cin == 64 && c2->cout_pad == 64 && c1->cin == 64 && c1->cout_pad == 64 && c1->fold <= 1,
+                    "resblock_pair: 64-channel pair needs two plain 64 -> 64 convs");
+  } else {
+    B200SVS_REQUIRE(L % 2 == 0, "resblock_pair: L=%d must be even (time-pair folding)", L);
+    B200SVS_REQUIRE(c2->fold == 2 && c2->cin == 64 && c2->cout_pad == 64, "resblock_pair: conv2 must be the folded 32-channel conv");
+    B200SVS_REQUIRE(c1->fold == 2 ? (c1->cin == 64 && c1->cout_pad == 64 && c1->dil == 1) : (c1->cin == 32 && c1->cout_pad == 32),
+                    "resblock_pair: conv1 must be the folded (64 -> 64) or plain (32 -> 32) 32-channel conv");
+  }
+  const bool f1 = wide || c1->fold == 2;            // conv1 works on 128-byte rows of 64 channels
   PairParams p;
   memset(&p, 0, sizeof(p));
-  p.B = B; p.Lh = L / 2;
+  p.B = B; p.Lh = wide ? L : L / 2;
   p.taps2 = c2->ntaps; p.p2 = c2->pad_left;
   B200SVS_REQUIRE(p.p2 >= 0 && p.p2 <= kMidGuard && p.taps2 - 1 - p.p2 <= kMidGuard && p.taps2 <= 8, "resblock_pair: conv2 taps=%d pad=%d",
                   p.taps2, p.p2);
@@ -456,7 +464,7 @@ extern "C" int b200svs_resblock_pair(const b200svs_conv_w* c1, const b200svs_con
   p.c1_folded = f1 ? 1 : 0;
   p.taps1 = c1->ntaps; p.dil1 = c1->dil; p.pad1 = c1->pad_left;
   B200SVS_REQUIRE(p.taps1 >= 1 && p.taps1 <= 16, "resblock_pair: conv1 taps=%d", p.taps1);
-  p.a_rows = f1 ? 128 + p.taps1 - 1 : 256 + (p.taps1 - 1) * p.dil1;
+  p.a_rows = f1 ? 128 + (p.taps1 - 1) * p.dil1 : 256 + (p.taps1 - 1) * p.dil1;
   p.a_boxes = p.a_rows > 256 ? 2 : 1;
   p.a_box_rows = ((p.a_rows + p.a_boxes - 1) / p.a_boxes + 7) / 8 * 8;
   p.a_stage_bytes = p.a_boxes * p.a_box_rows * 128;

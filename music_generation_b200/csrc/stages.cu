@@ -125,7 +125,9 @@ static int generator_stages(const b200svs_generator_w* w, const void* cur, int c
         const bool last = m == w->n_pairs - 1;
         const b200svs_conv_w& c1 = w->rb[i][j][m][0];
         const b200svs_conv_w& c2 = w->rb[i][j][m][1];
-        if (w->fuse_pairs && ch == 32 && c2.fold == 2 && T2 % 2 == 0) {
+        const bool fusable = (ch == 32 && c2.fold == 2 && T2 % 2 == 0) ||
+                             (ch == 64 && c1.fold <= 1 && c2.fold <= 1 && c1.ntaps + c2.ntaps <= 14);      // both weight sets resident
+        if (w->fuse_pairs && fusable) {
           // one kernel per pair (resblock_pair.cu); the output must not alias the input: cl and t16 ping-pong
           void* dst = (src == cl) ? t16 : cl;
           int r;

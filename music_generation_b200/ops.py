@@ -313,12 +313,22 @@ def encoder_fwd(tables, n_layers, x32, x16, lens):
     _lib.call("b200svs_encoder_fwd", tables, n_layers, _ptr(x32), _ptr(x16), _ptr(lens), B, T, _ptr(ws), ws.numel(), _stream())
 
 
+def pair_fusable(c1, c2, ch):
+    """Shapes b200svs_resblock_pair takes: the 32-channel stage (conv2 time-pair folded) and the 64-channel stage while both
+    weight sets stay resident in shared memory (kernel sizes up to 7)."""
+    if c2 is None or c1.f32 or c2.f32:
+        return False
+    if ch == 32:
+        return c2.fold == 2
+    return ch == 64 and c1.fold == 1 and c2.fold == 1 and c1.ntaps + c2.ntaps <= 14
+
+
 def resblock_pair(c1, c2, x, out, *, mrf=None, out_lrelu=True, post_slope=0.1, scale=1.0, res_unlrelu=10.0):
     """Fused ResBlock1 pair of the 32-channel Generator stage (b200svs_resblock_pair): out = x + c2(lrelu(c1(lrelu(x))))
     [+ mrf], x recovered from the activated 16-bit tensor.  x / out / mrf: dense [B, L, 32] fp16."""
     B, L, ch = x.shape
-    if ch != 32 or not x.is_contiguous() or not out.is_contiguous() or x.dtype != torch.float16:
-        raise ValueError("resblock_pair: dense [B, L, 32] fp16 tensors expected")
+    if ch not in (32, 64) or not x.is_contiguous() or not out.is_contiguous() or x.dtype != torch.float16:
+        raise ValueError("resblock_pair: dense [B, L, 32 | 64] fp16 tensors expected")
     if _lib.PROFILE is not None:
         n = float(B) * L * ch
         _lib.NEXT_META = (c2.tag, 2.0 * B * L * (c1.alg_macs_per_row / c1.fold + c2.alg_macs_per_row / c2.fold),

@@ -108,7 +108,7 @@ class SynthesizerTrn(nn.Module):
         # reference fills with bias-driven values and every consumer masks) are written as 0.  Off by default so that
         # `infer` matches the reference over the whole padded tensor; pipeline.Synthesiser turns it on.
         self.generator_bucket = bool(generator_bucket)
-        # 32-channel stage: one fused kernel per ResBlock pair (b200svs_resblock_pair, 4 instead of 10 B of HBM traffic per
+        # 32- and 64-channel stages (kernel sizes whose two weight sets fit in shared memory): one fused kernel per ResBlock pair (b200svs_resblock_pair, 4 instead of 10 B of HBM traffic per
         # element, bit-identical to the two conv launches; -1 % on the whole step).
         self.generator_pair_fused = bool(generator_pair_fused)
         # launch-bound (small) calls: replay the frame-level part of infer from a CUDA graph keyed by its shapes
@@ -620,7 +620,7 @@ class SynthesizerTrn(nn.Module):
                         kw["res16"] = srcr
                     else:
                         kw["res1"] = src32
-                    if c2 is not None and ract and mrf16 and self.generator_pair_fused and ch == 32 and c2.fold == 2:
+                    if c2 is not None and ract and mrf16 and self.generator_pair_fused and ops.pair_fusable(c1, c2, ch):
                         # one fused kernel per pair (resblock_pair.cu); output must not alias the input: cl16 / t16 ping-pong
                         dst16 = t16 if src16 is cl16 else cl16
                         if not last:

@@ -58,6 +58,29 @@ def test_fused_pair_is_bit_identical(k, d, mode):
     assert torch.equal(got, want), float((got.float() - want.float()).abs().max())
 
 
+@pytest.mark.parametrize("k,d", [(3, 1), (3, 5), (7, 1), (7, 3), (7, 5)])
+@pytest.mark.parametrize("mode", ["pair", "mrf_mid", "mrf_last"])
+def test_fused_pair_64_channels_is_bit_identical(k, d, mode):
+    """The 64-channel stage: rows are time steps, two plain 64 -> 64 convs (kernel sizes up to 7 keep both weight sets
+    resident)."""
+    B, L = 2, 2500 + 7
+    g = torch.Generator().manual_seed(10 * k + d)
+    w1, b1 = torch.randn(64, 64, k, generator=g) * (64 * k) ** -0.5, torch.randn(64, generator=g) * 0.1
+    w2, b2 = torch.randn(64, 64, k, generator=g) * (64 * k) ** -0.5, torch.randn(64, generator=g) * 0.1
+    c1, c2 = packer.pack_conv(w1, b1, dil=d).to(DEV), packer.pack_conv(w2, b2).to(DEV)
+    assert ops.pair_fusable(c1, c2, 64)
+    x = (torch.randn(B, L, 64, generator=g) * 0.8).half().to(DEV)
+    want, mrf = _two_launch(c1, c2, x, mode)
+    got = torch.full_like(x, 7.0)
+    kw = dict(pair=dict(out_lrelu=True, post_slope=0.1), mrf_mid=dict(out_lrelu=False),
+              mrf_last=dict(out_lrelu=True, post_slope=0.01, scale=1.0 / 3))[mode]
+    ops.resblock_pair(c1, c2, x, got, mrf=mrf, **kw)
+    torch.cuda.synchronize()
+    assert torch.equal(got, want), float((got.float() - want.float()).abs().max())
+    w11 = torch.randn(64, 64, 11, generator=g)
+    assert not ops.pair_fusable(packer.pack_conv(w11, None).to(DEV), packer.pack_conv(w11, None).to(DEV), 64)
+
+
 def test_fused_pair_in_place_mrf_and_large_shape():
     """out aliasing mrf (the MRF sum updated in place) on a shape with several tiles per SM."""
     c1, c2 = _convs(7, 3, seed=9)
@@ -91,4 +114,4 @@ def test_generator_with_fused_pairs_is_bit_identical(stage_api):
     l0 = _lib.launches(); oa = a._generator(z); l1 = _lib.launches(); ob = b._generator(z); l2 = _lib.launches()
     torch.cuda.synchronize()
     assert torch.equal(oa, ob)
-    assert (l2 - l1) - (l1 - l0) == 9                     # nine pairs of the 32-channel stage: 18 launches -> 9
+    assert (l2 - l1) - (l1 - l0) == 9 + 6                 # nine pairs at 32 channels + the k = 3 / 7 pairs at 64: one launch each less
