@@ -20,6 +20,10 @@ int b200svs_probe_rowshift(const void* a_f16, const void* b_f16, float* out, int
  * (int64); NULL switches it off.  Slot meanings: tools/trace_pair.py. */
 int b200svs_resblock_pair_set_trace(void* dev_buf, int32_t tiles_per_cta);
 
+/* Diagnostic: clock64 stamps of the attention_ts roles of CTA (1, 0, 0) into dev_buf[tiles][16] (int64); NULL switches it
+ * off.  Slot meanings: tools/trace_attn.py. */
+int b200svs_attention_set_trace(void* dev_buf, int32_t tiles);
+
 #ifdef __cplusplus
 }
 #endif

@@ -107,6 +107,7 @@ PROTOTYPES = {
     "b200svs_bct_to_btc": [_vp, _i32, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _vp, _vp],
     "b200svs_btc_to_bct": [_vp, _i32, _i32, _i32, _i32, _vp, _vp],
     "b200svs_resblock_pair_set_trace": [_vp, _i32],
+    "b200svs_attention_set_trace": [_vp, _i32],
     "b200svs_probe_rowshift": [_vp, _vp, _vp, _i32, _i32, _i32, _vp],
 }
 

@@ -18,59 +18,9 @@
 // every operand is an fp16 (hi, lo) pair with x = hi + lo to ~2^-22, and every product is three MMAs
 // (hi.hi + hi.lo + lo.hi) accumulated in fp32 - tensor-core speed at fp32-class accuracy.
 #include <type_traits>
-#include "common.cuh"
-#include "api_internal.h"
+#include "attention_common.cuh"
 
 namespace b200svs {
-
-constexpr int kTQ = 128;      // queries per CTA
-constexpr int kTK = 64;       // keys per tile
-constexpr int kHD = 96;       // head dim
-constexpr int kWin = 4;
-constexpr int kNR = 2 * kWin + 1;
-constexpr int kQChunkBytes = kTQ * 128;   // 16 KB  [128 rows][64 x 16-bit]
-constexpr int kKChunkBytes = kTK * 128;   //  8 KB
-constexpr int kVBytes = kHD * 128;        // 12 KB  [96 d rows][64 keys]
-constexpr int kPBytes = kTQ * 128;        // 16 KB  [128 q rows][64 keys]
-constexpr int kSoftWarps = 8;              // two per scheduler: warp w and w + 4 share query rows, split the columns
-constexpr int kAttnThreads = kSoftWarps * 32 + 64;    // softmax warps + MMA warp + TMA warp
-constexpr int kMmaWarp = kSoftWarps, kTmaWarp = kSoftWarps + 1;
-constexpr float kLog2e = 1.4426950408889634f;
-
-struct AttnTcParams {
-  const void* qk_hi; const void* qk_lo; int qk_ld;   // [B,T,2C] 16-bit (q | k)
-  float* out32; int out32_ld;
-  void* out16; int out16_ld; int out16_dtype; int out16_split;
-  const float* rel_k; const float* rel_v;
-  const int32_t* lens;
-  int B, T, C, H, dtype;
-};
-
-struct __align__(8) AttnBars {
-  uint64_t qbar;
-  uint64_t k_full[2], k_empty[2];
-  uint64_t v_full, v_empty;
-  uint64_t s_full[2], s_free[2];     // S_j in TMEM ready / read out by the softmax warps
-  uint64_t p_full, o_full;           // P_j published in shared memory / PV_j complete in TMEM
-  uint32_t tmem_base;
-};
-
-__device__ __forceinline__ float ld16f(const void* base, size_t idx, int dtype) {
-  if (dtype == B200SVS_DT_BF16) return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(base)[idx]);
-  return __half2float(reinterpret_cast<const __half*>(base)[idx]);
-}
-__device__ __forceinline__ uint32_t pk16(float a, float b, int dtype) {
-  return dtype == B200SVS_DT_BF16 ? cvt_bf16x2_sat(a, b) : cvt_f16x2_sat(a, b);      // saturating (common.cuh)
-}
-__device__ __forceinline__ float rt16(float a, int dtype) {   // round trip through the 16-bit type
-  if (dtype == B200SVS_DT_BF16) return __bfloat162float(cvt_bf16_sat(a));
-  return __half2float(cvt_f16_sat(a));
-}
-__device__ __forceinline__ float ex2f(float x) {              // 2^x, 2 ulp; ex2(-inf) = 0
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
 
 template <bool SPLIT>
 #ifndef B200SVS_ATTN_MINB_PLAIN
@@ -150,7 +100,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
       // ------------------------------------------------------------ TMA loader: Q, K0, then (K_{j+1}, V_j)
       auto load_k = [&](int j) {
         const int st = j & 1;
-        mbar_wait(&bars->k_empty[st], ((j >> 1) & 1) ^ 1);
+        attn_wait(&bars->k_empty[st], ((j >> 1) & 1) ^ 1);
         uint8_t* dst = smK + st * kKStage;
         mbar_arrive_expect_tx(&bars->k_full[st], kKStage);
         for (int c = 0; c < 2; ++c) {
@@ -166,7 +116,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
       load_k(0);
       for (int j = 0; j < n_kt; ++j) {
         if (j + 1 < n_kt) load_k(j + 1);
-        mbar_wait(&bars->v_empty, (j & 1) ^ 1);
+        attn_wait(&bars->v_empty, (j & 1) ^ 1);
         mbar_arrive_expect_tx(&bars->v_full, NP * kVBytes);
         tma_load_3d(smV, &tmVh, &bars->v_full, j * kTK, oc, b);
         if (SPLIT) tma_load_3d(smV + kVBytes, &tmVl, &bars->v_full, j * kTK, oc, b);
@@ -180,8 +130,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
       const uint32_t q_u = smem_u32(smQ), k_u = smem_u32(smK), v_u = smem_u32(smV), p_u = smem_u32(smP);
       auto issue_s = [&](int j) {      // S_j = Q . K_j^T  (d = 96 = 64 + 32)
         const int st = j & 1;
-        mbar_wait(&bars->k_full[st], (j >> 1) & 1);
-        mbar_wait(&bars->s_free[st], ((j >> 1) & 1) ^ 1);
+        attn_wait(&bars->k_full[st], (j >> 1) & 1);
+        attn_wait(&bars->s_free[st], ((j >> 1) & 1) ^ 1);
         tc_fence_after();
         uint32_t accum = 0;
 #pragma unroll
@@ -201,12 +151,12 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
         umma_commit(&bars->s_full[st]);
         umma_commit(&bars->k_empty[st]);
       };
-      mbar_wait(&bars->qbar, 0);
+      attn_wait(&bars->qbar, 0);
       issue_s(0);
       for (int j = 0; j < n_kt; ++j) {
         if (j + 1 < n_kt) issue_s(j + 1);
-        mbar_wait(&bars->p_full, j & 1);
-        mbar_wait(&bars->v_full, j & 1);
+        attn_wait(&bars->p_full, j & 1);
+        attn_wait(&bars->v_full, j & 1);
         tc_fence_after();
         uint32_t accum = 0;
 #pragma unroll
@@ -240,7 +190,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
       float a[5];
 #pragma unroll
       for (int w = 0; w < 5; ++w) a[w] = 0.f;
-      mbar_wait(&bars->qbar, 0);
+      attn_wait(&bars->qbar, 0);
 #pragma unroll 1
       for (int cell = 0; cell < kHD / 8; ++cell) {      // 12 cells of 8 channels: chunk 0 holds d 0..63, chunk 1 d 64..95
         const int c = cell >> 3, jc = cell & 7;
@@ -312,7 +262,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
     for (int j = 0; j < n_kt; ++j) {
       const int k0 = j * kTK;
       const int sb = j & 1;
-      mbar_wait(&bars->s_full[sb], (j >> 1) & 1);
+      attn_wait(&bars->s_full[sb], (j >> 1) & 1);
       tc_fence_after();
       const uint32_t ta = tmem_s + sb * kTK + lane_off + half * 32;      // this thread's 32 key columns
       const int kb = k0 + half * 32;                                       // first key of those columns
@@ -358,7 +308,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
       const float alpha = (m_run == -INFINITY) ? 0.f : ex2f(m_run - m_new);
       // ---- PV_{j-1} has to be folded into O (and the P buffer released by its MMAs) before P_j is written
       if (j > 0) {
-        mbar_wait(&bars->o_full, (j - 1) & 1);
+        attn_wait(&bars->o_full, (j - 1) & 1);
         tc_fence_after();
         fold(alpha_prev);
       }
@@ -408,7 +358,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars->p_full);
     }
-    mbar_wait(&bars->o_full, (n_kt - 1) & 1);
+    attn_wait(&bars->o_full, (n_kt - 1) & 1);
     tc_fence_after();
     fold(alpha_prev);
 
@@ -546,6 +496,14 @@ extern "C" int b200svs_attn_prep(const float* qkv, int32_t qkv_ld, void* qk_hi, 
   return check_launch("attn_prep_kernel");
 }
 
+static long long* g_attn_trace = nullptr;
+static int g_attn_trace_cap = 0;
+extern "C" int b200svs_attention_set_trace(void* dev_buf, int32_t tiles) {
+  g_attn_trace = static_cast<long long*>(dev_buf);
+  g_attn_trace_cap = dev_buf ? tiles : 0;
+  return 0;
+}
+
 extern "C" int b200svs_attention_tc(const void* qk_hi, const void* qk_lo, const void* vt_hi, const void* vt_lo,
                                     int32_t dtype, int32_t Tp, float* out32, int32_t out32_ld, void* out16,
                                     int32_t out16_ld, int32_t out16_dtype, int32_t out16_split, const float* rel_k,
@@ -587,6 +545,14 @@ extern "C" int b200svs_attention_tc(const void* qk_hi, const void* qk_lo, const 
   p.out32 = out32; p.out32_ld = out32_ld; p.out16 = out16; p.out16_ld = out16_ld; p.out16_dtype = out16_dtype;
   p.out16_split = out16_split; p.rel_k = rel_k; p.rel_v = rel_v; p.lens = lens;
   p.B = B; p.T = T; p.C = C; p.H = H; p.dtype = dtype;
+  p.trace = g_attn_trace; p.trace_cap = g_attn_trace_cap;
+  // B200SVS_ATTN_TS: 0 = operands from shared memory (this file); 1 = attention_ts for split launches; 2 (default) = also
+  // for plain launches, one CTA per SM (Q in TMEM, two PV accumulators); 3 = plain launches with two CTAs per SM (P in
+  // TMEM only).  Measured at 64 x 2584 frames: split 1298 -> 1000 us, plain 946 -> 861 (mode 2) / 920 (mode 3).
+  static const int ts_mode = [] { const char* e = getenv("B200SVS_ATTN_TS"); return e ? atoi(e) : 2; }();
+  static const int ts_parts = [] { const char* e = getenv("B200SVS_ATTN_TS_PARTS"); return e ? atoi(e) : 2; }();
+  if (ts_mode >= 1 && (split || ts_mode >= 2))
+    return launch_attention_ts(tmQ, tmK, tmV, p, split, ts_mode == 2, ts_parts, as_stream(stream));
   const int np = split ? 2 : 1;
   const size_t smem = (size_t)np * (2 * kQChunkBytes + 4 * kKChunkBytes + kVBytes + kPBytes) + 2 * kTQ * kNR * sizeof(float) + 2 * kNR * kHD * sizeof(float) + 6 * kTQ * sizeof(float) +
                       sizeof(AttnBars) + 1024;
