@@ -34,7 +34,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
   constexpr int NP = SPLIT ? 2 : 1;
   constexpr int kKStage = NP * 2 * kKChunkBytes;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS/STS, not generic LD/ST)
   uint8_t* smQ = smem;                                   // [NP][2 chunks][16 KB]
   uint8_t* smK = smQ + NP * 2 * kQChunkBytes;            // [2 stages][NP][2 chunks][8 KB]
   uint8_t* smV = smK + 2 * kKStage;                      // [NP][12 KB]

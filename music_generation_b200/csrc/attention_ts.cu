@@ -48,7 +48,7 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
   constexpr int kKStage = NP * 2 * kKChunkBytes;
   constexpr uint32_t kTmemCols = WIDE ? 512 : 256;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS/STS, not generic LD/ST)
   uint8_t* smQ = smem;                                   // [NP][2 chunks][16 KB]
   uint8_t* smK = smQ + NP * 2 * kQChunkBytes;            // [2 stages][NP][2 chunks][8 KB]
   uint8_t* smV = smK + 2 * kKStage;                      // [VST][NP][12 KB]
@@ -82,7 +82,7 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
     return;
   }
 
-  if (tid == 0) {
+  if (warp == kTmaW && lane == 0) {      // the loader thread: Q, K_0 and K_1 are in flight before the CTA-wide sync below
     mbar_init(&bars->qbar, 1);
     mbar_init(&bars->q_tmem, kSW);
     for (int i = 0; i < 2; ++i) {
@@ -92,7 +92,21 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
       mbar_init(&bars->o_full[i], 1);
     }
     fence_barrier_init();
-    prefetch_tmap(&tmQh); prefetch_tmap(&tmKh); prefetch_tmap(&tmVh);
+    const int nkt0 = (len + kTK - 1) / kTK;
+    mbar_arrive_expect_tx(&bars->qbar, NP * 2 * kQChunkBytes);
+    for (int c = 0; c < 2; ++c) {
+      tma_load_3d(smQ + c * kQChunkBytes, &tmQh, &bars->qbar, oc + c * 64, q0, b);
+      if (SPLIT) tma_load_3d(smQ + (2 + c) * kQChunkBytes, &tmQl, &bars->qbar, oc + c * 64, q0, b);
+    }
+    for (int j = 0; j < 2 && j < nkt0; ++j) {
+      mbar_arrive_expect_tx(&bars->k_full[j], kKStage);
+      uint8_t* dst = smK + j * kKStage;
+      for (int c = 0; c < 2; ++c) {
+        tma_load_3d(dst + c * kKChunkBytes, &tmKh, &bars->k_full[j], p.C + oc + c * 64, j * kTK, b);
+        if (SPLIT) tma_load_3d(dst + (2 + c) * kKChunkBytes, &tmKl, &bars->k_full[j], p.C + oc + c * 64, j * kTK, b);
+      }
+    }
+    prefetch_tmap(&tmVh);
   }
   if (warp == kMmaW) {
     tmem_alloc(&bars->tmem_base, kTmemCols);
@@ -121,7 +135,7 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
 
   if (warp == kTmaW) {
     if (lane == 0) {
-      // ------------------------------------------------------------ TMA loader: Q, K_0, K_1, then (V_j, K_{j+2}) per stage
+      // ------------------------------------------------------------ TMA loader (Q, K_0, K_1 went out at setup): V_j, K_{j+2}
       auto load_k = [&](int j, uint64_t* bar) {
         uint8_t* dst = smK + (j & 1) * kKStage;
         for (int c = 0; c < 2; ++c) {
@@ -129,15 +143,6 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
           if (SPLIT) tma_load_3d(dst + (2 + c) * kKChunkBytes, &tmKl, bar, p.C + oc + c * 64, j * kTK, b);
         }
       };
-      mbar_arrive_expect_tx(&bars->qbar, NP * 2 * kQChunkBytes);
-      for (int c = 0; c < 2; ++c) {
-        tma_load_3d(smQ + c * kQChunkBytes, &tmQh, &bars->qbar, oc + c * 64, q0, b);
-        if (SPLIT) tma_load_3d(smQ + (2 + c) * kQChunkBytes, &tmQl, &bars->qbar, oc + c * 64, q0, b);
-      }
-      for (int j = 0; j < 2 && j < n_kt; ++j) {
-        mbar_arrive_expect_tx(&bars->k_full[j], kKStage);
-        load_k(j, &bars->k_full[j]);
-      }
       for (int j = 0; j < n_kt; ++j) {
         const int st = j & 1;
         attn_wait(&bars->v_empty[st], ((j >> 1) & 1) ^ 1);          // PV_{j-2} complete (free on a fresh barrier)
@@ -230,7 +235,6 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
     const int q = warp & 3, part = warp >> 2;
     const int row = q * 32 + lane;
     const int t = q0 + row;
-    const size_t orow = static_cast<size_t>(b) * p.T + t;
     const float scale2 = rsqrtf(static_cast<float>(kHD)) * kLog2e;     // scores live in the log2 domain
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
     {   // (q_i / sqrt(d)) . rel_k[w]: the 9 band offsets are split over the parts (5 | 4, or 3 | 2 | 2 | 2).  On the way
@@ -240,7 +244,8 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
 #pragma unroll
       for (int w = 0; w < 5; ++w) a[w] = 0.f;
       attn_wait(&bars->qbar, 0);
-#pragma unroll 1
+      if (tid == 0) stamp(1, 14);      // Q landed
+#pragma unroll 3
       for (int cell = 0; cell < kHD / 8; ++cell) {      // 12 cells of 8 channels: chunk 0 holds d 0..63, chunk 1 d 64..95
         const int c = cell >> 3, jc = cell & 7;
         const uint8_t* src = smQ + c * kQChunkBytes + row * 128 + ((jc ^ (row & 7)) << 4);
@@ -280,6 +285,7 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
           }
         }
       }
+      if (tid == 0) stamp(1, 15);      // band dot products done
       if (WIDE) {
         tmem_st_wait();
         tc_fence_before();
@@ -464,10 +470,9 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
 #pragma unroll
     for (int c = 0; c < PARTS; ++c) l_tot += lsum[c * kTQ + row];
     const bool live = t < len;
-    const int oc = h * kHD + part * kOC;
     if (t < p.T) {
       if (live) {
-#pragma unroll 1
+#pragma unroll 3
         for (int w = 0; w < kNR; ++w) {
           const float sv = band[row * kNR + w];
           if (sv == -INFINITY) continue;
@@ -483,26 +488,35 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
       const float invl = live ? 1.0f / l_tot : 0.f;
 #pragma unroll
       for (int c = 0; c < kOC; ++c) o[c] = live ? o[c] * invl : 0.f;
-      if (p.out32) {
-        float* op = p.out32 + orow * p.out32_ld + oc;
+    }
+    // ---- stores.  A thread holds kOC columns of ONE row: stored directly, every instruction would touch 32 rows (32 half-used
+    // sectors).  The quadrant's 32 x 96 tile goes through shared memory instead (the Q / K buffers: every MMA and TMA load of
+    // this CTA has completed; row stride 100 floats keeps the float4 writes conflict-free) and is written out row by row,
+    // 24 lanes x 4 columns = one contiguous 384-byte (fp32) / 192-byte (16-bit) segment per instruction.
+    float* stage = reinterpret_cast<float*>(smem);
+    constexpr int kStageLd = kHD + 4;
+    static_assert(kTQ * kStageLd * sizeof(float) <= 2 * kQChunkBytes + 4 * kKChunkBytes, "output staging must fit in the Q + K buffers");
 #pragma unroll
-        for (int c = 0; c < kOC; c += 4) *reinterpret_cast<float4*>(op + c) = make_float4(o[c], o[c + 1], o[c + 2], o[c + 3]);
-      }
-      if (p.out16) {
-        uint16_t* op = reinterpret_cast<uint16_t*>(p.out16) + orow * p.out16_ld + oc;
-        const int odt = p.out16_split ? B200SVS_DT_F16 : p.out16_dtype;
-#pragma unroll
-        for (int c = 0; c < kOC; c += 8) {
-          const uint4 hi = make_uint4(pk16(o[c], o[c + 1], odt), pk16(o[c + 2], o[c + 3], odt), pk16(o[c + 4], o[c + 5], odt),
-                                      pk16(o[c + 6], o[c + 7], odt));
-          *reinterpret_cast<uint4*>(op + c) = hi;
+    for (int c = 0; c < kOC; c += 4)
+      *reinterpret_cast<float4*>(stage + row * kStageLd + part * kOC + c) = make_float4(o[c], o[c + 1], o[c + 2], o[c + 3]);
+    named_bar_sync(1 + q, 32 * PARTS);
+    if (lane < kHD / 4) {
+      const int odt = p.out16_split ? B200SVS_DT_F16 : p.out16_dtype;
+#pragma unroll 4
+      for (int i = part; i < 32; i += PARTS) {
+        const int r = q * 32 + i;
+        if (q0 + r >= p.T) break;
+        const size_t gro = static_cast<size_t>(b) * p.T + q0 + r;
+        const float4 v = *reinterpret_cast<const float4*>(stage + r * kStageLd + 4 * lane);
+        if (p.out32) *reinterpret_cast<float4*>(p.out32 + gro * p.out32_ld + h * kHD + 4 * lane) = v;
+        if (p.out16) {
+          uint16_t* op = reinterpret_cast<uint16_t*>(p.out16) + gro * p.out16_ld + h * kHD + 4 * lane;
+          const uint2 hi = make_uint2(pk16(v.x, v.y, odt), pk16(v.z, v.w, odt));
+          *reinterpret_cast<uint2*>(op) = hi;
           if (p.out16_split) {
-            float lo[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e) lo[e] = o[c + e] - rt16(o[c + e], odt);
-            *reinterpret_cast<uint4*>(op + p.C + c) =
-                make_uint4(pk16(lo[0], lo[1], odt), pk16(lo[2], lo[3], odt), pk16(lo[4], lo[5], odt), pk16(lo[6], lo[7], odt));
-            *reinterpret_cast<uint4*>(op + 2 * p.C + c) = hi;
+            *reinterpret_cast<uint2*>(op + p.C) = make_uint2(pk16(v.x - rt16(v.x, odt), v.y - rt16(v.y, odt), odt),
+                                                              pk16(v.z - rt16(v.z, odt), v.w - rt16(v.w, odt), odt));
+            *reinterpret_cast<uint2*>(op + 2 * p.C) = hi;
           }
         }
       }

@@ -740,7 +740,7 @@ conv1d_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                  const __grid_constant__ CUtensorMap tmO16, const __grid_constant__ CUtensorMap tmR16,
                  const __grid_constant__ CUtensorMap tmO16r, const ConvTcParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS/STS, not generic LD/ST)
   uint8_t* smA = smem;
   uint8_t* smW = smA + p.a_stages * p.a_stage_bytes;
   uint8_t* smE = smW + p.w_stages * p.w_stage_bytes;

@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(kPairThreads, 1)
 resblock_pair_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW1,
                      const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ CUtensorMap tmO, const PairParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS/STS, not generic LD/ST)
   uint8_t* smA = smem;                                                 // [na][a_stage_bytes]
   uint8_t* smM = smA + p.na * p.a_stage_bytes;                         // [nm][kMidBytes]
   uint8_t* smS = smM + p.nm * kMidBytes;                               // [2][kPairSlotBytes]

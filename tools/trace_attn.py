@@ -28,6 +28,7 @@ base = int(t[20, 0])
 for j in range(20, 26):
     print(f"tile {j}: " + " ".join(f"{names[s]}={int(t[j, s]) - base}" for s in range(13)))
 print("cycles per tile (softmax top to top):", [int(t[j + 1, 0]) - int(t[j, 0]) for j in range(10, 38)])
+print("prologue: setup done -> Q landed", int(t[1, 14]) - int(t[0, 14]), "-> band done", int(t[1, 15]) - int(t[1, 14]), "-> first top", int(t[0, 0]) - int(t[1, 15]))
 print("CTA: setup done -> first tile top", int(t[0, 0]) - int(t[0, 14]), "| main loop", int(t[0, 13]) - int(t[0, 0]), "| epilogue", int(t[0, 15]) - int(t[0, 13]),
       "| tiles", sum(1 for j in range(cap) if int(t[j, 0])))
 import time
