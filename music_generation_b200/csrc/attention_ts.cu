@@ -17,10 +17,16 @@
 #include <type_traits>
 #include "attention_common.cuh"
 
+#ifndef B200SVS_ATTN_ACC
+#define B200SVS_ATTN_ACC 1
+#endif
+
 namespace b200svs {
 
+constexpr int kRelKBytes = 2 * 2 * 16 * 128;     // 8 KB
+
 struct __align__(8) AttnTsBars {
-  uint64_t qbar, q_tmem;
+  uint64_t qbar, q_tmem, band_full;
   uint64_t k_full[2], v_full[2];     // stage j & 1: K_j / V_j landed
   uint64_t k_empty[2], v_empty[2];   // S_j / PV_j complete: the stage's K / V buffer may be overwritten
   uint64_t s_full[2];
@@ -41,6 +47,13 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
   constexpr int kSW = 4 * PARTS;                 // softmax warps
   constexpr int kThreads = kSW * 32 + 64;
   constexpr int kMmaW = kSW, kTmaW = kSW + 1;
+  // ACC: O accumulates in TENSOR MEMORY over all key tiles (every PV MMA after the first adds in place) instead of being
+  // folded into registers tile by tile.  The row maximum is then LAZY: it only moves when a tile's maximum exceeds it by
+  // more than kLazy (2^8: P <= 256, far inside fp16 / fp32-accumulate range), and only then the warp rescales its rows of O
+  // in TMEM (ld, multiply, st) before it publishes P_j - after the first tiles that is practically never, so the per-tile
+  // chain loses the PV wait and the fold (310 of ~1550 cycles) and the loop keeps 48 registers less.
+  constexpr bool ACC = WIDE && (B200SVS_ATTN_ACC != 0);
+  constexpr float kLazy = 8.0f;
   constexpr int KC = kTK / PARTS;                // key columns per thread
   constexpr int kOC = kHD / PARTS;               // O columns per thread
   constexpr int NP = SPLIT ? 2 : 1;
@@ -52,10 +65,10 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
   uint8_t* smQ = smem;                                   // [NP][2 chunks][16 KB]
   uint8_t* smK = smQ + NP * 2 * kQChunkBytes;            // [2 stages][NP][2 chunks][8 KB]
   uint8_t* smV = smK + 2 * kKStage;                      // [VST][NP][12 KB]
-  float* qrel = reinterpret_cast<float*>(smV + VST * NP * kVBytes);   // [128][9]  (q/sqrt(d)).rel_k * log2(e)
+  uint8_t* smRK = smV + VST * NP * kVBytes;              // rel_k as an MMA B operand: [hi | lo][2 chunks][16 rows x 128 B]
+  float* qrel = reinterpret_cast<float*>(smRK + kRelKBytes);    // [128][9]  (q/sqrt(d)).rel_k * log2(e)
   float* band = qrel + kTQ * kNR;                               // [128][9]  band scores (log2 domain)
-  float* relk_s = band + kTQ * kNR;                             // [9][96]
-  float* relv_s = relk_s + kNR * kHD;                           // [9][96]
+  float* relv_s = band + kTQ * kNR;                             // [9][96]
   float* pmax = relv_s + kNR * kHD;                             // [2 S buffers][PARTS][128] partial row maxima
   float* lsum = pmax + 2 * PARTS * kTQ;                         // [PARTS][128] partial row sums
   AttnTsBars* bars = reinterpret_cast<AttnTsBars*>(lsum + PARTS * kTQ);
@@ -85,6 +98,7 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
   if (warp == kTmaW && lane == 0) {      // the loader thread: Q, K_0 and K_1 are in flight before the CTA-wide sync below
     mbar_init(&bars->qbar, 1);
     mbar_init(&bars->q_tmem, kSW);
+    mbar_init(&bars->band_full, 1);
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bars->k_full[i], 1); mbar_init(&bars->v_full[i], 1);
       mbar_init(&bars->k_empty[i], 1); mbar_init(&bars->v_empty[i], 1);
@@ -112,16 +126,25 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
     tmem_alloc(&bars->tmem_base, kTmemCols);
     tmem_relinquish();
   }
-  for (int i = tid; i < kNR * kHD; i += kThreads) {
-    relk_s[i] = __ldg(p.rel_k + i);
-    relv_s[i] = __ldg(p.rel_v + i);
+  for (int i = tid; i < kNR * kHD; i += kThreads) relv_s[i] = __ldg(p.rel_v + i);
+  // rel_k [9][96] fp32 -> 16-bit (hi, lo) rows 0..8 of a 16-row K-major SWIZZLE_128B operand tile (rows 9..15 zero): the
+  // band dot products q . rel_k[w] are ONE N = 16 accumulator of MMAs (q.hi + q.lo [+ q_lo.hi]) instead of 430 FMAs per thread
+  for (int i = tid; i < 16 * kHD; i += kThreads) {
+    const int w = i / kHD, d = i - w * kHD, dd = d & 63;
+    const float v = w < kNR ? __ldg(p.rel_k + w * kHD + d) : 0.f;
+    const float vh = rt16(v, dt);
+    const uint32_t off = (d >> 6) * 2048 + (w >> 3) * 1024 + (w & 7) * 128 + (((dd >> 3) ^ (w & 7)) << 4) + (dd & 7) * 2;
+    *reinterpret_cast<uint16_t*>(smRK + off) = static_cast<uint16_t>(pk16(vh, 0.f, dt) & 0xffffu);
+    *reinterpret_cast<uint16_t*>(smRK + 4096 + off) = static_cast<uint16_t>(pk16(v - vh, 0.f, dt) & 0xffffu);
   }
+  fence_proxy_async();               // generic-proxy writes of the rel_k tile -> visible to the tensor core
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_s = bars->tmem_base;          // S : 2 x 64 columns (P_j overwrites S_j: hi 32 columns, lo 32)
   const uint32_t tmem_o = tmem_s + 128;             // PV: 96 columns, second buffer at +128 (WIDE)
   const uint32_t tmem_q = tmem_s + 384;             // Q hi 48 columns, Q lo at +64 (WIDE)
+  const uint32_t tmem_band = tmem_s + (WIDE ? 496 : 224);     // band dot products: 16 columns
   const int n_kt = (len + kTK - 1) / kTK;
 #ifdef B200SVS_ATTN_TRACE      // clock64 stamps of CTA (1,0,0) for tools/trace_attn.py (a -D build: the stamps cost ~5 %)
   const bool tr_cta = p.trace && blockIdx.x == 1 && blockIdx.y == 0 && blockIdx.z == 0;
@@ -185,6 +208,27 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
         }
       };
       if (WIDE) attn_wait(&bars->q_tmem, 0); else attn_wait(&bars->qbar, 0);
+      tc_fence_after();
+      {   // band dot products  D[128 x 16] = Q . rel_k^T  (rel_k always as hi + lo: fp32-class, like the FMAs it replaces)
+        const uint32_t idesc_b = make_idesc_f16(128, 16, dt == B200SVS_DT_BF16);
+        const uint32_t rk_u = smem_u32(smRK);
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+#pragma unroll
+          for (int pr = 0; pr < (SPLIT ? 3 : 2); ++pr) {
+            const int pa = pr == 2 ? 1 : 0, pb = pr == 1 ? 1 : 0;       // (hi,hi) (hi,lo) [(lo,hi)]
+            const uint64_t da = make_desc_k128(q_u + (pa * 2 + c) * kQChunkBytes);
+            const uint64_t db = make_desc_k128(rk_u + pb * 4096 + c * 2048);
+#pragma unroll
+            for (int k = 0; k < (c == 0 ? 4 : 2); ++k) {
+              const uint32_t accum = (c | pr | k) ? 1u : 0u;
+              if (WIDE) umma_f16_ts(tmem_band, tmem_q + pa * 64 + (c * 4 + k) * 8, db + 2 * k, idesc_b, accum);
+              else umma_f16(tmem_band, da + 2 * k, db + 2 * k, idesc_b, accum);
+            }
+          }
+        }
+        umma_commit(&bars->band_full);
+      }
       for (int j = 0; j < 2 && j < n_kt; ++j) {
         attn_wait(&bars->k_full[j], 0);
         tc_fence_after();
@@ -197,12 +241,12 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
       // and the two halves of S_{j+2}, where MMAs already queued cover the checks.  PV_j's accumulator is free because the
       // softmax warps fold PV_{j-2} (WIDE; PV_{j-1} otherwise) before they publish P_j.
       for (int j = 0; j < n_kt; ++j) {
-        const int sb = j & 1, ob = WIDE ? sb : 0;
+        const int sb = j & 1, ob = (WIDE && !ACC) ? sb : 0;
         stamp(j, 10);
         attn_wait(&bars->p_full[sb], (j >> 1) & 1);
         tc_fence_after();
         stamp(j, 11);
-        uint32_t accum = 0;
+        uint32_t accum = (ACC && j > 0) ? 1u : 0u;
 #pragma unroll
         for (int pr = 0; pr < (SPLIT ? 3 : 1); ++pr) {
           const int pa = pr == 2 ? 1 : 0, pb = pr == 1 ? 1 : 0;
@@ -237,66 +281,42 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
     const int t = q0 + row;
     const float scale2 = rsqrtf(static_cast<float>(kHD)) * kLog2e;     // scores live in the log2 domain
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
-    {   // (q_i / sqrt(d)) . rel_k[w]: the 9 band offsets are split over the parts (5 | 4, or 3 | 2 | 2 | 2).  On the way
-        // the Q row goes to TMEM: part c stores cells [12/PARTS * c, ..) - a cell = 8 channels = 4 columns.
-      const int w0 = (kNR * part + PARTS - 1) / PARTS, nw = (kNR * (part + 1) + PARTS - 1) / PARTS - w0;
-      float a[5];
-#pragma unroll
-      for (int w = 0; w < 5; ++w) a[w] = 0.f;
-      attn_wait(&bars->qbar, 0);
-      if (tid == 0) stamp(1, 14);      // Q landed
-#pragma unroll 3
-      for (int cell = 0; cell < kHD / 8; ++cell) {      // 12 cells of 8 channels: chunk 0 holds d 0..63, chunk 1 d 64..95
-        const int c = cell >> 3, jc = cell & 7;
-        const uint8_t* src = smQ + c * kQChunkBytes + row * 128 + ((jc ^ (row & 7)) << 4);
-        const uint4 qh = *reinterpret_cast<const uint4*>(src);
-        const uint32_t uh[4] = {qh.x, qh.y, qh.z, qh.w};
-        const bool mine = cell / (12 / PARTS) == part;         // warp-uniform
-        if (WIDE && mine) tmem_st4(tmem_q + lane_off + cell * 4, uh);
-        float qv[8];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          if (dt == B200SVS_DT_BF16) {
-            qv[2 * e] = __uint_as_float(uh[e] << 16); qv[2 * e + 1] = __uint_as_float(uh[e] & 0xFFFF0000u);
-          } else {
-            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&uh[e]));
-            qv[2 * e] = f.x; qv[2 * e + 1] = f.y;
-          }
-        }
-        if (SPLIT) {
-          const uint4 ql = *reinterpret_cast<const uint4*>(src + 2 * kQChunkBytes);
-          const uint32_t ul[4] = {ql.x, ql.y, ql.z, ql.w};
-          if (mine) tmem_st4(tmem_q + 64 + lane_off + cell * 4, ul);
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&ul[e]));
-            qv[2 * e] += f.x; qv[2 * e + 1] += f.y;
-          }
-        }
-#pragma unroll
-        for (int w = 0; w < 5; ++w) {
-          if (w < nw) {
-            const float4 k0v = *reinterpret_cast<const float4*>(relk_s + (w0 + w) * kHD + cell * 8);
-            const float4 k1v = *reinterpret_cast<const float4*>(relk_s + (w0 + w) * kHD + cell * 8 + 4);
-            float x = a[w];
-            x = fmaf(qv[0], k0v.x, x); x = fmaf(qv[1], k0v.y, x); x = fmaf(qv[2], k0v.z, x); x = fmaf(qv[3], k0v.w, x);
-            x = fmaf(qv[4], k1v.x, x); x = fmaf(qv[5], k1v.y, x); x = fmaf(qv[6], k1v.z, x); x = fmaf(qv[7], k1v.w, x);
-            a[w] = x;
-          }
-        }
-      }
-      if (tid == 0) stamp(1, 15);      // band dot products done
+    {   // Q row -> TMEM (WIDE): part c stores cells [12/PARTS * c, ..) - a cell = 8 channels = 4 columns; then the band
+        // dot products (q_i / sqrt(d)) . rel_k[w] come back from the tensor core (16 columns, 9 used)
+      const int w0 = (kNR * part + PARTS - 1) / PARTS, w1 = (kNR * (part + 1) + PARTS - 1) / PARTS;
       if (WIDE) {
+        attn_wait(&bars->qbar, 0);
+        if (tid == 0) stamp(1, 14);      // Q landed
+#pragma unroll
+        for (int i = 0; i < 12 / PARTS; ++i) {      // chunk 0 holds d 0..63 (cells 0..7), chunk 1 d 64..95
+          const int cell = part * (12 / PARTS) + i;
+          const int c = cell >> 3, jc = cell & 7;
+          const uint8_t* src = smQ + c * kQChunkBytes + row * 128 + ((jc ^ (row & 7)) << 4);
+          const uint4 qh = *reinterpret_cast<const uint4*>(src);
+          const uint32_t uh[4] = {qh.x, qh.y, qh.z, qh.w};
+          tmem_st4(tmem_q + lane_off + cell * 4, uh);
+          if (SPLIT) {
+            const uint4 ql = *reinterpret_cast<const uint4*>(src + 2 * kQChunkBytes);
+            const uint32_t ul[4] = {ql.x, ql.y, ql.z, ql.w};
+            tmem_st4(tmem_q + 64 + lane_off + cell * 4, ul);
+          }
+        }
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->q_tmem);
       }
+      attn_wait(&bars->band_full, 0);
+      tc_fence_after();
+      if (tid == 0) stamp(1, 15);        // band dot products done
+      uint32_t bv[16];
+      tmem_ld16_nowait(tmem_band + lane_off, bv);
+      tmem_ld_wait16(bv);
 #pragma unroll
-      for (int w = 0; w < 5; ++w) {
-        if (w < nw) {
-          qrel[row * kNR + w0 + w] = (t < p.T) ? a[w] * scale2 : 0.f;
-          band[row * kNR + w0 + w] = -INFINITY;
+      for (int w = 0; w < kNR; ++w) {
+        if (w >= w0 && w < w1) {
+          qrel[row * kNR + w] = (t < p.T) ? __uint_as_float(bv[w]) * scale2 : 0.f;
+          band[row * kNR + w] = -INFINITY;
         }
       }
       named_bar_sync(1 + q, 32 * PARTS);         // every part's band offsets are in place
@@ -334,8 +354,41 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
       }
     };
     auto o_wait = [&](int i) {                   // PV_i complete
-      if (WIDE) attn_wait(&bars->o_full[i & 1], (i >> 1) & 1); else attn_wait(&bars->o_full[0], i & 1);
+      if (WIDE && !ACC) attn_wait(&bars->o_full[i & 1], (i >> 1) & 1); else attn_wait(&bars->o_full[0], i & 1);
       tc_fence_after();
+    };
+    auto rescale = [&](float alpha) {            // ACC: this thread's 48 (24) columns of its row of O, in place in TMEM
+      const uint32_t ta = tmem_o + lane_off + part * kOC;
+      uint32_t r0[16];
+      tmem_ld16_nowait(ta, r0);
+      if constexpr (PARTS == 2) {
+        uint32_t r1[16], r2[16];
+        tmem_ld16_nowait(ta + 16, r1);
+        tmem_ld16_nowait(ta + 32, r2);
+        tmem_ld_wait16(r0);
+#pragma unroll
+        for (int e = 0; e < 16; ++e) r0[e] = __float_as_uint(__uint_as_float(r0[e]) * alpha);
+        tmem_st16(ta, r0);
+        tmem_ld_wait16(r1);
+#pragma unroll
+        for (int e = 0; e < 16; ++e) r1[e] = __float_as_uint(__uint_as_float(r1[e]) * alpha);
+        tmem_st16(ta + 16, r1);
+        tmem_ld_wait16(r2);
+#pragma unroll
+        for (int e = 0; e < 16; ++e) r2[e] = __float_as_uint(__uint_as_float(r2[e]) * alpha);
+        tmem_st16(ta + 32, r2);
+      } else {
+        uint32_t r1[8];
+        tmem_ld8_nowait(ta + 16, r1);
+        tmem_ld_wait16(r0);
+#pragma unroll
+        for (int e = 0; e < 16; ++e) r0[e] = __float_as_uint(__uint_as_float(r0[e]) * alpha);
+        tmem_st16(ta, r0);
+        tmem_ld_wait8(r1);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) r1[e] = __float_as_uint(__uint_as_float(r1[e]) * alpha);
+        tmem_st8(ta + 16, r1);
+      }
     };
 
     for (int j = 0; j < n_kt; ++j) {
@@ -389,8 +442,14 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
       named_bar_sync(1 + q, 32 * PARTS);               // also: ALL warps of the quadrant have read S_j - P_j may overwrite it
 #pragma unroll
       for (int c = 0; c < PARTS; ++c) mx = fmaxf(mx, pmax[(sb * PARTS + c) * kTQ + row]);
-      const float m_new = fmaxf(m_run, mx);
+      // ACC: lazy maximum - keep m_run unless this tile exceeds it by more than kLazy (identical in every warp of the
+      // quadrant: mx is the exchanged row maximum)
+      const float m_new = ACC ? ((m_run == -INFINITY || mx > m_run + kLazy) ? mx : m_run) : fmaxf(m_run, mx);
       const float alpha = (m_run == -INFINITY) ? 0.f : ex2f(m_run - m_new);
+      if (ACC && j > 0 && __any_sync(0xffffffffu, m_new != m_run)) {      // rare: rescale this warp's rows of O in place
+        o_wait(j - 1);                   // no PV MMA in flight on O: PV_{j-1} complete, PV_j not issued before P_j is published
+        rescale(alpha);                  // alpha == 1 exactly for the rows whose maximum stays
+      }
       const float a_fold = alpha_prev;                 // rescale factor that belongs to PV_{j-1}
       if (tracer) stamp(j, 3);
       // ---- one accumulator (!WIDE): PV_{j-1} has to be folded into O before PV_j may be issued
@@ -452,7 +511,7 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
       if (lane == 0) mbar_arrive(&bars->p_full[sb]);
       if (tracer) stamp(j, 5);
       // ---- two accumulators (WIDE): fold PV_{j-1} now, off the path that feeds the tensor core
-      if (WIDE && j > 0) {
+      if (WIDE && !ACC && j > 0) {
         o_wait(j - 1);
         if (tracer) stamp(j, 6);
         fold((j - 1) & 1, a_fold);
@@ -460,7 +519,8 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
       }
     }
     o_wait(n_kt - 1);
-    fold(WIDE ? ((n_kt - 1) & 1) : 0, alpha_prev);
+    if (ACC) fold(0, 0.f);               // o = the accumulated O (o starts at 0: 0 * 0 + O)
+    else fold(WIDE ? ((n_kt - 1) & 1) : 0, alpha_prev);
     if (tid == 0) stamp(0, 13);    // main loop done
 
     // ---- row sum over both halves, relative-value band term, normalisation, stores
@@ -535,7 +595,7 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
 static size_t ts_smem_bytes(bool split, bool wide, int parts) {
   const int np = split ? 2 : 1, vst = 2;
   size_t s = (size_t)np * (2 * kQChunkBytes + 4 * kKChunkBytes + vst * kVBytes) + 2 * kTQ * kNR * sizeof(float) +
-             2 * kNR * kHD * sizeof(float) + 3 * parts * kTQ * sizeof(float) + sizeof(AttnTsBars) + 1024;
+             kRelKBytes + kNR * kHD * sizeof(float) + 3 * parts * kTQ * sizeof(float) + sizeof(AttnTsBars) + 1024;
   // WIDE allocates all 512 TMEM columns: a second co-resident CTA would only block in tcgen05.alloc - ask for more than
   // half of the SM's shared memory so that it is not scheduled there in the first place
   if (wide && s < 120 * 1024) s = 120 * 1024;
