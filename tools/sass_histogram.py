@@ -1,12 +1,12 @@
 """Per-kernel histogram of the Blackwell-specific SASS mnemonics in libb200svs.so (cuobjdump -sass):
-UTCHMMA (tcgen05.mma), UTCBAR (tcgen05.commit), LDTM (tcgen05.ld), UTMALDG / UTMASTG (TMA load / store), UTCATOMSWS
+UTCHMMA (tcgen05.mma), UTCBAR (tcgen05.commit), LDTM / STTM (tcgen05.ld / st), UTMALDG / UTMASTG (TMA load / store), UTCATOMSWS
 (TMEM alloc), SYNCS (mbarrier), UBLKCP etc.   python tools/sass_histogram.py > profiles/sass_mnemonics_r2.txt"""
 import collections, os, re, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 lib = os.path.join(ROOT, "music_generation_b200", "lib", "libb200svs.so")
 sass = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
 pat = re.compile(r"^\s+/\*[0-9a-f]+\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)")
-want = ("UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UTMASTG", "UTMAPF", "UTCATOMSWS", "SYNCS", "UTMACMDFLUSH", "ELECT", "F2FP", "MUFU.EX2", "FADD2", "FMUL2", "HMMA", "ACQBULK", "UCGABAR")
+want = ("UTCHMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UTMAPF", "UTCATOMSWS", "SYNCS", "UTMACMDFLUSH", "ELECT", "F2FP", "MUFU.EX2", "FADD2", "FMUL2", "HMMA", "ACQBULK", "UCGABAR")
 per = collections.OrderedDict()
 cur = None
 for ln in sass.splitlines():
