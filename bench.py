@@ -261,6 +261,45 @@ def cpu_baseline_block(args):
     return out
 
 
+def same_box_gpu_reference(args, batch=16):
+    """the UNMODIFIED reference forward on this B200 in eager PyTorch (cuDNN / cuBLAS), fp32 with TF32 off
+    and on - the 'same-box GPU reference'.  Part of the cpu_baseline leg (the only place bench.py runs oracle/): the reference's
+    own SynthesizerTrn.infer, stock code path, `batch` utterances of the workload's length per call, median of 3 after 1 warm-up."""
+    import torch
+    frames, phones = args.frames, args.phones
+    arm = CpuArm(max(2000, frames))
+    if arm.net is None:
+        return {"unavailable": "no reference tree / stage"}
+    from music_generation_b200 import synthetic
+    dev = torch.device("cuda", 0)
+    net = arm.net.to(dev)
+    net.text_post_net.position_ids = net.text_post_net.position_ids.to(dev)
+    inp = {k: v.to(dev) for k, v in synthetic.make_inputs(batch, phones, seed=1234).items()}
+    ph_dur = synthetic.make_ph_dur(inp["x_lengths"].cpu(), phones, frames, seed=1234).to(dev)
+    noise = synthetic.make_noise(batch, 192, frames, seed=1234).to(dev)
+    out = {"batch": batch, "frames": frames, "what": "reference SynthesizerTrn.infer (" + arm.src + "), eager PyTorch on cuda:0"}
+    old = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+    try:
+        for name, tf32 in (("fp32", False), ("tf32", True)):
+            torch.backends.cuda.matmul.allow_tf32 = tf32
+            torch.backends.cudnn.allow_tf32 = tf32
+            times = []
+            for i in range(4):
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                arm.rh.run_reference_infer(net, inp, noise, ph_dur)
+                torch.cuda.synchronize()
+                if i:
+                    times.append(time.perf_counter() - t0)
+            out[name] = {"value": batch * audio_seconds(frames) / statistics.median(times), "unit": UNIT,
+                         "ms_per_call": 1e3 * statistics.median(times)}
+    finally:
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = old
+        del net, arm
+        torch.cuda.empty_cache()
+    return out
+
+
 # ---------------------------------------------------------------------------------------------------
 # GPU side
 # ---------------------------------------------------------------------------------------------------
@@ -477,6 +516,10 @@ def run_gpu_arm(args, rank, local_rank, world):
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu_baseline = cpu_baseline_block(args)
+        try:
+            cpu_baseline["same_box_gpu_eager"] = same_box_gpu_reference(args)
+        except Exception as e:                       # reported, never fatal: it is a side measurement
+            cpu_baseline["same_box_gpu_eager"] = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
