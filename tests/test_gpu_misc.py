@@ -60,6 +60,36 @@ def test_attention_tc_matches_reference_semantics(B, T, lens, split):
         assert max_abs(e32, r16.float().cpu()) < 6e-3
 
 
+@pytest.mark.parametrize("split", [False, True], ids=["plain", "split"])
+def test_attention_tc_rising_scores_exercise_the_lazy_rescale(split):
+    """attention_ts accumulates O in tensor memory and moves the running row maximum only when a key tile exceeds it by
+    more than 2^8, rescaling O in place.  Random scores never do that, so: keys whose magnitude grows
+    along the sequence (x1, x6, x40: the maximum jumps by far more than 8 in the log2 domain, twice, at different tiles
+    for different queries), a stretch of tiny keys in between (maximum must NOT move), and a ragged second row."""
+    B, T = 2, 700
+    qkv = _rand(B, T, 576, seed=11)
+    gain = torch.ones(T)
+    gain[130:300] = 6.0
+    gain[300:420] = 0.05
+    gain[420:] = 40.0
+    qkv[:, :, 192:384] *= gain[None, :, None]          # the k third of q|k|v
+    qkv[1, :, 192:384] = qkv[1].flip(0)[:, 192:384]    # row 1: the large keys come FIRST (no rescale after tile 0..4)
+    rel_k, rel_v = _rand(9, 96, seed=12, scale=96 ** -0.5), _rand(9, 96, seed=13, scale=96 ** -0.5)
+    ln = torch.tensor([700, 555], dtype=torch.int32)
+    # scores reach several hundred here, so rounding q / k to fp16 alone moves the fp32 result by 6e-2: the plain kernel is
+    # compared with the fp32 semantics of the fp16-ROUNDED inputs (what it is given), the split kernel with the exact ones
+    ref_in = qkv if split else qkv.half().float()
+    e32 = torch.empty(B, T, 192)
+    emu_ops.attention(ref_in, e32, None, rel_k, rel_v, ln)
+    r32 = torch.full((B, T, 192), 7.0, device=DEV)
+    ops.attention_tc(qkv.to(DEV), r32, None, rel_k.to(DEV), rel_v.to(DEV), ln.to(DEV), dtype=torch.float16, split=split)
+    torch.cuda.synchronize()
+    assert torch.isfinite(r32).all()
+    err = max_abs(e32, r32.cpu())
+    print(f"rising scores, {'split' if split else 'plain'}: max abs error {err:.3e}")
+    assert err < (2e-4 if split else 8e-3)
+
+
 def test_attention_tc_bf16():
     B, T = 2, 300
     qkv = _rand(B, T, 576, seed=4)
