@@ -315,6 +315,18 @@ size_t b200svs_encoder_workspace_bytes(const b200svs_encoder_layer_w* w, int32_t
 int b200svs_encoder_fwd(const b200svs_encoder_layer_w* w, int32_t n_layers, float* x32, void* x16, const int32_t* lens,
                         int32_t B, int32_t T, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Weight-stationary (transposed) conv for the 64-channel, dilation-1 ResBlock convs (VISinger/modules.py:210-223): the
+ * weights are the tensor core's A operand, resident in tensor memory as the banded [128 x (k+1)*64] matrix `w_img`
+ * (music_generation_b200/packer.py pack_conv_ws: row (s, co), column (j, ci) = W[co, ci, j - s] for 0 <= j - s < k), the
+ * activations the B operand straight from their channels-last layout.
+ *   res == NULL:  out = cvt16(out_lrelu ? lrelu(conv(x) + bias, post_slope) : conv(x) + bias)
+ *   res != NULL:  v = (conv(x) + bias + min(r, r * res_unlrelu) [+ mrf]) * scale;  out = cvt16(out_lrelu ? lrelu(v) : v)
+ * x / res / mrf / out: dense [B, T, 64] fp16, T even; ntaps 3, 7 or 11; out must not alias x or res (it may alias mrf).
+ * Same result as b200svs_conv1d_tc up to the fp32 summation order inside the tensor core (not bit-identical). */
+int b200svs_conv1d_ws(const void* w_img, const float* bias, int32_t ntaps, const void* x, int32_t B, int32_t T,
+                      const void* res, float res_unlrelu, const void* mrf, void* out, int32_t out_lrelu,
+                      float post_slope, float scale, void* stream);
+
 /* One ResBlock1 pair of the Generator's 32- or 64-channel stage, fused (VISinger/modules.py:210-223):
  *   v   = x + conv2(lrelu(conv1(lrelu(x)), 0.1))  [+ mrf]      x = min(r, r * res_unlrelu) recovered from the input tensor,
  *   out = cvt16(out_lrelu ? lrelu(v * scale, post_slope) : v * scale)

@@ -106,6 +106,7 @@ PROTOTYPES = {
     "b200svs_conv_post_tanh": [_vp, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _vp, _vp],
     "b200svs_bct_to_btc": [_vp, _i32, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _vp, _vp],
     "b200svs_btc_to_bct": [_vp, _i32, _i32, _i32, _i32, _vp, _vp],
+    "b200svs_conv1d_ws": [_vp, _vp, _i32, _vp, _i32, _i32, _vp, _f32, _vp, _vp, _i32, _f32, _f32, _vp],
     "b200svs_resblock_pair_set_trace": [_vp, _i32],
     "b200svs_attention_set_trace": [_vp, _i32],
     "b200svs_probe_rowshift": [_vp, _vp, _vp, _i32, _i32, _i32, _vp],

@@ -335,3 +335,17 @@ def resblock_pair(c1, c2, x, out, *, mrf=None, out_lrelu=True, post_slope=0.1, s
                           2.0 * n * (2 + (mrf is not None)) + c1.w.numel() * 2 + c2.w.numel() * 2)
     _lib.call("b200svs_resblock_pair", C.byref(conv_w(c1)), C.byref(conv_w(c2)), _ptr(x), B, L, _ptr(mrf), _ptr(out),
               1 if out_lrelu else 0, float(post_slope), float(scale), float(res_unlrelu), _stream())
+
+
+def conv1d_ws(cw, x, out, *, res=None, mrf=None, out_lrelu=True, post_slope=0.1, scale=1.0, res_unlrelu=10.0):
+    """Weight-stationary 64 -> 64 dilation-1 conv (b200svs_conv1d_ws; packer.pack_conv_ws).  res is None: out =
+    [lrelu](conv(x) + b); else out = [lrelu]((conv(x) + b + unlrelu(res) [+ mrf]) * scale).  Dense [B, T, 64] fp16, T even."""
+    B, T, ch = x.shape
+    if ch != 64 or x.dtype != torch.float16 or not x.is_contiguous() or not out.is_contiguous():
+        raise ValueError("conv1d_ws: dense [B, T, 64] fp16 tensors expected")
+    if _lib.PROFILE is not None:
+        n = float(B) * T * ch
+        _lib.NEXT_META = (cw.tag, 2.0 * B * T * 64 * 64 * cw.ntaps, 2.0 * n * (2 + (res is not None) + (mrf is not None)))
+    _lib.call("b200svs_conv1d_ws", _ptr(cw.img), _ptr(cw.bias), cw.ntaps, _ptr(x), B, T, _ptr(res), float(res_unlrelu),
+              _ptr(mrf), _ptr(out), 1 if out_lrelu else 0, float(post_slope), float(scale), _stream())
+    return out

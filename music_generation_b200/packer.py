@@ -155,6 +155,36 @@ def pack_conv_folded(weight, bias, *, dtype=torch.float16, block_n=None):
     return pc
 
 
+class PackedConvWs:
+    """Weights of a 64 -> 64 dilation-1 conv for b200svs_conv1d_ws: `img` int32 [128, (k+1)*32] is the tensor-memory image
+    of the banded A operand (row s*64 + co, fp16 pair w of chunk j = W[co, 2w / 2w+1, j - s], zero outside 0 <= j - s < k)."""
+
+    def __init__(self, img, bias, ntaps, tag=""):
+        self.img, self.bias, self.ntaps, self.tag = img, bias, ntaps, tag
+
+    def to(self, device):
+        return PackedConvWs(self.img.to(device), self.bias.to(device), self.ntaps, self.tag)
+
+
+def pack_conv_ws(weight, bias, tag=""):
+    """weight [64, 64, k] (k in 3, 7, 11), effective (weight-norm folded), dilation 1, 'same' padding."""
+    weight = weight.detach().float()
+    cout, cin, k = weight.shape
+    if cout != 64 or cin != 64 or k not in (3, 7, 11):
+        raise ValueError("pack_conv_ws: a 64 -> 64 conv with kernel size 3, 7 or 11 is expected")
+    if float(weight.abs().max()) > 65504.0:
+        raise ValueError("pack_conv_ws: |w| exceeds the fp16 range")
+    nj = k + 1
+    a = torch.zeros(2, cout, nj, cin)
+    for s_out in range(2):
+        for j in range(nj):
+            tap = j - s_out
+            if 0 <= tap < k:
+                a[s_out, :, j, :] = weight[:, :, tap]
+    img = a.reshape(128, nj * cin).to(torch.float16).contiguous().view(torch.int32)
+    return PackedConvWs(img.contiguous(), bias.detach().float().contiguous(), k, tag)
+
+
 def gate_block_n(hidden):
     """N tile of a gated conv: 192 (two tiles for hidden 192, N=192 MMAs) when hidden splits into 96-wide halves, else 128."""
     return 192 if hidden % 96 == 0 else 128

@@ -8,7 +8,7 @@ mkdir -p ../../build/variants
 for spec in "$@"; do
   name="${spec%%=*}"; flags="${spec#*=}"
   d=../../build/variants/obj_$name; mkdir -p $d
-  for f in api stages resblock_pair conv1d_tc conv1d_f32 attention attention_tc attention_ts pointwise probe song; do
+  for f in api stages resblock_pair conv1d_ws conv1d_tc conv1d_f32 attention attention_tc attention_ts pointwise probe song; do
     nvcc -O3 -std=c++17 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC $flags -c $f.cu -o $d/$f.o &
   done
   wait
