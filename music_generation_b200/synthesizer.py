@@ -701,6 +701,44 @@ class SynthesizerTrn(nn.Module):
         bct = lambda t: t.transpose(1, 2)
         return bct(z32), bct(stats[:, :, :Ci]), bct(stats[:, :, Ci:]), y_mask, bct(wo16.float())
 
+    @torch.no_grad()
+    def flow_forward(self, z, z_lengths, g=None):
+        """`self.spec_flow(z, y_mask, g=g)` of the reference in the FORWARD direction (ResidualCouplingBlock.forward with
+        reverse=False, models_ae.py:246-253; mean-only coupling layers, modules.py:329-349): the training-side map
+        z -> z_p.  z [B, inter, T] fp32 -> z_p [B, inter, T].  It is the exact inverse of the reverse flow of `infer`, so it
+        runs the same packed layers (Flips folded into the weights) in the opposite order with the coupling mean ADDED
+        (SURVEY.md 8f-4)."""
+        _require_cuda(z)
+        dev, dt, f32 = self.device, self.operand_dtype, torch.float32
+        with _device_guard(dev):
+            P = self._packed or self._pack()
+            B, Ci, T = z.shape
+            H, half = self.hidden_channels, Ci // 2
+            lens = z_lengths.to(device=dev, dtype=torch.int32).contiguous()
+            z32 = torch.empty(B, T, Ci, device=dev, dtype=f32)
+            z16 = torch.empty(B, T, Ci, device=dev, dtype=dt)
+            ops.bct_to_btc(z.contiguous().float(), out32=z32, out16=z16, lens=lens)
+            g_btc = None
+            if g is not None:
+                if not self.gin_channels:
+                    raise ValueError("model was built with gin_channels=0")
+                g_btc = g.to(device=dev, dtype=f32).reshape(B, 1, self.gin_channels).contiguous()
+            hx32 = torch.empty(B, T, H, device=dev, dtype=f32)
+            hx16 = torch.empty(B, T, H, device=dev, dtype=dt)
+            wo16 = torch.empty(B, T, H, device=dev, dtype=dt)
+            for fl in reversed(P["flow"]):
+                io, oo = fl["in_off"], fl["out_off"]
+                gcond = None
+                if g_btc is not None:
+                    gc = torch.empty(B, 1, fl["wn"]["cond"].cout, device=dev, dtype=f32)
+                    ops.conv1d(fl["wn"]["cond"], g_btc, out32=gc)
+                    gcond = gc.view(B, -1)
+                ops.conv1d(fl["pre"], z16[:, :, io:io + half], lens=lens, out32=hx32, out16=hx16)
+                self._wn(fl["wn"], hx32, hx16, lens, wo16, gcond)
+                ops.conv1d(fl["post"], wo16, alpha=1.0, res1=z32[:, :, oo:oo + half], lens=lens,
+                           out32=z32[:, :, oo:oo + half], out16=z16[:, :, oo:oo + half])
+        return z32.transpose(1, 2)
+
     def _graphed(self, fn, args, shape_key):
         """Run fn(*args) through a cached CUDA graph.  args: tensors or None; the graph owns static copies of them and
         of its outputs, results are cloned so that a later replay cannot overwrite what the caller holds."""

@@ -119,8 +119,10 @@ def main():
                 pz, pm, plogs, pmask, px = net.spec_encoder(y, mel_len, g=g)
             finally:
                 torch.randn_like = orig
+            pzp = net.spec_flow(pz, y_mask, g=g)                                # forward flow (training side), models_ae.py:246-253
         np.savez_compressed(os.path.join(out_dir, name + ".npz"), z=z.numpy(), spec=spec[:, ::8].numpy(), hid=hid.numpy(),
-                            o=o.numpy(), post_z=pz.numpy(), post_m=pm.numpy(), post_logs=plogs.numpy(), post_x=px.numpy())
+                            o=o.numpy(), post_z=pz.numpy(), post_m=pm.numpy(), post_logs=plogs.numpy(), post_x=px.numpy(),
+                            post_zp=pzp.numpy())
         print(name, "o", tuple(o.shape), "|o|max %.3f" % o.abs().max())
     json.dump({"cases": {k: list(v) for k, v in CASES.items()}, "g_cases": {k: list(v) for k, v in G_CASES.items()},
                "torch": torch.__version__,

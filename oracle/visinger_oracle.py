@@ -312,6 +312,29 @@ def flow_reverse(sd, z_p, x_mask, g=None, p="spec_flow"):
     return x
 
 
+def coupling_forward(sd, prefix, x, x_mask, g=None):
+    """modules.py:329-349 with reverse=False, mean_only=True (logs == 0, logdet unused here)."""
+    half = x.shape[1] // 2
+    x0, x1 = x[:, :half], x[:, half:]
+    h = conv(sd, prefix + ".pre", x0) * x_mask
+    h = wn(sd, prefix + ".enc", h, x_mask, g=g)
+    m = conv(sd, prefix + ".post", h) * x_mask
+    x1 = m + x1 * x_mask
+    return torch.cat([x0, x1], 1)
+
+
+def flow_forward(sd, z, x_mask, g=None, p="spec_flow"):
+    """models_ae.py:246-253, forward (training side: z_p = flow(z)): RCL0, Flip, RCL1, Flip, ..."""
+    n = 0
+    while f"{p}.spec_flows.{2 * n}.pre.weight" in sd:
+        n += 1
+    x = z
+    for i in range(n):
+        x = coupling_forward(sd, f"{p}.spec_flows.{2 * i}", x, x_mask, g=g)
+        x = torch.flip(x, [1])
+    return x
+
+
 def spec_decoder(sd, z, mel_len, g=None, p="spec_decoder"):
     x_mask = sequence_mask(mel_len, z.size(2)).unsqueeze(1).to(z.dtype)
     x = conv(sd, p + ".pre", z) * x_mask

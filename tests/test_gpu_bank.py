@@ -132,3 +132,10 @@ def test_posterior_encoder_on_device_matches_reference_golden():
     report("posterior_z_snr_db/gin256", round(s, 2))
     assert s > 50 and snr_db(gold["post_m"], m.cpu()) > 50 and snr_db(gold["post_x"], x.cpu()) > 45
     assert float(z[1, :, int(mel_len[1]):].abs().max()) == 0.0
+    # forward flow z -> z_p (reference spec_flow(z, y_mask, g), models_ae.py:246-253) on the reference's own posterior sample
+    zp = net.flow_forward(gold["post_z"].to(DEV), mel_len.to(DEV), g=g.to(DEV))
+    torch.cuda.synchronize()
+    s = snr_db(gold["post_zp"], zp.cpu())
+    report("flow_forward_snr_db/gin256", round(s, 2))
+    assert s > 50 and zp.shape == gold["post_zp"].shape
+    assert float(zp[1, :, int(mel_len[1]):].abs().max()) == 0.0

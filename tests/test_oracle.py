@@ -74,6 +74,10 @@ def test_oracle_speaker_conditioning_matches_reference_golden(name):
     pz, pm, plogs, pmask, px = vo.posterior_encoder(sd, posterior_spectrogram(name), mel_len, posterior_noise(name), g=g)
     for key, t in (("post_z", pz), ("post_m", pm), ("post_logs", plogs), ("post_x", px)):
         assert max_abs(gold[key], t) < 1e-4, key
+    # forward flow (training side, models_ae.py:246-253 with reverse=False) on the posterior sample, and its inverse
+    zp = vo.flow_forward(sd, gold["post_z"], y_mask, g=g)
+    assert max_abs(gold["post_zp"], zp) < 1e-4
+    assert max_abs(gold["post_z"], vo.flow_reverse(sd, zp, y_mask, g=g)) < 1e-4
 
 
 @pytest.mark.skipif(not ref_harness.available(), reason="reference tree only exists in the build container")
