@@ -16,6 +16,29 @@ SAMPLE_RATE = 22050
 LEAD_IN = int(0.2 * SAMPLE_RATE)
 
 
+def save_wav(path, song, sample_rate=SAMPLE_RATE):
+    """Writes an int16 mono song (what `syn_song` / `syn_long` return; a device tensor is copied to the host) as a PCM
+    WAV file - the file `scipy.io.wavfile.write(path, SAMPLE_RATE, wavs.astype(np.int16))` writes at the end of the
+    reference's drivers (pipline_inference_svs_v5.py:139, 256-258), byte for byte, with the standard library only."""
+    import wave
+    if isinstance(song, torch.Tensor):
+        if song.dtype != torch.int16 or song.dim() != 1:
+            raise ValueError("save_wav: a 1-D int16 tensor is expected")
+        data = song.detach().cpu().contiguous().numpy().tobytes()
+    else:
+        import numpy as np
+        a = np.ascontiguousarray(song)
+        if a.dtype != np.int16 or a.ndim != 1:
+            raise ValueError("save_wav: a 1-D int16 array is expected")
+        data = a.tobytes()
+    with wave.open(path, "wb") as f:
+        f.setnchannels(1)
+        f.setsampwidth(2)
+        f.setframerate(int(sample_rate))
+        f.writeframes(data)
+    return path
+
+
 class Synthesiser:
     def __init__(self, net_g, legacy_scalar=False):
         """net_g: a `music_generation_b200` SynthesizerTrn (loaded, on a CUDA device).

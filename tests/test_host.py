@@ -282,3 +282,21 @@ def test_state_dict_keys_match_reference(variant, gin):
     for k, v in ref.items():
         assert tuple(mine[k].shape) == tuple(v.shape), k
         assert mine[k].dtype == v.dtype, k
+
+
+def test_save_wav_writes_the_file_the_reference_driver_writes(tmp_path):
+    """pipline_inference_svs_v5.py:256-258 ends with scipy.io.wavfile.write(path, 22050, wavs.astype(np.int16)):
+    pipeline.save_wav must produce the same bytes from the int16 song (stdlib only on the product side)."""
+    import numpy as np
+    import scipy.io.wavfile
+    from music_generation_b200 import pipeline
+    rng = np.random.default_rng(7)
+    song = rng.integers(-32768, 32767, size=22050 * 2 + 4410 + 3, dtype=np.int16)
+    ours, ref = tmp_path / "ours.wav", tmp_path / "ref.wav"
+    pipeline.save_wav(str(ours), torch.from_numpy(song))
+    scipy.io.wavfile.write(str(ref), pipeline.SAMPLE_RATE, song)
+    assert ours.read_bytes() == ref.read_bytes()
+    sr, back = scipy.io.wavfile.read(str(ours))
+    assert sr == 22050 and np.array_equal(back, song)
+    with pytest.raises(ValueError):
+        pipeline.save_wav(str(ours), torch.zeros(4))
