@@ -31,7 +31,11 @@ struct __align__(8) AttnTsBars {
   uint64_t k_empty[2], v_empty[2];   // S_j / PV_j complete: the stage's K / V buffer may be overwritten
   uint64_t s_full[2];
   uint64_t p_full[2];                // P_j stored in TMEM (count = softmax warps)
-  uint64_t o_full[2];                // PV_j complete (its buffer is free again once P_{j+1} is published: the fold precedes it)
+  // PV_j complete: barrier j & 1, phase j >> 1.  TWO barriers although ACC has one accumulator: with O in tensor memory the
+  // softmax warps no longer wait for every PV, and a parity wait on a single barrier cannot tell phase j from phase j - 2 -
+  // the final wait returned while PV_{n-2} and PV_{n-1} were still running whenever the last tile was a quick one (found by
+  // tools/fuzz_attn.py at T % 128 == 0).  S_j complete implies PV_{j-2} complete, so per parity a waiter is never a phase behind.
+  uint64_t o_full[2];
   uint32_t tmem_base;
 };
 
@@ -257,7 +261,7 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
             accum = 1;
           }
         }
-        umma_commit(&bars->o_full[ob]);
+        umma_commit(&bars->o_full[sb]);
         umma_commit(&bars->v_empty[sb]);
         stamp(j, 12);
         if (j + 2 < n_kt) {
@@ -354,7 +358,7 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_const
       }
     };
     auto o_wait = [&](int i) {                   // PV_i complete
-      if (WIDE && !ACC) attn_wait(&bars->o_full[i & 1], (i >> 1) & 1); else attn_wait(&bars->o_full[0], i & 1);
+      attn_wait(&bars->o_full[i & 1], (i >> 1) & 1);
       tc_fence_after();
     };
     auto rescale = [&](float alpha) {            // ACC: this thread's 48 (24) columns of its row of O, in place in TMEM

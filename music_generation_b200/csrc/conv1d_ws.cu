@@ -29,7 +29,9 @@ constexpr int kWsC = 64;                     // channels in = out
 constexpr int kWsNT = 64;                    // time pairs per tile
 constexpr int kWsXTileBytes = 9 * 1024;      // one parity tile of the input: up to 64 + 2*3 rows of 128 B, 1024-aligned
 constexpr int kWsOTileBytes = kWsNT * 128;   // 8 KB: one parity tile of the output / residual / MRF staging
-constexpr int kWsXStages = 3, kWsRStages = 4, kWsOStages = 3;      // R: 4 stages of 16 KB (residual only) or 3 of 32 KB (+ MRF)
+// Staging / output stage counts are EVEN: the two epilogue groups take alternate tiles, so with an even count a stage always
+// belongs to the same group and every waiter sees every phase of its barrier (a parity wait cannot tell phase k from k - 2).
+constexpr int kWsXStages = 3, kWsRStages = 4, kWsOStages = 2;      // R: 4 stages of 16 KB (residual only) or 32 KB (+ MRF)
 constexpr int kWsEpiWarps = 8;              // per group; two groups work on alternate tiles
 constexpr int kWsThreads = 128 + 2 * kWsEpiWarps * 32;
 
@@ -73,7 +75,7 @@ conv1d_ws_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* smX = smem;                                              // [stages][2 parities][9 KB]
   uint8_t* smR = smX + kWsXStages * 2 * kWsXTileBytes;              // [stages][res | mrf][2 parities][8 KB]
-  uint8_t* smO = smR + 3 * 4 * kWsOTileBytes;                       // [stages][2 parities][8 KB]   (R area: 96 KB)
+  uint8_t* smO = smR + kWsRStages * p.r_stage_bytes;                // [stages][2 parities][8 KB]
   float* bias_s = reinterpret_cast<float*>(smO + kWsOStages * 2 * kWsOTileBytes);
   WsBars* bars = reinterpret_cast<WsBars*>(bias_s + kWsC);
 
@@ -309,8 +311,8 @@ extern "C" int b200svs_conv1d_ws(const void* w_img, const float* bias, int32_t n
   r = make_tmap(&tmM, 0, mrf ? mrf : x, 4, dims, strides, box_t, 128);
   if (r) return r;
 
-  p.rst = mrf ? 3 : 4; p.r_stage_bytes = (mrf ? 4 : 2) * kWsOTileBytes;
-  const size_t smem = (size_t)kWsXStages * 2 * kWsXTileBytes + (size_t)3 * 4 * kWsOTileBytes +
+  p.rst = kWsRStages; p.r_stage_bytes = (mrf ? 4 : 2) * kWsOTileBytes;
+  const size_t smem = (size_t)kWsXStages * 2 * kWsXTileBytes + (size_t)kWsRStages * p.r_stage_bytes +
                       (size_t)kWsOStages * 2 * kWsOTileBytes + kWsC * sizeof(float) + sizeof(WsBars) + 1024;
   const int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
   if (ntaps == 3) {

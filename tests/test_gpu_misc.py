@@ -90,6 +90,48 @@ def test_attention_tc_rising_scores_exercise_the_lazy_rescale(split):
     assert err < (2e-4 if split else 8e-3)
 
 
+@pytest.mark.parametrize("T", [256, 384, 512, 640, 768])
+@pytest.mark.parametrize("split", [False, True], ids=["plain", "split"])
+def test_attention_tc_quick_last_tile(T, split):
+    """Regression (found by tools/fuzz_attn.py): with T % 128 == 0 the second-to-last query tile ends on a key tile that
+    needs neither the band nor the length mask, the softmax warps reach the final PV wait early, and a parity wait on ONE
+    PV barrier returned two phases early (O read before the last two PV products had landed; intermittent, the upper
+    rows of that tile).  Repeated, because it was a race."""
+    qkv = _rand(1, T, 576, seed=T, scale=0.5)
+    rel_k, rel_v = _rand(9, 96, seed=2, scale=96 ** -0.5), _rand(9, 96, seed=3, scale=96 ** -0.5)
+    ln = torch.tensor([T], dtype=torch.int32)
+    e32 = torch.empty(1, T, 192)
+    emu_ops.attention(qkv if split else qkv.half().float(), e32, None, rel_k, rel_v, ln)
+    args = (rel_k.to(DEV), rel_v.to(DEV), ln.to(DEV))
+    q = qkv.to(DEV)
+    for _ in range(5):
+        r32 = torch.full((1, T, 192), 7.0, device=DEV)
+        ops.attention_tc(q, r32, None, *args, dtype=torch.float16, split=split)
+        torch.cuda.synchronize()
+        assert max_abs(e32, r32.cpu()) < (2e-5 if split else 4e-3)
+
+
+def test_attention_tc_random_shapes():
+    """Seeded fuzz over batch, length (around the 64-key / 128-query tile edges), ragged lengths and score scale."""
+    import random
+    rnd = random.Random(5)
+    for it in range(24):
+        B = rnd.randint(1, 3)
+        T = rnd.choice([1, 2, 5, 63, 64, 65, 127, 128, 129, 191, 200, 257, 320, 449, 640])
+        lens = [rnd.choice([T, rnd.randint(0, T), max(1, T // 2)]) for _ in range(B)]
+        sc = rnd.choice([0.5, 1.0, 2.0])
+        qkv = _rand(B, T, 576, seed=it, scale=sc)
+        rel_k, rel_v = _rand(9, 96, seed=100 + it, scale=96 ** -0.5), _rand(9, 96, seed=200 + it, scale=96 ** -0.5)
+        ln = torch.tensor(lens, dtype=torch.int32)
+        for split in (False, True):
+            e32 = torch.empty(B, T, 192)
+            emu_ops.attention(qkv if split else qkv.half().float(), e32, None, rel_k, rel_v, ln)
+            r32 = torch.full((B, T, 192), 7.0, device=DEV)
+            ops.attention_tc(qkv.to(DEV), r32, None, rel_k.to(DEV), rel_v.to(DEV), ln.to(DEV), dtype=torch.float16, split=split)
+            torch.cuda.synchronize()
+            assert max_abs(e32, r32.cpu()) < (2e-4 if split else 1e-2), (B, T, lens, sc, split)
+
+
 def test_attention_tc_bf16():
     B, T = 2, 300
     qkv = _rand(B, T, 576, seed=4)
