@@ -320,6 +320,28 @@ def test_config1_shape_10s_utterance():
     assert snr_db(ref[0], o) >= SNR_DB_TOL and max_abs(ref[0], o) <= MAX_ABS_TOL
 
 
+@pytest.mark.parametrize("T", [768, 1024])
+def test_frame_count_multiple_of_128_matches_oracle(T):
+    """T % 128 == 0: every query tile of the frame-level attention is full and the second-to-last one ends on a key tile
+    without band or mask - the shape on which attention_ts once read its accumulator early.  Whole forward
+    against the oracle, three times (it was a race)."""
+    net, sd = build_model("ae", device=DEV)
+    P = T // 10
+    inp = synthetic.make_inputs(1, P, seed=T)
+    ph_dur = synthetic.make_ph_dur(inp["x_lengths"], P, T, seed=T)
+    noise = synthetic.make_noise(1, 192, T, seed=T)
+    taps = {}
+    ref = vo.infer(sd, noise=noise, ph_dur=ph_dur, taps=taps, **inp)
+    for rep in range(3):
+        res = _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise.to(DEV), f0_score=taps["f0_coarse"].to(DEV))
+        o = res[0].cpu()
+        assert o.shape == (1, 1, T * 256)
+        s, m = snr_db(ref[0], o), max_abs(ref[0], o)
+        assert s >= SNR_DB_TOL and m <= MAX_ABS_TOL, (rep, s, m)
+        assert snr_db(ref[5], res[5].cpu()) > 50, rep                                  # mel_predict (attention output path)
+    report(f"waveform_snr_db/t{T}_multiple_of_128", round(s, 2))
+
+
 def test_generator_only_config2_properties():
     """BASELINE config 2 (Generator on z[16,192,2048]) at full size via size-independent properties:
     (i) time-shift equivariance away from the edges, (ii) chunked == unchunked (bit-exact),
