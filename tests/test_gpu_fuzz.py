@@ -46,3 +46,21 @@ def test_infer_random_shapes_against_oracle(stage_api):
         assert s >= SNR_DB_TOL and m <= MAX_ABS_TOL, (it, B, P, T, ragged, s, m)
         assert snr_db(ref[5], res[5].cpu()) > 50, (it, B, P, T)          # mel_predict: the attention path
     report(f"waveform_snr_db/fuzz_worst_{'stage_api' if stage_api else 'per_op'}", round(worst, 2))
+
+
+@pytest.mark.parametrize("B,P,T", [(1, 1, 1), (1, 2, 2), (2, 2, 3), (1, 3, 7), (3, 4, 17)])
+def test_infer_tiny_shapes_against_oracle(B, P, T):
+    """Degenerate sizes: one phoneme / one frame (256 samples), fewer frames than any tile, odd frame counts."""
+    net, sd = build_model("ae", device=DEV)
+    inp = synthetic.make_inputs(B, P, seed=B * 100 + T)
+    ph_dur = synthetic.make_ph_dur(inp["x_lengths"], P, T, seed=T)
+    Tm = int(ph_dur.sum(1).max())
+    noise = synthetic.make_noise(B, 192, Tm, seed=T)
+    taps = {}
+    ref = vo.infer(sd, noise=noise, ph_dur=ph_dur, taps=taps, **inp)
+    res = _infer(net, inp, ph_dur=ph_dur.to(DEV), noise=noise.to(DEV), f0_score=taps["f0_coarse"].to(DEV))
+    torch.cuda.synchronize()
+    o = res[0].cpu()
+    assert o.shape == ref[0].shape == (B, 1, Tm * 256)
+    assert torch.equal(res[1].cpu(), ref[1])
+    assert snr_db(ref[0], o) >= SNR_DB_TOL and max_abs(ref[0], o) <= MAX_ABS_TOL
