@@ -245,24 +245,29 @@ __global__ void __launch_bounds__(256) sample_prior_kernel(const float* stats, i
 }
 
 // ------------------------------------------------------------------ conv_post (C -> 1, k taps) + tanh
-// A block owns kPostTile consecutive output samples of one utterance.  Every input row (C contiguous 16-bit
+// A block owns kPostTile consecutive input rows of one utterance (kPostTile - (k - 1) outputs).  Every input row (C contiguous 16-bit
 // channels, 128-bit loads) is read ONCE: its thread forms the k partial dot products row . w[tap] and leaves
 // them in shared memory; after a barrier each output sample sums its k partials (tap j of sample t is the
 // partial j of row t + j - pad) and applies tanh.  Weights are broadcast reads from shared memory.
-constexpr int kPostTile = 256;
+constexpr int kPostThreads = 128;
+constexpr int kPostRows = 4;                          // input rows per thread: every weight read from shared memory feeds 4 rows
+constexpr int kPostTile = kPostThreads * kPostRows;   // input rows per block
 constexpr int kPostMaxTaps = 16;
 constexpr int kPostMaxC = 64;
-template <bool BF>
-__global__ void __launch_bounds__(kPostTile) conv_post_tanh_kernel(const void* x, int x_ld, const float* w, int B, int L,
-                                                                    int C, int ktaps, int tiles_per_row, float* out) {
+// KT: compile-time tap count (7 for the shipped conv_post), 0 = runtime `ktaps`.  The first version ran one row per thread:
+// 823 instructions per warp-row for 224 FMAs, the L1 / shared pipe 83 % busy with the broadcast weight reads (ncu).
+template <bool BF, int KT>
+__global__ void __launch_bounds__(kPostThreads) conv_post_tanh_kernel(const void* x, int x_ld, const float* w, int B, int L,
+                                                                       int C, int ktaps_rt, int tiles_per_row, float* out) {
   extern __shared__ float smem_post[];
+  const int ktaps = KT ? KT : ktaps_rt;
+  constexpr int kAcc = KT ? KT : kPostMaxTaps;
   float* ws = smem_post;                               // [ktaps][C]
   float* part = ws + ktaps * C;                        // [ktaps][kPostTile + kPostMaxTaps]
   constexpr int kStride = kPostTile + kPostMaxTaps;
   for (int i = threadIdx.x; i < ktaps * C; i += blockDim.x) ws[i] = w[i];
   __syncthreads();
-  // one input row per thread: a block of 256 threads covers 256 input rows = 256 - (ktaps - 1) outputs (with 256
-  // outputs per block the ktaps - 1 halo rows were a second pass that one warp ran while seven waited)
+  // a block covers kPostTile input rows = kPostTile - (ktaps - 1) outputs; thread r owns rows r, r + 128, r + 256, r + 384
   const int pad = ktaps / 2;
   const int outs = kPostTile - (ktaps - 1);
   const int b = blockIdx.x / tiles_per_row;
@@ -270,52 +275,65 @@ __global__ void __launch_bounds__(kPostTile) conv_post_tanh_kernel(const void* x
   const uint16_t* xb = reinterpret_cast<const uint16_t*>(x) + static_cast<size_t>(b) * L * x_ld;
   {
     const int r = threadIdx.x;
-    const int t = t0 - pad + r;
-    float acc[kPostMaxTaps];
+    float acc[kPostRows][kAcc];
+    const uint4* src[kPostRows];
+    bool ok[kPostRows];
 #pragma unroll
-    for (int k = 0; k < kPostMaxTaps; ++k) acc[k] = 0.f;
-    if (t >= 0 && t < L) {
-      const uint4* src = reinterpret_cast<const uint4*>(xb + static_cast<size_t>(t) * x_ld);
-      const int n8 = C / 8;
-      uint4 qa = __ldg(src), qb = n8 > 1 ? __ldg(src + 1) : qa;      // two 16-byte loads in flight ahead of the FMAs
-      for (int c8 = 0; c8 < n8; ++c8) {
-        const uint4 q = qa;
-        qa = qb;
-        if (c8 + 2 < n8) qb = __ldg(src + c8 + 2);
+    for (int i = 0; i < kPostRows; ++i) {
+      const int t = t0 - pad + r + i * kPostThreads;
+      ok[i] = t >= 0 && t < L;
+      src[i] = reinterpret_cast<const uint4*>(xb + static_cast<size_t>(ok[i] ? t : 0) * x_ld);
+#pragma unroll
+      for (int k = 0; k < kAcc; ++k) acc[i][k] = 0.f;
+    }
+    const int n8 = C / 8;
+    for (int c8 = 0; c8 < n8; ++c8) {
+      float xv[kPostRows][8];
+#pragma unroll
+      for (int i = 0; i < kPostRows; ++i) {
+        const uint4 q = ok[i] ? __ldg(src[i] + c8) : make_uint4(0, 0, 0, 0);      // rows outside the sequence: zeros (conv padding)
         const uint32_t u[4] = {q.x, q.y, q.z, q.w};
-        float xv[8];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           if (BF) {
-            xv[2 * j] = __uint_as_float(u[j] << 16); xv[2 * j + 1] = __uint_as_float(u[j] & 0xFFFF0000u);
+            xv[i][2 * j] = __uint_as_float(u[j] << 16); xv[i][2 * j + 1] = __uint_as_float(u[j] & 0xFFFF0000u);
           } else {
             const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&u[j]));
-            xv[2 * j] = f.x; xv[2 * j + 1] = f.y;
+            xv[i][2 * j] = f.x; xv[i][2 * j + 1] = f.y;
           }
         }
+      }
 #pragma unroll
-        for (int k = 0; k < kPostMaxTaps; ++k) {
-          if (k < ktaps) {
-            const float4 w0 = *reinterpret_cast<const float4*>(ws + k * C + c8 * 8);
-            const float4 w1 = *reinterpret_cast<const float4*>(ws + k * C + c8 * 8 + 4);
-            float a = acc[k];
-            a = fmaf(xv[0], w0.x, a); a = fmaf(xv[1], w0.y, a); a = fmaf(xv[2], w0.z, a); a = fmaf(xv[3], w0.w, a);
-            a = fmaf(xv[4], w1.x, a); a = fmaf(xv[5], w1.y, a); a = fmaf(xv[6], w1.z, a); a = fmaf(xv[7], w1.w, a);
-            acc[k] = a;
+      for (int k = 0; k < kAcc; ++k) {
+        if (KT || k < ktaps) {
+          const float4 w0 = *reinterpret_cast<const float4*>(ws + k * C + c8 * 8);
+          const float4 w1 = *reinterpret_cast<const float4*>(ws + k * C + c8 * 8 + 4);
+#pragma unroll
+          for (int i = 0; i < kPostRows; ++i) {
+            float a = acc[i][k];
+            a = fmaf(xv[i][0], w0.x, a); a = fmaf(xv[i][1], w0.y, a); a = fmaf(xv[i][2], w0.z, a); a = fmaf(xv[i][3], w0.w, a);
+            a = fmaf(xv[i][4], w1.x, a); a = fmaf(xv[i][5], w1.y, a); a = fmaf(xv[i][6], w1.z, a); a = fmaf(xv[i][7], w1.w, a);
+            acc[i][k] = a;
           }
         }
       }
     }
 #pragma unroll
-    for (int k = 0; k < kPostMaxTaps; ++k)
-      if (k < ktaps) part[k * kStride + r] = acc[k];
+    for (int i = 0; i < kPostRows; ++i)
+#pragma unroll
+      for (int k = 0; k < kAcc; ++k)
+        if (KT || k < ktaps) part[k * kStride + r + i * kPostThreads] = acc[i][k];
   }
   __syncthreads();
-  const int t = t0 + threadIdx.x;
-  if (static_cast<int>(threadIdx.x) < outs && t < L) {
-    float v = 0.f;
-    for (int k = 0; k < ktaps; ++k) v += part[k * kStride + threadIdx.x + k];     // same tap order as a direct conv
-    out[static_cast<size_t>(b) * L + t] = tanhf(v);
+#pragma unroll
+  for (int i = 0; i < kPostRows; ++i) {
+    const int o = threadIdx.x + i * kPostThreads;
+    const int t = t0 + o;
+    if (o < outs && t < L) {
+      float v = 0.f;
+      for (int k = 0; k < ktaps; ++k) v += part[k * kStride + o + k];     // same tap order as a direct conv
+      out[static_cast<size_t>(b) * L + t] = tanhf(v);
+    }
   }
 }
 
@@ -459,10 +477,13 @@ int b200svs_conv_post_tanh(const void* x, int32_t x_dtype, int32_t x_ld, const f
   const int tiles_per_row = (L + outs - 1) / outs;
   const size_t smem = (static_cast<size_t>(ktaps) * C + static_cast<size_t>(ktaps) * (kPostTile + kPostMaxTaps)) * sizeof(float);
   const unsigned grid = static_cast<unsigned>(B) * tiles_per_row;
-  if (x_dtype == B200SVS_DT_BF16)
-    conv_post_tanh_kernel<true><<<grid, kPostTile, smem, as_stream(stream)>>>(x, x_ld, w, B, L, C, ktaps, tiles_per_row, out);
-  else
-    conv_post_tanh_kernel<false><<<grid, kPostTile, smem, as_stream(stream)>>>(x, x_ld, w, B, L, C, ktaps, tiles_per_row, out);
+  if (x_dtype == B200SVS_DT_BF16) {
+    if (ktaps == 7) conv_post_tanh_kernel<true, 7><<<grid, kPostThreads, smem, as_stream(stream)>>>(x, x_ld, w, B, L, C, ktaps, tiles_per_row, out);
+    else conv_post_tanh_kernel<true, 0><<<grid, kPostThreads, smem, as_stream(stream)>>>(x, x_ld, w, B, L, C, ktaps, tiles_per_row, out);
+  } else {
+    if (ktaps == 7) conv_post_tanh_kernel<false, 7><<<grid, kPostThreads, smem, as_stream(stream)>>>(x, x_ld, w, B, L, C, ktaps, tiles_per_row, out);
+    else conv_post_tanh_kernel<false, 0><<<grid, kPostThreads, smem, as_stream(stream)>>>(x, x_ld, w, B, L, C, ktaps, tiles_per_row, out);
+  }
   return check_launch("conv_post_tanh_kernel");
 }
 
