@@ -74,6 +74,76 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LnParams p) {
   }
 }
 
+// Vectorised variant for C % 4 == 0 (C <= 256) with 16-byte aligned rows: lane l owns channels [4l, 4l+4) and [128 + 4l, ..),
+// float4 loads / stores, 8-byte 16-bit stores.  The scalar kernel above spent 423 warp instructions per row and ran with its
+// issue slots 82 % busy at 4.8 TB/s (ncu); same two-pass arithmetic, the partial sums are grouped per lane differently.
+__global__ void __launch_bounds__(256) layernorm_v4_kernel(const LnParams p) {
+  const long long row = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= static_cast<long long>(p.B) * p.T) return;
+  const int b = static_cast<int>(row / p.T), t = static_cast<int>(row - static_cast<long long>(b) * p.T);
+  const bool live = p.lens ? (t < __ldg(p.lens + b)) : true;
+  float4 v[2];
+  bool on[2];
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int c = 4 * lane + 128 * i;
+    on[i] = c < p.C;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (on[i]) {
+      a = __ldg(reinterpret_cast<const float4*>(p.x + row * p.x_ld + c));
+      if (p.res) {
+        const float4 r = __ldg(reinterpret_cast<const float4*>(p.res + row * p.res_ld + c));
+        a.x += r.x; a.y += r.y; a.z += r.z; a.w += r.w;
+      }
+    }
+    v[i] = a;
+    sum += (a.x + a.y) + (a.z + a.w);
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
+  const float mean = sum / p.C;
+  float var = 0.f;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    if (on[i]) {
+      const float d0 = v[i].x - mean, d1 = v[i].y - mean, d2 = v[i].z - mean, d3 = v[i].w - mean;
+      var += (d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3);
+    }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) var += __shfl_xor_sync(0xffffffffu, var, off);
+  const float rstd = rsqrtf(var / p.C + p.eps);
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    if (!on[i]) continue;
+    const int c = 4 * lane + 128 * i;
+    const float4 g = __ldg(reinterpret_cast<const float4*>(p.gamma + c)), be = __ldg(reinterpret_cast<const float4*>(p.beta + c));
+    float4 y;
+    y.x = live ? (v[i].x - mean) * rstd * g.x + be.x : 0.f;
+    y.y = live ? (v[i].y - mean) * rstd * g.y + be.y : 0.f;
+    y.z = live ? (v[i].z - mean) * rstd * g.z + be.z : 0.f;
+    y.w = live ? (v[i].w - mean) * rstd * g.w + be.w : 0.f;
+    if (p.out32) *reinterpret_cast<float4*>(p.out32 + row * p.out32_ld + c) = y;
+    if (p.out16) {
+      uint16_t* o = reinterpret_cast<uint16_t*>(p.out16) + row * p.out16_ld + c;
+      if (p.out16_dtype == B200SVS_DT_BF16) {
+        *reinterpret_cast<uint2*>(o) = make_uint2(cvt_bf16x2_sat(y.x, y.y), cvt_bf16x2_sat(y.z, y.w));
+      } else {
+        const uint2 hi = make_uint2(cvt_f16x2_sat(y.x, y.y), cvt_f16x2_sat(y.z, y.w));
+        *reinterpret_cast<uint2*>(o) = hi;
+        if (p.out16_dtype == B200SVS_DT_F16_SPLIT) {
+          const float2 h0 = __half22float2(*reinterpret_cast<const __half2*>(&hi.x));
+          const float2 h1 = __half22float2(*reinterpret_cast<const __half2*>(&hi.y));
+          *reinterpret_cast<uint2*>(o + p.C) = make_uint2(cvt_f16x2_sat(y.x - h0.x, y.y - h0.y), cvt_f16x2_sat(y.z - h1.x, y.w - h1.y));
+          *reinterpret_cast<uint2*>(o + 2 * p.C) = hi;
+        }
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------ TextEncoder input embedding
 __global__ void text_embed_kernel(const int64_t* phon, const int64_t* pitch, const int64_t* tone, const float* dur,
                                   const float* e_ph, const float* e_pitch, const float* e_tone, const float* w_dur,
@@ -394,7 +464,11 @@ int b200svs_layernorm(const float* x, int32_t x_ld, const float* res, int32_t re
   B200SVS_REQUIRE(B > 0 && T > 0 && C > 0 && C <= 256, "layernorm: B=%d T=%d C=%d (C <= 256)", B, T, C);
   LnParams p{x, x_ld, res, res_ld, gamma, beta, eps, lens, out32, out32_ld, out16, out16_ld, out16_dtype, B, T, C};
   const long long rows = static_cast<long long>(B) * T;
-  layernorm_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, as_stream(stream)>>>(p);
+  auto al = [](const void* q, int a) { return (reinterpret_cast<uintptr_t>(q) & (a - 1)) == 0; };
+  const bool v4 = C % 4 == 0 && x_ld % 4 == 0 && al(x, 16) && (!res || (res_ld % 4 == 0 && al(res, 16))) && al(gamma, 16) && al(beta, 16) &&
+                  (!out32 || (out32_ld % 4 == 0 && al(out32, 16))) && (!out16 || (out16_ld % 4 == 0 && al(out16, 8)));
+  if (v4) layernorm_v4_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, as_stream(stream)>>>(p);
+  else layernorm_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, as_stream(stream)>>>(p);
   return check_launch("layernorm_kernel");
 }
 
